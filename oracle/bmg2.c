@@ -1,0 +1,904 @@
+/*
+ * oracle/bmg2.c -- TEST INFRASTRUCTURE, NOT PRODUCT CODE.
+ *
+ * CPU restatement (plain C, fp64, no FMA contraction: build with
+ * -ffp-contract=off) of the serial 2D BoxMG kernels of the reference
+ * (OVGULIU/cedar, src/2d/ftn/BMG2_SymStd_*.f90).  Only tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+ * may load this library; the product path (cedar_b200/, include/) never does.
+ *
+ * Every function keeps the loop order and the floating-point expression order
+ * of the Fortran routine it cites, so that the CUDA kernels (compiled with
+ * -fmad=false) can be compared bit for bit.  Non-periodic branches only
+ * (periodic boundary conditions are a "next" row of SURVEY.md section 8(f)).
+ *
+ * Parity pin: the multilevel driver in ml2.c built on these kernels reproduces
+ * the residual history printed in the reference README.md:52-63 (see
+ * tests/test_oracle_golden.py); LAPACK restatements are checked against
+ * scipy.linalg.lapack in tests/test_oracle_lapack.py.
+ *
+ * Arrays are Fortran ordered, 1-based in the comments, i fastest:
+ *   Q(II,JJ), SO(II,JJ,NStncl), SOR(II,JJ,2), CI(IIC,JJC,8).
+ */
+#include <math.h>
+#include <stddef.h>
+#include <string.h>
+#include <float.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#include "oracle.h"
+
+/* stencil slots, src/2d/ftn/BMG_stencils_f90.h:29-37,70-71 */
+enum { KO = 1, KW = 2, KS = 3, KSW = 4, KNW = 5 };
+enum { LL = 1, LR = 2, LA = 3, LB = 4, LSW = 5, LNW = 6, LNE = 7, LSE = 8 };
+enum { MSOR = 2 };
+
+#define A2(a, n1, i, j) (a)[(size_t)((j)-1) * (n1) + (size_t)((i)-1)]
+#define A3(a, n1, n2, i, j, k) \
+    (a)[((size_t)((k)-1) * (n2) + (size_t)((j)-1)) * (n1) + (size_t)((i)-1)]
+
+void orc_set_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
+int orc_get_max_threads(void)
+{
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+
+/* ------------------------------------------------------------------------
+ * LAPACK restatements (third-party: system LAPACK, unpinned version; call
+ * sites BMG2_SymStd_SETUP_lines_x.f90:86, relax_lines_x.f90:115,145,
+ * SETUP_cg_LU.f90:118, SOLVE_cg.f90:104).  Reference LAPACK 3.x algorithms.
+ * ---------------------------------------------------------------------- */
+
+/* DPTTRF: L*D*L' of an SPD tridiagonal; d[0..n-1], e[0..n-2] (unblocked form
+ * of the 4-way unrolled reference loop; same operations per element). */
+int orc_dpttrf(int n, double *d, double *e)
+{
+    for (int i = 0; i < n - 1; i++) {
+        if (d[i] <= 0.0) return i + 1;
+        double ei = e[i];
+        e[i] = ei / d[i];
+        d[i + 1] = d[i + 1] - e[i] * ei;
+    }
+    if (n > 0 && d[n - 1] <= 0.0) return n;
+    return 0;
+}
+
+/* DPTTRS/DPTTS2 with NRHS=1: solve L*D*L' x = b in place. */
+void orc_dptts2(int n, const double *d, const double *e, double *b)
+{
+    if (n <= 1) {
+        if (n == 1) b[0] = b[0] * (1.0 / d[0]); /* DSCAL(1/d) path of DPTTS2 */
+        return;
+    }
+    for (int i = 1; i < n; i++) b[i] = b[i] - b[i - 1] * e[i - 1];
+    b[n - 1] = b[n - 1] / d[n - 1];
+    for (int i = n - 2; i >= 0; i--) b[i] = b[i] / d[i] - b[i + 1] * e[i];
+}
+
+/* DPBTRF('U') unblocked (DPBTF2; the blocked path needs KD > 32, never the
+ * case for the coarsest grids of the hot path).  ab is column major
+ * (ldab, n), diagonal in row kd+1 (1-based). */
+int orc_dpbtf2_upper(int n, int kd, double *ab, int ldab)
+{
+#define AB(i, j) ab[(size_t)((j)-1) * ldab + ((i)-1)]
+    int kld = ldab - 1 > 1 ? ldab - 1 : 1;
+    for (int j = 1; j <= n; j++) {
+        double ajj = AB(kd + 1, j);
+        if (ajj <= 0.0) return j;
+        ajj = sqrt(ajj);
+        AB(kd + 1, j) = ajj;
+        int kn = kd < n - j ? kd : n - j;
+        if (kn > 0) {
+            /* x = AB(kd, j+1) with stride kld : row j of U right of diag */
+            double *x = &AB(kd, j + 1);
+            double r = 1.0 / ajj;
+            for (int p = 0; p < kn; p++) x[(size_t)p * kld] = r * x[(size_t)p * kld];
+            /* DSYR('Upper', kn, -1, x, kld, AB(kd+1,j+1), kld) */
+            double *a = &AB(kd + 1, j + 1);
+            for (int q = 0; q < kn; q++) {
+                double xq = x[(size_t)q * kld];
+                if (xq != 0.0) {
+                    double temp = -1.0 * xq;
+                    for (int p = 0; p <= q; p++)
+                        a[(size_t)q * kld + p] = a[(size_t)q * kld + p] + x[(size_t)p * kld] * temp;
+                }
+            }
+        }
+    }
+    return 0;
+#undef AB
+}
+
+/* DPBTRS('U', n, kd, 1, ...) = DTBSV(U,T,N) then DTBSV(U,N,N). */
+void orc_dpbtrs_upper(int n, int kd, const double *ab, int ldab, double *x)
+{
+#define AB(i, j) ab[(size_t)((j)-1) * ldab + ((i)-1)]
+    int kplus1 = kd + 1;
+    for (int j = 1; j <= n; j++) {
+        double temp = x[j - 1];
+        int l = kplus1 - j;
+        int i0 = j - kd > 1 ? j - kd : 1;
+        for (int i = i0; i <= j - 1; i++) temp = temp - AB(l + i, j) * x[i - 1];
+        temp = temp / AB(kplus1, j);
+        x[j - 1] = temp;
+    }
+    for (int j = n; j >= 1; j--) {
+        if (x[j - 1] != 0.0) {
+            int l = kplus1 - j;
+            x[j - 1] = x[j - 1] / AB(kplus1, j);
+            double temp = x[j - 1];
+            int i0 = j - kd > 1 ? j - kd : 1;
+            for (int i = j - 1; i >= i0; i--) x[i - 1] = x[i - 1] - temp * AB(l + i, j);
+        }
+    }
+#undef AB
+}
+
+/* ------------------------------------------------------------------------
+ * BMG2_SymStd_SETUP_recip.f90:63-67
+ * ---------------------------------------------------------------------- */
+void orc2_setup_recip(const double *so, double *sor, int nx, int ny, int nstncl, int nsorv)
+{
+    (void)nstncl; (void)nsorv;
+#pragma omp parallel for schedule(static)
+    for (int j = 2; j <= ny - 1; j++)
+        for (int i = 2; i <= nx - 1; i++)
+            A3(sor, nx, ny, i, j, MSOR) = 1.0 / A3(so, nx, ny, i, j, KO);
+}
+
+/* ------------------------------------------------------------------------
+ * BMG2_SymStd_relax_GS.f90:68-135 (non-periodic)
+ * ---------------------------------------------------------------------- */
+int orc2_relax_gs(int k, const double *so, const double *qf, double *q, const double *sor,
+                  int II, int JJ, int kf, int ifd, int nstncl, int nsorv,
+                  int irelax_sym, int updown, int jpn)
+{
+    (void)nstncl; (void)nsorv;
+    if (jpn != 0 && jpn != -4) return -1;
+    int J1 = JJ - 1, I1 = II - 1;
+    int lstart, lend, lstride;
+    if (irelax_sym == 0 || (updown == 0 && irelax_sym == 1)) {
+        lstart = 2; lend = 3; lstride = 1;
+    } else {
+        lstart = 3; lend = 2; lstride = -1;
+    }
+#define SO(i, j, kk) A3(so, II, JJ, i, j, kk)
+#define Q(i, j) A2(q, II, i, j)
+#define QF(i, j) A2(qf, II, i, j)
+#define SOR(i, j, kk) A3(sor, II, JJ, i, j, kk)
+    if (k < kf || ifd != 1) {
+        for (int jbeg = lstart; jbeg != lend + lstride; jbeg += lstride) {
+            int jend = 2 * ((J1 - jbeg) / 2) + jbeg;
+            /* the reference nests IBEG inside J; points of one colour are
+             * independent and a row of colour (jbeg,ibeg2) only reads rows of
+             * the other j-parity plus its own row's first colour, so running
+             * the two i-colours row by row is the literal order. */
+#pragma omp parallel for schedule(static)
+            for (int j = jbeg; j <= jend; j += 2) {
+                for (int ibeg = lstart; ibeg != lend + lstride; ibeg += lstride) {
+                    int iend = 2 * ((I1 - ibeg) / 2) + ibeg;
+                    for (int i = ibeg; i <= iend; i += 2) {
+                        Q(i, j) = (QF(i, j)
+                                   + SO(i, j, KW) * Q(i - 1, j)
+                                   + SO(i + 1, j, KW) * Q(i + 1, j)
+                                   + SO(i, j, KS) * Q(i, j - 1)
+                                   + SO(i, j + 1, KS) * Q(i, j + 1)
+                                   + SO(i, j, KSW) * Q(i - 1, j - 1)
+                                   + SO(i + 1, j, KNW) * Q(i + 1, j - 1)
+                                   + SO(i, j + 1, KNW) * Q(i - 1, j + 1)
+                                   + SO(i + 1, j + 1, KSW) * Q(i + 1, j + 1))
+                                  * SOR(i, j, MSOR);
+                    }
+                }
+            }
+        }
+    } else {
+        for (int jo = lstart; jo != lend + lstride; jo += lstride) {
+#pragma omp parallel for schedule(static)
+            for (int j = 2; j <= J1; j++) {
+                int ibeg = (j + jo) % 2 + 2;
+                int iend = 2 * ((I1 - ibeg) / 2) + ibeg;
+                for (int i = ibeg; i <= iend; i += 2) {
+                    Q(i, j) = (QF(i, j)
+                               + SO(i, j, KW) * Q(i - 1, j)
+                               + SO(i + 1, j, KW) * Q(i + 1, j)
+                               + SO(i, j, KS) * Q(i, j - 1)
+                               + SO(i, j + 1, KS) * Q(i, j + 1))
+                              * SOR(i, j, MSOR);
+                }
+            }
+        }
+    }
+    return 0;
+#undef SO
+#undef Q
+#undef QF
+#undef SOR
+}
+
+/* ------------------------------------------------------------------------
+ * BMG2_SymStd_residual.f90:87-119
+ * ---------------------------------------------------------------------- */
+void orc2_residual(int k, const double *so, const double *qf, const double *q, double *res,
+                   int II, int JJ, int kf, int ifd, int nstncl)
+{
+    (void)nstncl;
+    int J1 = JJ - 1, I1 = II - 1;
+#define SO(i, j, kk) A3(so, II, JJ, i, j, kk)
+#define Q(i, j) A2(q, II, i, j)
+#define QF(i, j) A2(qf, II, i, j)
+#define RES(i, j) A2(res, II, i, j)
+    if (k < kf || ifd != 1) {
+#pragma omp parallel for schedule(static)
+        for (int j = 2; j <= J1; j++)
+            for (int i = 2; i <= I1; i++)
+                RES(i, j) = QF(i, j)
+                            + SO(i, j, KW) * Q(i - 1, j)
+                            + SO(i + 1, j, KW) * Q(i + 1, j)
+                            + SO(i, j, KS) * Q(i, j - 1)
+                            + SO(i, j + 1, KS) * Q(i, j + 1)
+                            + SO(i, j, KSW) * Q(i - 1, j - 1)
+                            + SO(i + 1, j, KNW) * Q(i + 1, j - 1)
+                            + SO(i, j + 1, KNW) * Q(i - 1, j + 1)
+                            + SO(i + 1, j + 1, KSW) * Q(i + 1, j + 1)
+                            - SO(i, j, KO) * Q(i, j);
+    } else {
+#pragma omp parallel for schedule(static)
+        for (int j = 2; j <= J1; j++)
+            for (int i = 2; i <= I1; i++)
+                RES(i, j) = QF(i, j)
+                            + SO(i, j, KW) * Q(i - 1, j)
+                            + SO(i + 1, j, KW) * Q(i + 1, j)
+                            + SO(i, j, KS) * Q(i, j - 1)
+                            + SO(i, j + 1, KS) * Q(i, j + 1)
+                            - SO(i, j, KO) * Q(i, j);
+    }
+#undef SO
+#undef Q
+#undef QF
+#undef RES
+}
+
+/* ------------------------------------------------------------------------
+ * BMG2_SymStd_restrict.f90:73-94 (non-periodic)
+ * ---------------------------------------------------------------------- */
+int orc2_restrict(const double *q, double *qc, const double *ci,
+                  int Nx, int Ny, int Nxc, int Nyc, int jpn)
+{
+    if (jpn != 0 && jpn != -4) return -1;
+    (void)Ny;
+#define CI(i, j, kk) A3(ci, Nxc, Nyc, i, j, kk)
+#define Q(i, j) A2(q, Nx, i, j)
+#define QC(i, j) A2(qc, Nxc, i, j)
+#pragma omp parallel for schedule(static)
+    for (int jc = 2; jc <= Nyc - 1; jc++) {
+        int j = 2 * (jc - 1);
+        for (int ic = 2; ic <= Nxc - 1; ic++) {
+            int i = 2 * (ic - 1);
+            QC(ic, jc) = CI(ic, jc, LNE) * Q(i - 1, j - 1)
+                         + CI(ic, jc, LA) * Q(i, j - 1)
+                         + CI(ic + 1, jc, LNW) * Q(i + 1, j - 1)
+                         + CI(ic, jc, LR) * Q(i - 1, j)
+                         + Q(i, j)
+                         + CI(ic + 1, jc, LL) * Q(i + 1, j)
+                         + CI(ic, jc + 1, LSE) * Q(i - 1, j + 1)
+                         + CI(ic, jc + 1, LB) * Q(i, j + 1)
+                         + CI(ic + 1, jc + 1, LSW) * Q(i + 1, j + 1);
+        }
+    }
+    return 0;
+#undef CI
+#undef Q
+#undef QC
+}
+
+/* ------------------------------------------------------------------------
+ * BMG2_SymStd_interp_add.f90:88-141 (non-periodic).  RES is scaled in place
+ * by 1/SO(.,.,KO) (l.101-105) -- a persistent side effect.
+ * ---------------------------------------------------------------------- */
+int orc2_interp_add(double *q, const double *qc, double *res, const double *so, const double *ci,
+                    int IIC, int JJC, int IIF, int JJF, int nstncl, int jpn)
+{
+    (void)nstncl;
+    if (jpn != 0 && jpn != -4) return -1;
+    int JJF1 = JJF - 1, IIF1 = IIF - 1;
+    int IICF = (IIF - 2) / 2 + 3, JJCF = (JJF - 2) / 2 + 3;
+    int IICF1 = IICF - 1, JJCF1 = JJCF - 1;
+#define CI(i, j, kk) A3(ci, IIC, JJC, i, j, kk)
+#define Q(i, j) A2(q, IIF, i, j)
+#define QC(i, j) A2(qc, IIC, i, j)
+#define RES(i, j) A2(res, IIF, i, j)
+#define SO(i, j, kk) A3(so, IIF, JJF, i, j, kk)
+#pragma omp parallel for schedule(static)
+    for (int j = 2; j <= JJF1; j++)
+        for (int i = 2; i <= IIF1; i++)
+            RES(i, j) = RES(i, j) / SO(i, j, KO);
+
+    {
+        int j = 2, i = 2;
+        Q(2, j) = Q(2, j) + QC(2, 2);
+        for (int ic = 3; ic <= IICF1; ic++) {
+            i = i + 2;
+            Q(i, j) = Q(i, j) + QC(ic, 2);
+            double a = CI(ic, 2, LR) * QC(ic, 2) + CI(ic, 2, LL) * QC(ic - 1, 2);
+            Q(i - 1, j) = Q(i - 1, j) + a + RES(i - 1, j);
+        }
+    }
+#pragma omp parallel for schedule(static)
+    for (int jc = 3; jc <= JJCF1; jc++) {
+        int j = 2 * (jc - 1);
+        int i = 2;
+        Q(2, j) = Q(2, j) + QC(2, jc);
+        double aq = CI(2, jc, LA) * QC(2, jc) + CI(2, jc, LB) * QC(2, jc - 1);
+        Q(2, j - 1) = Q(2, j - 1) + aq + RES(2, j - 1);
+        for (int ic = 3; ic <= IICF1; ic++) {
+            i = i + 2;
+            Q(i, j) = Q(i, j) + QC(ic, jc);
+            double a = CI(ic, jc, LR) * QC(ic, jc) + CI(ic, jc, LL) * QC(ic - 1, jc);
+            Q(i - 1, j) = Q(i - 1, j) + a + RES(i - 1, j);
+            aq = CI(ic, jc, LA) * QC(ic, jc) + CI(ic, jc, LB) * QC(ic, jc - 1);
+            Q(i, j - 1) = Q(i, j - 1) + aq + RES(i, j - 1);
+            a = CI(ic, jc, LSW) * QC(ic - 1, jc - 1) + CI(ic, jc, LNW) * QC(ic - 1, jc)
+                + CI(ic, jc, LNE) * QC(ic, jc) + CI(ic, jc, LSE) * QC(ic, jc - 1);
+            Q(i - 1, j - 1) = Q(i - 1, j - 1) + a + RES(i - 1, j - 1);
+        }
+    }
+    return 0;
+#undef CI
+#undef Q
+#undef QC
+#undef RES
+#undef SO
+}
+
+/* ------------------------------------------------------------------------
+ * BMG2_SymStd_SETUP_interp_OI.f90:84-256 (non-periodic)
+ * ---------------------------------------------------------------------- */
+static inline double oi_min2(double a, double b) { return a < b ? a : b; }
+static inline double oi_max2(double a, double b) { return a > b ? a : b; }
+
+int orc2_setup_interp_oi(const double *so, const double *soc, double *ci,
+                         int IIF, int JJF, int IIC, int JJC, int ifd, int nstncl,
+                         int jpn, int irelax)
+{
+    (void)soc; (void)nstncl; (void)irelax;
+    if (jpn != 0 && jpn != -4) return -1;
+    const double ZEPS = DBL_EPSILON; /* EPSILON(1.D0), l.78 */
+    int IIC1 = IIC - 1, JJC1 = JJC - 1;
+    int IICF = (IIF - 2) / 2 + 3, JJCF = (JJF - 2) / 2 + 3;
+    int IICF1 = IICF - 1, JJCF1 = JJCF - 1;
+#define SO(i, j, kk) A3(so, IIF, JJF, i, j, kk)
+#define CI(i, j, kk) A3(ci, IIC, JJC, i, j, kk)
+    if (ifd != 1) {
+#pragma omp parallel for schedule(static)
+        for (int jc = 2; jc <= JJC1; jc++) {
+            int j = 2 * (jc - 1);
+            for (int ic = 3; ic <= IICF1; ic++) {
+                int i = 2 * (ic - 1);
+                double a = SO(i, j, KW) + SO(i, j, KNW) + SO(i, j + 1, KSW);
+                double b = SO(i - 1, j, KW) + SO(i - 1, j, KSW) + SO(i - 1, j + 1, KNW);
+                double ep = oi_min2(fabs(a / SO(i - 1, j, KO)), fabs(b / SO(i - 1, j, KO)));
+                double sum = a + b + SO(i - 1, j, KS) + SO(i - 1, j + 1, KS);
+                sum = a + b + (SO(i - 1, j, KO) - sum)
+                                  * oi_max2(SO(i - 1, j, KO) - (1.0 + ep) * sum, 0.0)
+                                  / (fabs(SO(i - 1, j, KO) - (1.0 + ep) * sum) + ZEPS);
+                sum = 1.0 / sum;
+                CI(ic, jc, LR) = a * sum;
+                CI(ic, jc, LL) = b * sum;
+            }
+        }
+#pragma omp parallel for schedule(static)
+        for (int jc = 3; jc <= JJCF1; jc++) {
+            int j = 2 * (jc - 1);
+            for (int ic = 2; ic <= IIC1; ic++) {
+                int i = 2 * (ic - 1);
+                double a = SO(i, j, KS) + SO(i, j, KNW) + SO(i + 1, j, KSW);
+                double b = SO(i, j - 1, KS) + SO(i, j - 1, KSW) + SO(i + 1, j - 1, KNW);
+                double ep = oi_min2(fabs(a / SO(i, j - 1, KO)), fabs(b / SO(i, j - 1, KO)));
+                double sum = a + b + SO(i, j - 1, KW) + SO(i + 1, j - 1, KW);
+                sum = a + b + (SO(i, j - 1, KO) - sum)
+                                  * oi_max2(SO(i, j - 1, KO) - (1.0 + ep) * sum, 0.0)
+                                  / (fabs(SO(i, j - 1, KO) - (1.0 + ep) * sum) + ZEPS);
+                sum = 1.0 / sum;
+                CI(ic, jc, LA) = a * sum;
+                CI(ic, jc, LB) = b * sum;
+            }
+        }
+#pragma omp parallel for schedule(static)
+        for (int jc = 3; jc <= JJCF1; jc++) {
+            int j = 2 * (jc - 1);
+            for (int ic = 3; ic <= IICF1; ic++) {
+                int i = 2 * (ic - 1);
+                double sum = SO(i - 1, j - 1, KW) + SO(i - 1, j, KNW) + SO(i - 1, j, KS)
+                             + SO(i, j, KSW) + SO(i, j - 1, KW) + SO(i, j - 1, KNW)
+                             + SO(i - 1, j - 1, KS) + SO(i - 1, j - 1, KSW);
+                double o = SO(i - 1, j - 1, KO);
+                double ep = oi_min2(
+                    oi_min2(fabs((SO(i - 1, j - 1, KSW) + SO(i - 1, j - 1, KW) + SO(i - 1, j, KNW)) / o),
+                            fabs((SO(i - 1, j, KNW) + SO(i - 1, j, KS) + SO(i, j, KSW)) / o)),
+                    oi_min2(fabs((SO(i, j, KSW) + SO(i, j - 1, KW) + SO(i, j - 1, KNW)) / o),
+                            fabs((SO(i, j - 1, KNW) + SO(i - 1, j - 1, KS) + SO(i - 1, j - 1, KSW)) / o)));
+                sum = sum + (o - sum) * oi_max2(o - (1.0 + ep) * sum, 0.0)
+                                / (fabs(o - (1.0 + ep) * sum) + ZEPS);
+                double s = 1.0 / sum;
+                CI(ic, jc, LSW) = (SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LL)
+                                   + SO(i - 1, j - 1, KW) * CI(ic - 1, jc, LB)
+                                   + SO(i - 1, j - 1, KSW)) * s;
+                CI(ic, jc, LSE) = (SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LR)
+                                   + SO(i, j - 1, KW) * CI(ic, jc, LB)
+                                   + SO(i, j - 1, KNW)) * s;
+                CI(ic, jc, LNW) = (SO(i - 1, j - 1, KW) * CI(ic - 1, jc, LA)
+                                   + SO(i - 1, j, KS) * CI(ic, jc, LL)
+                                   + SO(i - 1, j, KNW)) * s;
+                CI(ic, jc, LNE) = (SO(i - 1, j, KS) * CI(ic, jc, LR)
+                                   + SO(i, j - 1, KW) * CI(ic, jc, LA)
+                                   + SO(i, j, KSW)) * s;
+            }
+        }
+    } else {
+#pragma omp parallel for schedule(static)
+        for (int jc = 2; jc <= JJC1; jc++) {
+            int j = 2 * (jc - 1);
+            for (int ic = 3; ic <= IICF1; ic++) {
+                int i = 2 * (ic - 1);
+                double a = SO(i, j, KW);
+                double b = SO(i - 1, j, KW);
+                double ep = oi_min2(fabs(a / SO(i - 1, j, KO)), fabs(b / SO(i - 1, j, KO)));
+                double sum = a + b + SO(i - 1, j, KS) + SO(i - 1, j + 1, KS);
+                sum = a + b + (SO(i - 1, j, KO) - sum)
+                                  * oi_max2(SO(i - 1, j, KO) - (1.0 + ep) * sum, 0.0)
+                                  / (fabs(SO(i - 1, j, KO) - (1.0 + ep) * sum) + ZEPS);
+                sum = 1.0 / sum;
+                CI(ic, jc, LR) = a * sum;
+                CI(ic, jc, LL) = b * sum;
+            }
+        }
+#pragma omp parallel for schedule(static)
+        for (int jc = 3; jc <= JJCF1; jc++) {
+            int j = 2 * (jc - 1);
+            for (int ic = 2; ic <= IIC1; ic++) {
+                int i = 2 * (ic - 1);
+                double a = SO(i, j, KS);
+                double b = SO(i, j - 1, KS);
+                double ep = oi_min2(fabs(a / SO(i, j - 1, KO)), fabs(b / SO(i, j - 1, KO)));
+                double sum = a + b + SO(i, j - 1, KW) + SO(i + 1, j - 1, KW);
+                sum = a + b + (SO(i, j - 1, KO) - sum)
+                                  * oi_max2(SO(i, j - 1, KO) - (1.0 + ep) * sum, 0.0)
+                                  / (fabs(SO(i, j - 1, KO) - (1.0 + ep) * sum) + ZEPS);
+                sum = 1.0 / sum;
+                CI(ic, jc, LA) = a * sum;
+                CI(ic, jc, LB) = b * sum;
+            }
+        }
+#pragma omp parallel for schedule(static)
+        for (int jc = 3; jc <= JJCF1; jc++) {
+            int j = 2 * (jc - 1);
+            for (int ic = 3; ic <= IICF1; ic++) {
+                int i = 2 * (ic - 1);
+                double o = SO(i - 1, j - 1, KO);
+                double sum = SO(i - 1, j - 1, KW) + SO(i - 1, j, KS) + SO(i, j - 1, KW)
+                             + SO(i - 1, j - 1, KS);
+                double ep = oi_min2(oi_min2(fabs(SO(i - 1, j - 1, KW) / o), fabs(SO(i - 1, j, KS) / o)),
+                                    oi_min2(fabs(SO(i, j - 1, KW) / o), fabs(SO(i - 1, j - 1, KS) / o)));
+                sum = sum + (o - sum) * oi_max2(o - (1.0 + ep) * sum, 0.0)
+                                / (fabs(o - (1.0 + ep) * sum) + ZEPS);
+                double s = 1.0 / sum;
+                CI(ic, jc, LSW) = (SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LL)
+                                   + SO(i - 1, j - 1, KW) * CI(ic - 1, jc, LB)) * s;
+                CI(ic, jc, LSE) = (SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LR)
+                                   + SO(i, j - 1, KW) * CI(ic, jc, LB)) * s;
+                CI(ic, jc, LNW) = (SO(i - 1, j - 1, KW) * CI(ic - 1, jc, LA)
+                                   + SO(i - 1, j, KS) * CI(ic, jc, LL)) * s;
+                CI(ic, jc, LNE) = (SO(i - 1, j, KS) * CI(ic, jc, LR)
+                                   + SO(i, j - 1, KW) * CI(ic, jc, LA)) * s;
+            }
+        }
+    }
+    return 0;
+#undef SO
+#undef CI
+}
+
+/* ------------------------------------------------------------------------
+ * BMG2_SymStd_SETUP_ITLI_ex.f90:94-213 (9-pt fine) and 252-330 (5-pt fine),
+ * Galerkin coarse operator, non-periodic.
+ * ---------------------------------------------------------------------- */
+int orc2_setup_itli_ex(const double *so, double *soc, const double *ci,
+                       int IIF, int JJF, int IIC, int JJC, int ifd, int nstncl, int ipn)
+{
+    (void)nstncl;
+    if (ipn != 0 && ipn != -4) return -1;
+    int IIC1 = IIC - 1, JJC1 = JJC - 1;
+#define SO(i, j, kk) A3(so, IIF, JJF, i, j, kk)
+#define CI(i, j, kk) A3(ci, IIC, JJC, i, j, kk)
+#define SOC(i, j, kk) A3(soc, IIC, JJC, i, j, kk)
+    if (ifd != 1) {
+#pragma omp parallel for schedule(static)
+        for (int jc = 2; jc <= JJC1; jc++) {
+            int j = 2 * (jc - 1);
+            for (int ic = 2; ic <= IIC1; ic++) {
+                int i = 2 * (ic - 1);
+                double co = SO(i, j + 1, KNW) * CI(ic, jc + 1, LSW)
+                            + SO(i, j, KW) * CI(ic, jc, LL)
+                            + SO(i, j, KSW) * CI(ic, jc, LNW);
+                double cs = SO(i, j - 1, KW) * CI(ic, jc, LNW) + SO(i, j, KNW) * CI(ic, jc, LL);
+                double csw = -SO(i - 1, j - 1, KO) * CI(ic, jc, LNW)
+                             + SO(i - 1, j - 1, KW) * CI(ic - 1, jc, LA) + SO(i - 1, j, KNW)
+                             + SO(i - 1, j, KS) * CI(ic, jc, LL);
+                double cw = -SO(i - 1, j, KO) * CI(ic, jc, LL) + SO(i - 1, j, KS) * CI(ic, jc, LNW)
+                            + SO(i - 1, j, KSW) * CI(ic - 1, jc, LA)
+                            + SO(i - 1, j, KW) + SO(i - 1, j + 1, KNW) * CI(ic - 1, jc + 1, LB)
+                            + SO(i - 1, j + 1, KS) * CI(ic, jc + 1, LSW);
+                double cnw = -SO(i - 1, j + 1, KO) * CI(ic, jc + 1, LSW)
+                             + SO(i - 1, j + 1, KS) * CI(ic, jc, LL) + SO(i - 1, j + 1, KSW)
+                             + SO(i - 1, j + 1, KW) * CI(ic - 1, jc + 1, LB);
+                double cn = SO(i, j + 1, KSW) * CI(ic, jc, LL) + SO(i, j + 1, KW) * CI(ic, jc + 1, LSW);
+                SOC(ic, jc, KW) = co + CI(ic, jc, LA) * cs + CI(ic, jc, LNE) * csw
+                                  + CI(ic, jc, LR) * cw + CI(ic, jc + 1, LSE) * cnw
+                                  + CI(ic, jc + 1, LB) * cn;
+                double cosw = SO(i, j, KSW) * CI(ic, jc, LSW);
+                double cssw = SO(i, j - 1, KSW) * CI(ic, jc - 1, LL) + SO(i, j - 1, KW) * CI(ic, jc, LSW);
+                double cswsw = -SO(i - 1, j - 1, KO) * CI(ic, jc, LSW)
+                               + SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LL) + SO(i - 1, j - 1, KSW)
+                               + SO(i - 1, j - 1, KW) * CI(ic - 1, jc, LB);
+                double cwsw = SO(i - 1, j, KS) * CI(ic, jc, LSW) + SO(i - 1, j, KSW) * CI(ic - 1, jc, LB);
+                SOC(ic, jc, KSW) = cosw + CI(ic, jc, LA) * cssw + CI(ic, jc, LNE) * cswsw
+                                   + CI(ic, jc, LR) * cwsw;
+                double coa = SO(i, j, KSW) * CI(ic, jc, LSE) + SO(i, j, KS) * CI(ic, jc, LB)
+                             + SO(i + 1, j, KNW) * CI(ic + 1, jc, LSW);
+                double cea = SO(i + 1, j, KS) * CI(ic + 1, jc, LSW) + SO(i + 1, j, KSW) * CI(ic, jc, LB);
+                double csea = -SO(i + 1, j - 1, KO) * CI(ic + 1, jc, LSW)
+                              + SO(i + 1, j - 1, KS) * CI(ic + 1, jc - 1, LL) + SO(i + 1, j - 1, KSW)
+                              + SO(i + 1, j - 1, KW) * CI(ic, jc, LB);
+                double csa = -SO(i, j - 1, KO) * CI(ic, jc, LB) + SO(i + 1, j - 1, KW) * CI(ic + 1, jc, LSW)
+                             + SO(i + 1, j - 1, KNW) * CI(ic + 1, jc - 1, LL)
+                             + SO(i, j - 1, KS) + SO(i, j - 1, KSW) * CI(ic, jc - 1, LR)
+                             + SO(i, j - 1, KW) * CI(ic, jc, LSE);
+                double cswa = -SO(i - 1, j - 1, KO) * CI(ic, jc, LSE) + SO(i, j - 1, KW) * CI(ic, jc, LB)
+                              + SO(i, j - 1, KNW) + SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LR);
+                double cwa = SO(i, j, KNW) * CI(ic, jc, LB) + SO(i - 1, j, KS) * CI(ic, jc, LSE);
+                SOC(ic, jc, KS) = coa + CI(ic + 1, jc, LL) * cea + CI(ic + 1, jc, LNW) * csea
+                                  + CI(ic, jc, LA) * csa + CI(ic, jc, LNE) * cswa
+                                  + CI(ic, jc, LR) * cwa;
+                double conw = SO(i - 1, j, KNW) * CI(ic, jc, LSE);
+                double cenw = SO(i, j, KNW) * CI(ic, jc, LB) + SO(i - 1, j, KS) * CI(ic, jc, LSE);
+                double csenw = -SO(i - 1, j - 1, KO) * CI(ic, jc, LSE) + SO(i, j - 1, KW) * CI(ic, jc, LB)
+                               + SO(i, j - 1, KNW) + SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LR);
+                double cfnw = SO(i - 1, j - 1, KW) * CI(ic, jc, LSE)
+                              + SO(i - 1, j - 1, KNW) * CI(ic, jc - 1, LR);
+                SOC(ic, jc, KNW) = conw + CI(ic, jc, LL) * cenw + CI(ic, jc, LNW) * csenw
+                                   + CI(ic - 1, jc, LA) * cfnw;
+            }
+        }
+#pragma omp parallel for schedule(static)
+        for (int jc = 2; jc <= JJC1; jc++) {
+            int j = 2 * (jc - 1);
+            for (int ic = 2; ic <= IIC1; ic++) {
+                int i = 2 * (ic - 1);
+                double co = SO(i, j, KW) * CI(ic, jc, LR) + SO(i, j + 1, KNW) * CI(ic, jc + 1, LSE)
+                            + SO(i, j + 1, KS) * CI(ic, jc + 1, LB)
+                            + SO(i + 1, j + 1, KSW) * CI(ic + 1, jc + 1, LSW)
+                            + SO(i + 1, j, KW) * CI(ic + 1, jc, LL)
+                            + SO(i + 1, j, KNW) * CI(ic + 1, jc, LNW)
+                            + SO(i, j, KS) * CI(ic, jc, LA) + SO(i, j, KSW) * CI(ic, jc, LNE)
+                            - SO(i, j, KO);
+                double cw = -SO(i - 1, j, KO) * CI(ic, jc, LR) + SO(i - 1, j + 1, KS) * CI(ic, jc + 1, LSE)
+                            + SO(i, j + 1, KSW) * CI(ic, jc + 1, LB)
+                            + SO(i, j, KW) + SO(i, j, KNW) * CI(ic, jc, LA)
+                            + SO(i - 1, j, KS) * CI(ic, jc, LNE);
+                double cnw = -SO(i - 1, j + 1, KO) * CI(ic, jc + 1, LSE) + SO(i, j + 1, KW) * CI(ic, jc + 1, LB)
+                             + SO(i, j + 1, KNW) + SO(i - 1, j + 1, KS) * CI(ic, jc, LR);
+                double cn = -SO(i, j + 1, KO) * CI(ic, jc + 1, LB) + SO(i + 1, j + 1, KNW) * CI(ic + 1, jc, LL)
+                            + SO(i, j + 1, KS) + SO(i, j + 1, KSW) * CI(ic, jc, LR)
+                            + SO(i, j + 1, KW) * CI(ic, jc + 1, LSE)
+                            + SO(i + 1, j + 1, KW) * CI(ic + 1, jc + 1, LSW);
+                double cne = -SO(i + 1, j + 1, KO) * CI(ic + 1, jc + 1, LSW)
+                             + SO(i + 1, j + 1, KS) * CI(ic + 1, jc, LL) + SO(i + 1, j + 1, KSW)
+                             + SO(i + 1, j + 1, KW) * CI(ic, jc + 1, LB);
+                double ce = -SO(i + 1, j, KO) * CI(ic + 1, jc, LL) + SO(i + 1, j, KS) * CI(ic + 1, jc, LNW)
+                            + SO(i + 1, j, KSW) * CI(ic, jc, LA)
+                            + SO(i + 1, j, KW) + SO(i + 1, j + 1, KNW) * CI(ic, jc + 1, LB)
+                            + SO(i + 1, j + 1, KS) * CI(ic + 1, jc + 1, LSW);
+                double cse = -SO(i + 1, j - 1, KO) * CI(ic + 1, jc, LNW) + SO(i + 1, j - 1, KW) * CI(ic, jc, LA)
+                             + SO(i + 1, j, KNW) + SO(i + 1, j, KS) * CI(ic + 1, jc, LL);
+                double cs = -SO(i, j - 1, KO) * CI(ic, jc, LA) + SO(i, j - 1, KW) * CI(ic, jc, LNE)
+                            + SO(i, j, KNW) * CI(ic, jc, LR)
+                            + SO(i, j, KS) + SO(i + 1, j, KSW) * CI(ic + 1, jc, LL)
+                            + SO(i + 1, j - 1, KW) * CI(ic + 1, jc, LNW);
+                double csw = -SO(i - 1, j - 1, KO) * CI(ic, jc, LNE) + SO(i - 1, j, KS) * CI(ic, jc, LR)
+                             + SO(i, j, KSW) + SO(i, j - 1, KW) * CI(ic, jc, LA);
+                SOC(ic, jc, KO) = -CI(ic, jc + 1, LSE) * cnw - CI(ic, jc + 1, LB) * cn
+                                  - CI(ic + 1, jc + 1, LSW) * cne - CI(ic, jc, LR) * cw - co
+                                  - CI(ic + 1, jc, LL) * ce - CI(ic, jc, LNE) * csw
+                                  - CI(ic, jc, LA) * cs - CI(ic + 1, jc, LNW) * cse;
+            }
+        }
+    } else {
+#pragma omp parallel for schedule(static)
+        for (int jc = 2; jc <= JJC1; jc++) {
+            int j = 2 * (jc - 1);
+            for (int ic = 2; ic <= IIC1; ic++) {
+                int i = 2 * (ic - 1);
+                double co = SO(i, j, KW) * CI(ic, jc, LL);
+                double cs = SO(i, j - 1, KW) * CI(ic, jc, LNW);
+                double csw = -SO(i - 1, j - 1, KO) * CI(ic, jc, LNW)
+                             + SO(i - 1, j - 1, KW) * CI(ic - 1, jc, LA) + SO(i - 1, j, KS) * CI(ic, jc, LL);
+                double cw = -SO(i - 1, j, KO) * CI(ic, jc, LL) + SO(i - 1, j, KS) * CI(ic, jc, LNW)
+                            + SO(i - 1, j, KW) + SO(i - 1, j + 1, KS) * CI(ic, jc + 1, LSW);
+                double cnw = -SO(i - 1, j + 1, KO) * CI(ic, jc + 1, LSW) + SO(i - 1, j + 1, KS) * CI(ic, jc, LL)
+                             + SO(i - 1, j + 1, KW) * CI(ic - 1, jc + 1, LB);
+                double cn = SO(i, j + 1, KW) * CI(ic, jc + 1, LSW);
+                SOC(ic, jc, KW) = co + CI(ic, jc, LA) * cs + CI(ic, jc, LNE) * csw
+                                  + CI(ic, jc, LR) * cw + CI(ic, jc + 1, LSE) * cnw
+                                  + CI(ic, jc + 1, LB) * cn;
+                double cssw = SO(i, j - 1, KW) * CI(ic, jc, LSW);
+                double cswsw = -SO(i - 1, j - 1, KO) * CI(ic, jc, LSW)
+                               + SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LL)
+                               + SO(i - 1, j - 1, KW) * CI(ic - 1, jc, LB);
+                double cwsw = SO(i - 1, j, KS) * CI(ic, jc, LSW);
+                SOC(ic, jc, KSW) = CI(ic, jc, LA) * cssw + CI(ic, jc, LNE) * cswsw + CI(ic, jc, LR) * cwsw;
+                double coa = SO(i, j, KS) * CI(ic, jc, LB);
+                double cea = SO(i + 1, j, KS) * CI(ic + 1, jc, LSW);
+                double csea = -SO(i + 1, j - 1, KO) * CI(ic + 1, jc, LSW)
+                              + SO(i + 1, j - 1, KS) * CI(ic + 1, jc - 1, LL)
+                              + SO(i + 1, j - 1, KW) * CI(ic, jc, LB);
+                double csa = -SO(i, j - 1, KO) * CI(ic, jc, LB) + SO(i + 1, j - 1, KW) * CI(ic + 1, jc, LSW)
+                             + SO(i, j - 1, KS) + SO(i, j - 1, KW) * CI(ic, jc, LSE);
+                double cswa = -SO(i - 1, j - 1, KO) * CI(ic, jc, LSE) + SO(i, j - 1, KW) * CI(ic, jc, LB)
+                              + SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LR);
+                double cwa = SO(i - 1, j, KS) * CI(ic, jc, LSE);
+                SOC(ic, jc, KS) = coa + CI(ic + 1, jc, LL) * cea + CI(ic + 1, jc, LNW) * csea
+                                  + CI(ic, jc, LA) * csa + CI(ic, jc, LNE) * cswa
+                                  + CI(ic, jc, LR) * cwa;
+                double cenw = SO(i - 1, j, KS) * CI(ic, jc, LSE);
+                double csenw = -SO(i - 1, j - 1, KO) * CI(ic, jc, LSE) + SO(i, j - 1, KW) * CI(ic, jc, LB)
+                               + SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LR);
+                double csnw = SO(i - 1, j - 1, KW) * CI(ic, jc, LSE);
+                SOC(ic, jc, KNW) = CI(ic, jc, LL) * cenw + CI(ic, jc, LNW) * csenw
+                                   + CI(ic - 1, jc, LA) * csnw;
+                co = SO(i, j, KW) * CI(ic, jc, LR) + SO(i, j + 1, KS) * CI(ic, jc + 1, LB)
+                     + SO(i + 1, j, KW) * CI(ic + 1, jc, LL)
+                     + SO(i, j, KS) * CI(ic, jc, LA) - SO(i, j, KO);
+                cw = -SO(i - 1, j, KO) * CI(ic, jc, LR) + SO(i - 1, j + 1, KS) * CI(ic, jc + 1, LSE)
+                     + SO(i, j, KW) + SO(i - 1, j, KS) * CI(ic, jc, LNE);
+                cnw = -SO(i - 1, j + 1, KO) * CI(ic, jc + 1, LSE) + SO(i, j + 1, KW) * CI(ic, jc + 1, LB)
+                      + SO(i - 1, j + 1, KS) * CI(ic, jc, LR);
+                cn = -SO(i, j + 1, KO) * CI(ic, jc + 1, LB) + SO(i, j + 1, KS)
+                     + SO(i, j + 1, KW) * CI(ic, jc + 1, LSE)
+                     + SO(i + 1, j + 1, KW) * CI(ic + 1, jc + 1, LSW);
+                double cne = -SO(i + 1, j + 1, KO) * CI(ic + 1, jc + 1, LSW)
+                             + SO(i + 1, j + 1, KS) * CI(ic + 1, jc, LL)
+                             + SO(i + 1, j + 1, KW) * CI(ic, jc + 1, LB);
+                double ce = -SO(i + 1, j, KO) * CI(ic + 1, jc, LL) + SO(i + 1, j, KS) * CI(ic + 1, jc, LNW)
+                            + SO(i + 1, j, KW) + SO(i + 1, j + 1, KS) * CI(ic + 1, jc + 1, LSW);
+                double cse = -SO(i + 1, j - 1, KO) * CI(ic + 1, jc, LNW) + SO(i + 1, j - 1, KW) * CI(ic, jc, LA)
+                             + SO(i + 1, j, KS) * CI(ic + 1, jc, LL);
+                cs = -SO(i, j - 1, KO) * CI(ic, jc, LA) + SO(i, j - 1, KW) * CI(ic, jc, LNE)
+                     + SO(i, j, KS) + SO(i + 1, j - 1, KW) * CI(ic + 1, jc, LNW);
+                csw = -SO(i - 1, j - 1, KO) * CI(ic, jc, LNE) + SO(i - 1, j, KS) * CI(ic, jc, LR)
+                      + SO(i, j - 1, KW) * CI(ic, jc, LA);
+                SOC(ic, jc, KO) = -CI(ic, jc + 1, LSE) * cnw - CI(ic, jc + 1, LB) * cn
+                                  - CI(ic + 1, jc + 1, LSW) * cne - CI(ic, jc, LR) * cw - co
+                                  - CI(ic + 1, jc, LL) * ce - CI(ic, jc, LNE) * csw
+                                  - CI(ic, jc, LA) * cs - CI(ic + 1, jc, LNW) * cse;
+            }
+        }
+    }
+    return 0;
+#undef SO
+#undef CI
+#undef SOC
+}
+
+/* ------------------------------------------------------------------------
+ * BMG2_SymStd_SETUP_lines_x.f90:68-87 / SETUP_lines_y.f90:69-88
+ * SOR(.,.,1)=D, SOR(.,.,2)=sub-diagonal factor; y-lines stored transposed.
+ * ---------------------------------------------------------------------- */
+int orc2_setup_lines_x(const double *so, double *sor, int Nx, int Ny, int nstncl, int jpn)
+{
+    (void)nstncl;
+    if (jpn != 0 && jpn != -4) return -1;
+#define SO(i, j, kk) A3(so, Nx, Ny, i, j, kk)
+#define SOR(i, j, kk) A3(sor, Nx, Ny, i, j, kk)
+#pragma omp parallel for schedule(static)
+    for (int j = 2; j <= Ny - 1; j++) {
+        for (int i = 2; i <= Nx - 1; i++) {
+            SOR(i, j, 2) = -SO(i, j, KW);
+            SOR(i, j, 1) = SO(i, j, KO);
+        }
+        orc_dpttrf(Nx - 2, &SOR(2, j, 1), &SOR(3, j, 2));
+    }
+    return 0;
+#undef SO
+#undef SOR
+}
+
+int orc2_setup_lines_y(const double *so, double *sor, int Nx, int Ny, int nstncl, int jpn)
+{
+    (void)nstncl;
+    if (jpn != 0 && jpn != -4) return -1;
+#define SO(i, j, kk) A3(so, Nx, Ny, i, j, kk)
+#define SOR(j, i, kk) A3(sor, Ny, Nx, j, i, kk)
+#pragma omp parallel for schedule(static)
+    for (int i = 2; i <= Nx - 1; i++) {
+        for (int j = 2; j <= Ny - 1; j++) {
+            SOR(j, i, 2) = -SO(i, j, KS);
+            SOR(j, i, 1) = SO(i, j, KO);
+        }
+        orc_dpttrf(Ny - 2, &SOR(2, i, 1), &SOR(3, i, 2));
+    }
+    return 0;
+#undef SO
+#undef SOR
+}
+
+/* ------------------------------------------------------------------------
+ * BMG2_SymStd_relax_lines_x.f90:76-170 (non-periodic)
+ * ---------------------------------------------------------------------- */
+int orc2_relax_lines_x(int k, const double *so, const double *qf, double *q, const double *sor,
+                       double *b, int II, int JJ, int kf, int ifd, int nstncl,
+                       int irelax_sym, int updown, int jpn)
+{
+    (void)nstncl; (void)b;
+    if (jpn != 0 && jpn != -4) return -1;
+    int J1 = JJ - 1, I1 = II - 1;
+    int jb0, jb1, jbs;
+    if (irelax_sym == 0 || (updown == 0 && irelax_sym == 1)) {
+        jb0 = 3; jb1 = 2; jbs = -1;
+    } else {
+        jb0 = 2; jb1 = 3; jbs = 1;
+    }
+#define SO(i, j, kk) A3(so, II, JJ, i, j, kk)
+#define Q(i, j) A2(q, II, i, j)
+#define QF(i, j) A2(qf, II, i, j)
+#define SOR(i, j, kk) A3(sor, II, JJ, i, j, kk)
+    for (int jbeg = jb0; jbeg != jb1 + jbs; jbeg += jbs) {
+        int jend = 2 * ((J1 - jbeg) / 2) + jbeg;
+        if (k < kf || ifd != 1) {
+#pragma omp parallel for schedule(static)
+            for (int j = jbeg; j <= jend; j += 2) {
+                for (int i = 2; i <= I1; i++)
+                    Q(i, j) = QF(i, j) + SO(i, j, KS) * Q(i, j - 1) + SO(i, j + 1, KS) * Q(i, j + 1)
+                              + SO(i, j, KSW) * Q(i - 1, j - 1) + SO(i + 1, j, KNW) * Q(i + 1, j - 1)
+                              + SO(i, j + 1, KNW) * Q(i - 1, j + 1)
+                              + SO(i + 1, j + 1, KSW) * Q(i + 1, j + 1);
+                orc_dptts2(I1 - 1, &SOR(2, j, 1), &SOR(3, j, 2), &Q(2, j));
+            }
+        } else {
+#pragma omp parallel for schedule(static)
+            for (int j = jbeg; j <= jend; j += 2) {
+                for (int i = 2; i <= I1; i++)
+                    Q(i, j) = QF(i, j) + SO(i, j, KS) * Q(i, j - 1) + SO(i, j + 1, KS) * Q(i, j + 1);
+                orc_dptts2(I1 - 1, &SOR(2, j, 1), &SOR(3, j, 2), &Q(2, j));
+            }
+        }
+    }
+    return 0;
+#undef SO
+#undef Q
+#undef QF
+#undef SOR
+}
+
+/* ------------------------------------------------------------------------
+ * BMG2_SymStd_relax_lines_y.f90:75-166 (non-periodic); SOR is (JJ,II,2).
+ * ---------------------------------------------------------------------- */
+int orc2_relax_lines_y(int k, const double *so, const double *qf, double *q, const double *sor,
+                       double *bwork, int II, int JJ, int kf, int ifd, int nstncl,
+                       int irelax_sym, int updown, int jpn)
+{
+    (void)nstncl; (void)bwork;
+    if (jpn != 0 && jpn != -4) return -1;
+    int J1 = JJ - 1, I1 = II - 1;
+    int ib0, ib1, ibs;
+    if (irelax_sym == 0 || (updown == 0 && irelax_sym == 1)) {
+        ib0 = 3; ib1 = 2; ibs = -1;
+    } else {
+        ib0 = 2; ib1 = 3; ibs = 1;
+    }
+#define SO(i, j, kk) A3(so, II, JJ, i, j, kk)
+#define Q(i, j) A2(q, II, i, j)
+#define QF(i, j) A2(qf, II, i, j)
+#define SOR(j, i, kk) A3(sor, JJ, II, j, i, kk)
+    for (int ibeg = ib0; ibeg != ib1 + ibs; ibeg += ibs) {
+        int iend = 2 * ((I1 - ibeg) / 2) + ibeg;
+#pragma omp parallel
+        {
+            double *B = (double *)__builtin_malloc(sizeof(double) * (size_t)(JJ + 1));
+#pragma omp for schedule(static)
+            for (int i = ibeg; i <= iend; i += 2) {
+                if (k < kf || ifd != 1) {
+                    for (int j = 2; j <= J1; j++)
+                        B[j] = QF(i, j) + SO(i, j, KW) * Q(i - 1, j) + SO(i + 1, j, KW) * Q(i + 1, j)
+                               + SO(i, j, KSW) * Q(i - 1, j - 1) + SO(i + 1, j, KNW) * Q(i + 1, j - 1)
+                               + SO(i, j + 1, KNW) * Q(i - 1, j + 1)
+                               + SO(i + 1, j + 1, KSW) * Q(i + 1, j + 1);
+                } else {
+                    for (int j = 2; j <= J1; j++)
+                        B[j] = QF(i, j) + SO(i, j, KW) * Q(i - 1, j) + SO(i + 1, j, KW) * Q(i + 1, j);
+                }
+                orc_dptts2(J1 - 1, &SOR(2, i, 1), &SOR(3, i, 2), &B[2]);
+                for (int j = 2; j <= J1; j++) Q(i, j) = B[j];
+            }
+            __builtin_free(B);
+        }
+    }
+    return 0;
+#undef SO
+#undef Q
+#undef QF
+#undef SOR
+}
+
+/* ------------------------------------------------------------------------
+ * BMG2_SymStd_SETUP_cg_LU.f90:92-118 (9-pt) / 236-256 (5-pt), definite,
+ * non-periodic.  ABD(NABD1,NABD2), NABD1 = II.
+ * ---------------------------------------------------------------------- */
+int orc2_setup_cg_lu(const double *so, int II, int JJ, int nstncl,
+                     double *abd, int nabd1, int nabd2, int ibc)
+{
+    if (ibc != 0 && ibc != -4) return -1;
+    int I1 = II - 1, J1 = JJ - 1, I2 = I1 - 1;
+    int N = I2 * (J1 - 1);
+    int kk = 0;
+    if (nabd1 < II || nabd2 < N) return -2;
+#define SO(i, j, kq) A3(so, II, JJ, i, j, kq)
+#define ABD(i, j) abd[(size_t)((j)-1) * nabd1 + ((i)-1)]
+    for (int j = 2; j <= J1; j++)
+        for (int i = 2; i <= I1; i++) {
+            kk++;
+            ABD(II, kk) = SO(i, j, KO);
+            ABD(I1, kk) = -SO(i, j, KW);
+            ABD(3, kk) = nstncl == 5 ? -SO(i + 1, j, KNW) : 0.0;
+            ABD(2, kk) = -SO(i, j, KS);
+            ABD(1, kk) = nstncl == 5 ? -SO(i, j, KSW) : 0.0;
+        }
+    if (ibc < 0) ABD(II, kk) = ABD(II, kk) + SO(I1, J1, KO);
+    return orc_dpbtf2_upper(N, I1, abd, nabd1);
+#undef SO
+#undef ABD
+}
+
+/* BMG2_SymStd_SOLVE_cg.f90:93-122 (definite, non-periodic) */
+int orc2_solve_cg(double *q, const double *qf, int II, int JJ,
+                  const double *abd, double *bbd, int nabd1, int nabd2, int jpn)
+{
+    (void)nabd2;
+    if (jpn != 0) return -1;
+    int I1 = II - 1, J1 = JJ - 1;
+    int kk = 0;
+    for (int j = 2; j <= J1; j++)
+        for (int i = 2; i <= I1; i++) bbd[kk++] = A2(qf, II, i, j);
+    orc_dpbtrs_upper(kk, I1, abd, nabd1, bbd);
+    kk = 0;
+    for (int j = 2; j <= J1; j++)
+        for (int i = 2; i <= I1; i++) A2(q, II, i, j) = bbd[kk++];
+    return 0;
+}
+
+/* grid_func::lp_norm<2>, include/cedar/2d/grid_func.h:42-53: sequential sum,
+ * j outer, i inner, over the interior. */
+double orc2_l2norm(const double *q, int II, int JJ)
+{
+    double result = 0;
+    for (int j = 2; j <= JJ - 1; j++)
+        for (int i = 2; i <= II - 1; i++) {
+            double v = A2(q, II, i, j);
+            result += v * v; /* std::pow(v,2) == v*v exactly */
+        }
+    return sqrt(result); /* std::pow(result, 0.5) is exact-sqrt for glibc */
+}
