@@ -1,0 +1,70 @@
+"""ctypes bindings of the C ABI (``include/bmgx.h``) -- the reference-side stub
+a maintainer would write to call the B200 kernels from Python.  Device pointers
+are plain integers (e.g. ``torch.Tensor.data_ptr()``)."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libbmgx.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+        "(there is no CPU fallback)")
+
+lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+
+_p = C.c_void_p
+_i = C.c_int
+_u = C.c_uint32
+_d = C.c_double
+_z = C.c_size_t
+
+SIGNATURES = {
+    "bmgx_version": (C.c_char_p, []),
+    "bmgx_last_error": (C.c_char_p, []),
+    "bmgx_launch_count": (C.c_ulonglong, []),
+    "bmgx_get_bc": (None, [_i, C.POINTER(_i)]),
+    "bmgx_fill": (_i, [_p, _z, _d, _p]),
+    "bmgx_norm_work_len": (_z, []),
+    "bmgx2_sumsq": (_i, [_p, _u, _u, _p, _p, _p]),
+    "bmgx3_sumsq": (_i, [_p, _u, _u, _u, _p, _p, _p]),
+    "bmgx2_SETUP_recip": (_i, [_p, _p, _u, _u, _i, _i, _p]),
+    "bmgx2_relax_GS": (_i, [_i, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "bmgx2_relax_GS_oop": (_i, [_i, _p, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "bmgx2_SETUP_lines_x": (_i, [_p, _p, _u, _u, _i, _i, _p]),
+    "bmgx2_SETUP_lines_y": (_i, [_p, _p, _u, _u, _i, _i, _p]),
+    "bmgx2_relax_lines_x": (_i, [_i, _p, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
+    "bmgx2_relax_lines_y": (_i, [_i, _p, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
+    "bmgx2_residual": (_i, [_i, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "bmgx2_restrict": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _p]),
+    "bmgx2_interp_add": (_i, [_p, _p, _p, _p, _p, _u, _u, _u, _u, _i, _i, _p]),
+    "bmgx2_SETUP_interp_OI": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _i, _i, _i, _p]),
+    "bmgx2_SETUP_ITLI_ex": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _i, _i, _p]),
+    "bmgx2_SETUP_cg_LU": (_i, [_p, _u, _u, _i, _p, _u, _u, _i, _p]),
+    "bmgx2_SOLVE_cg": (_i, [_p, _p, _u, _u, _p, _p, _u, _u, _i, _p]),
+}
+
+for _name, (_res, _args) in SIGNATURES.items():
+    if hasattr(lib, _name):
+        _f = getattr(lib, _name)
+        _f.restype = _res
+        _f.argtypes = _args
+
+
+class BmgxError(RuntimeError):
+    pass
+
+
+def check(status):
+    if status != 0:
+        raise BmgxError(f"bmgx status {status}: {lib.bmgx_last_error().decode()}")
+
+
+def declared_symbols(header=None):
+    """Names of every function declared in include/bmgx.h (for the export test)."""
+    import re
+    header = header or os.path.join(_HERE, "..", "include", "bmgx.h")
+    txt = open(header).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(bmgx[0-9a-zA-Z_]*)\s*\(", txt)))

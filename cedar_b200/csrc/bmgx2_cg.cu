@@ -1,0 +1,138 @@
+// bmgx2_cg.cu -- coarsest-grid direct solve: banded Cholesky on the device.
+// Reference: src/2d/ftn/BMG2_SymStd_SETUP_cg_LU.f90:92-118 (9-pt), 236-256 (5-pt)
+//            + LAPACK DPBTRF('U') (unblocked DPBTF2 path, KD <= 32 or not),
+//            src/2d/ftn/BMG2_SymStd_SOLVE_cg.f90:93-122 + LAPACK DPBTRS('U').
+// The factorisation runs in one CTA (the rank-1 trailing update is spread over
+// the threads; each entry sees the same operations in the same order as
+// DPBTF2, so the factor is bitwise the oracle's).  The solve keeps DTBSV's
+// sequential accumulation order in one thread: the coarsest grids of the hot
+// path have 9..49 unknowns.
+#include "bmgx_common.cuh"
+
+#define ABD(i, j) abd[(size_t)((j)-1) * nabd1 + ((i)-1)]
+
+__global__ void __launch_bounds__(256)
+k_cg_assemble(const double *__restrict__ so, unsigned II, unsigned JJ, int nstncl, double *__restrict__ abd,
+              unsigned nabd1, int ibc)
+{
+    unsigned I1 = II - 1, J1 = JJ - 1, I2 = I1 - 1;
+    unsigned N = I2 * (J1 - 1);
+    for (unsigned kk = blockIdx.x * blockDim.x + threadIdx.x + 1; kk <= N; kk += gridDim.x * blockDim.x) {
+        unsigned i = (kk - 1) % I2 + 2, j = (kk - 1) / I2 + 2;
+        double d = so[IX3(II, JJ, i, j, KO)];
+        if (ibc < 0 && kk == N) d = d + so[IX3(II, JJ, I1, J1, KO)];
+        ABD(II, kk) = d;
+        ABD(I1, kk) = -so[IX3(II, JJ, i, j, KW)];
+        ABD(3, kk) = nstncl == 5 ? -so[IX3(II, JJ, i + 1, j, KNW)] : 0.0;
+        ABD(2, kk) = -so[IX3(II, JJ, i, j, KS)];
+        ABD(1, kk) = nstncl == 5 ? -so[IX3(II, JJ, i, j, KSW)] : 0.0;
+        // rows 4..I1-1 of the band are zero fill (ABD arrives zeroed from the caller)
+    }
+}
+
+// DPBTF2('U'): AB(kd+1,j) diagonal; one CTA.
+__global__ void __launch_bounds__(256) k_dpbtf2_upper(int n, int kd, double *abd, int nabd1, int *info)
+{
+    int kld = nabd1 - 1 > 1 ? nabd1 - 1 : 1;
+    __shared__ double s_r;
+    __shared__ int s_bad;
+    if (threadIdx.x == 0) s_bad = 0;
+    __syncthreads();
+    for (int j = 1; j <= n; j++) {
+        if (threadIdx.x == 0) {
+            double ajj = ABD(kd + 1, j);
+            if (ajj <= 0.0) {
+                s_bad = j;
+            } else {
+                ajj = sqrt(ajj);
+                ABD(kd + 1, j) = ajj;
+                s_r = 1.0 / ajj;
+            }
+        }
+        __syncthreads();
+        if (s_bad) break;
+        int kn = kd < n - j ? kd : n - j;
+        if (kn > 0) {
+            double *x = &ABD(kd, j + 1);
+            double r = s_r;
+            for (int p = threadIdx.x; p < kn; p += blockDim.x) x[(size_t)p * kld] = r * x[(size_t)p * kld];
+            __syncthreads();
+            double *a = &ABD(kd + 1, j + 1);
+            // DSYR upper: a(p,q) += x(p) * (-x(q)), p <= q
+            int tot = kn * kn;
+            for (int t = threadIdx.x; t < tot; t += blockDim.x) {
+                int q = t / kn, p = t % kn;
+                if (p <= q) {
+                    double xq = x[(size_t)q * kld];
+                    if (xq != 0.0) {
+                        double temp = -1.0 * xq;
+                        a[(size_t)q * kld + p] = a[(size_t)q * kld + p] + x[(size_t)p * kld] * temp;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0 && info) *info = s_bad;
+}
+
+extern "C" int bmgx2_SETUP_cg_LU(const double *so, bmgx_len ii, bmgx_len jj, int nstncl, double *abd,
+                                 bmgx_len nabd1, bmgx_len nabd2, int ibc, bmgx_stream_t s)
+{
+    if (!bmgx_nonperiodic(ibc)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SETUP_cg_LU: periodic BCs not supported");
+    if (ii < 3 || jj < 3) return bmgx_set_error(BMGX_ERR_ARG, "SETUP_cg_LU: empty grid");
+    unsigned n = (ii - 2) * (jj - 2);
+    if (nabd1 < ii || nabd2 < n) return bmgx_set_error(BMGX_ERR_ARG, "SETUP_cg_LU: ABD too small");
+    cudaStream_t st = (cudaStream_t)s;
+    cudaError_t e = cudaMemsetAsync(abd, 0, sizeof(double) * (size_t)nabd1 * nabd2, st);
+    if (e != cudaSuccess) return bmgx_set_cuda_error(e, "SETUP_cg_LU/memset");
+    bmgx_count_launch();
+    k_cg_assemble<<<cdiv(n, 256) > 1024 ? 1024 : cdiv(n, 256), 256, 0, st>>>(so, ii, jj, nstncl, abd, nabd1, ibc);
+    BMGX_LAUNCH_CHECK("SETUP_cg_LU/assemble");
+    k_dpbtf2_upper<<<1, 256, 0, st>>>((int)n, (int)(ii - 1), abd, (int)nabd1, nullptr);
+    BMGX_LAUNCH_CHECK("SETUP_cg_LU/dpbtf2");
+    return BMGX_OK;
+}
+
+// copy rhs -> DTBSV(U,T,N) -> DTBSV(U,N,N) -> copy back; single thread keeps
+// the reference accumulation order.
+__global__ void k_solve_cg(double *q, const double *__restrict__ qf, unsigned II, unsigned JJ,
+                           const double *__restrict__ abd, double *bbd, unsigned nabd1)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    int I1 = II - 1, J1 = JJ - 1;
+    int kd = I1, kplus1 = kd + 1;
+    int n = 0;
+    for (int j = 2; j <= J1; j++)
+        for (int i = 2; i <= I1; i++) bbd[n++] = qf[IX2(II, i, j)];
+    for (int j = 1; j <= n; j++) {
+        double temp = bbd[j - 1];
+        int l = kplus1 - j;
+        int i0 = j - kd > 1 ? j - kd : 1;
+        for (int i = i0; i <= j - 1; i++) temp = temp - ABD(l + i, j) * bbd[i - 1];
+        temp = temp / ABD(kplus1, j);
+        bbd[j - 1] = temp;
+    }
+    for (int j = n; j >= 1; j--) {
+        if (bbd[j - 1] != 0.0) {
+            int l = kplus1 - j;
+            bbd[j - 1] = bbd[j - 1] / ABD(kplus1, j);
+            double temp = bbd[j - 1];
+            int i0 = j - kd > 1 ? j - kd : 1;
+            for (int i = j - 1; i >= i0; i--) bbd[i - 1] = bbd[i - 1] - temp * ABD(l + i, j);
+        }
+    }
+    n = 0;
+    for (int j = 2; j <= J1; j++)
+        for (int i = 2; i <= I1; i++) q[IX2(II, i, j)] = bbd[n++];
+}
+
+extern "C" int bmgx2_SOLVE_cg(double *q, const double *qf, bmgx_len ii, bmgx_len jj, const double *abd, double *bbd,
+                              bmgx_len nabd1, bmgx_len nabd2, int jpn, bmgx_stream_t s)
+{
+    (void)nabd2;
+    if (jpn != BMGX_BCs_definite) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SOLVE_cg: only definite, non-periodic");
+    k_solve_cg<<<1, 32, 0, (cudaStream_t)s>>>(q, qf, ii, jj, abd, bbd, nabd1);
+    BMGX_LAUNCH_CHECK("SOLVE_cg");
+    return BMGX_OK;
+}

@@ -1,0 +1,101 @@
+// bmgx2_relax.cu -- 2D multicolour point Gauss-Seidel (reference:
+// src/2d/ftn/BMG2_SymStd_relax_GS.f90:68-135) and SETUP_recip.
+//
+// Colour order (F-index parity, first interior index is 2):
+//   9-pt: (j even,i even) (j even,i odd) (j odd,i even) (j odd,i odd) on DOWN,
+//         exact reverse on UP (relax_GS.f90:78-114);
+//   5-pt: red-black, pass JO=2 then 3 on DOWN, IBEG = mod(J+JO,2)+2
+//         (relax_GS.f90:120-135).
+// Term order inside the update is the reference's, and the file is compiled
+// with -fmad=false, so results are bitwise those of the oracle.
+#include "bmgx_common.cuh"
+
+__global__ void k_setup_recip(const double *__restrict__ so, double *__restrict__ sor, unsigned nx, unsigned ny)
+{
+    unsigned i = blockIdx.x * blockDim.x + threadIdx.x + 2;
+    unsigned j = blockIdx.y + 2;
+    if (i <= nx - 1 && j <= ny - 1) sor[IX3(nx, ny, i, j, MSOR)] = 1.0 / so[IX3(nx, ny, i, j, KO)];
+}
+
+extern "C" int bmgx2_SETUP_recip(const double *so, double *sor, bmgx_len nx, bmgx_len ny, int nstncl, int nsor_v,
+                                 bmgx_stream_t s)
+{
+    (void)nstncl;
+    if (nsor_v < 2) return bmgx_set_error(BMGX_ERR_ARG, "SETUP_recip: nsor_v < 2");
+    if (nx < 3 || ny < 3) return BMGX_OK;
+    dim3 g(cdiv(nx - 2, 256), ny - 2);
+    k_setup_recip<<<g, 256, 0, (cudaStream_t)s>>>(so, sor, nx, ny);
+    BMGX_LAUNCH_CHECK("SETUP_recip");
+    return BMGX_OK;
+}
+
+// ---- in-place, one launch per colour ---------------------------------------
+template <bool NINE>
+__global__ void __launch_bounds__(128)
+k_relax_colour(const double *__restrict__ so, const double *__restrict__ qf, double *q,
+               const double *__restrict__ sor, unsigned II, unsigned JJ,
+               unsigned ibeg9, unsigned jbeg, unsigned jstep, unsigned jo5)
+{
+    unsigned j = jbeg + jstep * blockIdx.y;
+    unsigned ibeg = NINE ? ibeg9 : ((j + jo5) % 2 + 2);
+    unsigned i = ibeg + 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    if (i > II - 1 || j > JJ - 1) return;
+    size_t c = IX2(II, i, j);
+    size_t pl = (size_t)II * JJ;
+    const double *kw = so + (KW - 1) * pl, *ks = so + (KS - 1) * pl;
+    double acc = qf[c] + kw[c] * q[c - 1] + kw[c + 1] * q[c + 1] + ks[c] * q[c - II] + ks[c + II] * q[c + II];
+    if (NINE) {
+        const double *ksw = so + (KSW - 1) * pl, *knw = so + (KNW - 1) * pl;
+        acc = acc + ksw[c] * q[c - II - 1] + knw[c + 1] * q[c - II + 1] + knw[c + II] * q[c + II - 1]
+              + ksw[c + II + 1] * q[c + II + 1];
+    }
+    q[c] = acc * sor[(MSOR - 1) * pl + c];
+}
+
+extern "C" int bmgx2_relax_GS(int k, const double *so, const double *qf, double *q, const double *sor, bmgx_len ii,
+                              bmgx_len jj, int kf, int ifd, int nstncl, int nsorv, int irelax_sym, int updown,
+                              int jpn, bmgx_stream_t s)
+{
+    (void)nstncl; (void)nsorv;
+    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_GS: periodic BCs not supported");
+    if (ii < 3 || jj < 3) return BMGX_OK;
+    cudaStream_t st = (cudaStream_t)s;
+    bool fwd = (irelax_sym == BMGX_RELAX_NONSYM) || (updown == BMGX_DOWN && irelax_sym == BMGX_RELAX_SYM);
+    unsigned I1 = ii - 1, J1 = jj - 1;
+    if (k < kf || ifd != 1) {
+        for (int a = 0; a < 2; a++) {
+            unsigned jbeg = fwd ? 2 + a : 3 - a;
+            if (jbeg > J1) continue;
+            unsigned nrow = (J1 - jbeg) / 2 + 1;
+            for (int b = 0; b < 2; b++) {
+                unsigned ibeg = fwd ? 2 + b : 3 - b;
+                if (ibeg > I1) continue;
+                unsigned ncol = (I1 - ibeg) / 2 + 1;
+                dim3 g(cdiv(ncol, 128), nrow);
+                k_relax_colour<true><<<g, 128, 0, st>>>(so, qf, q, sor, ii, jj, ibeg, jbeg, 2, 0);
+                BMGX_LAUNCH_CHECK("relax_GS/9");
+            }
+        }
+    } else {
+        for (int a = 0; a < 2; a++) {
+            unsigned jo = fwd ? 2 + a : 3 - a;
+            unsigned ncol = (I1 - 2) / 2 + 1;  // upper bound on points per row of one colour
+            dim3 g(cdiv(ncol, 128), J1 - 1);
+            k_relax_colour<false><<<g, 128, 0, st>>>(so, qf, q, sor, ii, jj, 0, 2, 1, jo);
+            BMGX_LAUNCH_CHECK("relax_GS/5");
+        }
+    }
+    return BMGX_OK;
+}
+
+extern "C" int bmgx2_relax_GS_oop(int k, const double *so, const double *qf, const double *q_in, double *q_out,
+                                  const double *sor, bmgx_len ii, bmgx_len jj, int kf, int ifd, int nstncl,
+                                  int nsorv, int irelax_sym, int updown, int jpn, bmgx_stream_t s)
+{
+    if (q_in == q_out) return bmgx_set_error(BMGX_ERR_ARG, "relax_GS_oop: q_in aliases q_out");
+    cudaError_t e = cudaMemcpyAsync(q_out, q_in, sizeof(double) * (size_t)ii * jj, cudaMemcpyDeviceToDevice,
+                                    (cudaStream_t)s);
+    if (e != cudaSuccess) return bmgx_set_cuda_error(e, "relax_GS_oop/copy");
+    bmgx_count_launch();
+    return bmgx2_relax_GS(k, so, qf, q_out, sor, ii, jj, kf, ifd, nstncl, nsorv, irelax_sym, updown, jpn, s);
+}

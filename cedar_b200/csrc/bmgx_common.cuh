@@ -1,0 +1,34 @@
+// bmgx_common.cuh -- shared helpers for the sm_100a BoxMG kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/bmgx.h"
+
+// Fortran-order, 1-based accessors (ghost layer included): the kernels keep the
+// reference's index conventions so every formula can be checked against the
+// .f90 line it mirrors.
+#define IX2(n1, i, j) ((size_t)((j)-1) * (size_t)(n1) + (size_t)((i)-1))
+#define IX3(n1, n2, i, j, k) (((size_t)((k)-1) * (size_t)(n2) + (size_t)((j)-1)) * (size_t)(n1) + (size_t)((i)-1))
+
+// stencil slots, src/2d/ftn/BMG_stencils_f90.h:29-37
+enum { KO = 1, KW = 2, KS = 3, KSW = 4, KNW = 5 };
+enum { LL = 1, LR = 2, LA = 3, LB = 4, LSW = 5, LNW = 6, LNE = 7, LSE = 8 };
+enum { MSOR = 2 };
+
+int bmgx_set_cuda_error(cudaError_t e, const char *where);
+int bmgx_set_error(int code, const char *msg);
+void bmgx_count_launch(unsigned n = 1);
+
+#define BMGX_LAUNCH_CHECK(where)                                          \
+    do {                                                                  \
+        cudaError_t e__ = cudaGetLastError();                             \
+        if (e__ != cudaSuccess) return bmgx_set_cuda_error(e__, where);   \
+        bmgx_count_launch();                                              \
+    } while (0)
+
+static inline bool bmgx_nonperiodic(int jpn) { return jpn == BMGX_BCs_definite || jpn == BMGX_BCs_indef_nonper; }
+static inline unsigned cdiv(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
+
+// streaming (read-once) load: keep it out of L1
+__device__ __forceinline__ double ldg_stream(const double *p) { return __ldcs(p); }

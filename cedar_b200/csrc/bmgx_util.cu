@@ -1,0 +1,128 @@
+// bmgx_util.cu -- error state, launch counter, fill, deterministic sum of squares.
+#include "bmgx_common.cuh"
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+
+static thread_local char g_err[512] = "";
+static std::atomic<unsigned long long> g_launches{0};
+
+int bmgx_set_cuda_error(cudaError_t e, const char *where)
+{
+    snprintf(g_err, sizeof(g_err), "%s: %s", where, cudaGetErrorString(e));
+    return BMGX_ERR_CUDA;
+}
+int bmgx_set_error(int code, const char *msg)
+{
+    snprintf(g_err, sizeof(g_err), "%s", msg);
+    return code;
+}
+void bmgx_count_launch(unsigned n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+extern "C" const char *bmgx_version(void) { return "bmgx 0.1 (sm_100a)"; }
+extern "C" const char *bmgx_last_error(void) { return g_err; }
+extern "C" unsigned long long bmgx_launch_count(void) { return g_launches.load(); }
+
+// src/2d/ftn/BMG_get_bc.f90:13-22
+extern "C" void bmgx_get_bc(int per_mask, int *ibc)
+{
+    static const int bcmap[8] = {0, 2, 1, 3, 5, 6, 7, 8};
+    *ibc = bcmap[per_mask & 7];
+}
+
+__global__ void k_fill(double *a, size_t n, double v)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) a[i] = v;
+}
+
+extern "C" int bmgx_fill(double *a, size_t n, double v, bmgx_stream_t s)
+{
+    if (n == 0) return BMGX_OK;
+    if (v == 0.0) {
+        cudaError_t e = cudaMemsetAsync(a, 0, n * sizeof(double), (cudaStream_t)s);
+        if (e != cudaSuccess) return bmgx_set_cuda_error(e, "bmgx_fill");
+        bmgx_count_launch();
+        return BMGX_OK;
+    }
+    unsigned nb = cdiv(n, 256);
+    if (nb > 148 * 16) nb = 148 * 16;
+    k_fill<<<nb, 256, 0, (cudaStream_t)s>>>(a, n, v);
+    BMGX_LAUNCH_CHECK("bmgx_fill");
+    return BMGX_OK;
+}
+
+// ---- deterministic sum of squares over the interior ------------------------
+// Stage 1: NB blocks, each sums a fixed, contiguous set of rows with a fixed
+// in-block tree; stage 2: one block folds the NB partials in a fixed tree.
+// The result does not depend on scheduling (bitwise reproducible run to run).
+#define NORM_NB 1184  // 148 SMs x 8
+extern "C" size_t bmgx_norm_work_len(void) { return NORM_NB; }
+
+__device__ __forceinline__ double block_sum_256(double v)
+{
+    __shared__ double sh[8];
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) sh[w] = v;
+    __syncthreads();
+    double r = 0.0;
+    if (w == 0) {
+        r = l < 8 ? sh[l] : 0.0;
+        for (int o = 4; o > 0; o >>= 1) r += __shfl_down_sync(0xffffffffu, r, o);
+    }
+    __syncthreads();
+    return r;  // valid in thread 0
+}
+
+__global__ void __launch_bounds__(256) k_sumsq_stage1(const double *__restrict__ q, unsigned II, size_t nrows, size_t rowstride2,
+                                                      unsigned JJ, double *__restrict__ part)
+{
+    // "rows" enumerates interior (j[,k]) lines; line r -> j = r % (JJ-2) + 1 (0-based), k = r / (JJ-2) + 1
+    size_t r0 = nrows * blockIdx.x / gridDim.x, r1 = nrows * (blockIdx.x + 1) / gridDim.x;
+    double acc = 0.0;
+    unsigned nj = JJ - 2;
+    for (size_t r = r0; r < r1; r++) {
+        size_t j = r % nj + 1, k = r / nj;
+        const double *row = q + (rowstride2 ? (k + 1) * rowstride2 : 0) + j * (size_t)II;
+        for (unsigned i = 1 + threadIdx.x; i < II - 1; i += 256) {
+            double v = row[i];
+            acc += v * v;
+        }
+    }
+    double t = block_sum_256(acc);
+    if (threadIdx.x == 0) part[blockIdx.x] = t;
+}
+
+__global__ void __launch_bounds__(256) k_sumsq_stage2(const double *__restrict__ part, int n, double *out)
+{
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += 256) acc += part[i];
+    double t = block_sum_256(acc);
+    if (threadIdx.x == 0) *out = t;
+}
+
+extern "C" int bmgx2_sumsq(const double *q, bmgx_len ii, bmgx_len jj, double *work, double *out, bmgx_stream_t s)
+{
+    if (ii < 3 || jj < 3) return bmgx_set_error(BMGX_ERR_ARG, "bmgx2_sumsq: empty interior");
+    size_t nrows = jj - 2;
+    int nb = nrows < NORM_NB ? (int)nrows : NORM_NB;
+    k_sumsq_stage1<<<nb, 256, 0, (cudaStream_t)s>>>(q, ii, nrows, 0, jj, work);
+    BMGX_LAUNCH_CHECK("bmgx2_sumsq/1");
+    k_sumsq_stage2<<<1, 256, 0, (cudaStream_t)s>>>(work, nb, out);
+    BMGX_LAUNCH_CHECK("bmgx2_sumsq/2");
+    return BMGX_OK;
+}
+
+extern "C" int bmgx3_sumsq(const double *q, bmgx_len ii, bmgx_len jj, bmgx_len kk, double *work, double *out, bmgx_stream_t s)
+{
+    if (ii < 3 || jj < 3 || kk < 3) return bmgx_set_error(BMGX_ERR_ARG, "bmgx3_sumsq: empty interior");
+    size_t nrows = (size_t)(jj - 2) * (kk - 2);
+    int nb = nrows < NORM_NB ? (int)nrows : NORM_NB;
+    k_sumsq_stage1<<<nb, 256, 0, (cudaStream_t)s>>>(q, ii, nrows, (size_t)ii * jj, jj, work);
+    BMGX_LAUNCH_CHECK("bmgx3_sumsq/1");
+    k_sumsq_stage2<<<1, 256, 0, (cudaStream_t)s>>>(work, nb, out);
+    BMGX_LAUNCH_CHECK("bmgx3_sumsq/2");
+    return BMGX_OK;
+}

@@ -1,0 +1,154 @@
+/*
+ * bmgx.h -- C ABI of the B200-native BoxMG kernels (libbmgx.so).
+ *
+ * This is the drop-in boundary: one entry point per `BIND(C)` Fortran routine
+ * that the reference's kernel wrapper classes call (cedar include/cedar/2d headers,
+ * src/2d sources).  Argument order and meaning follow the
+ * reference interface cited at each prototype, with three changes:
+ *   - every array pointer is a DEVICE pointer (fp64, Fortran order, i fastest,
+ *     1 ghost layer: Q(II,JJ), SO(II,JJ,NStncl), SOR(II,JJ,2), CI(IIC,JJC,8));
+ *   - every function takes a trailing `bmgx_stream_t` (a cudaStream_t; 0 = the
+ *     legacy default stream) and only enqueues work: no host synchronisation,
+ *     so all of them are CUDA-graph capturable;
+ *   - every function returns an int status (0 = ok) instead of calling back
+ *     into a logger; nothing throws across this boundary.
+ * Scalars the Fortran takes by reference (BMG2_SymStd_residual) are by value.
+ *
+ * There is no CPU fallback: if no CUDA device is usable the calls return
+ * BMGX_ERR_CUDA.
+ */
+#ifndef BMGX_H
+#define BMGX_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef double   bmgx_real;   /* cedar real_t, include/cedar/types.h:44 */
+typedef uint32_t bmgx_len;    /* cedar len_t,  include/cedar/types.h:43 */
+typedef void    *bmgx_stream_t;
+
+enum {
+    BMGX_OK = 0,
+    BMGX_ERR_CUDA = 1,        /* CUDA runtime error, see bmgx_last_error() */
+    BMGX_ERR_UNSUPPORTED = 2, /* e.g. periodic boundary conditions (not yet) */
+    BMGX_ERR_ARG = 3
+};
+
+/* src/2d/ftn/BMG_parameters_f90.h:345-413 */
+enum { BMGX_BCs_definite = 0, BMGX_BCs_indef_nonper = -4 };
+enum { BMGX_RELAX_NONSYM = 0, BMGX_RELAX_SYM = 1 };
+enum { BMGX_DOWN = 0, BMGX_UP = 1 };
+
+const char *bmgx_version(void);
+const char *bmgx_last_error(void);
+/* number of kernels this library has launched so far (process wide) */
+unsigned long long bmgx_launch_count(void);
+
+/* BMG_get_bc, src/2d/ftn/BMG_get_bc.f90:1-24 */
+void bmgx_get_bc(int per_mask, int *ibc);
+
+/* ---- utilities used by the host layer (grid_func::set / lp_norm) ---------- */
+/* array<>::set(v) over n doubles */
+int bmgx_fill(bmgx_real *a, size_t n, bmgx_real v, bmgx_stream_t s);
+/* sum of squares of the interior of Q(II,JJ[,KK]) -> *out (device double),
+ * grid_func::lp_norm<2>, include/cedar/2d/grid_func.h:42-53 (the caller takes
+ * the sqrt).  Deterministic (fixed reduction tree).  work: >= bmgx_norm_work_len()
+ * doubles of device scratch. */
+size_t bmgx_norm_work_len(void);
+int bmgx2_sumsq(const bmgx_real *q, bmgx_len ii, bmgx_len jj, bmgx_real *work,
+                bmgx_real *out, bmgx_stream_t s);
+int bmgx3_sumsq(const bmgx_real *q, bmgx_len ii, bmgx_len jj, bmgx_len kk, bmgx_real *work,
+                bmgx_real *out, bmgx_stream_t s);
+
+/* ---- 2D ------------------------------------------------------------------ */
+
+/* BMG2_SymStd_SETUP_recip(so, sor, nx, ny, nstncl, nsor_v)
+ * include/cedar/2d/relax.h:11-12, src/2d/ftn/BMG2_SymStd_SETUP_recip.f90 */
+int bmgx2_SETUP_recip(const bmgx_real *so, bmgx_real *sor, bmgx_len nx, bmgx_len ny,
+                      int nstncl, int nsor_v, bmgx_stream_t s);
+
+/* BMG2_SymStd_relax_GS(k, so, qf, q, sor, ii, jj, kf, ifd, nstncl, nsorv,
+ *                      irelax_sym, updown, jpn)
+ * include/cedar/2d/relax.h:13-15, src/2d/ftn/BMG2_SymStd_relax_GS.f90 */
+int bmgx2_relax_GS(int k, const bmgx_real *so, const bmgx_real *qf, bmgx_real *q,
+                   const bmgx_real *sor, bmgx_len ii, bmgx_len jj, int kf, int ifd,
+                   int nstncl, int nsorv, int irelax_sym, int updown, int jpn,
+                   bmgx_stream_t s);
+
+/* Out-of-place form of the same sweep (B200-native fast path): reads q_in,
+ * writes the relaxed iterate (interior + copied ghost ring) to q_out; all
+ * colours in ONE pass over memory.  q_in and q_out must not alias. */
+int bmgx2_relax_GS_oop(int k, const bmgx_real *so, const bmgx_real *qf, const bmgx_real *q_in,
+                       bmgx_real *q_out, const bmgx_real *sor, bmgx_len ii, bmgx_len jj,
+                       int kf, int ifd, int nstncl, int nsorv, int irelax_sym, int updown,
+                       int jpn, bmgx_stream_t s);
+
+/* BMG2_SymStd_SETUP_lines_x / _y (so, sor, nx, ny, nstncl, jpn)
+ * include/cedar/2d/relax.h:16-19; LAPACK DPTTRF is replaced on device. */
+int bmgx2_SETUP_lines_x(const bmgx_real *so, bmgx_real *sor, bmgx_len nx, bmgx_len ny,
+                        int nstncl, int jpn, bmgx_stream_t s);
+int bmgx2_SETUP_lines_y(const bmgx_real *so, bmgx_real *sor, bmgx_len nx, bmgx_len ny,
+                        int nstncl, int jpn, bmgx_stream_t s);
+
+/* BMG2_SymStd_relax_lines_x / _y (k, so, qf, q, sor, b, ii, jj, kf, ifd,
+ *                                 nstncl, irelax_sym, updown, jpn)
+ * include/cedar/2d/relax.h:20-25; `b` is scratch of >= ii*jj doubles. */
+int bmgx2_relax_lines_x(int k, const bmgx_real *so, const bmgx_real *qf, bmgx_real *q,
+                        const bmgx_real *sor, bmgx_real *b, bmgx_len ii, bmgx_len jj,
+                        int kf, int ifd, int nstncl, int irelax_sym, int updown, int jpn,
+                        bmgx_stream_t s);
+int bmgx2_relax_lines_y(int k, const bmgx_real *so, const bmgx_real *qf, bmgx_real *q,
+                        const bmgx_real *sor, bmgx_real *b, bmgx_len ii, bmgx_len jj,
+                        int kf, int ifd, int nstncl, int irelax_sym, int updown, int jpn,
+                        bmgx_stream_t s);
+
+/* BMG2_SymStd_residual(k, so, qf, q, res, ii, jj, kf, ifd, nstncl, ibc,
+ *                      irelax, irelax_sym, updown)   [by reference there]
+ * include/cedar/2d/residual.h:9-10 */
+int bmgx2_residual(int k, const bmgx_real *so, const bmgx_real *qf, const bmgx_real *q,
+                   bmgx_real *res, bmgx_len ii, bmgx_len jj, int kf, int ifd, int nstncl,
+                   int ibc, int irelax, int irelax_sym, int updown, bmgx_stream_t s);
+
+/* BMG2_SymStd_restrict(q, qc, ci, nx, ny, nxc, nyc, jpn), src/2d/restrict.cc:6-9 */
+int bmgx2_restrict(const bmgx_real *q, bmgx_real *qc, const bmgx_real *ci, bmgx_len nx,
+                   bmgx_len ny, bmgx_len nxc, bmgx_len nyc, int jpn, bmgx_stream_t s);
+
+/* BMG2_SymStd_interp_add(q, qc, res, so, ci, iic, jjc, iif, jjf, nstncl, jpn)
+ * src/2d/interp.cc:8-10.  `res` is scaled in place by 1/diag as in the
+ * reference (BMG2_SymStd_interp_add.f90:101-105). */
+int bmgx2_interp_add(bmgx_real *q, const bmgx_real *qc, bmgx_real *res, const bmgx_real *so,
+                     const bmgx_real *ci, bmgx_len iic, bmgx_len jjc, bmgx_len iif,
+                     bmgx_len jjf, int nstncl, int jpn, bmgx_stream_t s);
+
+/* BMG2_SymStd_SETUP_interp_OI(so, soc, ci, iif, jjf, iic, jjc, ifd, nstncl,
+ *                             jpn, irelax), src/2d/interp.cc:11-13 */
+int bmgx2_SETUP_interp_OI(const bmgx_real *so, const bmgx_real *soc, bmgx_real *ci,
+                          bmgx_len iif, bmgx_len jjf, bmgx_len iic, bmgx_len jjc, int ifd,
+                          int nstncl, int jpn, int irelax, bmgx_stream_t s);
+
+/* BMG2_SymStd_SETUP_ITLI_ex(so, soc, ci, iif, jjf, iic, jjc, ifd, nstncl, ipn)
+ * include/cedar/2d/coarsen.h:10-12 (Galerkin coarse operator) */
+int bmgx2_SETUP_ITLI_ex(const bmgx_real *so, bmgx_real *soc, const bmgx_real *ci,
+                        bmgx_len iif, bmgx_len jjf, bmgx_len iic, bmgx_len jjc, int ifd,
+                        int nstncl, int ipn, bmgx_stream_t s);
+
+/* BMG2_SymStd_SETUP_cg_LU(so, ii, jj, nstncl, abd, nabd1, nabd2, ibc)
+ * include/cedar/2d/solve_cg.h:10 ; LAPACK DPBTRF replaced on device. */
+int bmgx2_SETUP_cg_LU(const bmgx_real *so, bmgx_len ii, bmgx_len jj, int nstncl,
+                      bmgx_real *abd, bmgx_len nabd1, bmgx_len nabd2, int ibc,
+                      bmgx_stream_t s);
+
+/* BMG2_SymStd_SOLVE_cg(q, qf, ii, jj, abd, bbd, nabd1, nabd2, jpn)
+ * src/2d/solve_cg.cc:6 ; bbd is DEVICE scratch of nabd2 doubles. */
+int bmgx2_SOLVE_cg(bmgx_real *q, const bmgx_real *qf, bmgx_len ii, bmgx_len jj,
+                   const bmgx_real *abd, bmgx_real *bbd, bmgx_len nabd1, bmgx_len nabd2,
+                   int jpn, bmgx_stream_t s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BMGX_H */

@@ -1,0 +1,200 @@
+"""GPU parity tests (through the C ABI) of the 2D kernels against the CPU oracle.
+
+Bitwise for every stencil kernel (same expression order, -fmad=false vs
+-ffp-contract=off); 1e-12 relative for the line solves (warp-scan evaluation
+order differs from DPTTS2's sequential loop)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle
+from oracle import P
+from tests.util import (assert_bitwise, coarse_n, dev, host, ptr, random_gf, random_op2)
+
+pytestmark = pytest.mark.gpu
+
+SIZES = [(1, 1), (2, 3), (3, 3), (7, 5), (16, 16), (31, 31), (37, 64), (130, 97), (400, 257)]
+
+
+@pytest.fixture(scope="module")
+def abi(cuda):
+    import cedar_b200.abi as a
+    return a
+
+
+def ifd_of(nine):
+    return 0 if nine else 1
+
+
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", SIZES)
+def test_residual(cuda, abi, nx, ny, nine):
+    rng = np.random.default_rng(nx * 1000 + ny + nine)
+    so = random_op2(nx, ny, nine, rng)
+    q = random_gf(nx, ny, rng); b = random_gf(nx, ny, rng)
+    ref = np.zeros_like(q)
+    oracle.lib().orc2_residual(0, P(so), P(b), P(q), P(ref), nx + 2, ny + 2, 0, ifd_of(nine), so.shape[0])
+    d_so, d_q, d_b = dev(cuda, so), dev(cuda, q), dev(cuda, b)
+    d_r = cuda.zeros_like(d_q)
+    abi.check(abi.lib.bmgx2_residual(0, ptr(d_so), ptr(d_b), ptr(d_q), ptr(d_r), nx + 2, ny + 2, 0, ifd_of(nine),
+                                     so.shape[0], 0, 0, 0, 0, None))
+    assert_bitwise(host(d_r), ref, "residual")
+
+
+@pytest.mark.parametrize("updown", [0, 1])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", SIZES)
+def test_relax_gs(cuda, abi, nx, ny, nine, updown):
+    rng = np.random.default_rng(nx * 77 + ny + 5 * nine + updown)
+    so = random_op2(nx, ny, nine, rng)
+    q = random_gf(nx, ny, rng); b = random_gf(nx, ny, rng)
+    sor = np.zeros((2, ny + 2, nx + 2))
+    L = oracle.lib()
+    L.orc2_setup_recip(P(so), P(sor), nx + 2, ny + 2, so.shape[0], 2)
+    d_so, d_q, d_b = dev(cuda, so), dev(cuda, q), dev(cuda, b)
+    d_sor = cuda.zeros(sor.shape, dtype=cuda.float64, device="cuda")
+    abi.check(abi.lib.bmgx2_SETUP_recip(ptr(d_so), ptr(d_sor), nx + 2, ny + 2, so.shape[0], 2, None))
+    assert_bitwise(host(d_sor), sor, "SETUP_recip")
+    d_q2 = cuda.full_like(d_q, 7.0)
+    for sweep in range(3):
+        assert L.orc2_relax_gs(1, P(so), P(b), P(q), P(sor), nx + 2, ny + 2, 1, ifd_of(nine), so.shape[0], 2, 1, updown, 0) == 0
+        # out-of-place form first (reads d_q), then the in-place one
+        abi.check(abi.lib.bmgx2_relax_GS_oop(1, ptr(d_so), ptr(d_b), ptr(d_q), ptr(d_q2), ptr(d_sor), nx + 2, ny + 2,
+                                             1, ifd_of(nine), so.shape[0], 2, 1, updown, 0, None))
+        abi.check(abi.lib.bmgx2_relax_GS(1, ptr(d_so), ptr(d_b), ptr(d_q), ptr(d_sor), nx + 2, ny + 2, 1, ifd_of(nine),
+                                         so.shape[0], 2, 1, updown, 0, None))
+        assert_bitwise(host(d_q), q, f"relax_GS sweep {sweep}")
+        assert_bitwise(host(d_q2), q, f"relax_GS_oop sweep {sweep}")
+
+
+def _setup_pair(nx, ny, nine, rng):
+    so = random_op2(nx, ny, nine, rng)
+    nxc, nyc = coarse_n(nx), coarse_n(ny)
+    ci = np.zeros((8, nyc + 2, nxc + 2))
+    soc = np.zeros((5, nyc + 2, nxc + 2))
+    return so, nxc, nyc, ci, soc
+
+
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [s for s in SIZES if min(s) >= 3])
+def test_setup_interp_and_galerkin(cuda, abi, nx, ny, nine):
+    rng = np.random.default_rng(nx * 13 + ny + nine)
+    so, nxc, nyc, ci, soc = _setup_pair(nx, ny, nine, rng)
+    L = oracle.lib()
+    nst = so.shape[0]
+    assert L.orc2_setup_interp_oi(P(so), P(soc), P(ci), nx + 2, ny + 2, nxc + 2, nyc + 2, ifd_of(nine), nst, 0, 0) == 0
+    assert L.orc2_setup_itli_ex(P(so), P(soc), P(ci), nx + 2, ny + 2, nxc + 2, nyc + 2, ifd_of(nine), nst, 0) == 0
+    d_so = dev(cuda, so)
+    d_ci = cuda.zeros(ci.shape, dtype=cuda.float64, device="cuda")
+    d_soc = cuda.zeros(soc.shape, dtype=cuda.float64, device="cuda")
+    abi.check(abi.lib.bmgx2_SETUP_interp_OI(ptr(d_so), ptr(d_soc), ptr(d_ci), nx + 2, ny + 2, nxc + 2, nyc + 2,
+                                            ifd_of(nine), nst, 0, 0, None))
+    assert_bitwise(host(d_ci), ci, "SETUP_interp_OI")
+    abi.check(abi.lib.bmgx2_SETUP_ITLI_ex(ptr(d_so), ptr(d_soc), ptr(d_ci), nx + 2, ny + 2, nxc + 2, nyc + 2,
+                                          ifd_of(nine), nst, 0, None))
+    assert_bitwise(host(d_soc), soc, "SETUP_ITLI_ex")
+    # structural invariants: R = P^T  <Rr, v> == <r, Pv>
+    r = random_gf(nx, ny, rng); v = random_gf(nxc, nyc, rng)
+    rc = np.zeros_like(v)
+    assert L.orc2_restrict(P(r), P(rc), P(ci), nx + 2, ny + 2, nxc + 2, nyc + 2, 0) == 0
+    d_r, d_rc = dev(cuda, r), cuda.zeros(v.shape, dtype=cuda.float64, device="cuda")
+    abi.check(abi.lib.bmgx2_restrict(ptr(d_r), ptr(d_rc), ptr(d_ci), nx + 2, ny + 2, nxc + 2, nyc + 2, 0, None))
+    assert_bitwise(host(d_rc), rc, "restrict")
+    # interp_add: q += P v + res/diag at F points
+    q = random_gf(nx, ny, rng); res = random_gf(nx, ny, rng)
+    d_q, d_res, d_v = dev(cuda, q), dev(cuda, res), dev(cuda, v)
+    assert L.orc2_interp_add(P(q), P(v), P(res), P(so), P(ci), nxc + 2, nyc + 2, nx + 2, ny + 2, nst, 0) == 0
+    abi.check(abi.lib.bmgx2_interp_add(ptr(d_q), ptr(d_v), ptr(d_res), ptr(d_so), ptr(d_ci), nxc + 2, nyc + 2,
+                                       nx + 2, ny + 2, nst, 0, None))
+    assert_bitwise(host(d_q)[1:-1, 1:-1], q[1:-1, 1:-1], "interp_add q")
+    assert_bitwise(host(d_res), res, "interp_add res (in-place scaling)")
+    # adjointness with res = 0: <R r, v> == <r, P v>
+    q0 = np.zeros((ny + 2, nx + 2)); z = np.zeros_like(q0)
+    L.orc2_interp_add(P(q0), P(v), P(z), P(so), P(ci), nxc + 2, nyc + 2, nx + 2, ny + 2, nst, 0)
+    lhs = float((rc[1:-1, 1:-1] * v[1:-1, 1:-1]).sum()); rhs = float((r[1:-1, 1:-1] * q0[1:-1, 1:-1]).sum())
+    assert abs(lhs - rhs) <= 1e-10 * max(abs(lhs), abs(rhs), 1.0)
+
+
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(3, 3), (4, 4), (3, 5), (7, 4), (12, 9)])
+def test_coarse_solve(cuda, abi, nx, ny, nine):
+    rng = np.random.default_rng(nx * 3 + ny + nine)
+    so = random_op2(nx, ny, nine, rng)
+    nst = so.shape[0]
+    nabd1, nabd2 = nx + 2, nx * ny
+    abd = np.zeros((nabd2, nabd1)); bbd = np.zeros(nabd2)
+    L = oracle.lib()
+    assert L.orc2_setup_cg_lu(P(so), nx + 2, ny + 2, nst, P(abd), nabd1, nabd2, 0) == 0
+    b = random_gf(nx, ny, rng); x = np.zeros_like(b)
+    assert L.orc2_solve_cg(P(x), P(b), nx + 2, ny + 2, P(abd), P(bbd), nabd1, nabd2, 0) == 0
+    d_so, d_b = dev(cuda, so), dev(cuda, b)
+    d_abd = cuda.full(abd.shape, 3.0, dtype=cuda.float64, device="cuda")
+    d_bbd = cuda.zeros(nabd2, dtype=cuda.float64, device="cuda")
+    d_x = cuda.zeros_like(d_b)
+    abi.check(abi.lib.bmgx2_SETUP_cg_LU(ptr(d_so), nx + 2, ny + 2, nst, ptr(d_abd), nabd1, nabd2, 0, None))
+    assert_bitwise(host(d_abd), abd, "SETUP_cg_LU")
+    abi.check(abi.lib.bmgx2_SOLVE_cg(ptr(d_x), ptr(d_b), nx + 2, ny + 2, ptr(d_abd), ptr(d_bbd), nabd1, nabd2, 0, None))
+    assert_bitwise(host(d_x), x, "SOLVE_cg")
+    # and it really solves A x = b
+    r = np.zeros_like(b)
+    L.orc2_residual(0, P(so), P(b), P(x), P(r), nx + 2, ny + 2, 0, ifd_of(nine), nst)
+    assert np.abs(r).max() <= 1e-9 * np.abs(b).max()
+
+
+@pytest.mark.parametrize("updown", [0, 1])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(3, 3), (7, 5), (31, 33), (64, 40), (130, 97), (300, 1000)])
+def test_lines(cuda, abi, nx, ny, nine, updown):
+    rng = np.random.default_rng(nx * 5 + ny + nine + 2 * updown)
+    so = random_op2(nx, ny, nine, rng)
+    nst = so.shape[0]
+    L = oracle.lib()
+    II, JJ = nx + 2, ny + 2
+    sorx = np.zeros((2, JJ, II)); sory = np.zeros((2, II, JJ))
+    assert L.orc2_setup_lines_x(P(so), P(sorx), II, JJ, nst, 0) == 0
+    assert L.orc2_setup_lines_y(P(so), P(sory), II, JJ, nst, 0) == 0
+    d_so = dev(cuda, so)
+    d_sorx = cuda.zeros(sorx.shape, dtype=cuda.float64, device="cuda")
+    d_sory = cuda.zeros(sory.shape, dtype=cuda.float64, device="cuda")
+    abi.check(abi.lib.bmgx2_SETUP_lines_x(ptr(d_so), ptr(d_sorx), II, JJ, nst, 0, None))
+    abi.check(abi.lib.bmgx2_SETUP_lines_y(ptr(d_so), ptr(d_sory), II, JJ, nst, 0, None))
+    assert_bitwise(host(d_sorx)[:, 1:-1, 1:-1], sorx[:, 1:-1, 1:-1], "SETUP_lines_x")
+    assert_bitwise(host(d_sory)[:, 1:-1, 1:-1], sory[:, 1:-1, 1:-1], "SETUP_lines_y")
+    q = random_gf(nx, ny, rng); b = random_gf(nx, ny, rng)
+    d_q, d_b = dev(cuda, q), dev(cuda, b)
+    d_w = cuda.zeros_like(d_q)
+    work = np.zeros(max(II, JJ) + 2)
+    for sweep in range(2):
+        assert L.orc2_relax_lines_x(1, P(so), P(b), P(q), P(sorx), P(work), II, JJ, 1, ifd_of(nine), nst, 1, updown, 0) == 0
+        abi.check(abi.lib.bmgx2_relax_lines_x(1, ptr(d_so), ptr(d_b), ptr(d_q), ptr(d_sorx), ptr(d_w), II, JJ, 1,
+                                              ifd_of(nine), nst, 1, updown, 0, None))
+        scale = np.abs(q).max()
+        assert np.abs(host(d_q) - q).max() <= 1e-12 * scale, "relax_lines_x"
+        assert L.orc2_relax_lines_y(1, P(so), P(b), P(q), P(sory), P(work), II, JJ, 1, ifd_of(nine), nst, 1, updown, 0) == 0
+        abi.check(abi.lib.bmgx2_relax_lines_y(1, ptr(d_so), ptr(d_b), ptr(d_q), ptr(d_sory), ptr(d_w), II, JJ, 1,
+                                              ifd_of(nine), nst, 1, updown, 0, None))
+        scale = np.abs(q).max()
+        assert np.abs(host(d_q) - q).max() <= 1e-12 * scale, "relax_lines_y"
+
+
+@pytest.mark.parametrize("nx,ny", [(1, 1), (5, 9), (300, 1000), (2049, 1025)])
+def test_sumsq(cuda, abi, nx, ny):
+    rng = np.random.default_rng(nx + ny)
+    q = rng.standard_normal((ny + 2, nx + 2))  # ghosts non-zero on purpose: must be ignored
+    d_q = dev(cuda, q)
+    d_w = cuda.zeros(abi.lib.bmgx_norm_work_len(), dtype=cuda.float64, device="cuda")
+    d_o = cuda.zeros(1, dtype=cuda.float64, device="cuda")
+    abi.check(abi.lib.bmgx2_sumsq(ptr(d_q), nx + 2, ny + 2, ptr(d_w), ptr(d_o), None))
+    got = float(host(d_o)[0])
+    ref = oracle.lib().orc2_l2norm(P(q), nx + 2, ny + 2) ** 2
+    assert abs(got - ref) <= 1e-13 * ref
+    a2 = d_o.clone()
+    abi.check(abi.lib.bmgx2_sumsq(ptr(d_q), nx + 2, ny + 2, ptr(d_w), ptr(d_o), None))
+    assert float(host(a2)[0]) == float(host(d_o)[0])  # run-to-run deterministic
+
+
+def test_periodic_is_refused(cuda, abi):
+    d = cuda.zeros((5, 6, 6), dtype=cuda.float64, device="cuda")
+    st = abi.lib.bmgx2_relax_GS(1, ptr(d), ptr(d[0]), ptr(d[1]), ptr(d), 6, 6, 1, 0, 5, 2, 1, 0, 2, None)
+    assert st == 2 and b"periodic" in abi.lib.bmgx_last_error()
