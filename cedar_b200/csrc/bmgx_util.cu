@@ -126,3 +126,74 @@ extern "C" int bmgx3_sumsq(const double *q, bmgx_len ii, bmgx_len jj, bmgx_len k
     BMGX_LAUNCH_CHECK("bmgx3_sumsq/2");
     return BMGX_OK;
 }
+
+// ---- runtime support for the host layer -----------------------------------
+#define RT(call, where)                                                \
+    do {                                                               \
+        cudaError_t e__ = (call);                                      \
+        if (e__ != cudaSuccess) return bmgx_set_cuda_error(e__, where); \
+        return BMGX_OK;                                                \
+    } while (0)
+
+extern "C" int bmgx_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+extern "C" int bmgx_set_device(int dev) { RT(cudaSetDevice(dev), "bmgx_set_device"); }
+extern "C" int bmgx_malloc(void **p, size_t bytes) { RT(cudaMalloc(p, bytes ? bytes : 8), "bmgx_malloc"); }
+extern "C" int bmgx_free(void *p) { RT(cudaFree(p), "bmgx_free"); }
+extern "C" int bmgx_host_alloc(void **p, size_t bytes) { RT(cudaHostAlloc(p, bytes ? bytes : 8, cudaHostAllocDefault), "bmgx_host_alloc"); }
+extern "C" int bmgx_host_free(void *p) { RT(cudaFreeHost(p), "bmgx_host_free"); }
+extern "C" int bmgx_memcpy_h2d(void *dst, const void *src, size_t bytes, bmgx_stream_t s)
+{
+    RT(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, (cudaStream_t)s), "bmgx_memcpy_h2d");
+}
+extern "C" int bmgx_memcpy_d2h(void *dst, const void *src, size_t bytes, bmgx_stream_t s)
+{
+    RT(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, (cudaStream_t)s), "bmgx_memcpy_d2h");
+}
+extern "C" int bmgx_memcpy_d2d(void *dst, const void *src, size_t bytes, bmgx_stream_t s)
+{
+    RT(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)s), "bmgx_memcpy_d2d");
+}
+extern "C" int bmgx_memset0(void *dst, size_t bytes, bmgx_stream_t s)
+{
+    bmgx_count_launch();
+    RT(cudaMemsetAsync(dst, 0, bytes, (cudaStream_t)s), "bmgx_memset0");
+}
+extern "C" int bmgx_stream_create(bmgx_stream_t *s)
+{
+    RT(cudaStreamCreateWithFlags((cudaStream_t *)s, cudaStreamNonBlocking), "bmgx_stream_create");
+}
+extern "C" int bmgx_stream_destroy(bmgx_stream_t s) { RT(cudaStreamDestroy((cudaStream_t)s), "bmgx_stream_destroy"); }
+extern "C" int bmgx_stream_sync(bmgx_stream_t s) { RT(cudaStreamSynchronize((cudaStream_t)s), "bmgx_stream_sync"); }
+extern "C" int bmgx_device_sync(void) { RT(cudaDeviceSynchronize(), "bmgx_device_sync"); }
+extern "C" int bmgx_event_create(void **ev) { RT(cudaEventCreate((cudaEvent_t *)ev), "bmgx_event_create"); }
+extern "C" int bmgx_event_destroy(void *ev) { RT(cudaEventDestroy((cudaEvent_t)ev), "bmgx_event_destroy"); }
+extern "C" int bmgx_event_record(void *ev, bmgx_stream_t s) { RT(cudaEventRecord((cudaEvent_t)ev, (cudaStream_t)s), "bmgx_event_record"); }
+extern "C" int bmgx_event_sync(void *ev) { RT(cudaEventSynchronize((cudaEvent_t)ev), "bmgx_event_sync"); }
+extern "C" int bmgx_event_elapsed_ms(void *a, void *b, float *ms) { RT(cudaEventElapsedTime(ms, (cudaEvent_t)a, (cudaEvent_t)b), "bmgx_event_elapsed_ms"); }
+
+extern "C" int bmgx_graph_begin(bmgx_stream_t s)
+{
+    RT(cudaStreamBeginCapture((cudaStream_t)s, cudaStreamCaptureModeThreadLocal), "bmgx_graph_begin");
+}
+extern "C" int bmgx_graph_end(bmgx_stream_t s, void **graph_exec)
+{
+    cudaGraph_t g = nullptr;
+    cudaError_t e = cudaStreamEndCapture((cudaStream_t)s, &g);
+    if (e != cudaSuccess) return bmgx_set_cuda_error(e, "bmgx_graph_end/capture");
+    cudaGraphExec_t ex = nullptr;
+    e = cudaGraphInstantiate(&ex, g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) return bmgx_set_cuda_error(e, "bmgx_graph_end/instantiate");
+    *graph_exec = (void *)ex;
+    return BMGX_OK;
+}
+extern "C" int bmgx_graph_launch(void *graph_exec, bmgx_stream_t s)
+{
+    RT(cudaGraphLaunch((cudaGraphExec_t)graph_exec, (cudaStream_t)s), "bmgx_graph_launch");
+}
+extern "C" int bmgx_graph_destroy(void *graph_exec) { RT(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec), "bmgx_graph_destroy"); }

@@ -51,6 +51,35 @@ unsigned long long bmgx_launch_count(void);
 /* BMG_get_bc, src/2d/ftn/BMG_get_bc.f90:1-24 */
 void bmgx_get_bc(int per_mask, int *ibc);
 
+/* ---- runtime support for the host layer ---------------------------------- */
+/* Thin, C-callable wrappers so the C++ host layer (include/cedar) needs no
+ * CUDA headers.  All return BMGX_OK or BMGX_ERR_CUDA. */
+int bmgx_device_count(void);
+int bmgx_set_device(int dev);
+int bmgx_malloc(void **p, size_t bytes);              /* cudaMalloc */
+int bmgx_free(void *p);
+int bmgx_host_alloc(void **p, size_t bytes);          /* pinned host memory */
+int bmgx_host_free(void *p);
+int bmgx_memcpy_h2d(void *dst, const void *src, size_t bytes, bmgx_stream_t s);  /* async */
+int bmgx_memcpy_d2h(void *dst, const void *src, size_t bytes, bmgx_stream_t s);  /* async */
+int bmgx_memcpy_d2d(void *dst, const void *src, size_t bytes, bmgx_stream_t s);  /* async */
+int bmgx_memset0(void *dst, size_t bytes, bmgx_stream_t s);
+int bmgx_stream_create(bmgx_stream_t *s);
+int bmgx_stream_destroy(bmgx_stream_t s);
+int bmgx_stream_sync(bmgx_stream_t s);
+int bmgx_device_sync(void);
+/* CUDA events for device-side timing on the launching stream */
+int bmgx_event_create(void **ev);
+int bmgx_event_destroy(void *ev);
+int bmgx_event_record(void *ev, bmgx_stream_t s);
+int bmgx_event_sync(void *ev);
+int bmgx_event_elapsed_ms(void *start, void *stop, float *ms);
+/* CUDA-graph capture of a sequence of bmgx calls (one V-cycle) */
+int bmgx_graph_begin(bmgx_stream_t s);
+int bmgx_graph_end(bmgx_stream_t s, void **graph_exec);
+int bmgx_graph_launch(void *graph_exec, bmgx_stream_t s);
+int bmgx_graph_destroy(void *graph_exec);
+
 /* ---- utilities used by the host layer (grid_func::set / lp_norm) ---------- */
 /* array<>::set(v) over n doubles */
 int bmgx_fill(bmgx_real *a, size_t n, bmgx_real v, bmgx_stream_t s);

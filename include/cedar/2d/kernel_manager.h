@@ -1,0 +1,14 @@
+// cedar/2d/kernel_manager.h -- builds the serial 2D registry with the CUDA
+// kernels registered (and selected) under the name "system", the name the
+// reference uses for its Fortran-backed defaults (src/2d/kernel_manager.cc:16-42).
+#ifndef CEDAR_2D_KERNEL_MANAGER_H
+#define CEDAR_2D_KERNEL_MANAGER_H
+#include <cedar/kernel_manager.h>
+#include <cedar/kernel_registry.h>
+#include <cedar/2d/types.h>
+namespace cedar { namespace cdr2 {
+using kman_ptr = std::shared_ptr<kernel_manager<klist<stypes, exec_mode::serial>>>;
+kman_ptr build_kernel_manager(config &conf);
+kman_ptr build_kernel_manager(std::shared_ptr<kernel_params> params);
+}}
+#endif

@@ -1,0 +1,88 @@
+// cedar/2d/relax.h -- CUDA-backed point and line relaxation kernels, registered
+// under the same interfaces as the reference's rbgs / lines<rdir>
+// (include/cedar/2d/relax.h:28-190): k = kf = 1, ifd from the stencil type,
+// BMG_RELAX_SYM always (the relax_symmetric parameter is not consulted there
+// either), boundary code from kernel_params::per_mask().
+#ifndef CEDAR_2D_RELAX_H
+#define CEDAR_2D_RELAX_H
+
+#include <map>
+#include <type_traits>
+
+#include <cedar/2d/types.h>
+#include <cedar/kernels/point_relax.h>
+#include <cedar/kernels/line_relax.h>
+#include <cedar/gpu.h>
+
+namespace cedar { namespace cdr2 {
+
+class rbgs : public kernels::point_relax<stypes>
+{
+public:
+	void setup(const stencil_op<five_pt> &so, relax_stencil &sor) override { setup_impl(so, sor); }
+	void setup(const stencil_op<nine_pt> &so, relax_stencil &sor) override { setup_impl(so, sor); }
+	void run(const stencil_op<five_pt> &so, grid_func &x, const grid_func &b, const relax_stencil &sor,
+	         cycle::Dir cdir) override { run_impl(so, x, b, sor, cdir); }
+	void run(const stencil_op<nine_pt> &so, grid_func &x, const grid_func &b, const relax_stencil &sor,
+	         cycle::Dir cdir) override { run_impl(so, x, b, sor, cdir); }
+
+	template <class sten> void setup_impl(const stencil_op<sten> &so, relax_stencil &sor)
+	{
+		gpu::check(bmgx2_SETUP_recip(so.cdev(), sor.dev(), so.len(0), so.len(1), stencil_ndirs<sten>::value, 2,
+		                             gpu::stream()), "SETUP_recip");
+	}
+	template <class sten>
+	void run_impl(const stencil_op<sten> &so, grid_func &x, const grid_func &b, const relax_stencil &sor, cycle::Dir cdir)
+	{
+		int ifd = std::is_same<sten, five_pt>::value ? 1 : 0;
+		int updown = cdir == cycle::Dir::UP ? BMGX_UP : BMGX_DOWN;
+		int ibc;
+		bmgx_get_bc(params->per_mask(), &ibc);
+		gpu::check(bmgx2_relax_GS(1, so.cdev(), b.cdev(), x.dev(), sor.cdev(), so.len(0), so.len(1), 1, ifd,
+		                          stencil_ndirs<sten>::value, 2, BMGX_RELAX_SYM, updown, ibc, gpu::stream()),
+		           "relax_GS");
+	}
+};
+
+template <relax_dir rdir> class lines : public kernels::line_relax<stypes, rdir>
+{
+public:
+	void setup(const stencil_op<five_pt> &so, relax_stencil &sor) override { setup_impl(so, sor); }
+	void setup(const stencil_op<nine_pt> &so, relax_stencil &sor) override { setup_impl(so, sor); }
+	void run(const stencil_op<five_pt> &so, grid_func &x, const grid_func &b, const relax_stencil &sor, grid_func &res,
+	         cycle::Dir cdir) override { run_impl(so, x, b, sor, res, cdir); }
+	void run(const stencil_op<nine_pt> &so, grid_func &x, const grid_func &b, const relax_stencil &sor, grid_func &res,
+	         cycle::Dir cdir) override { run_impl(so, x, b, sor, res, cdir); }
+
+	template <class sten> void setup_impl(const stencil_op<sten> &so, relax_stencil &sor)
+	{
+		int jpn;
+		bmgx_get_bc(this->params->per_mask(), &jpn);
+		if (rdir == relax_dir::x)
+			gpu::check(bmgx2_SETUP_lines_x(so.cdev(), sor.dev(), so.len(0), so.len(1), stencil_ndirs<sten>::value, jpn,
+			                               gpu::stream()), "SETUP_lines_x");
+		else
+			gpu::check(bmgx2_SETUP_lines_y(so.cdev(), sor.dev(), so.len(0), so.len(1), stencil_ndirs<sten>::value, jpn,
+			                               gpu::stream()), "SETUP_lines_y");
+	}
+	template <class sten>
+	void run_impl(const stencil_op<sten> &so, grid_func &x, const grid_func &b, const relax_stencil &sor,
+	              grid_func &res, cycle::Dir cdir)
+	{
+		int ifd = std::is_same<sten, five_pt>::value ? 1 : 0;
+		int updown = cdir == cycle::Dir::UP ? BMGX_UP : BMGX_DOWN;
+		int ibc;
+		bmgx_get_bc(this->params->per_mask(), &ibc);
+		if (rdir == relax_dir::x)
+			gpu::check(bmgx2_relax_lines_x(1, so.cdev(), b.cdev(), x.dev(), sor.cdev(), res.dev(), so.len(0), so.len(1),
+			                               1, ifd, stencil_ndirs<sten>::value, BMGX_RELAX_SYM, updown, ibc,
+			                               gpu::stream()), "relax_lines_x");
+		else
+			gpu::check(bmgx2_relax_lines_y(1, so.cdev(), b.cdev(), x.dev(), sor.cdev(), res.dev(), so.len(0), so.len(1),
+			                               1, ifd, stencil_ndirs<sten>::value, BMGX_RELAX_SYM, updown, ibc,
+			                               gpu::stream()), "relax_lines_y");
+	}
+};
+
+}}
+#endif

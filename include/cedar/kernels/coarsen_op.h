@@ -1,0 +1,29 @@
+// cedar/kernels/coarsen_op.h -- abstract kernel interface `kernels::coarsen_op`.
+// Signatures follow the reference include/cedar/kernels/coarsen_op.h (l.23-40); an
+// implementation overrides the overloads it supports, anything left out logs
+// "routine not provided" instead of throwing (the reference's error behaviour).
+#ifndef CEDAR_KERNELS_COARSEN_OP_H
+#define CEDAR_KERNELS_COARSEN_OP_H
+
+#include <cedar/kernel.h>
+#include <cedar/types.h>
+
+namespace cedar { namespace kernels {
+
+template <class solver_types> class coarsen_op : public kernel<solver_types>
+{
+public:
+	template <class sten> using stencil_op = typename kernel<solver_types>::template stencil_op<sten>;
+	using comp_sten = typename kernel<solver_types>::comp_sten;
+	using full_sten = typename kernel<solver_types>::full_sten;
+	using grid_func = typename kernel<solver_types>::grid_func;
+	using prolong_op = typename kernel<solver_types>::prolong_op;
+	using restrict_op = typename kernel<solver_types>::restrict_op;
+	using relax_stencil = typename kernel<solver_types>::relax_stencil;
+	static const std::string name() { return "coarsen operator"; }
+	virtual void run(const prolong_op &P, const stencil_op<comp_sten> &fop, stencil_op<full_sten> &cop) { log::error << name() << ": run routine not provided" << std::endl; }
+	virtual void run(const prolong_op &P, const stencil_op<full_sten> &fop, stencil_op<full_sten> &cop) { log::error << name() << ": run routine not provided" << std::endl; }
+};
+
+}}
+#endif

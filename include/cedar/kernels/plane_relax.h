@@ -1,0 +1,31 @@
+// cedar/kernels/plane_relax.h -- abstract kernel interface `kernels::plane_relax`.
+// Signatures follow the reference include/cedar/kernels/plane_relax.h (l.21-31); an
+// implementation overrides the overloads it supports, anything left out logs
+// "routine not provided" instead of throwing (the reference's error behaviour).
+#ifndef CEDAR_KERNELS_PLANE_RELAX_H
+#define CEDAR_KERNELS_PLANE_RELAX_H
+
+#include <cedar/kernel.h>
+#include <cedar/types.h>
+
+namespace cedar { namespace kernels {
+
+template <class solver_types, relax_dir rdir> class plane_relax : public kernel<solver_types>
+{
+public:
+	template <class sten> using stencil_op = typename kernel<solver_types>::template stencil_op<sten>;
+	using comp_sten = typename kernel<solver_types>::comp_sten;
+	using full_sten = typename kernel<solver_types>::full_sten;
+	using grid_func = typename kernel<solver_types>::grid_func;
+	using prolong_op = typename kernel<solver_types>::prolong_op;
+	using restrict_op = typename kernel<solver_types>::restrict_op;
+	using relax_stencil = typename kernel<solver_types>::relax_stencil;
+	static const std::string name() { return std::string("plane relaxation ") + relax_dir_name<rdir>::value; }
+	virtual void setup(const stencil_op<comp_sten> &so) { log::error << name() << ": setup routine not provided" << std::endl; }
+	virtual void setup(const stencil_op<full_sten> &so) { log::error << name() << ": setup routine not provided" << std::endl; }
+	virtual void run(const stencil_op<comp_sten> &so, grid_func &x, const grid_func &b, cycle::Dir cdir) { log::error << name() << ": run routine not provided" << std::endl; }
+	virtual void run(const stencil_op<full_sten> &so, grid_func &x, const grid_func &b, cycle::Dir cdir) { log::error << name() << ": run routine not provided" << std::endl; }
+};
+
+}}
+#endif

@@ -1,0 +1,29 @@
+// cedar/kernels/setup_interp.h -- abstract kernel interface `kernels::setup_interp`.
+// Signatures follow the reference include/cedar/kernels/setup_interp.h (l.30-47); an
+// implementation overrides the overloads it supports, anything left out logs
+// "routine not provided" instead of throwing (the reference's error behaviour).
+#ifndef CEDAR_KERNELS_SETUP_INTERP_H
+#define CEDAR_KERNELS_SETUP_INTERP_H
+
+#include <cedar/kernel.h>
+#include <cedar/types.h>
+
+namespace cedar { namespace kernels {
+
+template <class solver_types> class setup_interp : public kernel<solver_types>
+{
+public:
+	template <class sten> using stencil_op = typename kernel<solver_types>::template stencil_op<sten>;
+	using comp_sten = typename kernel<solver_types>::comp_sten;
+	using full_sten = typename kernel<solver_types>::full_sten;
+	using grid_func = typename kernel<solver_types>::grid_func;
+	using prolong_op = typename kernel<solver_types>::prolong_op;
+	using restrict_op = typename kernel<solver_types>::restrict_op;
+	using relax_stencil = typename kernel<solver_types>::relax_stencil;
+	static const std::string name() { return "setup interpolation"; }
+	virtual void run(const stencil_op<comp_sten> &fop, const stencil_op<full_sten> &cop, prolong_op &P) { log::error << name() << ": run routine not provided" << std::endl; }
+	virtual void run(const stencil_op<full_sten> &fop, const stencil_op<full_sten> &cop, prolong_op &P) { log::error << name() << ": run routine not provided" << std::endl; }
+};
+
+}}
+#endif

@@ -1,0 +1,31 @@
+// cedar/kernels/solve_cg.h -- abstract kernel interface `kernels::solve_cg`.
+// Signatures follow the reference include/cedar/kernels/solve_cg.h (l.20-28); an
+// implementation overrides the overloads it supports, anything left out logs
+// "routine not provided" instead of throwing (the reference's error behaviour).
+#ifndef CEDAR_KERNELS_SOLVE_CG_H
+#define CEDAR_KERNELS_SOLVE_CG_H
+
+#include <cedar/kernel.h>
+#include <cedar/types.h>
+
+namespace cedar { namespace kernels {
+
+template <class solver_types> class solve_cg : public kernel<solver_types>
+{
+public:
+	template <class sten> using stencil_op = typename kernel<solver_types>::template stencil_op<sten>;
+	using comp_sten = typename kernel<solver_types>::comp_sten;
+	using full_sten = typename kernel<solver_types>::full_sten;
+	using grid_func = typename kernel<solver_types>::grid_func;
+	using prolong_op = typename kernel<solver_types>::prolong_op;
+	using restrict_op = typename kernel<solver_types>::restrict_op;
+	using relax_stencil = typename kernel<solver_types>::relax_stencil;
+	static const std::string name() { return "coarse-grid solve"; }
+	virtual void setup(const stencil_op<comp_sten> &so, grid_func &ABD) { log::error << name() << ": setup routine not provided" << std::endl; }
+	virtual void setup(const stencil_op<full_sten> &so, grid_func &ABD) { log::error << name() << ": setup routine not provided" << std::endl; }
+	// bbd: the reference passes host scratch of ABD.len(1) reals; device implementations may ignore it
+	virtual void run(grid_func &x, const grid_func &b, const grid_func &ABD, real_t *bbd) { log::error << name() << ": run routine not provided" << std::endl; }
+};
+
+}}
+#endif

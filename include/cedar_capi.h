@@ -1,0 +1,68 @@
+/*
+ * cedar_capi.h -- C API of the C++ host layer (libcedar_b200.so) for bindings
+ * (Python ctypes in tests/ and bench.py).  It plays the role of the reference's
+ * include/cedar/capi.h (bmg2_operator_* / bmg2_solver_*): create an operator,
+ * fill it on the host, build a solver (= setup phase), run solves.
+ * Arrays handed in or out are HOST arrays in Cedar layout ((nx+2)(ny+2)[ndirs],
+ * i fastest); the library moves them to and from the GPU.
+ * All functions return 0 on success; the message of the last failure is
+ * available from cdr_last_error().
+ */
+#ifndef CEDAR_B200_CAPI_H
+#define CEDAR_B200_CAPI_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cdr2_operator cdr2_operator;
+typedef struct cdr2_solver cdr2_solver;
+
+const char *cdr_last_error(void);
+unsigned long long cdr_gpu_launches(void);
+/* log levels like the "log" key of config.json, comma separated ("status,error"; "" = silent) */
+void cdr_set_log(const char *levels);
+
+/* nstencil = 3 (five_pt) or 5 (nine_pt).  The returned host pointer views the
+ * operator storage (nstencil planes of (nx+2)(ny+2)); fill it before building
+ * the solver. */
+int cdr2_operator_create(int nstencil, unsigned nx, unsigned ny, cdr2_operator **op);
+double *cdr2_operator_data(cdr2_operator *op);
+/* gallery: "poisson", "diag_diffusion" (uses dx, dy), "fe" */
+int cdr2_operator_gallery(const char *name, unsigned nx, unsigned ny, double dx, double dy, cdr2_operator **op);
+void cdr2_operator_destroy(cdr2_operator *op);
+
+/* setup phase.  config_json: text of a Cedar config.json ("" or NULL = defaults) */
+int cdr2_solver_create(cdr2_operator *op, const char *config_json, cdr2_solver **solver);
+void cdr2_solver_destroy(cdr2_solver *solver);
+int cdr2_solver_nlevels(cdr2_solver *solver);
+int cdr2_solver_level_shape(cdr2_solver *solver, int lvl, unsigned *nx, unsigned *ny);
+/* copies a level array to host memory: which = "A","P","x","res","b","SOR0","SOR1","ABD";
+ * n = capacity of out in doubles; *written = doubles copied */
+int cdr2_solver_level_array(cdr2_solver *solver, int lvl, const char *which, double *out, size_t n, size_t *written);
+
+/* host-buffer solve: uploads b (and x as initial guess), runs multilevel::solve,
+ * downloads x.  hist receives the relative residual after each cycle. */
+int cdr2_solver_solve(cdr2_solver *solver, const double *b, double *x, double *hist, int hist_cap, int *niter,
+                      double *res0);
+/* one V-cycle on host buffers (upload x,b; cycle; download x) */
+int cdr2_solver_vcycle(cdr2_solver *solver, const double *b, double *x);
+
+/* device-resident timing: keeps b and x on the GPU, runs `warmup` + `n` cycles
+ * (x reset to 0 before each), returns the mean device time per cycle in ms
+ * measured with CUDA events on the launching stream. */
+int cdr2_solver_time_vcycles(cdr2_solver *solver, const double *b, int warmup, int n, float *ms_per_cycle);
+/* device-resident full solve (x0 = 0) repeated `n` times after `warmup`; mean ms per solve */
+int cdr2_solver_time_solves(cdr2_solver *solver, const double *b, int warmup, int n, float *ms_per_solve, int *niter);
+
+/* one-shot end-to-end call: host operator + rhs in, solution out (operator
+ * upload, setup, solve to tolerance, download) */
+int cdr2_solve_host(int nstencil, unsigned nx, unsigned ny, const double *so, const double *b, double *x,
+                    const char *config_json, double *hist, int hist_cap, int *niter);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
