@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""bench.py -- BoxMG V-cycle throughput on B200 (BASELINE.json metric: MDOF/s).
+
+A "step" is ONE V-cycle of the configured BoxMG hierarchy over one right-hand
+side (all levels: relax, residual, restrict, coarse solve, interp_add, relax),
+run through the C++ host layer (`cdr2::solver<>::vcycle`) over the C-ABI CUDA
+kernels.  Default workload = BASELINE.json configs[1]: 2D 9-point (gallery::fe)
+4097^2, 4-colour point relaxation, V(1,1).
+
+  value   MDOF/s, device-resident (b, x and the hierarchy already in HBM)
+  e2e     MDOF/s through the host-buffer API: b and x copied H2D from pinned
+          memory and x copied D2H inside every timed step
+  setup   one-off Galerkin setup time (interpolation + RAP on every level)
+  solve   full solve to `tol` (iterations, ms)
+  roofline   the dominant kernel (fine-level point-GS sweep) timed alone
+  cpu_baseline   the CPU oracle (restatement of the reference's serial path,
+          OpenMP over rows) on the host cores, same workload
+
+`--impl reference` times that CPU implementation as the reference arm (the
+reference itself -- Fortran+MPI+Boost+LAPACK -- cannot be built on this image;
+DESIGN.md "Oracle").
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+METRIC = "MDOF/s per V-cycle (fine-grid unknowns / V-cycle time)"
+BYTES_PER_PT = {"relax9": 64, "relax5": 48}  # algorithmic bytes per fine point per sweep
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=4097, help="interior unknowns per dimension")
+    ap.add_argument("--gallery", default="fe", choices=["fe", "poisson", "diag_diffusion"])
+    ap.add_argument("--relaxation", default="point")
+    ap.add_argument("--pre", type=int, default=1)
+    ap.add_argument("--post", type=int, default=1)
+    ap.add_argument("--tol", type=float, default=1e-10)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true")
+    return ap.parse_args()
+
+
+def workload(a):
+    return {"workload": f"2D {9 if a.gallery == 'fe' else 5}-point {a.gallery} {a.n}^2, {a.relaxation} relaxation, "
+                        f"V({a.pre},{a.post}), BoxMG Galerkin hierarchy",
+            "nx": a.n, "ny": a.n, "relaxation": a.relaxation, "cycle": f"V({a.pre},{a.post})",
+            "l2": "inputs larger than L2 (fine level alone is > 1 GB)"}
+
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows = []
+        self.p = None
+        self.index = index
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.p = None
+
+    def _read(self):
+        for line in self.p.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        self.t.join(timeout=2)
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) >= 9 and r[5 + k].lower() == "active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_vcycles(a, steps, warmup, threads=None):
+    """Time `steps` V-cycles of the CPU oracle on the host cores.  Returns (MDOF/s, ms/step, cores, setup_s)."""
+    import oracle
+    L = oracle.lib()
+    if threads:
+        L.orc_set_threads(threads)
+    cores = L.orc_get_max_threads()
+    so = oracle.gallery2(a.gallery, a.n, a.n, 1.0, 1e-4 if a.gallery == "diag_diffusion" else 1.0)
+    b = oracle.rhs_sin2(a.n, a.n)
+    t0 = time.perf_counter()
+    s = oracle.Solver2(so, a.relaxation, a.pre, a.post)
+    setup_s = time.perf_counter() - t0
+    x = np.zeros_like(b)
+    for _ in range(warmup):
+        s.vcycle(x, b)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        s.vcycle(x, b)
+    dt = (time.perf_counter() - t0) / max(steps, 1)
+    return a.n * a.n / dt / 1e6, dt * 1e3, cores, setup_s
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(1, min(a.steps, 10))
+    val, ms, cores, setup_s = cpu_vcycles(a, steps, min(a.warmup, 2))
+    sample = f"{steps} full V-cycles of the same workload ({a.n}^2), oracle port with OpenMP over {cores} threads"
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "MDOF/s", "n_gpus": a.gpus, "steps": steps,
+            "warmup": min(a.warmup, 2), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload(a),
+            "cpu_baseline": {"value": val, "unit": "MDOF/s", "cores": cores, "kind": "port", "sample": sample,
+                             "setup_s": setup_s},
+            "e2e": {"value": val, "unit": "MDOF/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def time_fine_sweep(a, torch, reps=20):
+    """Dominant kernel alone: one fine-level point-GS sweep through the C ABI,
+    CUDA events on the launching stream (the legacy default stream)."""
+    import ctypes as C
+    import cedar_b200.abi as abi
+    import oracle
+    n = a.n
+    nine = a.gallery == "fe"
+    so = torch.from_numpy(oracle.gallery2(a.gallery, n, n, 1.0, 1e-4 if a.gallery == "diag_diffusion" else 1.0)).cuda()
+    II = n + 2
+    q = torch.zeros((II, II), dtype=torch.float64, device="cuda")
+    b = torch.from_numpy(oracle.rhs_sin2(n, n)).cuda()
+    sor = torch.zeros((2, II, II), dtype=torch.float64, device="cuda")
+    P = lambda t: C.c_void_p(t.data_ptr())
+    nst = so.shape[0]
+    abi.check(abi.lib.bmgx2_SETUP_recip(P(so), P(sor), II, II, nst, 2, None))
+    e0, e1 = C.c_void_p(), C.c_void_p()
+    abi.lib.bmgx_event_create(C.byref(e0)); abi.lib.bmgx_event_create(C.byref(e1))
+    call = lambda ud: abi.check(abi.lib.bmgx2_relax_GS(1, P(so), P(b), P(q), P(sor), II, II, 1, 0 if nine else 1,
+                                                      nst, 2, 1, ud, 0, None))
+    for i in range(3):
+        call(i & 1)
+    torch.cuda.synchronize()
+    l0 = abi.lib.bmgx_launch_count()
+    abi.lib.bmgx_event_record(e0, None)
+    for i in range(reps):
+        call(i & 1)
+    abi.lib.bmgx_event_record(e1, None)
+    abi.lib.bmgx_event_sync(e1)
+    launches = (abi.lib.bmgx_launch_count() - l0) / reps
+    ms = C.c_float()
+    abi.lib.bmgx_event_elapsed_ms(e0, e1, C.byref(ms))
+    abi.lib.bmgx_event_destroy(e0); abi.lib.bmgx_event_destroy(e1)
+    per = ms.value / reps
+    alg = BYTES_PER_PT["relax9" if nine else "relax5"] * n * n
+    del so, q, b, sor
+    torch.cuda.empty_cache()
+    return per, alg, launches
+
+
+def main():
+    a = parse()
+    if a.impl == "reference":
+        return run_reference(a)
+
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the BoxMG kernels have no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    import oracle
+    import cedar_b200.solver as cs
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    n = a.n
+    dofs = n * n
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+
+    # ---- problem + setup (timed once; includes operator upload) ------------
+    dy = 1e-4 if a.gallery == "diag_diffusion" else 1.0
+    op = cs.Operator2(gallery=a.gallery, nx=n, ny=n, dx=1.0, dy=dy)
+    b = oracle.rhs_sin2(n, n)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    sol = cs.Solver2(op, relaxation=a.relaxation, nrelax_pre=a.pre, nrelax_post=a.post, maxiter=100, tol=a.tol,
+                     cuda_graph=not a.no_graph)
+    torch.cuda.synchronize()
+    setup_first_s = time.perf_counter() - t0
+
+    # ---- device-resident V-cycles: value -----------------------------------
+    sampler = ClockSampler(local)
+    sol.time_vcycles(b, warmup=max(a.warmup, 3), n=1)  # warm-up (graph capture happens here)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    l0 = cs.gpu_launches()
+    ms_dev = sol.time_vcycles(b, warmup=0, n=a.steps)  # CUDA events around each cycle, mean
+    launches = cs.gpu_launches() - l0
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- end to end through the host-buffer API ----------------------------
+    hb, hx = sol.buffers()
+    hb[...] = b
+    for _ in range(2):
+        hx[...] = 0.0
+        sol.vcycle_pinned()
+    barrier()
+    t_e2e = 0.0
+    for _ in range(a.steps):
+        hx[...] = 0.0            # host-side reset of the iterate, outside the timed region
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        sol.vcycle_pinned()      # H2D b, H2D x, cycle, D2H x (synchronises)
+        t_e2e += time.perf_counter() - t0
+    ms_e2e = t_e2e / a.steps * 1e3
+    bytes_gf = (n + 2) * (n + 2) * 8
+
+    # ---- full solve to tol (device resident) -------------------------------
+    ms_solve, iters = sol.time_solves(b, warmup=1, n=2)
+
+    # max over ranks
+    if world > 1:
+        t = torch.tensor([ms_dev, ms_e2e, ms_solve], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_dev, ms_e2e, ms_solve = [float(v) for v in t.tolist()]
+
+    if rank == 0:
+        del sol
+        torch.cuda.empty_cache()
+        per_sweep_ms, alg_bytes, sweep_launches = time_fine_sweep(a, torch)
+        ach = alg_bytes / (per_sweep_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": world * dofs / (ms_dev * 1e-3) / 1e6, "unit": "MDOF/s", "n_gpus": world,
+            "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_dev, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": dict(workload(a), parallelism=("1 GPU" if world == 1 else
+                                                     f"{world} independent replicas (one {n}^2 problem per GPU)")),
+            "e2e": {"value": world * dofs / (ms_e2e * 1e-3) / 1e6, "unit": "MDOF/s", "ms_per_step": ms_e2e,
+                    "h2d_bytes_per_step": 2 * bytes_gf, "d2h_bytes_per_step": bytes_gf,
+                    "call": "cdr2_solver_vcycle_pinned (pinned host b,x -> device -> x back)"},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "setup": {"ms": setup_first_s * 1e3, "what": "operator upload + interpolation + Galerkin RAP on all levels "
+                      "+ relaxation/coarse-solve setup (first call, includes CUDA context warm-up)"},
+            "solve": {"tol": a.tol, "iterations": iters, "ms": ms_solve, "mdof_per_s": dofs / (ms_solve * 1e-3) / 1e6},
+            "roofline": {"bound": "hbm", "kernel": "bmgx2_relax_GS fine-level sweep (all colours)",
+                         "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                         "peak_source": peak_src, "ms_per_launch": per_sweep_ms, "launches_per_sweep": sweep_launches,
+                         "algorithmic_bytes": alg_bytes, "traffic": None},
+        }
+        # whole-cycle roofline: SURVEY 8(d) 360 B/pt (9-pt V(1,1)) / 312 (5-pt fine)
+        cyc_bytes = (360 if a.gallery == "fe" else 312) * dofs if (a.pre, a.post) == (1, 1) and a.relaxation == "point" else None
+        if cyc_bytes:
+            line["roofline"]["vcycle_frac"] = cyc_bytes / (ms_dev * 1e-3) / 1e9 / hbm_peak
+        if not a.no_cpu_baseline and world == 1:
+            val, ms, cores, setup_s = cpu_vcycles(a, 5, 1)
+            line["cpu_baseline"] = {"value": val, "unit": "MDOF/s", "cores": cores, "kind": "port",
+                                    "sample": f"5 full V-cycles of the same workload ({n}^2) after 1 warm-up",
+                                    "ms_per_step": ms, "setup_s": setup_s}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -187,6 +187,33 @@ int cdr2_solver_vcycle(cdr2_solver *s, const double *b, double *x)
 	});
 }
 
+int cdr2_solver_buffers(cdr2_solver *s, double **b, double **x)
+{
+	return guard([&] { *b = s->b.data(); *x = s->x.data(); });
+}
+
+int cdr2_solver_vcycle_pinned(cdr2_solver *s)
+{
+	return guard([&] {
+		s->b.data(); s->x.data();  // the caller wrote the host side: device copies are stale
+		if (s->s5) s->s5->vcycle(s->x, s->b); else s->s9->vcycle(s->x, s->b);
+		s->x.cdata();              // download (synchronises)
+	});
+}
+
+int cdr2_solver_solve_pinned(cdr2_solver *s, double *hist, int hist_cap, int *niter, double *res0)
+{
+	return guard([&] {
+		s->b.data(); s->x.data();
+		const std::vector<real_t> *h;
+		if (s->s5) { s->s5->solve(s->b, s->x); h = &s->s5->history(); if (res0) *res0 = s->s5->res0(); }
+		else { s->s9->solve(s->b, s->x); h = &s->s9->history(); if (res0) *res0 = s->s9->res0(); }
+		s->x.cdata();
+		if (niter) *niter = static_cast<int>(h->size());
+		for (int i = 0; hist && i < hist_cap && i < static_cast<int>(h->size()); i++) hist[i] = (*h)[i];
+	});
+}
+
 int cdr2_solver_time_vcycles(cdr2_solver *s, const double *b, int warmup, int n, float *ms_per_cycle)
 {
 	return guard([&] {

@@ -33,6 +33,9 @@ lib.cdr2_solver_vcycle.argtypes = [C.c_void_p, _dp, _dp]
 lib.cdr2_solver_time_vcycles.argtypes = [C.c_void_p, _dp, C.c_int, C.c_int, C.POINTER(C.c_float)]
 lib.cdr2_solver_time_solves.argtypes = [C.c_void_p, _dp, C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int)]
 lib.cdr2_solve_host.argtypes = [C.c_int, C.c_uint, C.c_uint, _dp, _dp, _dp, C.c_char_p, _dp, C.c_int, C.POINTER(C.c_int)]
+lib.cdr2_solver_buffers.argtypes = [C.c_void_p, C.POINTER(_dp), C.POINTER(_dp)]
+lib.cdr2_solver_vcycle_pinned.argtypes = [C.c_void_p]
+lib.cdr2_solver_solve_pinned.argtypes = [C.c_void_p, _dp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double)]
 lib.cdr_set_log.argtypes = [C.c_char_p]
 
 
@@ -134,6 +137,24 @@ class Solver2:
     def vcycle(self, x, b):
         _check(lib.cdr2_solver_vcycle(self.h, _P(b), _P(x)))
         return x
+
+    def buffers(self):
+        """(b, x): numpy views of the solver's pinned host staging buffers."""
+        pb, px = _dp(), _dp()
+        _check(lib.cdr2_solver_buffers(self.h, C.byref(pb), C.byref(px)))
+        shape = (self.op.ny + 2, self.op.nx + 2)
+        return np.ctypeslib.as_array(pb, shape=shape), np.ctypeslib.as_array(px, shape=shape)
+
+    def vcycle_pinned(self):
+        """upload b, x from the pinned buffers; one cycle; download x"""
+        _check(lib.cdr2_solver_vcycle_pinned(self.h))
+
+    def solve_pinned(self, maxiter_cap=1000):
+        hist = np.zeros(maxiter_cap)
+        n = C.c_int()
+        r0 = C.c_double()
+        _check(lib.cdr2_solver_solve_pinned(self.h, _P(hist), maxiter_cap, C.byref(n), C.byref(r0)))
+        return hist[:n.value], r0.value
 
     def time_vcycles(self, b, warmup=3, n=10):
         ms = C.c_float()

@@ -50,6 +50,14 @@ int cdr2_solver_solve(cdr2_solver *solver, const double *b, double *x, double *h
 /* one V-cycle on host buffers (upload x,b; cycle; download x) */
 int cdr2_solver_vcycle(cdr2_solver *solver, const double *b, double *x);
 
+/* Pinned host staging buffers owned by the solver ((nx+2)(ny+2) doubles each):
+ * fill *b (and *x as initial guess) in place, then call the _pinned variants,
+ * which upload b and x, run on the device and download x into the same buffer
+ * -- no intermediate host copy. */
+int cdr2_solver_buffers(cdr2_solver *solver, double **b, double **x);
+int cdr2_solver_vcycle_pinned(cdr2_solver *solver);
+int cdr2_solver_solve_pinned(cdr2_solver *solver, double *hist, int hist_cap, int *niter, double *res0);
+
 /* device-resident timing: keeps b and x on the GPU, runs `warmup` + `n` cycles
  * (x reset to 0 before each), returns the mean device time per cycle in ms
  * measured with CUDA events on the launching stream. */

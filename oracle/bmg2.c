@@ -15,7 +15,7 @@
  * Parity pin: the multilevel driver in ml2.c built on these kernels reproduces
  * the residual history printed in the reference README.md:52-63 (see
  * tests/test_oracle_golden.py); LAPACK restatements are checked against
- * scipy.linalg.lapack in tests/test_oracle_lapack.py.
+ * scipy.linalg.lapack in tests/test_oracle_golden.py.
  *
  * Arrays are Fortran ordered, 1-based in the comments, i fastest:
  *   Q(II,JJ), SO(II,JJ,NStncl), SOR(II,JJ,2), CI(IIC,JJC,8).
