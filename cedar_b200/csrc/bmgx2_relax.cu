@@ -87,15 +87,3 @@ extern "C" int bmgx2_relax_GS(int k, const double *so, const double *qf, double 
     }
     return BMGX_OK;
 }
-
-extern "C" int bmgx2_relax_GS_oop(int k, const double *so, const double *qf, const double *q_in, double *q_out,
-                                  const double *sor, bmgx_len ii, bmgx_len jj, int kf, int ifd, int nstncl,
-                                  int nsorv, int irelax_sym, int updown, int jpn, bmgx_stream_t s)
-{
-    if (q_in == q_out) return bmgx_set_error(BMGX_ERR_ARG, "relax_GS_oop: q_in aliases q_out");
-    cudaError_t e = cudaMemcpyAsync(q_out, q_in, sizeof(double) * (size_t)ii * jj, cudaMemcpyDeviceToDevice,
-                                    (cudaStream_t)s);
-    if (e != cudaSuccess) return bmgx_set_cuda_error(e, "relax_GS_oop/copy");
-    bmgx_count_launch();
-    return bmgx2_relax_GS(k, so, qf, q_out, sor, ii, jj, kf, ifd, nstncl, nsorv, irelax_sym, updown, jpn, s);
-}

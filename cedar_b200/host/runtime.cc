@@ -136,9 +136,13 @@ const void *dual_buffer::host_ro() const { ensure_host(); return h; }
 void *dual_buffer::dev_rw() { ensure_dev(); hvalid = false; return d; }
 const void *dual_buffer::dev_ro() const { ensure_dev(); return d; }
 
+static thread_local std::vector<dual_buffer::swap_event> *g_swap_rec = nullptr;
+void dual_buffer::set_swap_recorder(std::vector<swap_event> *rec) { g_swap_rec = rec; }
+
 void dual_buffer::swap_device(dual_buffer &o)
 {
 	ensure_dev(); o.ensure_dev();
+	if (g_swap_rec) g_swap_rec->push_back(swap_event{this, &o, d, o.d});
 	std::swap(d, o.d);
 	hvalid = o.hvalid = false;
 }

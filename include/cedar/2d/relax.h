@@ -38,10 +38,19 @@ public:
 		int updown = cdir == cycle::Dir::UP ? BMGX_UP : BMGX_DOWN;
 		int ibc;
 		bmgx_get_bc(params->per_mask(), &ibc);
-		gpu::check(bmgx2_relax_GS(1, so.cdev(), b.cdev(), x.dev(), sor.cdev(), so.len(0), so.len(1), 1, ifd,
-		                          stencil_ndirs<sten>::value, 2, BMGX_RELAX_SYM, updown, ibc, gpu::stream()),
-		           "relax_GS");
+		// one pass over memory for all colours: relax out of place into a scratch
+		// array of the same shape, then exchange the two device buffers (x keeps
+		// its identity on the host side; its device pointer alternates)
+		auto &tmp = scratch[std::make_pair(x.len(0), x.len(1))];
+		if (tmp.size() != x.size()) tmp = grid_func(x.shape(0), x.shape(1));
+		const real_t *xin = x.cdev();
+		gpu::check(bmgx2_relax_GS_oop(1, so.cdev(), b.cdev(), xin, tmp.dev(), sor.cdev(), so.len(0), so.len(1), 1, ifd,
+		                              stencil_ndirs<sten>::value, 2, BMGX_RELAX_SYM, updown, ibc, gpu::stream()),
+		           "relax_GS_oop");
+		x.swap_device(tmp);
 	}
+private:
+	std::map<std::pair<len_t, len_t>, grid_func> scratch;
 };
 
 template <relax_dir rdir> class lines : public kernels::line_relax<stypes, rdir>

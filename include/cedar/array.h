@@ -18,6 +18,7 @@
 #include <cassert>
 #include <cstring>
 #include <tuple>
+#include <vector>
 
 #include <cedar/types.h>
 #include <cedar/array_base.h>
@@ -45,6 +46,12 @@ public:
 	void swap_device(dual_buffer &o);     // both end up device-valid, host stale
 	void zero();                          // all zero, wherever the data lives
 	bool on_device() const { return dvalid; }
+	const void *raw_dev() const { return d; }
+	// While a recorder is installed (CUDA-graph capture of a cycle) every
+	// swap_device is logged with the device pointers it exchanged, so that the
+	// host bookkeeping can be replayed together with the graph.
+	struct swap_event { dual_buffer *a, *b; const void *pa, *pb; };
+	static void set_swap_recorder(std::vector<swap_event> *rec);
 private:
 	void release();
 	void steal(dual_buffer &o);
@@ -135,6 +142,7 @@ public:
 		buf.swap_device(o.buf);
 	}
 	bool on_device() const { return buf.on_device(); }
+	detail::dual_buffer &buffer() { return buf; }
 };
 
 template <typename len_type, typename data_type, unsigned short ND>

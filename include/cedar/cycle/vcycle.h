@@ -7,7 +7,11 @@
 #ifndef CEDAR_CYCLE_VCYCLE_H
 #define CEDAR_CYCLE_VCYCLE_H
 
+#include <map>
+#include <vector>
+
 #include <cedar/cycle/types.h>
+#include <cedar/array.h>
 #include <cedar/gpu.h>
 
 namespace cedar { namespace cycle {
@@ -40,30 +44,40 @@ public:
 		if (levels.size() == 1) { coarse_solver(x, b); return; }
 		// info-level logging reads norms back inside the cycle: not capturable
 		if (!use_graph || log::info.active()) { ncycle(0, x, b); return; }
-		const void *kx = x.dev(), *kb = b.cdev();
-		if (kx != key_x || kb != key_b) { drop_graph(); key_x = kx; key_b = kb; eager_done = false; }
-		if (!eager_done) {
-			ncycle(0, x, b);
-			eager_done = true;
-		} else if (!graph) {
+		// A captured graph bakes device pointers in.  Kernels may exchange device
+		// buffers (the fused relaxation ping-pongs x with a scratch array), so the
+		// graph is keyed by the pointer state of (x, b, every level's x): a cycle
+		// with an odd number of sweeps simply alternates between two graphs.
+		std::vector<const void *> key = state_key(x, b);
+		if (!warmed) {
+			ncycle(0, x, b);   // first pass: makes every level array (and scratch) device resident
+			warmed = true;
+			return;
+		}
+		auto it = graphs.find(key);
+		if (it != graphs.end() && !replayable(it->second, x)) { bmgx_graph_destroy(it->second.graph); graphs.erase(it); it = graphs.end(); }
+		if (it == graphs.end()) {
+			if (graphs.size() >= 8) drop_graph();
+			entry e;
+			e.xbuf = &x.buffer();
 			unsigned long long before = bmgx_launch_count();
 			gpu::check(bmgx_graph_begin(gpu::stream()), "vcycle graph capture");
-			ncycle(0, x, b);
-			gpu::check(bmgx_graph_end(gpu::stream(), &graph), "vcycle graph instantiate");
-			graph_nodes = bmgx_launch_count() - before;
-			if (x.dev() != kx) {
-				// a kernel exchanged device buffers an odd number of times: the
-				// captured pointers would not line up on replay -- stay eager
-				drop_graph(); use_graph = false; key_x = nullptr;
-				log::error << "vcycle: cycle does not preserve buffer identity, CUDA graph disabled" << std::endl;
-				ncycle(0, x, b);
-				return;
-			}
-			// the capture already counted this cycle's launches once
-			gpu::check(bmgx_graph_launch(graph, gpu::stream()), "vcycle graph launch");
-		} else {
-			launch_graph();
+			detail::dual_buffer::set_swap_recorder(&e.swaps);
+			try { ncycle(0, x, b); }
+			catch (...) { detail::dual_buffer::set_swap_recorder(nullptr); void *g = nullptr; bmgx_graph_end(gpu::stream(), &g); if (g) bmgx_graph_destroy(g); throw; }
+			detail::dual_buffer::set_swap_recorder(nullptr);
+			gpu::check(bmgx_graph_end(gpu::stream(), &e.graph), "vcycle graph instantiate");
+			e.nodes = bmgx_launch_count() - before;
+			// capture only recorded the work; the host bookkeeping (buffer exchanges)
+			// already reflects the state after the cycle, so one launch makes it true
+			gpu::check(bmgx_graph_launch(e.graph, gpu::stream()), "vcycle graph launch");
+			graphs.emplace(std::move(key), std::move(e));
+			return;
 		}
+		entry &e = it->second;
+		gpu::check(bmgx_graph_launch(e.graph, gpu::stream()), "vcycle graph launch");
+		gpu::add_launches(e.nodes);
+		for (auto &sw : e.swaps) resolve(e, sw.a, x)->swap_device(*resolve(e, sw.b, x));
 	}
 
 	void ncycle(std::size_t lvl, grid_func &x, const grid_func &b, int n = 1)
@@ -107,22 +121,48 @@ public:
 		}
 	}
 
-	bool graph_active() const { return graph != nullptr; }
+	bool graph_active() const { return !graphs.empty(); }
 private:
-	void launch_graph()
+	struct entry
 	{
-		gpu::check(bmgx_graph_launch(graph, gpu::stream()), "vcycle graph launch");
-		gpu::add_launches(graph_nodes);
+		void *graph = nullptr;
+		unsigned long long nodes = 0;
+		std::vector<detail::dual_buffer::swap_event> swaps;
+		detail::dual_buffer *xbuf = nullptr;   // the caller's x at capture time
+	};
+	std::vector<const void *> state_key(grid_func &x, const grid_func &b)
+	{
+		std::vector<const void *> key;
+		key.push_back(x.dev());
+		key.push_back(b.cdev());
+		for (std::size_t l = 1; l < levels.size(); l++) key.push_back(levels.get(l).x.cdev());
+		return key;
+	}
+	static detail::dual_buffer *resolve(const entry &e, detail::dual_buffer *p, grid_func &x)
+	{
+		return p == e.xbuf ? &x.buffer() : p;
+	}
+	// the recorded exchanges must start from the pointers the graph was captured with
+	bool replayable(const entry &e, grid_func &x)
+	{
+		std::map<detail::dual_buffer *, const void *> cur;
+		for (auto &sw : e.swaps) {
+			detail::dual_buffer *a = resolve(e, sw.a, x), *b = resolve(e, sw.b, x);
+			if (!cur.count(a)) cur[a] = a->raw_dev();
+			if (!cur.count(b)) cur[b] = b->raw_dev();
+			if (cur[a] != sw.pa || cur[b] != sw.pb) return false;
+			std::swap(cur[a], cur[b]);
+		}
+		return true;
 	}
 	void drop_graph()
 	{
-		if (graph) { bmgx_graph_destroy(graph); graph = nullptr; }
+		for (auto &kv : graphs) bmgx_graph_destroy(kv.second.graph);
+		graphs.clear();
 	}
 	bool use_graph;
-	bool eager_done = false;
-	const void *key_x = nullptr, *key_b = nullptr;
-	void *graph = nullptr;
-	unsigned long long graph_nodes = 0;
+	bool warmed = false;
+	std::map<std::vector<const void *>, entry> graphs;
 };
 
 }}
