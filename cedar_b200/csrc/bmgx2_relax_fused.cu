@@ -255,7 +255,9 @@ extern "C" int bmgx2_relax_GS_oop(int k, const double *so, const double *qf, con
     // one resident wave: 148 SMs x 4 CTAs
     unsigned nb_target = 592 / nstrips; if (nb_target < 1) nb_target = 1;
     unsigned band_h = (jj + nb_target - 1) / nb_target;
-    if (band_h < 16) band_h = 16;
+    // short bands on small grids: the row loop is a latency chain (one global
+    // load round trip per step), so coarse levels want many short CTAs
+    if (band_h < 4) band_h = 4;
     band_h += band_h & 1;
     dim3 grid(nstrips, (jj + band_h - 1) / band_h);
     cudaStream_t st = (cudaStream_t)s;
