@@ -1,0 +1,95 @@
+"""CPU tests: the hand-written oracle (oracle/bmg2.c) against the REFERENCE's own
+Fortran kernels, transliterated and compiled at build time into
+oracle/_ref/libbmgref.so by oracle/f2c_ref.py (built where /root/reference
+exists; the prebuilt library travels).  Bitwise on every 2D kernel."""
+import numpy as np
+import pytest
+
+import oracle
+from oracle import P, ref
+from tests.util import coarse_n, random_gf, random_op2
+
+pytestmark = pytest.mark.skipif(not ref.available(), reason="oracle/_ref/libbmgref.so not built (no /root/reference)")
+
+SIZES = [(3, 3), (7, 5), (16, 16), (37, 64), (130, 97)]
+
+
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", SIZES)
+def test_2d_kernels_bitwise_vs_reference(nx, ny, nine):
+    R, L = ref.lib(), oracle.lib()
+    rng = np.random.default_rng(nx * 31 + ny + nine)
+    so = random_op2(nx, ny, nine, rng)
+    nst, ifd = so.shape[0], (0 if nine else 1)
+    II, JJ = nx + 2, ny + 2
+    q, b = random_gf(nx, ny, rng), random_gf(nx, ny, rng)
+    # residual (by-reference scalars in the reference)
+    r1, r2 = np.zeros_like(q), np.zeros_like(q)
+    L.orc2_residual(0, P(so), P(b), P(q), P(r1), II, JJ, 0, ifd, nst)
+    R.BMG2_SymStd_residual(ref.ip(0), P(so), P(b), P(q), P(r2), ref.ip(II), ref.ip(JJ), ref.ip(0), ref.ip(ifd),
+                           ref.ip(nst), ref.ip(0), ref.ip(0), ref.ip(1), ref.ip(0))
+    assert np.array_equal(r1, r2)
+    # point relaxation
+    s1, s2 = np.zeros((2, JJ, II)), np.zeros((2, JJ, II))
+    L.orc2_setup_recip(P(so), P(s1), II, JJ, nst, 2)
+    R.BMG2_SymStd_SETUP_recip(P(so), P(s2), II, JJ, nst, 2)
+    assert np.array_equal(s1, s2)
+    for ud in (0, 1):
+        q1, q2 = q.copy(), q.copy()
+        L.orc2_relax_gs(1, P(so), P(b), P(q1), P(s1), II, JJ, 1, ifd, nst, 2, 1, ud, 0)
+        R.BMG2_SymStd_relax_GS(1, P(so), P(b), P(q2), P(s2), II, JJ, 1, ifd, nst, 2, 1, ud, 0)
+        assert np.array_equal(q1, q2)
+    # interpolation setup, Galerkin, restriction, interpolate-and-add
+    nxc, nyc = coarse_n(nx), coarse_n(ny)
+    ci1 = np.zeros((8, nyc + 2, nxc + 2)); ci2 = ci1.copy()
+    c1 = np.zeros((5, nyc + 2, nxc + 2)); c2 = c1.copy()
+    L.orc2_setup_interp_oi(P(so), P(c1), P(ci1), II, JJ, nxc + 2, nyc + 2, ifd, nst, 0, 0)
+    R.BMG2_SymStd_SETUP_interp_OI(P(so), P(c2), P(ci2), II, JJ, nxc + 2, nyc + 2, ifd, nst, 0, 0)
+    assert np.array_equal(ci1, ci2)
+    L.orc2_setup_itli_ex(P(so), P(c1), P(ci1), II, JJ, nxc + 2, nyc + 2, ifd, nst, 0)
+    R.BMG2_SymStd_SETUP_ITLI_ex(P(so), P(c2), P(ci2), II, JJ, nxc + 2, nyc + 2, ifd, nst, 0)
+    assert np.array_equal(c1, c2)
+    v = random_gf(nxc, nyc, rng)
+    rc1, rc2 = np.zeros_like(v), np.zeros_like(v)
+    L.orc2_restrict(P(q), P(rc1), P(ci1), II, JJ, nxc + 2, nyc + 2, 0)
+    R.BMG2_SymStd_restrict(P(q), P(rc2), P(ci2), II, JJ, nxc + 2, nyc + 2, 0)
+    assert np.array_equal(rc1, rc2)
+    qa, qb, ra, rb = q.copy(), q.copy(), b.copy(), b.copy()
+    L.orc2_interp_add(P(qa), P(v), P(ra), P(so), P(ci1), nxc + 2, nyc + 2, II, JJ, nst, 0)
+    R.BMG2_SymStd_interp_add(P(qb), P(v), P(rb), P(so), P(ci2), nxc + 2, nyc + 2, II, JJ, nst, 0)
+    assert np.array_equal(qa, qb) and np.array_equal(ra, rb)
+    # line relaxation (LAPACK bound to the restated DPTTRF / DPTTS2)
+    x1, x2 = np.zeros((2, JJ, II)), np.zeros((2, JJ, II))
+    y1, y2 = np.zeros((2, II, JJ)), np.zeros((2, II, JJ))
+    L.orc2_setup_lines_x(P(so), P(x1), II, JJ, nst, 0); R.BMG2_SymStd_SETUP_lines_x(P(so), P(x2), II, JJ, nst, 0)
+    L.orc2_setup_lines_y(P(so), P(y1), II, JJ, nst, 0); R.BMG2_SymStd_SETUP_lines_y(P(so), P(y2), II, JJ, nst, 0)
+    assert np.array_equal(x1[:, 1:-1, 1:-1], x2[:, 1:-1, 1:-1]) and np.array_equal(y1[:, 1:-1, 1:-1], y2[:, 1:-1, 1:-1])
+    w = np.zeros(4 * max(II, JJ))
+    for ud in (0, 1):
+        q1, q2 = q.copy(), q.copy()
+        L.orc2_relax_lines_x(1, P(so), P(b), P(q1), P(x1), P(w), II, JJ, 1, ifd, nst, 1, ud, 0)
+        R.BMG2_SymStd_relax_lines_x(1, P(so), P(b), P(q2), P(x2), P(w), II, JJ, 1, ifd, nst, 1, ud, 0)
+        assert np.array_equal(q1, q2)
+        L.orc2_relax_lines_y(1, P(so), P(b), P(q1), P(y1), P(w), II, JJ, 1, ifd, nst, 1, ud, 0)
+        R.BMG2_SymStd_relax_lines_y(1, P(so), P(b), P(q2), P(y2), P(w), II, JJ, 1, ifd, nst, 1, ud, 0)
+        assert np.array_equal(q1, q2)
+
+
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(3, 3), (4, 5), (7, 4)])
+def test_2d_coarse_solve_bitwise_vs_reference(nx, ny, nine):
+    R, L = ref.lib(), oracle.lib()
+    rng = np.random.default_rng(nx * 7 + ny + nine)
+    so = random_op2(nx, ny, nine, rng)
+    nst = so.shape[0]
+    II, JJ = nx + 2, ny + 2
+    n1, n2 = nx + 2, nx * ny
+    a1, a2 = np.zeros((n2, n1)), np.zeros((n2, n1))
+    assert L.orc2_setup_cg_lu(P(so), II, JJ, nst, P(a1), n1, n2, 0) == 0
+    R.BMG2_SymStd_SETUP_cg_LU(P(so), ref.ip(II), ref.ip(JJ), ref.ip(nst), P(a2), ref.ip(n1), ref.ip(n2), ref.ip(0))
+    assert np.array_equal(a1, a2)
+    b = random_gf(nx, ny, rng)
+    x1, x2, w1, w2 = np.zeros_like(b), np.zeros_like(b), np.zeros(n2), np.zeros(n2)
+    L.orc2_solve_cg(P(x1), P(b), II, JJ, P(a1), P(w1), n1, n2, 0)
+    R.BMG2_SymStd_SOLVE_cg(P(x2), P(b), II, JJ, P(a2), P(w2), n1, n2, 0)
+    assert np.array_equal(x1, x2)
