@@ -133,3 +133,76 @@ class Solver2:
             lib().orc2_solver_destroy(self.h)
         except Exception:
             pass
+
+
+# ---------------------------------------------------------------------------
+# 3D: arrays of shape (ndirs, nz+2, ny+2, nx+2) / (nz+2, ny+2, nx+2)
+# ---------------------------------------------------------------------------
+
+def gallery3(name, nx, ny, nz):
+    L = lib()
+    nst = 14 if name == "fe" else 4
+    so = np.zeros((nst, nz + 2, ny + 2, nx + 2))
+    if name == "poisson":
+        L.orc3_gallery_poisson(P(so), nx, ny, nz)
+    elif name == "fe":
+        L.orc3_gallery_fe(P(so), nx, ny, nz)
+    else:
+        raise ValueError(name)
+    return so
+
+
+def rhs_sin3(nx, ny, nz):
+    b = np.zeros((nz + 2, ny + 2, nx + 2))
+    lib().orc3_rhs_sin(P(b), nx, ny, nz)
+    return b
+
+
+def exact_sin3(nx, ny, nz):
+    q = np.zeros((nz + 2, ny + 2, nx + 2))
+    lib().orc3_exact_sin(P(q), nx, ny, nz)
+    return q
+
+
+class Solver3:
+    """Mirror of cdr3::solver<fsten> (point relaxation) on the CPU oracle."""
+
+    def __init__(self, so, nrelax_pre=2, nrelax_post=1, num_levels=-1, min_coarse=3):
+        self.so = np.ascontiguousarray(so)
+        nst, kk, jj, ii = self.so.shape
+        self.nx, self.ny, self.nz = ii - 2, jj - 2, kk - 2
+        self.h = C.c_void_p(lib().orc3_solver_create(P(self.so), self.nx, self.ny, self.nz, nst, nrelax_pre,
+                                                     nrelax_post, num_levels, min_coarse))
+        self.nlevels = lib().orc3_solver_nlevels(self.h)
+
+    def level_shape(self, lvl):
+        nx, ny, nz = C.c_int(), C.c_int(), C.c_int()
+        lib().orc3_solver_level_shape(self.h, lvl, C.byref(nx), C.byref(ny), C.byref(nz))
+        return nx.value, ny.value, nz.value
+
+    def level_array(self, lvl, which):
+        names = {"A": 0, "P": 1, "x": 2, "res": 3, "b": 4, "SOR0": 5}
+        nx, ny, nz = self.level_shape(lvl)
+        nd = {"A": (4 if (lvl == 0 and self.so.shape[0] == 4) else 14), "P": 26, "SOR0": 2}.get(which, 1)
+        ptr = lib().orc3_solver_level_ptr(self.h, lvl, names[which])
+        if not ptr:
+            return None
+        a = np.ctypeslib.as_array(ptr, shape=(nd, nz + 2, ny + 2, nx + 2))
+        return a if nd > 1 else a[0]
+
+    def vcycle(self, x, b):
+        lib().orc3_solver_vcycle(self.h, P(x), P(b))
+
+    def solve(self, b, x=None, maxiter=10, tol=1e-8):
+        if x is None:
+            x = np.zeros_like(b)
+        hist = np.zeros(maxiter)
+        res0 = C.c_double()
+        it = lib().orc3_solver_solve(self.h, P(b), P(x), maxiter, C.c_double(tol), P(hist), C.byref(res0))
+        return x, hist[:it], res0.value
+
+    def __del__(self):
+        try:
+            lib().orc3_solver_destroy(self.h)
+        except Exception:
+            pass

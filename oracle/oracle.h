@@ -70,6 +70,43 @@ void orc2_solver_vcycle(orc2_solver *s, double *x, const double *b);
 int orc2_solver_solve(orc2_solver *s, const double *b, double *x, int maxiter, double tol,
                       double *rel_hist, double *res0);
 
+/* 3D kernels: argument lists follow the BIND(C) interfaces of
+ * src/3d/ftn/BMG3_SymStd_*.f90 (include/cedar/3d/relax.h:11-16, residual.h:9-12,
+ * src/3d/restrict.cc:7-10, src/3d/interp.cc:7-11, 3d/interp.h:11-15, 3d/coarsen.h:12-16). */
+void orc3_setup_recip(const double *so, double *sor, int II, int JJ, int KK, int nstncl, int nsorv);
+int orc3_relax_gs(int kg, const double *so, const double *qf, double *q, const double *sor, int II, int JJ, int KK,
+                  int ifd, int nstncl, int nsorv, int irelax_sym, int updown, int jpn);
+void orc3_residual(int kg, int nog, int ifd, const double *q, const double *qf, const double *so, double *res,
+                   int II, int JJ, int KK, int nstncl);
+int orc3_restrict(const double *q, double *qc, const double *ci, int Nx, int Ny, int Nz, int Nxc, int Nyc, int Nzc,
+                  int jpn);
+int orc3_interp_add(double *q, const double *qc, const double *so, double *res, const double *ci, int IIC, int JJC,
+                    int KKC, int IIF, int JJF, int KKF, int nstncl, int jpn);
+int orc3_setup_interp_oi(const double *so, const double *soc, double *ci, int IIF, int JJF, int KKF, int IIC,
+                         int JJC, int KKC, int ifd, int nstncl, int irelax, int jpn, double *yo);
+/* ITLI07_ex (ifd == 1) and ITLI27_ex in one entry point */
+int orc3_setup_itli_ex(const double *so, double *soc, const double *ci, int IIF, int JJF, int KKF, int IIC, int JJC,
+                       int KKC, int ifd, int nstncl, int ipn);
+int orc3_setup_cg_lu(const double *so, int II, int JJ, int KK, int nstncl, double *abd, int nabd1, int nabd2, int ibc);
+int orc3_solve_cg(double *q, const double *qf, int II, int JJ, int KK, const double *abd, double *bbd, int nabd1,
+                  int nabd2, int jpn);
+double orc3_l2norm(const double *q, int II, int JJ, int KK);
+void orc3_gallery_poisson(double *so, int nx, int ny, int nz);
+void orc3_gallery_fe(double *so, int nx, int ny, int nz);
+void orc3_rhs_sin(double *b, int nx, int ny, int nz);
+void orc3_exact_sin(double *q, int nx, int ny, int nz);
+
+typedef struct orc3_solver orc3_solver;
+orc3_solver *orc3_solver_create(const double *so, int nx, int ny, int nz, int nstncl, int nrelax_pre, int nrelax_post,
+                                int num_levels, int min_coarse);
+void orc3_solver_destroy(orc3_solver *s);
+int orc3_solver_nlevels(const orc3_solver *s);
+void orc3_solver_level_shape(const orc3_solver *s, int lvl, int *nx, int *ny, int *nz);
+double *orc3_solver_level_ptr(orc3_solver *s, int lvl, int which);
+void orc3_solver_vcycle(orc3_solver *s, double *x, const double *b);
+int orc3_solver_solve(orc3_solver *s, const double *b, double *x, int maxiter, double tol, double *rel_hist,
+                      double *res0);
+
 #ifdef __cplusplus
 }
 #endif

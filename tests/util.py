@@ -65,3 +65,48 @@ def assert_bitwise(a, b, what=""):
         k = tuple(idx[0])
         raise AssertionError(f"{what}: {len(idx)} of {a.size} entries differ; first at {k}: {a[k]!r} vs {b[k]!r}; "
                              f"max abs diff {np.nanmax(np.abs(a - b))}")
+
+
+# 3D entry order (src/3d/ftn/BMG_stencils_f90.h:43-48) and, per entry, the two
+# grid points it couples relative to its storage point S: (a, b) = offsets of the
+# two end points (read off BMG3_SymStd_residual.f90:74-100)
+ENTRIES3 = ["p", "pw", "ps", "b", "psw", "pnw", "bw", "bnw", "bn", "bne", "be", "bse", "bs", "bsw"]
+ENDS3 = {1: ((0, 0, 0), (-1, 0, 0)), 2: ((0, 0, 0), (0, -1, 0)), 3: ((0, 0, 0), (0, 0, -1)),
+         4: ((0, 0, 0), (-1, -1, 0)), 5: ((0, -1, 0), (-1, 0, 0)), 6: ((0, 0, 0), (-1, 0, -1)),
+         7: ((0, -1, 0), (-1, 0, -1)), 8: ((0, -1, 0), (0, 0, -1)), 9: ((-1, -1, 0), (0, 0, -1)),
+         10: ((-1, 0, 0), (0, 0, -1)), 11: ((-1, 0, 0), (0, -1, -1)), 12: ((0, 0, 0), (0, -1, -1)),
+         13: ((0, 0, 0), (-1, -1, -1))}
+SEVEN3 = (1, 2, 3)
+
+
+def random_op3(nx, ny, nz, full, rng, hetero=True):
+    """Heterogeneous symmetric diagonally dominant 7/27-point operator in Cedar
+    storage: (ndirs, nz+2, ny+2, nx+2); a coupling is present iff both end points
+    are interior (src/3d/gallery.cc); the diagonal is the row sum of all couplings
+    plus a positive shift (so boundary couplings are "kept in the centre")."""
+    nst = 14 if full else 4
+    so = np.zeros((nst, nz + 2, ny + 2, nx + 2))
+    rowsum = np.zeros((nz + 2, ny + 2, nx + 2))
+    n = (nx, ny, nz)
+    for e in (range(1, 14) if full else SEVEN3):
+        (a, b) = ENDS3[e]
+        # storage points S (0-based array index) for which S+a and S+b are interior (1..n)
+        lo = [max(1 - a[d], 1 - b[d], 1) for d in range(3)]
+        hi = [min(n[d] - a[d], n[d] - b[d], n[d] + 1) for d in range(3)]
+        if any(lo[d] > hi[d] for d in range(3)):
+            continue
+        shape = (hi[2] - lo[2] + 1, hi[1] - lo[1] + 1, hi[0] - lo[0] + 1)
+        v = 10.0 ** rng.uniform(-2, 2, size=shape) if hetero else np.ones(shape)
+        so[e, lo[2]:hi[2] + 1, lo[1]:hi[1] + 1, lo[0]:hi[0] + 1] = v
+        for end in (a, b):
+            rowsum[lo[2] + end[2]:hi[2] + 1 + end[2], lo[1] + end[1]:hi[1] + 1 + end[1],
+                   lo[0] + end[0]:hi[0] + 1 + end[0]] += v
+    shift = (10.0 ** rng.uniform(-2, 1, size=rowsum.shape) if hetero else 1.0)
+    so[0, 1:-1, 1:-1, 1:-1] = (rowsum * (1.0 + 0.05 * rng.uniform(size=rowsum.shape)) + shift)[1:-1, 1:-1, 1:-1]
+    return so
+
+
+def random_gf3(nx, ny, nz, rng):
+    q = np.zeros((nz + 2, ny + 2, nx + 2))
+    q[1:-1, 1:-1, 1:-1] = rng.standard_normal((nz, ny, nx))
+    return q
