@@ -43,6 +43,16 @@ SIGNATURES = {
     "bmgx2_SETUP_ITLI_ex": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _i, _i, _p]),
     "bmgx2_SETUP_cg_LU": (_i, [_p, _u, _u, _i, _p, _u, _u, _i, _p]),
     "bmgx2_SOLVE_cg": (_i, [_p, _p, _u, _u, _p, _p, _u, _u, _i, _p]),
+    "bmgx3_SETUP_recip": (_i, [_p, _p, _u, _u, _u, _i, _i, _p]),
+    "bmgx3_relax_GS": (_i, [_i, _p, _p, _p, _p, _u, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
+    "bmgx3_residual": (_i, [_i, _i, _i, _p, _p, _p, _p, _u, _u, _u, _i, _p]),
+    "bmgx3_restrict": (_i, [_p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _p]),
+    "bmgx3_interp_add": (_i, [_p, _p, _p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _i, _p]),
+    "bmgx3_SETUP_interp_OI": (_i, [_p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _i, _i, _i, _p, _p]),
+    "bmgx3_SETUP_ITLI07_ex": (_i, [_p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _p]),
+    "bmgx3_SETUP_ITLI27_ex": (_i, [_p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _p]),
+    "bmgx3_SETUP_cg_LU": (_i, [_p, _u, _u, _u, _i, _p, _u, _u, _i, _p]),
+    "bmgx3_SOLVE_cg": (_i, [_p, _p, _u, _u, _u, _p, _p, _u, _u, _i, _p]),
 }
 
 for _name, (_res, _args) in SIGNATURES.items():

@@ -12,6 +12,7 @@ using namespace cedar;
 using namespace cedar::cdr2;
 
 static thread_local std::string g_err;
+void cdr_set_error(const std::string &msg) { g_err = msg; }
 
 struct cdr2_operator
 {

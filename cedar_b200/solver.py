@@ -184,3 +184,117 @@ def solve_host(so, b, config_json=None, **kw):
     cfg = config_json if config_json is not None else make_config(**kw)
     _check(lib.cdr2_solve_host(nst, ii - 2, jj - 2, _P(so), _P(b), _P(x), cfg.encode(), _P(hist), 1000, C.byref(n)))
     return x, hist[:n.value]
+
+
+# ---------------------------------------------------------------------------- 3D
+_vp = C.c_void_p
+lib.cdr3_operator_data.restype = _dp
+lib.cdr3_operator_data.argtypes = [_vp]
+lib.cdr3_operator_create.argtypes = [C.c_int, C.c_uint, C.c_uint, C.c_uint, C.POINTER(_vp)]
+lib.cdr3_operator_gallery.argtypes = [C.c_char_p, C.c_uint, C.c_uint, C.c_uint, C.POINTER(_vp)]
+lib.cdr3_operator_destroy.argtypes = [_vp]
+lib.cdr3_solver_create.argtypes = [_vp, C.c_char_p, C.POINTER(_vp)]
+lib.cdr3_solver_destroy.argtypes = [_vp]
+lib.cdr3_solver_nlevels.argtypes = [_vp]
+lib.cdr3_solver_level_shape.argtypes = [_vp, C.c_int, C.POINTER(C.c_uint), C.POINTER(C.c_uint), C.POINTER(C.c_uint)]
+lib.cdr3_solver_level_array.argtypes = [_vp, C.c_int, C.c_char_p, _dp, C.c_size_t, C.POINTER(C.c_size_t)]
+lib.cdr3_solver_solve.argtypes = [_vp, _dp, _dp, _dp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double)]
+lib.cdr3_solver_vcycle.argtypes = [_vp, _dp, _dp]
+lib.cdr3_solver_buffers.argtypes = [_vp, C.POINTER(_dp), C.POINTER(_dp)]
+lib.cdr3_solver_vcycle_pinned.argtypes = [_vp]
+lib.cdr3_solver_time_vcycles.argtypes = [_vp, _dp, C.c_int, C.c_int, C.POINTER(C.c_float)]
+lib.cdr3_solver_time_solves.argtypes = [_vp, _dp, C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int)]
+
+
+class Operator3:
+    """Host-side 3D stencil operator, shape (ndirs, nz+2, ny+2, nx+2); ndirs = 4 or 14."""
+
+    def __init__(self, so=None, gallery=None, nx=None, ny=None, nz=None):
+        self.h = C.c_void_p()
+        if gallery is not None:
+            _check(lib.cdr3_operator_gallery(gallery.encode(), nx, ny, nz, C.byref(self.h)))
+            self.nst = 14 if gallery == "fe" else 4
+            self.nx, self.ny, self.nz = nx, ny, nz
+        else:
+            so = np.ascontiguousarray(so, dtype=np.float64)
+            self.nst, kk, jj, ii = so.shape
+            self.nx, self.ny, self.nz = ii - 2, jj - 2, kk - 2
+            _check(lib.cdr3_operator_create(self.nst, self.nx, self.ny, self.nz, C.byref(self.h)))
+            self.array()[...] = so
+
+    def array(self):
+        p = lib.cdr3_operator_data(self.h)
+        if not p:
+            raise CedarError(lib.cdr_last_error().decode())
+        return np.ctypeslib.as_array(p, shape=(self.nst, self.nz + 2, self.ny + 2, self.nx + 2))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib.cdr3_operator_destroy(self.h)
+            self.h = None
+
+
+class Solver3:
+    """cdr3::solver<fsten> on the GPU (setup at construction)."""
+    NDIRS = {"P": 26, "SOR0": 2, "x": 1, "res": 1, "b": 1}
+
+    def __init__(self, op, config_json=None, **kw):
+        self.op = op
+        self.h = C.c_void_p()
+        cfg = config_json if config_json is not None else make_config(**kw)
+        _check(lib.cdr3_solver_create(op.h, cfg.encode(), C.byref(self.h)))
+        self.nlevels = lib.cdr3_solver_nlevels(self.h)
+
+    def level_shape(self, lvl):
+        nx, ny, nz = C.c_uint(), C.c_uint(), C.c_uint()
+        _check(lib.cdr3_solver_level_shape(self.h, lvl, C.byref(nx), C.byref(ny), C.byref(nz)))
+        return nx.value, ny.value, nz.value
+
+    def level_array(self, lvl, which):
+        nx, ny, nz = self.level_shape(lvl)
+        nd = self.NDIRS.get(which, (self.op.nst if lvl == 0 else 14))
+        out = np.zeros((nd, nz + 2, ny + 2, nx + 2))
+        w = C.c_size_t()
+        _check(lib.cdr3_solver_level_array(self.h, lvl, which.encode(), _P(out), out.size, C.byref(w)))
+        if w.value == 0:
+            return None
+        assert w.value == out.size, (w.value, out.size)
+        return out if nd > 1 else out[0]
+
+    def solve(self, b, x=None, maxiter_cap=1000):
+        b = np.ascontiguousarray(b, dtype=np.float64)
+        x = np.zeros_like(b) if x is None else np.ascontiguousarray(x, dtype=np.float64)
+        hist = np.zeros(maxiter_cap)
+        n = C.c_int()
+        r0 = C.c_double()
+        _check(lib.cdr3_solver_solve(self.h, _P(b), _P(x), _P(hist), maxiter_cap, C.byref(n), C.byref(r0)))
+        return x, hist[:n.value], r0.value
+
+    def vcycle(self, x, b):
+        _check(lib.cdr3_solver_vcycle(self.h, _P(b), _P(x)))
+        return x
+
+    def buffers(self):
+        pb, px = _dp(), _dp()
+        _check(lib.cdr3_solver_buffers(self.h, C.byref(pb), C.byref(px)))
+        shape = (self.op.nz + 2, self.op.ny + 2, self.op.nx + 2)
+        return np.ctypeslib.as_array(pb, shape=shape), np.ctypeslib.as_array(px, shape=shape)
+
+    def vcycle_pinned(self):
+        _check(lib.cdr3_solver_vcycle_pinned(self.h))
+
+    def time_vcycles(self, b, warmup=3, n=10):
+        ms = C.c_float()
+        _check(lib.cdr3_solver_time_vcycles(self.h, _P(np.ascontiguousarray(b)), warmup, n, C.byref(ms)))
+        return ms.value
+
+    def time_solves(self, b, warmup=1, n=3):
+        ms = C.c_float()
+        it = C.c_int()
+        _check(lib.cdr3_solver_time_solves(self.h, _P(np.ascontiguousarray(b)), warmup, n, C.byref(ms), C.byref(it)))
+        return ms.value, it.value
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib.cdr3_solver_destroy(self.h)
+            self.h = None

@@ -177,6 +177,62 @@ int bmgx2_SOLVE_cg(bmgx_real *q, const bmgx_real *qf, bmgx_len ii, bmgx_len jj,
                    const bmgx_real *abd, bmgx_real *bbd, bmgx_len nabd1, bmgx_len nabd2,
                    int jpn, bmgx_stream_t s);
 
+/* ---- 3D ------------------------------------------------------------------
+ * Arrays: Q(II,JJ,KK), SO(II,JJ,KK,NStncl) with NStncl = 4 (seven_pt: p,pw,ps,b)
+ * or 14 (xxvii_pt), SOR(II,JJ,KK,2), CI(IIC,JJC,KKC,26); slot order of
+ * src/3d/ftn/BMG_stencils_f90.h:43-64. */
+
+/* BMG3_SymStd_SETUP_recip(so, sor, nx, ny, nz, nstncl, nsorv), include/cedar/3d/relax.h:11-13 */
+int bmgx3_SETUP_recip(const bmgx_real *so, bmgx_real *sor, bmgx_len nx, bmgx_len ny, bmgx_len nz,
+                      int nstncl, int nsorv, bmgx_stream_t s);
+
+/* BMG3_SymStd_relax_GS(kg, so, qf, q, sor, ii, jj, kk, ifd, nstncl, nsorv, irelax_sym,
+ *                      updown, jpn), include/cedar/3d/relax.h:14-16 */
+int bmgx3_relax_GS(int kg, const bmgx_real *so, const bmgx_real *qf, bmgx_real *q,
+                   const bmgx_real *sor, bmgx_len ii, bmgx_len jj, bmgx_len kk, int ifd, int nstncl,
+                   int nsorv, int irelax_sym, int updown, int jpn, bmgx_stream_t s);
+
+/* BMG3_SymStd_residual(kg, nog, ifd, q, qf, so, res, ii, jj, kk, nstncl),
+ * include/cedar/3d/residual.h:9-12 */
+int bmgx3_residual(int kg, int nog, int ifd, const bmgx_real *q, const bmgx_real *qf,
+                   const bmgx_real *so, bmgx_real *res, bmgx_len ii, bmgx_len jj, bmgx_len kk,
+                   int nstncl, bmgx_stream_t s);
+
+/* BMG3_SymStd_restrict(q, qc, ci, nx, ny, nz, nxc, nyc, nzc, jpn), src/3d/restrict.cc:7-10 */
+int bmgx3_restrict(const bmgx_real *q, bmgx_real *qc, const bmgx_real *ci, bmgx_len nx, bmgx_len ny,
+                   bmgx_len nz, bmgx_len nxc, bmgx_len nyc, bmgx_len nzc, int jpn, bmgx_stream_t s);
+
+/* BMG3_SymStd_interp_add(q, qc, so, res, ci, iic, jjc, kkc, iif, jjf, kkf, nstncl, jpn),
+ * src/3d/interp.cc:7-11; `res` is scaled in place by 1/diag as in the reference */
+int bmgx3_interp_add(bmgx_real *q, const bmgx_real *qc, const bmgx_real *so, bmgx_real *res,
+                     const bmgx_real *ci, bmgx_len iic, bmgx_len jjc, bmgx_len kkc, bmgx_len iif,
+                     bmgx_len jjf, bmgx_len kkf, int nstncl, int jpn, bmgx_stream_t s);
+
+/* BMG3_SymStd_SETUP_interp_OI(so, soc, ci, iif, jjf, kkf, iic, jjc, kkc, ifd, nstncl, irelax,
+ *                             jpn, yo), include/cedar/3d/interp.h:11-15; the `yo` scratch of
+ * the reference is not needed (may be NULL) */
+int bmgx3_SETUP_interp_OI(const bmgx_real *so, const bmgx_real *soc, bmgx_real *ci, bmgx_len iif,
+                          bmgx_len jjf, bmgx_len kkf, bmgx_len iic, bmgx_len jjc, bmgx_len kkc,
+                          int ifd, int nstncl, int irelax, int jpn, bmgx_real *yo, bmgx_stream_t s);
+
+/* BMG3_SymStd_SETUP_ITLI07_ex / ITLI27_ex(so, soc, ci, iif, jjf, kkf, iic, jjc, kkc, ipn),
+ * include/cedar/3d/coarsen.h:12-16 (Galerkin coarse operator, 7- / 27-point fine operator) */
+int bmgx3_SETUP_ITLI07_ex(const bmgx_real *so, bmgx_real *soc, const bmgx_real *ci, bmgx_len iif,
+                          bmgx_len jjf, bmgx_len kkf, bmgx_len iic, bmgx_len jjc, bmgx_len kkc,
+                          int ipn, bmgx_stream_t s);
+int bmgx3_SETUP_ITLI27_ex(const bmgx_real *so, bmgx_real *soc, const bmgx_real *ci, bmgx_len iif,
+                          bmgx_len jjf, bmgx_len kkf, bmgx_len iic, bmgx_len jjc, bmgx_len kkc,
+                          int ipn, bmgx_stream_t s);
+
+/* BMG3_SymStd_SETUP_cg_LU(so, ii, jj, kk, nstncl, abd, nabd1, nabd2, ibc) and
+ * BMG3_SymStd_SOLVE_cg(q, qf, ii, jj, kk, abd, bbd, nabd1, nabd2, ibc),
+ * include/cedar/3d/solve_cg.h; bbd is DEVICE scratch of nabd2 doubles */
+int bmgx3_SETUP_cg_LU(const bmgx_real *so, bmgx_len ii, bmgx_len jj, bmgx_len kk, int nstncl,
+                      bmgx_real *abd, bmgx_len nabd1, bmgx_len nabd2, int ibc, bmgx_stream_t s);
+int bmgx3_SOLVE_cg(bmgx_real *q, const bmgx_real *qf, bmgx_len ii, bmgx_len jj, bmgx_len kk,
+                   const bmgx_real *abd, bmgx_real *bbd, bmgx_len nabd1, bmgx_len nabd2, int jpn,
+                   bmgx_stream_t s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,9 @@
+#ifndef CEDAR_3D_GALLERY_H
+#define CEDAR_3D_GALLERY_H
+#include <cedar/3d/stencil_op.h>
+namespace cedar { namespace cdr3 { namespace gallery {
+// problem generators of the reference (src/3d/gallery.cc:7-56, 111-190)
+stencil_op<seven_pt> poisson(len_t nx, len_t ny, len_t nz);
+stencil_op<xxvii_pt> fe(len_t nx, len_t ny, len_t nz);
+}}}
+#endif

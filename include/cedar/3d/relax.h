@@ -1,0 +1,44 @@
+// cedar/3d/relax.h -- CUDA-backed 3D point relaxation, registered under the same
+// interface as the reference's rbgs (include/cedar/3d/relax.h:22-100): ifd from the
+// stencil type, BMG_RELAX_SYM always, boundary code from kernel_params::per_mask().
+#ifndef CEDAR_3D_RELAX_H
+#define CEDAR_3D_RELAX_H
+
+#include <type_traits>
+
+#include <cedar/3d/types.h>
+#include <cedar/kernels/point_relax.h>
+#include <cedar/gpu.h>
+
+namespace cedar { namespace cdr3 {
+
+class rbgs : public kernels::point_relax<stypes>
+{
+public:
+	void setup(const stencil_op<seven_pt> &so, relax_stencil &sor) override { setup_impl(so, sor); }
+	void setup(const stencil_op<xxvii_pt> &so, relax_stencil &sor) override { setup_impl(so, sor); }
+	void run(const stencil_op<seven_pt> &so, grid_func &x, const grid_func &b, const relax_stencil &sor,
+	         cycle::Dir cdir) override { run_impl(so, x, b, sor, cdir); }
+	void run(const stencil_op<xxvii_pt> &so, grid_func &x, const grid_func &b, const relax_stencil &sor,
+	         cycle::Dir cdir) override { run_impl(so, x, b, sor, cdir); }
+
+	template <class sten> void setup_impl(const stencil_op<sten> &so, relax_stencil &sor)
+	{
+		gpu::check(bmgx3_SETUP_recip(so.cdev(), sor.dev(), so.len(0), so.len(1), so.len(2), stencil_ndirs<sten>::value,
+		                             2, gpu::stream()), "SETUP_recip3");
+	}
+	template <class sten>
+	void run_impl(const stencil_op<sten> &so, grid_func &x, const grid_func &b, const relax_stencil &sor, cycle::Dir cdir)
+	{
+		int ifd = std::is_same<sten, seven_pt>::value ? 1 : 0;
+		int updown = cdir == cycle::Dir::UP ? BMGX_UP : BMGX_DOWN;
+		int ibc;
+		bmgx_get_bc(params->per_mask(), &ibc);
+		gpu::check(bmgx3_relax_GS(1, so.cdev(), b.cdev(), x.dev(), sor.cdev(), so.len(0), so.len(1), so.len(2), ifd,
+		                          stencil_ndirs<sten>::value, 2, BMGX_RELAX_SYM, updown, ibc, gpu::stream()),
+		           "relax_GS3");
+	}
+};
+
+}}
+#endif

@@ -70,6 +70,29 @@ int cdr2_solver_time_solves(cdr2_solver *solver, const double *b, int warmup, in
 int cdr2_solve_host(int nstencil, unsigned nx, unsigned ny, const double *so, const double *b, double *x,
                     const char *config_json, double *hist, int hist_cap, int *niter);
 
+
+/* ---- 3D (cdr3::solver): same protocol; nstencil = 4 (seven_pt) or 14 (xxvii_pt),
+ * arrays (nx+2)(ny+2)(nz+2)[ndirs] ---- */
+typedef struct cdr3_operator cdr3_operator;
+typedef struct cdr3_solver cdr3_solver;
+int cdr3_operator_create(int nstencil, unsigned nx, unsigned ny, unsigned nz, cdr3_operator **op);
+double *cdr3_operator_data(cdr3_operator *op);
+/* gallery: "poisson" (7-point), "fe" (27-point) */
+int cdr3_operator_gallery(const char *name, unsigned nx, unsigned ny, unsigned nz, cdr3_operator **op);
+void cdr3_operator_destroy(cdr3_operator *op);
+int cdr3_solver_create(cdr3_operator *op, const char *config_json, cdr3_solver **solver);
+void cdr3_solver_destroy(cdr3_solver *solver);
+int cdr3_solver_nlevels(cdr3_solver *solver);
+int cdr3_solver_level_shape(cdr3_solver *solver, int lvl, unsigned *nx, unsigned *ny, unsigned *nz);
+int cdr3_solver_level_array(cdr3_solver *solver, int lvl, const char *which, double *out, size_t n, size_t *written);
+int cdr3_solver_solve(cdr3_solver *solver, const double *b, double *x, double *hist, int hist_cap, int *niter,
+                      double *res0);
+int cdr3_solver_vcycle(cdr3_solver *solver, const double *b, double *x);
+int cdr3_solver_buffers(cdr3_solver *solver, double **b, double **x);
+int cdr3_solver_vcycle_pinned(cdr3_solver *solver);
+int cdr3_solver_time_vcycles(cdr3_solver *solver, const double *b, int warmup, int n, float *ms_per_cycle);
+int cdr3_solver_time_solves(cdr3_solver *solver, const double *b, int warmup, int n, float *ms_per_solve, int *niter);
+
 #ifdef __cplusplus
 }
 #endif
