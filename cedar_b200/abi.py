@@ -43,6 +43,9 @@ SIGNATURES = {
     "bmgx2_SETUP_ITLI_ex": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _i, _i, _p]),
     "bmgx2_SETUP_cg_LU": (_i, [_p, _u, _u, _i, _p, _u, _u, _i, _p]),
     "bmgx2_SOLVE_cg": (_i, [_p, _p, _u, _u, _p, _p, _u, _u, _i, _p]),
+    "bmgx2_relax_GS_pass": (_i, [_i, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "bmgx2_SETUP_interp_OI_stage": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _i, _i, _i, _i, _p]),
+    "bmgx2_line_copy": (_i, [_p, _u, _u, _i, _u, _i, _u, _p, _i, _p]),
     "bmgx3_SETUP_recip": (_i, [_p, _p, _u, _u, _u, _i, _i, _p]),
     "bmgx3_relax_GS": (_i, [_i, _p, _p, _p, _p, _u, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx3_residual": (_i, [_i, _i, _i, _p, _p, _p, _p, _u, _u, _u, _i, _p]),

@@ -52,11 +52,11 @@ k_relax_colour(const double *__restrict__ so, const double *__restrict__ qf, dou
     q[c] = acc * sor[(MSOR - 1) * pl + c];
 }
 
-extern "C" int bmgx2_relax_GS(int k, const double *so, const double *qf, double *q, const double *sor, bmgx_len ii,
-                              bmgx_len jj, int kf, int ifd, int nstncl, int nsorv, int irelax_sym, int updown,
-                              int jpn, bmgx_stream_t s)
+// passes: bit n set = run the n-th colour pass of the sweep (9-point: 4 passes, 5-point: 2)
+static int relax_gs_passes(int k, const double *so, const double *qf, double *q, const double *sor, bmgx_len ii,
+                           bmgx_len jj, int kf, int ifd, int irelax_sym, int updown, int jpn, unsigned passes,
+                           bmgx_stream_t s)
 {
-    (void)nstncl; (void)nsorv;
     if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_GS: periodic BCs not supported");
     if (ii < 3 || jj < 3) return BMGX_OK;
     cudaStream_t st = (cudaStream_t)s;
@@ -68,6 +68,7 @@ extern "C" int bmgx2_relax_GS(int k, const double *so, const double *qf, double 
             if (jbeg > J1) continue;
             unsigned nrow = (J1 - jbeg) / 2 + 1;
             for (int b = 0; b < 2; b++) {
+                if (!(passes & (1u << (2 * a + b)))) continue;
                 unsigned ibeg = fwd ? 2 + b : 3 - b;
                 if (ibeg > I1) continue;
                 unsigned ncol = (I1 - ibeg) / 2 + 1;
@@ -78,6 +79,7 @@ extern "C" int bmgx2_relax_GS(int k, const double *so, const double *qf, double 
         }
     } else {
         for (int a = 0; a < 2; a++) {
+            if (!(passes & (1u << a))) continue;
             unsigned jo = fwd ? 2 + a : 3 - a;
             unsigned ncol = (I1 - 2) / 2 + 1;  // upper bound on points per row of one colour
             dim3 g(cdiv(ncol, 128), J1 - 1);
@@ -86,4 +88,24 @@ extern "C" int bmgx2_relax_GS(int k, const double *so, const double *qf, double 
         }
     }
     return BMGX_OK;
+}
+
+extern "C" int bmgx2_relax_GS(int k, const double *so, const double *qf, double *q, const double *sor, bmgx_len ii,
+                              bmgx_len jj, int kf, int ifd, int nstncl, int nsorv, int irelax_sym, int updown,
+                              int jpn, bmgx_stream_t s)
+{
+    (void)nstncl; (void)nsorv;
+    return relax_gs_passes(k, so, qf, q, sor, ii, jj, kf, ifd, irelax_sym, updown, jpn, 0xfu, s);
+}
+
+// One colour pass of the sweep (pass = 0..3 for 9-point, 0..1 for 5-point, in sweep order):
+// the block-decomposed solver exchanges ghost values between the passes, like the
+// reference's MPI kernel (src/2d/ftn/mpi/BMG2_SymStd_relax_GS.f90:101-134).
+extern "C" int bmgx2_relax_GS_pass(int k, const double *so, const double *qf, double *q, const double *sor, bmgx_len ii,
+                                   bmgx_len jj, int kf, int ifd, int nstncl, int nsorv, int irelax_sym, int updown,
+                                   int jpn, int pass, bmgx_stream_t s)
+{
+    (void)nstncl; (void)nsorv;
+    if (pass < 0 || pass > 3) return bmgx_set_error(BMGX_ERR_ARG, "relax_GS_pass: pass out of range");
+    return relax_gs_passes(k, so, qf, q, sor, ii, jj, kf, ifd, irelax_sym, updown, jpn, 1u << pass, s);
 }

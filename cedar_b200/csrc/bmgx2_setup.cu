@@ -106,29 +106,51 @@ k_interp_centres(const double *__restrict__ so, double *ci, unsigned IIF, unsign
     }
 }
 
-extern "C" int bmgx2_SETUP_interp_OI(const double *so, const double *soc, double *ci, bmgx_len IIF, bmgx_len JJF,
-                                     bmgx_len IIC, bmgx_len JJC, int ifd, int nstncl, int jpn, int irelax,
-                                     bmgx_stream_t s)
+// stages: bit 0 = edge F-points (LL,LR,LA,LB), bit 1 = cell centres (LSW..LSE)
+static int interp_oi_stages(const double *so, double *ci, bmgx_len IIF, bmgx_len JJF, bmgx_len IIC, bmgx_len JJC, int ifd,
+                            int jpn, unsigned stages, bmgx_stream_t s)
 {
-    (void)soc; (void)nstncl; (void)irelax;
     if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SETUP_interp_OI: periodic BCs not supported");
     if (IIC < 3 || JJC < 3) return BMGX_OK;
     unsigned IICF1 = (IIF - 2) / 2 + 2, JJCF1 = (JJF - 2) / 2 + 2;
     cudaStream_t st = (cudaStream_t)s;
     dim3 b(64, 4);
-    // edges: ic in 2..max(IICF1, IIC-1), jc in 2..max(JJCF1, JJC-1)
-    unsigned mi = IICF1 > IIC - 1 ? IICF1 : IIC - 1, mj = JJCF1 > JJC - 1 ? JJCF1 : JJC - 1;
-    dim3 g1(cdiv(mi - 1, 64), cdiv(mj - 1, 4));
-    if (ifd != 1) k_interp_edges<true><<<g1, b, 0, st>>>(so, ci, IIF, JJF, IIC, JJC, IICF1, JJCF1);
-    else k_interp_edges<false><<<g1, b, 0, st>>>(so, ci, IIF, JJF, IIC, JJC, IICF1, JJCF1);
-    BMGX_LAUNCH_CHECK("SETUP_interp_OI/edges");
-    if (IICF1 >= 3 && JJCF1 >= 3) {
+    if (stages & 1u) {
+        // edges: ic in 2..max(IICF1, IIC-1), jc in 2..max(JJCF1, JJC-1)
+        unsigned mi = IICF1 > IIC - 1 ? IICF1 : IIC - 1, mj = JJCF1 > JJC - 1 ? JJCF1 : JJC - 1;
+        dim3 g1(cdiv(mi - 1, 64), cdiv(mj - 1, 4));
+        if (ifd != 1) k_interp_edges<true><<<g1, b, 0, st>>>(so, ci, IIF, JJF, IIC, JJC, IICF1, JJCF1);
+        else k_interp_edges<false><<<g1, b, 0, st>>>(so, ci, IIF, JJF, IIC, JJC, IICF1, JJCF1);
+        BMGX_LAUNCH_CHECK("SETUP_interp_OI/edges");
+    }
+    if ((stages & 2u) && IICF1 >= 3 && JJCF1 >= 3) {
         dim3 g2(cdiv(IICF1 - 2, 64), cdiv(JJCF1 - 2, 4));
         if (ifd != 1) k_interp_centres<true><<<g2, b, 0, st>>>(so, ci, IIF, JJF, IIC, JJC, IICF1, JJCF1);
         else k_interp_centres<false><<<g2, b, 0, st>>>(so, ci, IIF, JJF, IIC, JJC, IICF1, JJCF1);
         BMGX_LAUNCH_CHECK("SETUP_interp_OI/centres");
     }
     return BMGX_OK;
+}
+
+extern "C" int bmgx2_SETUP_interp_OI(const double *so, const double *soc, double *ci, bmgx_len IIF, bmgx_len JJF,
+                                     bmgx_len IIC, bmgx_len JJC, int ifd, int nstncl, int jpn, int irelax,
+                                     bmgx_stream_t s)
+{
+    (void)soc; (void)nstncl; (void)irelax;
+    return interp_oi_stages(so, ci, IIF, JJF, IIC, JJC, ifd, jpn, 3u, s);
+}
+
+// The two dependent stages separately (stage 1 = edges, 2 = cell centres): the
+// block-decomposed solver exchanges the edge weights of the ghost lines in between
+// (the reference's MPI kernel does the same between its loops,
+// src/2d/ftn/mpi/BMG2_SymStd_SETUP_interp_OI.f90).
+extern "C" int bmgx2_SETUP_interp_OI_stage(const double *so, const double *soc, double *ci, bmgx_len IIF, bmgx_len JJF,
+                                           bmgx_len IIC, bmgx_len JJC, int ifd, int nstncl, int jpn, int irelax,
+                                           int stage, bmgx_stream_t s)
+{
+    (void)soc; (void)nstncl; (void)irelax;
+    if (stage != 1 && stage != 2) return bmgx_set_error(BMGX_ERR_ARG, "SETUP_interp_OI_stage: stage must be 1 or 2");
+    return interp_oi_stages(so, ci, IIF, JJF, IIC, JJC, ifd, jpn, 1u << (stage - 1), s);
 }
 
 // ---- Galerkin coarse operator ----------------------------------------------

@@ -197,3 +197,35 @@ extern "C" int bmgx_graph_launch(void *graph_exec, bmgx_stream_t s)
     RT(cudaGraphLaunch((cudaGraphExec_t)graph_exec, (cudaStream_t)s), "bmgx_graph_launch");
 }
 extern "C" int bmgx_graph_destroy(void *graph_exec) { RT(cudaGraphExecDestroy((cudaGraphExec_t)graph_exec), "bmgx_graph_destroy"); }
+
+// ---- ghost-line staging for the block-decomposed solver -----------------------
+// Copies line `index` (1-based; dir 0: the column i = index, all j; dir 1: the row
+// j = index, all i) of every selected plane of A(II,JJ,nplanes) to (to_buf != 0) or
+// from a contiguous buffer laid out [selected plane][position along the line].
+__global__ void __launch_bounds__(256)
+k_line_copy(double *a, unsigned II, unsigned JJ, unsigned nplanes, unsigned mask, int dir, unsigned index,
+            double *buf, int to_buf)
+{
+    const unsigned len = dir == 0 ? JJ : II;
+    const unsigned t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= len) return;
+    unsigned slot = 0;
+    for (unsigned p = 0; p < nplanes; p++) {
+        if (!(mask & (1u << p))) continue;
+        const size_t off = (size_t)p * II * JJ + (dir == 0 ? (size_t)t * II + (index - 1) : (size_t)(index - 1) * II + t);
+        if (to_buf) buf[(size_t)slot * len + t] = a[off];
+        else a[off] = buf[(size_t)slot * len + t];
+        slot++;
+    }
+}
+
+extern "C" int bmgx2_line_copy(double *a, bmgx_len ii, bmgx_len jj, int nplanes, unsigned plane_mask, int dir,
+                               bmgx_len index, double *buf, int to_buf, bmgx_stream_t s)
+{
+    if (dir < 0 || dir > 1 || nplanes < 1 || nplanes > 32 || index < 1 || index > (dir == 0 ? ii : jj))
+        return bmgx_set_error(BMGX_ERR_ARG, "line_copy: bad arguments");
+    const unsigned len = dir == 0 ? jj : ii;
+    k_line_copy<<<cdiv(len, 256), 256, 0, (cudaStream_t)s>>>(a, ii, jj, nplanes, plane_mask, dir, index, buf, to_buf);
+    BMGX_LAUNCH_CHECK("line_copy");
+    return BMGX_OK;
+}

@@ -37,6 +37,7 @@ lib.cdr2_solver_buffers.argtypes = [C.c_void_p, C.POINTER(_dp), C.POINTER(_dp)]
 lib.cdr2_solver_vcycle_pinned.argtypes = [C.c_void_p]
 lib.cdr2_solver_solve_pinned.argtypes = [C.c_void_p, _dp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double)]
 lib.cdr_set_log.argtypes = [C.c_char_p]
+lib.cdr2_solver_vcycle_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
 
 
 class CedarError(RuntimeError):

@@ -177,6 +177,25 @@ int bmgx2_SOLVE_cg(bmgx_real *q, const bmgx_real *qf, bmgx_len ii, bmgx_len jj,
                    const bmgx_real *abd, bmgx_real *bbd, bmgx_len nabd1, bmgx_len nabd2,
                    int jpn, bmgx_stream_t s);
 
+/* ---- entry points of the block-decomposed (multi-GPU) 2D path ----------------
+ * The reference's MPI kernels (src/2d/ftn/mpi/) exchange ghost values between the
+ * colour passes of a sweep and between the stages of the interpolation setup; these
+ * entry points expose the same cut points of the serial kernels. */
+/* one colour pass (0..3 nine-point, 0..1 five-point, in sweep order) of bmgx2_relax_GS */
+int bmgx2_relax_GS_pass(int k, const bmgx_real *so, const bmgx_real *qf, bmgx_real *q,
+                        const bmgx_real *sor, bmgx_len ii, bmgx_len jj, int kf, int ifd,
+                        int nstncl, int nsorv, int irelax_sym, int updown, int jpn, int pass,
+                        bmgx_stream_t s);
+/* stage 1 (edge weights LL,LR,LA,LB) or 2 (cell-centre weights) of bmgx2_SETUP_interp_OI */
+int bmgx2_SETUP_interp_OI_stage(const bmgx_real *so, const bmgx_real *soc, bmgx_real *ci,
+                                bmgx_len iif, bmgx_len jjf, bmgx_len iic, bmgx_len jjc, int ifd,
+                                int nstncl, int jpn, int irelax, int stage, bmgx_stream_t s);
+/* ghost-line staging: copy column (dir 0) / row (dir 1) `index` (1-based) of the planes
+ * selected by plane_mask of A(II,JJ,nplanes) to (to_buf != 0) or from a contiguous
+ * buffer [selected plane][position]; what halo-2d's pack/unpack did on the host */
+int bmgx2_line_copy(bmgx_real *a, bmgx_len ii, bmgx_len jj, int nplanes, unsigned plane_mask,
+                    int dir, bmgx_len index, bmgx_real *buf, int to_buf, bmgx_stream_t s);
+
 /* ---- 3D ------------------------------------------------------------------
  * Arrays: Q(II,JJ,KK), SO(II,JJ,KK,NStncl) with NStncl = 4 (seven_pt: p,pw,ps,b)
  * or 14 (xxvii_pt), SOR(II,JJ,KK,2), CI(IIC,JJC,KKC,26); slot order of

@@ -50,6 +50,10 @@ int cdr2_solver_solve(cdr2_solver *solver, const double *b, double *x, double *h
 /* one V-cycle on host buffers (upload x,b; cycle; download x) */
 int cdr2_solver_vcycle(cdr2_solver *solver, const double *b, double *x);
 
+/* one V-cycle on DEVICE buffers ((nx+2)(ny+2) doubles each), enqueued on `stream`
+ * (a cudaStream_t; NULL = the library's own stream): no host traffic, no synchronisation */
+int cdr2_solver_vcycle_dev(cdr2_solver *solver, const double *b_dev, double *x_dev, void *stream);
+
 /* Pinned host staging buffers owned by the solver ((nx+2)(ny+2) doubles each):
  * fill *b (and *x as initial guess) in place, then call the _pinned variants,
  * which upload b and x, run on the device and download x into the same buffer

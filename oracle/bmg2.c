@@ -371,6 +371,7 @@ int orc2_interp_add(double *q, const double *qc, double *res, const double *so, 
 static inline double oi_min2(double a, double b) { return a < b ? a : b; }
 static inline double oi_max2(double a, double b) { return a > b ? a : b; }
 
+static int oi_stage_mask = 3;   /* bit 0: edge weights, bit 1: cell-centre weights */
 int orc2_setup_interp_oi(const double *so, const double *soc, double *ci,
                          int IIF, int JJF, int IIC, int JJC, int ifd, int nstncl,
                          int jpn, int irelax)
@@ -385,7 +386,7 @@ int orc2_setup_interp_oi(const double *so, const double *soc, double *ci,
 #define CI(i, j, kk) A3(ci, IIC, JJC, i, j, kk)
     if (ifd != 1) {
 #pragma omp parallel for schedule(static)
-        for (int jc = 2; jc <= JJC1; jc++) {
+        for (int jc = 2; jc <= ((oi_stage_mask & 1) ? JJC1 : 0); jc++) {
             int j = 2 * (jc - 1);
             for (int ic = 3; ic <= IICF1; ic++) {
                 int i = 2 * (ic - 1);
@@ -402,7 +403,7 @@ int orc2_setup_interp_oi(const double *so, const double *soc, double *ci,
             }
         }
 #pragma omp parallel for schedule(static)
-        for (int jc = 3; jc <= JJCF1; jc++) {
+        for (int jc = 3; jc <= ((oi_stage_mask & 1) ? JJCF1 : 0); jc++) {
             int j = 2 * (jc - 1);
             for (int ic = 2; ic <= IIC1; ic++) {
                 int i = 2 * (ic - 1);
@@ -419,7 +420,7 @@ int orc2_setup_interp_oi(const double *so, const double *soc, double *ci,
             }
         }
 #pragma omp parallel for schedule(static)
-        for (int jc = 3; jc <= JJCF1; jc++) {
+        for (int jc = 3; jc <= ((oi_stage_mask & 2) ? JJCF1 : 0); jc++) {
             int j = 2 * (jc - 1);
             for (int ic = 3; ic <= IICF1; ic++) {
                 int i = 2 * (ic - 1);
@@ -451,7 +452,7 @@ int orc2_setup_interp_oi(const double *so, const double *soc, double *ci,
         }
     } else {
 #pragma omp parallel for schedule(static)
-        for (int jc = 2; jc <= JJC1; jc++) {
+        for (int jc = 2; jc <= ((oi_stage_mask & 1) ? JJC1 : 0); jc++) {
             int j = 2 * (jc - 1);
             for (int ic = 3; ic <= IICF1; ic++) {
                 int i = 2 * (ic - 1);
@@ -468,7 +469,7 @@ int orc2_setup_interp_oi(const double *so, const double *soc, double *ci,
             }
         }
 #pragma omp parallel for schedule(static)
-        for (int jc = 3; jc <= JJCF1; jc++) {
+        for (int jc = 3; jc <= ((oi_stage_mask & 1) ? JJCF1 : 0); jc++) {
             int j = 2 * (jc - 1);
             for (int ic = 2; ic <= IIC1; ic++) {
                 int i = 2 * (ic - 1);
@@ -485,7 +486,7 @@ int orc2_setup_interp_oi(const double *so, const double *soc, double *ci,
             }
         }
 #pragma omp parallel for schedule(static)
-        for (int jc = 3; jc <= JJCF1; jc++) {
+        for (int jc = 3; jc <= ((oi_stage_mask & 2) ? JJCF1 : 0); jc++) {
             int j = 2 * (jc - 1);
             for (int ic = 3; ic <= IICF1; ic++) {
                 int i = 2 * (ic - 1);
@@ -511,6 +512,17 @@ int orc2_setup_interp_oi(const double *so, const double *soc, double *ci,
     return 0;
 #undef SO
 #undef CI
+}
+
+/* one stage of the above (1 = edges, 2 = cell centres); the block-decomposed solver
+ * exchanges the ghost-line edge weights in between */
+int orc2_setup_interp_oi_stage(const double *so, const double *soc, double *ci, int IIF, int JJF, int IIC, int JJC,
+                               int ifd, int nstncl, int jpn, int irelax, int stage)
+{
+    oi_stage_mask = 1 << (stage - 1);
+    int rc = orc2_setup_interp_oi(so, soc, ci, IIF, JJF, IIC, JJC, ifd, nstncl, jpn, irelax);
+    oi_stage_mask = 3;
+    return rc;
 }
 
 /* ------------------------------------------------------------------------
@@ -901,4 +913,43 @@ double orc2_l2norm(const double *q, int II, int JJ)
             result += v * v; /* std::pow(v,2) == v*v exactly */
         }
     return sqrt(result); /* std::pow(result, 0.5) is exact-sqrt for glibc */
+}
+
+/* One colour pass of orc2_relax_gs (pass = position in the sweep order: 9-point
+ * 2*a+b for the a-th row parity and b-th column parity, 5-point the a-th colour):
+ * the cut points at which the reference's MPI kernel exchanges ghost values
+ * (src/2d/ftn/mpi/BMG2_SymStd_relax_GS.f90:101-134).  Used by the CPU tests of the
+ * block-decomposed solver's host logic. */
+int orc2_relax_gs_pass(int k, const double *so, const double *qf, double *q, const double *sor,
+                       int II, int JJ, int kf, int ifd, int nstncl, int nsorv,
+                       int irelax_sym, int updown, int jpn, int pass)
+{
+    (void)nstncl; (void)nsorv;
+    if (jpn != 0 && jpn != -4) return -1;
+    const int J1 = JJ - 1, I1 = II - 1;
+    const int fwd = irelax_sym == 0 || (updown == 0 && irelax_sym == 1);
+#define SO(i, j, kk) A3(so, II, JJ, i, j, kk)
+#define Q(i, j) A2(q, II, i, j)
+    if (k < kf || ifd != 1) {
+        const int a = pass / 2, b = pass % 2;
+        const int jbeg = fwd ? 2 + a : 3 - a, ibeg = fwd ? 2 + b : 3 - b;
+        for (int j = jbeg; j <= J1; j += 2)
+            for (int i = ibeg; i <= I1; i += 2)
+                Q(i, j) = (A2(qf, II, i, j) + SO(i, j, KW) * Q(i - 1, j) + SO(i + 1, j, KW) * Q(i + 1, j)
+                           + SO(i, j, KS) * Q(i, j - 1) + SO(i, j + 1, KS) * Q(i, j + 1)
+                           + SO(i, j, KSW) * Q(i - 1, j - 1) + SO(i + 1, j, KNW) * Q(i + 1, j - 1)
+                           + SO(i, j + 1, KNW) * Q(i - 1, j + 1) + SO(i + 1, j + 1, KSW) * Q(i + 1, j + 1))
+                          * A3(sor, II, JJ, i, j, MSOR);
+    } else {
+        if (pass > 1) return 0;
+        const int jo = fwd ? 2 + pass : 3 - pass;
+        for (int j = 2; j <= J1; j++)
+            for (int i = (j + jo) % 2 + 2; i <= I1; i += 2)
+                Q(i, j) = (A2(qf, II, i, j) + SO(i, j, KW) * Q(i - 1, j) + SO(i + 1, j, KW) * Q(i + 1, j)
+                           + SO(i, j, KS) * Q(i, j - 1) + SO(i, j + 1, KS) * Q(i, j + 1))
+                          * A3(sor, II, JJ, i, j, MSOR);
+    }
+    return 0;
+#undef SO
+#undef Q
 }

@@ -22,6 +22,9 @@ void orc2_setup_recip(const double *so, double *sor, int nx, int ny, int nstncl,
 int orc2_relax_gs(int k, const double *so, const double *qf, double *q, const double *sor,
                   int II, int JJ, int kf, int ifd, int nstncl, int nsorv,
                   int irelax_sym, int updown, int jpn);
+int orc2_relax_gs_pass(int k, const double *so, const double *qf, double *q, const double *sor,
+                       int II, int JJ, int kf, int ifd, int nstncl, int nsorv,
+                       int irelax_sym, int updown, int jpn, int pass);
 void orc2_residual(int k, const double *so, const double *qf, const double *q, double *res,
                    int II, int JJ, int kf, int ifd, int nstncl);
 int orc2_restrict(const double *q, double *qc, const double *ci,
@@ -31,6 +34,8 @@ int orc2_interp_add(double *q, const double *qc, double *res, const double *so, 
 int orc2_setup_interp_oi(const double *so, const double *soc, double *ci,
                          int IIF, int JJF, int IIC, int JJC, int ifd, int nstncl,
                          int jpn, int irelax);
+int orc2_setup_interp_oi_stage(const double *so, const double *soc, double *ci, int IIF, int JJF, int IIC, int JJC,
+                               int ifd, int nstncl, int jpn, int irelax, int stage);
 int orc2_setup_itli_ex(const double *so, double *soc, const double *ci,
                        int IIF, int JJF, int IIC, int JJC, int ifd, int nstncl, int ipn);
 int orc2_setup_lines_x(const double *so, double *sor, int Nx, int Ny, int nstncl, int jpn);
