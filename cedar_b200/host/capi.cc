@@ -193,14 +193,12 @@ int cdr2_solver_vcycle_dev(cdr2_solver *s, const double *b_dev, double *x_dev, v
 	return guard([&] {
 		// device-resident caller (the block-decomposed solver's agglomerated coarse
 		// levels): no host traffic; everything is enqueued on the caller's stream
-		bmgx_stream_t prev = gpu::stream();
-		if (stream) gpu::set_stream(stream);
+		gpu::stream_guard on_callers_stream(stream);
 		size_t bytes = s->b.size() * sizeof(double);
 		gpu::check(bmgx_memcpy_d2d(s->b.dev(), b_dev, bytes, gpu::stream()), "vcycle_dev b");
 		gpu::check(bmgx_memcpy_d2d(s->x.dev(), x_dev, bytes, gpu::stream()), "vcycle_dev x");
 		if (s->s5) s->s5->vcycle(s->x, s->b); else s->s9->vcycle(s->x, s->b);
 		gpu::check(bmgx_memcpy_d2d(x_dev, s->x.cdev(), bytes, gpu::stream()), "vcycle_dev x out");
-		if (stream) gpu::set_stream(prev);
 	});
 }
 

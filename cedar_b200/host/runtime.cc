@@ -37,6 +37,15 @@ void set_stream(bmgx_stream_t s)
 	g_stream_own = false;
 }
 
+stream_guard::stream_guard(bmgx_stream_t s) : prev(g_stream), prev_own(g_stream_own), active(s != nullptr)
+{
+	if (active) { g_stream = s; g_stream_own = false; }
+}
+stream_guard::~stream_guard()
+{
+	if (active) { g_stream = prev; g_stream_own = prev_own; }
+}
+
 void sync() { check(bmgx_stream_sync(stream()), "stream sync"); }
 unsigned long long launches() { return bmgx_launch_count() + g_extra.load(); }
 void add_launches(unsigned long long n) { g_extra.fetch_add(n); }

@@ -25,6 +25,18 @@ bool available();
 // the stream every kernel of this process is enqueued on (created on first use)
 bmgx_stream_t stream();
 void set_stream(bmgx_stream_t s);
+// run on a caller-provided stream for the lifetime of the guard (nullptr = no change);
+// the library's own stream, if any, is kept and comes back afterwards
+struct stream_guard
+{
+	explicit stream_guard(bmgx_stream_t s);
+	~stream_guard();
+	stream_guard(const stream_guard &) = delete;
+	stream_guard &operator=(const stream_guard &) = delete;
+private:
+	bmgx_stream_t prev;
+	bool prev_own, active;
+};
 void sync();
 // running count of device launches issued through the host layer, including
 // the nodes of replayed CUDA graphs
