@@ -167,6 +167,14 @@ extern "C" int bmgx_stream_create(bmgx_stream_t *s)
 {
     RT(cudaStreamCreateWithFlags((cudaStream_t *)s, cudaStreamNonBlocking), "bmgx_stream_create");
 }
+extern "C" int bmgx_stream_is_capturing(bmgx_stream_t s, int *capturing)
+{
+    cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+    cudaError_t e = cudaStreamIsCapturing((cudaStream_t)s, &st);
+    if (e != cudaSuccess) return bmgx_set_cuda_error(e, "bmgx_stream_is_capturing");
+    *capturing = st == cudaStreamCaptureStatusActive;
+    return BMGX_OK;
+}
 extern "C" int bmgx_stream_destroy(bmgx_stream_t s) { RT(cudaStreamDestroy((cudaStream_t)s), "bmgx_stream_destroy"); }
 extern "C" int bmgx_stream_sync(bmgx_stream_t s) { RT(cudaStreamSynchronize((cudaStream_t)s), "bmgx_stream_sync"); }
 extern "C" int bmgx_device_sync(void) { RT(cudaDeviceSynchronize(), "bmgx_device_sync"); }

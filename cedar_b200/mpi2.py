@@ -497,6 +497,35 @@ class DistSolver2:
             else:
                 self._ncycle(0, x, b)
 
+    def vcycle_graphed(self, x, b, warm=4):
+        """vcycle() replayed from one CUDA graph per (x, b) pair: the kernels, the NCCL ghost
+        exchanges and the agglomerated serial cycle (a child graph) are captured together, so a
+        replay costs one launch instead of several hundred.  All ranks must call it together."""
+        key = tuple(sorted((k, x[k].data_ptr(), b[k].data_ptr()) for k in self.owned))
+        g = self._graphs.get(key) if hasattr(self, "_graphs") else None
+        if g is None:
+            if not hasattr(self, "_graphs"):
+                self._graphs = {}
+            saved = {k: x[k].clone() for k in self.owned}
+            for _ in range(warm):          # lets the serial coarse solver reach its replay state
+                self.vcycle(x, b)
+            self.stream.synchronize()
+            for k in self.owned:
+                x[k].copy_(saved[k])
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            l0, e0 = self.K.launches, self.exchanges
+            with torch.cuda.graph(g, stream=self.stream):
+                self._ncycle(0, x, b) if self.ndist > 0 else self.vcycle(x, b)
+            self._graph_cost = (self.K.launches - l0, self.exchanges - e0)
+            self._graphs[key] = g
+            for k in self.owned:
+                x[k].copy_(saved[k])
+        with self._on_stream():
+            g.replay()
+        self.K.launches += self._graph_cost[0]
+        self.exchanges += self._graph_cost[1]
+
     def _norm(self, arrs):
         tot = self._zeros(1)
         for blk in self.owned:
@@ -566,3 +595,64 @@ def join_blocks(parts, decomp, lvl=0):
         t = t.detach().cpu().numpy() if hasattr(t, "detach") else np.asarray(t)
         g[..., 1 + y0:1 + y0 + nyl, 1 + x0:1 + x0 + nxl] = t[..., 1:-1, 1:-1]
     return g
+
+
+# ------------------------------------------------------------------ block-wise problem generators
+def gallery_fe_block(dec, b):
+    """own entries of gallery::fe (src/2d/gallery.cc:78-113) for block b: centre 8, every
+    coupling between two interior points 1"""
+    x0, y0, nxl, nyl = dec.extent(0, b)
+    so = np.zeros((5, nyl + 2, nxl + 2))
+    gi = x0 + np.arange(nxl)[None, :]
+    gj = y0 + np.arange(nyl)[:, None]
+    own = so[:, 1:-1, 1:-1]
+    own[0] = 8.0
+    own[1] = (gi >= 1) * np.ones((nyl, 1))
+    own[2] = (gj >= 1) * np.ones((1, nxl))
+    own[3] = (gi >= 1) * (gj >= 1)
+    own[4] = (gi >= 1) * (gj >= 1)
+    return so
+
+
+def gallery_hetero_block(dec, b, nblk=64, seed=20260411):
+    """own entries of the heterogeneous 9-point operator of config 5:
+    bilinear-FE-like stencil of -div(D grad u), D piecewise constant on an nblk x nblk
+    checkerboard of log-uniform blocks D = 10**U(-3,3); every coupling is the mean of D over
+    the cells it crosses, the centre is the sum of the eight couplings (Dirichlet boundary
+    couplings kept in the centre, as gallery::fe does)."""
+    gnx, gny = dec.gn[0]
+    rng = np.random.default_rng(seed)
+    D = 10.0 ** rng.uniform(-3, 3, size=(nblk, nblk))
+    x0, y0, nxl, nyl = dec.extent(0, b)
+
+    def cell(ci, cj):       # coefficient of the cell whose lower-left grid node is (ci, cj), nodes 0..gn+1
+        bi = np.clip(ci * nblk // (gnx + 1), 0, nblk - 1)
+        bj = np.clip(cj * nblk // (gny + 1), 0, nblk - 1)
+        return D[bj, bi]
+
+    gi = (x0 + 1 + np.arange(nxl))[None, :] + np.zeros((nyl, 1), dtype=int)     # node indices 1..gn of own points
+    gj = (y0 + 1 + np.arange(nyl))[:, None] + np.zeros((1, nxl), dtype=int)
+    sw, se, nw, ne = cell(gi - 1, gj - 1), cell(gi, gj - 1), cell(gi - 1, gj), cell(gi, gj)
+    cw, cs_, ce, cn = 0.5 * (sw + nw), 0.5 * (sw + se), 0.5 * (se + ne), 0.5 * (nw + ne)
+    so = np.zeros((5, nyl + 2, nxl + 2))
+    own = so[:, 1:-1, 1:-1]
+    own[0] = cw + cs_ + ce + cn + sw + se + nw + ne
+    own[1] = cw * (gi >= 2)
+    own[2] = cs_ * (gj >= 2)
+    own[3] = sw * ((gi >= 2) & (gj >= 2))
+    # KNW stored at S couples (S-y) and (S-x): it crosses the cell south-west of S
+    own[4] = sw * ((gi >= 2) & (gj >= 2))
+    return so
+
+
+def rhs_sin_block(dec, b):
+    """examples/basic-2d-ser/poisson.cc:15-37 on block b"""
+    gnx, gny = dec.gn[0]
+    x0, y0, nxl, nyl = dec.extent(0, b)
+    hx, hy = 1.0 / (gnx + 1), 1.0 / (gny + 1)
+    x = ((x0 + 1 + np.arange(nxl)) * hx)[None, :]
+    y = ((y0 + 1 + np.arange(nyl)) * hy)[:, None]
+    out = np.zeros((nyl + 2, nxl + 2))
+    pi = math.pi
+    out[1:-1, 1:-1] = 8 * (pi * pi) * np.sin(2 * pi * x) * np.sin(2 * pi * y) * (hx * hy)
+    return out

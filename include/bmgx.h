@@ -67,6 +67,8 @@ int bmgx_memset0(void *dst, size_t bytes, bmgx_stream_t s);
 int bmgx_stream_create(bmgx_stream_t *s);
 int bmgx_stream_destroy(bmgx_stream_t s);
 int bmgx_stream_sync(bmgx_stream_t s);
+/* 1 if the stream is being captured into a CUDA graph by the caller */
+int bmgx_stream_is_capturing(bmgx_stream_t s, int *capturing);
 int bmgx_device_sync(void);
 /* CUDA events for device-side timing on the launching stream */
 int bmgx_event_create(void **ev);

@@ -44,6 +44,12 @@ public:
 		if (levels.size() == 1) { coarse_solver(x, b); return; }
 		// info-level logging reads norms back inside the cycle: not capturable
 		if (!use_graph || log::info.active()) { ncycle(0, x, b); return; }
+		// the caller is capturing this stream into its own graph (the block-decomposed
+		// solver's whole-cycle graph): record the kernels directly, an executable graph
+		// cannot be launched into a capture
+		int outer_capture = 0;
+		gpu::check(bmgx_stream_is_capturing(gpu::stream(), &outer_capture), "stream capture status");
+		if (outer_capture) { ncycle(0, x, b); return; }
 		// A captured graph bakes device pointers in.  Kernels may exchange device
 		// buffers (the fused relaxation ping-pongs x with a scratch array), so the
 		// graph is keyed by the pointer state of (x, b, every level's x): a cycle
