@@ -47,6 +47,9 @@ SIGNATURES = {
     "bmgx2_relax_GS_pass": (_i, [_i, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx2_SETUP_interp_OI_stage": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _i, _i, _i, _i, _p]),
     "bmgx2_line_copy": (_i, [_p, _u, _u, _i, _u, _i, _u, _p, _i, _p]),
+    "bmgx3_plane_copy": (_i, [_p, _p, _u, _u, _u, _i, _u, _i, _p]),
+    "bmgx3_plane_coeff": (_i, [_p, _p, _u, _u, _u, _i, _i, _u, _p]),
+    "bmgx3_plane_rhs": (_i, [_p, _p, _p, _p, _u, _u, _u, _i, _i, _u, _p]),
     "bmgx3_SETUP_recip": (_i, [_p, _p, _u, _u, _u, _i, _i, _p]),
     "bmgx3_relax_GS": (_i, [_i, _p, _p, _p, _p, _u, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx3_residual": (_i, [_i, _i, _i, _p, _p, _p, _p, _u, _u, _u, _i, _p]),

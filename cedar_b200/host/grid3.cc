@@ -7,6 +7,7 @@
 #include <cedar/3d/gallery.h>
 #include <cedar/3d/kernel_manager.h>
 #include <cedar/3d/relax.h>
+#include <cedar/3d/relax_planes.h>
 #include <cedar/3d/residual.h>
 #include <cedar/3d/restrict.h>
 #include <cedar/3d/interp.h>
@@ -141,6 +142,9 @@ kman_ptr build_kernel_manager(std::shared_ptr<kernel_params> params)
 	using namespace cedar::kernels;
 	auto kman = std::make_shared<kernel_manager<klist<stypes, exec_mode::serial>>>(params);
 	kman->add<point_relax<stypes>, rbgs>("system");
+	kman->add<plane_relax<stypes, relax_dir::xy>, planes<relax_dir::xy>>("system");
+	kman->add<plane_relax<stypes, relax_dir::xz>, planes<relax_dir::xz>>("system");
+	kman->add<plane_relax<stypes, relax_dir::yz>, planes<relax_dir::yz>>("system");
 	kman->add<coarsen_op<stypes>, galerkin>("system");
 	kman->add<interp_add<stypes>, interp_b200>("system");
 	kman->add<restriction<stypes>, restrict_b200>("system");
@@ -149,6 +153,9 @@ kman_ptr build_kernel_manager(std::shared_ptr<kernel_params> params)
 	kman->add<solve_cg<stypes>, solve_cg_b200>("system");
 
 	kman->set<point_relax<stypes>>("system");
+	kman->set<plane_relax<stypes, relax_dir::xy>>("system");
+	kman->set<plane_relax<stypes, relax_dir::xz>>("system");
+	kman->set<plane_relax<stypes, relax_dir::yz>>("system");
 	kman->set<coarsen_op<stypes>>("system");
 	kman->set<interp_add<stypes>>("system");
 	kman->set<restriction<stypes>>("system");

@@ -254,6 +254,20 @@ int bmgx3_SOLVE_cg(bmgx_real *q, const bmgx_real *qf, bmgx_len ii, bmgx_len jj, 
                    const bmgx_real *abd, bmgx_real *bbd, bmgx_len nabd1, bmgx_len nabd2, int jpn,
                    bmgx_stream_t s);
 
+/* ---- plane relaxation staging (3D <-> 2D) ---------------------------------
+ * dir: 0 = xy planes (plane index k), 1 = xz (index j), 2 = yz (index i); ipl is the
+ * 1-based plane index; the 2D arrays are (II,JJ), (II,KK), (JJ,KK) with ghosts. */
+/* copy32 (to2d != 0) / copy23, src/3d/relax_planes.cc:181-238 */
+int bmgx3_plane_copy(bmgx_real *x3, bmgx_real *x2, bmgx_len ii, bmgx_len jj, bmgx_len kk, int dir,
+                     bmgx_len ipl, int to2d, bmgx_stream_t s);
+/* copy_coeff for one plane, include/cedar/3d/relax_planes.h:77-161: so2 (3 or 5 planes) */
+int bmgx3_plane_coeff(const bmgx_real *so3, bmgx_real *so2, bmgx_len ii, bmgx_len jj, bmgx_len kk,
+                      int nstncl, int dir, bmgx_len ipl, bmgx_stream_t s);
+/* copy_rhs, src/3d/relax_planes.cc:26-178: b2 = b + (off-plane couplings) * x */
+int bmgx3_plane_rhs(const bmgx_real *so, const bmgx_real *x, const bmgx_real *b, bmgx_real *b2,
+                    bmgx_len ii, bmgx_len jj, bmgx_len kk, int nstncl, int dir, bmgx_len ipl,
+                    bmgx_stream_t s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,86 @@
+"""GPU parity of 3D plane relaxation (include/cedar/3d/relax_planes.h over the C ABI):
+staging kernels bitwise against numpy restatements of copy32/copy23/copy_coeff/copy_rhs
+(src/3d/relax_planes.cc), and the full solver with plane-xy/xz/yz/xyz relaxation against
+the CPU oracle (oracle/planes3.py) to 1e-10 (the in-plane line solves are warp scans on
+the GPU, 1e-12 relative to the sequential LAPACK order; everything else is bitwise)."""
+import numpy as np
+import pytest
+
+import oracle
+from oracle import planes3
+from tests.util import assert_bitwise, dev, host, ptr, random_gf3, random_op3
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def abi(cuda):
+    import cedar_b200.abi as a
+    return a
+
+
+@pytest.fixture(scope="module")
+def cs(cuda):
+    import cedar_b200.solver as s
+    return s
+
+
+@pytest.mark.parametrize("full", [False, True])
+@pytest.mark.parametrize("d", ["xy", "xz", "yz"])
+def test_staging_kernels(cuda, abi, d, full):
+    nx, ny, nz = 13, 9, 11
+    rng = np.random.default_rng(3 + full)
+    so = random_op3(nx, ny, nz, full, rng)
+    x, b = random_gf3(nx, ny, nz, rng), random_gf3(nx, ny, nz, rng)
+    II, JJ, KK = nx + 2, ny + 2, nz + 2
+    code = {"xy": 0, "xz": 1, "yz": 2}[d]
+    npl = {"xy": nz, "xz": ny, "yz": nx}[d]
+    d_so, d_x, d_b = dev(cuda, so), dev(cuda, x), dev(cuda, b)
+    shape2 = planes3._plane(x, d, 1).shape
+    for ipl in (1, 2, npl):
+        # copy32
+        d_x2 = cuda.zeros(shape2, dtype=cuda.float64, device="cuda")
+        abi.check(abi.lib.bmgx3_plane_copy(ptr(d_x), ptr(d_x2), II, JJ, KK, code, ipl + 1, 1, None))
+        assert_bitwise(host(d_x2), planes3._plane(x, d, ipl), "copy32")
+        # copy_rhs
+        offs = (planes3._RHS27 if full else planes3._RHS7)[d]
+        acc = planes3._plane(b, d, ipl)[1:-1, 1:-1].copy()
+        for off in offs:
+            e, s = planes3._CPL[off]
+            acc = acc + planes3._plane_int(planes3._shift(so[e], s), d, ipl) * planes3._plane_int(planes3._shift(x, off), d, ipl)
+        d_b2 = cuda.zeros(shape2, dtype=cuda.float64, device="cuda")
+        abi.check(abi.lib.bmgx3_plane_rhs(ptr(d_so), ptr(d_x), ptr(d_b), ptr(d_b2), II, JJ, KK, so.shape[0], code, ipl + 1, None))
+        assert_bitwise(host(d_b2)[1:-1, 1:-1], acc, "copy_rhs")
+        # copy_coeff
+        slots = planes3._COEFF[d][:5 if full else 3]
+        want = np.stack([planes3._plane(so[e], d, ipl) for e in slots])
+        d_so2 = cuda.zeros(want.shape, dtype=cuda.float64, device="cuda")
+        abi.check(abi.lib.bmgx3_plane_coeff(ptr(d_so), ptr(d_so2), II, JJ, KK, so.shape[0], code, ipl + 1, None))
+        assert_bitwise(host(d_so2), want, "copy_coeff")
+        # copy23
+        y2 = rng.standard_normal(shape2)
+        abi.check(abi.lib.bmgx3_plane_copy(ptr(d_x), ptr(dev(cuda, y2)), II, JJ, KK, code, ipl + 1, 0, None))
+        xw = x.copy()
+        planes3._plane(xw, d, ipl)[...] = y2
+        assert_bitwise(host(d_x), xw, "copy23")
+        d_x.copy_(dev(cuda, x))
+
+
+@pytest.mark.parametrize("case", [("poisson", 17, 17, 17, "plane-xyz"), ("fe", 17, 17, 17, "plane-xyz"),
+                                  ("poisson", 20, 13, 17, "plane-xy"), ("fe", 12, 21, 17, "plane-xz"),
+                                  ("poisson", 17, 12, 20, "plane-yz"), ("fe", 33, 33, 33, "plane-xyz")])
+def test_plane_solver_matches_oracle(cs, case):
+    name, nx, ny, nz, relax = case
+    so = oracle.gallery3(name, nx, ny, nz)
+    b = oracle.rhs_sin3(nx, ny, nz)
+    ref = planes3.Solver3Planes(so, relax, 1, 1)
+    xr, hr, r0r = ref.solve(b, maxiter=6, tol=1e-10)
+    sol = cs.Solver3(cs.Operator3(so), relaxation=relax, nrelax_pre=1, nrelax_post=1, maxiter=6, tol=1e-10)
+    assert sol.nlevels == ref.nlevels
+    x, h, r0 = sol.solve(b)
+    assert len(h) == len(hr)
+    assert abs(r0 - r0r) <= 1e-13 * r0r
+    assert np.all(np.abs(h - hr) <= 1e-8 * hr + 2e-15), (h, hr)
+    # thousands of line-relaxed plane cycles, each 1e-12 away from the sequential LAPACK order
+    assert np.max(np.abs(x - xr)) <= 1e-7 * np.max(np.abs(xr))
+    assert h[-1] < h[0] * 1e-2          # it smooths: the reference's plane tests only ask for convergence
