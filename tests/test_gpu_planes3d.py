@@ -83,4 +83,8 @@ def test_plane_solver_matches_oracle(cs, case):
     assert np.all(np.abs(h - hr) <= 1e-8 * hr + 2e-15), (h, hr)
     # thousands of line-relaxed plane cycles, each 1e-12 away from the sequential LAPACK order
     assert np.max(np.abs(x - xr)) <= 1e-7 * np.max(np.abs(xr))
-    assert h[-1] < h[0] * 1e-2          # it smooths: the reference's plane tests only ask for convergence
+    # it converges.  How fast depends on the reference quirk kept on purpose (relax_planes.h:77-161: every
+    # plane solver gets the coefficients of the LAST interior plane): harmless on the fine level of the
+    # constant-coefficient galleries, but the Galerkin coarse operators are not plane-invariant near the
+    # boundary, so deeper hierarchies (33^3: 5 levels) contract by only ~0.7 per cycle, here and in the oracle
+    assert h[-1] < h[0] * (1e-2 if max(nx, ny, nz) <= 20 else 0.5)
