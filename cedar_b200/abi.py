@@ -52,6 +52,7 @@ SIGNATURES = {
     "bmgx3_plane_rhs": (_i, [_p, _p, _p, _p, _u, _u, _u, _i, _i, _u, _p]),
     "bmgx3_SETUP_recip": (_i, [_p, _p, _u, _u, _u, _i, _i, _p]),
     "bmgx3_relax_GS": (_i, [_i, _p, _p, _p, _p, _u, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
+    "bmgx3_relax_GS_oop": (_i, [_i, _p, _p, _p, _p, _p, _u, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx3_residual": (_i, [_i, _i, _i, _p, _p, _p, _p, _u, _u, _u, _i, _p]),
     "bmgx3_restrict": (_i, [_p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _p]),
     "bmgx3_interp_add": (_i, [_p, _p, _p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _i, _p]),

@@ -11,11 +11,21 @@
 //
 // Solve: with the factor known, DPTTS2 is two first-order linear recurrences,
 //     y(i) = b(i) - e(i-1) y(i-1),      x(i) = y(i)/d(i) - e(i) x(i+1),
-// evaluated here as warp-wide affine scans (parallel cyclic reduction of a
-// bidiagonal system): one warp per line, 32 unknowns per step, 5 shuffle
-// rounds, carry to the next 32.  The operation order differs from the
-// sequential LAPACK loop, so parity with the oracle is to rounding (the tests
-// use 1e-12 relative), not bitwise.
+// i.e. a chain of affine maps.  One CTA per line, the line staged in shared
+// memory (right-hand side and sub-diagonal factor, chunk-padded so both the
+// coalesced "interleaved" phases and the per-thread "chunk" phases are free of
+// bank conflicts: chunks have odd length):
+//   1. interleaved: build the right-hand side (reference term order), stage L;
+//   2. chunk: every thread composes the affine maps of its C consecutive
+//      unknowns, a block-wide scan of the chunk maps (warp shuffles + one
+//      cross-warp step) yields the value entering each chunk, and the thread
+//      re-runs the plain sequential recurrence over its chunk from that value;
+//   3. interleaved: divide by D (coalesced read);  4. chunk: the same, backwards;
+//   5. interleaved: store the line.
+// Inside a chunk the arithmetic is DPTTS2's; only the chunk-entry values are
+// rounded differently, so parity with the oracle is to rounding (tests: 1e-12
+// relative), not bitwise.  Lines too long for shared memory (> ~13000 unknowns)
+// fall back to the warp-per-line scan kernels further down.
 #include "bmgx_common.cuh"
 
 // ---------------------------------------------------------------- setup ----
@@ -98,6 +108,204 @@ __device__ __forceinline__ Aff scan_down(Aff v, int lane)
     return v;
 }
 
+// ---- block-per-line solver ----------------------------------------------------
+// The line lives in shared memory at slot p-1 (positions p = 1..m).  Thread t owns
+// the chunk of C consecutive positions starting at 1 + t*C; C is odd, so the
+// per-thread chunk walks (stride C doubles between threads) are bank-conflict free
+// without padding, and the interleaved phases are trivially so.
+
+// exclusive block scan of affine maps in thread order (map of thread 0 applied
+// first): returns the composition of the maps of all threads before this one
+__device__ __forceinline__ Aff block_scan_excl(Aff v, Aff *wsum, Aff *wpre)
+{
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    Aff inc = scan_up(v, lane);
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        Aff w;
+        if (lane < nw) w = wsum[lane]; else { w.a = 1.0; w.b = 0.0; }
+        Aff wi = scan_up(w, lane);
+        Aff ex;
+        ex.a = __shfl_up_sync(0xffffffffu, wi.a, 1);
+        ex.b = __shfl_up_sync(0xffffffffu, wi.b, 1);
+        if (lane == 0) { ex.a = 1.0; ex.b = 0.0; }
+        wpre[lane] = ex;
+    }
+    __syncthreads();
+    const Aff pre = wpre[warp];
+    Aff e;
+    e.a = __shfl_up_sync(0xffffffffu, inc.a, 1);
+    e.b = __shfl_up_sync(0xffffffffu, inc.b, 1);
+    if (lane == 0) { e.a = 1.0; e.b = 0.0; }
+    Aff r;
+    r.a = e.a * pre.a;
+    r.b = e.a * pre.b + e.b;
+    return r;
+}
+
+// one bidiagonal sweep over the staged line: forward  v(p) = v(p) - L(p)   v(p-1)  (p = 2..m)
+//                                            backward v(p) = v(p) - L(p+1) v(p+1)  (p = m-1..1)
+// sv[p-1] = v(p), se[p-1] = L(p)
+template <bool BWD>
+__device__ __forceinline__ void block_bidiag(double *sv, const double *se, unsigned m, unsigned C, Aff *wsum, Aff *wpre)
+{
+    const unsigned t = threadIdx.x;
+    const unsigned ch = BWD ? blockDim.x - 1 - t : t;   // backward: thread 0 owns the last chunk
+    const unsigned p0 = 1 + ch * C;
+    const bool act = p0 <= m;
+    const unsigned p1 = act ? min(m, p0 + C - 1) : 0;
+    Aff f;
+    f.a = 1.0; f.b = 0.0;
+    if (act) {
+        if (!BWD) {
+            for (unsigned p = p0; p <= p1; p++) {
+                const double l = p > 1 ? se[p - 1] : 0.0;
+                f.a = -(l * f.a);
+                f.b = sv[p - 1] - l * f.b;
+            }
+        } else {
+            for (unsigned p = p1; p >= p0; p--) {
+                const double l = p < m ? se[p] : 0.0;
+                f.a = -(l * f.a);
+                f.b = sv[p - 1] - l * f.b;
+            }
+        }
+    }
+    const Aff pre = block_scan_excl(f, wsum, wpre);
+    if (act) {
+        double y = pre.b;   // the value entering the line is 0
+        if (!BWD) {
+            for (unsigned p = p0; p <= p1; p++) {
+                const double l = p > 1 ? se[p - 1] : 0.0;
+                y = sv[p - 1] - l * y;
+                sv[p - 1] = y;
+            }
+        } else {
+            for (unsigned p = p1; p >= p0; p--) {
+                const double l = p < m ? se[p] : 0.0;
+                y = sv[p - 1] - l * y;
+                sv[p - 1] = y;
+            }
+        }
+    }
+}
+
+// the staged solve: sv holds the right-hand side, se the L factor; D read coalesced
+__device__ __forceinline__ void block_ldl_solve(double *sv, const double *se, const double *__restrict__ D,
+                                                unsigned m, unsigned C, Aff *wsum, Aff *wpre)
+{
+    __syncthreads();
+    block_bidiag<false>(sv, se, m, C, wsum, wpre);
+    __syncthreads();
+#pragma unroll 4
+    for (unsigned p = 1 + threadIdx.x; p <= m; p += blockDim.x) sv[p - 1] = sv[p - 1] / __ldg(D + p);
+    __syncthreads();
+    block_bidiag<true>(sv, se, m, C, wsum, wpre);
+    __syncthreads();
+}
+
+// x-lines: one CTA per line j of one colour (rows j-1, j+1 belong to the other colour
+// and are not written in this pass)
+template <bool NINE>
+__global__ void __launch_bounds__(1024)
+k_linex_block(const double *__restrict__ so, const double *__restrict__ qf, double *q,
+              const double *__restrict__ sor, unsigned II, unsigned JJ, unsigned jbeg, unsigned C)
+{
+    extern __shared__ double lsm[];
+    __shared__ Aff wsum[32], wpre[32];
+    const unsigned m = II - 2;
+    double *sv = lsm, *se = lsm + m + 1;
+    const unsigned j = jbeg + 2 * blockIdx.x;  // F-index
+    const size_t pl = (size_t)II * JJ;
+    const double *ks = so + (KS - 1) * pl, *ksw = so + (KSW - 1) * pl, *knw = so + (KNW - 1) * pl;
+    const size_t row = (size_t)(j - 1) * II;
+    const double *Lf = sor + pl + row;
+#pragma unroll 2
+    for (unsigned i = 1 + threadIdx.x; i <= m; i += blockDim.x) {  // 0-based i = position
+        const size_t c = row + i;
+        double r = __ldg(qf + c) + __ldg(ks + c) * q[c - II] + __ldg(ks + c + II) * q[c + II];
+        if (NINE)
+            r = r + __ldg(ksw + c) * q[c - II - 1] + __ldg(knw + c + 1) * q[c - II + 1]
+                + __ldg(knw + c + II) * q[c + II - 1] + __ldg(ksw + c + II + 1) * q[c + II + 1];
+        sv[i - 1] = r;
+        se[i - 1] = __ldg(Lf + i);
+    }
+    block_ldl_solve(sv, se, sor + row, m, C, wsum, wpre);
+    for (unsigned i = 1 + threadIdx.x; i <= m; i += blockDim.x) q[row + i] = sv[i - 1];
+}
+
+// y-lines, step 2: one CTA per line i on the transposed right-hand side B(j,i), in place
+__global__ void __launch_bounds__(1024)
+k_liney_block(double *__restrict__ B, const double *__restrict__ sor, unsigned II, unsigned JJ, unsigned ibeg,
+              unsigned C)
+{
+    extern __shared__ double lsm[];
+    __shared__ Aff wsum[32], wpre[32];
+    const unsigned m = JJ - 2;
+    double *sv = lsm, *se = lsm + m + 1;
+    const unsigned i = ibeg + 2 * blockIdx.x;  // F-index
+    const size_t row = (size_t)(i - 1) * JJ;
+    const double *Lf = sor + (size_t)II * JJ + row;
+#pragma unroll 4
+    for (unsigned p = 1 + threadIdx.x; p <= m; p += blockDim.x) {
+        sv[p - 1] = B[row + p];
+        se[p - 1] = __ldg(Lf + p);
+    }
+    block_ldl_solve(sv, se, sor + row, m, C, wsum, wpre);
+    for (unsigned p = 1 + threadIdx.x; p <= m; p += blockDim.x) B[row + p] = sv[p - 1];
+}
+
+// odd chunk length C and CTA width for a line of m unknowns; false if it does not fit.
+// Shared memory (16 B per unknown) bounds the lines resident per SM; the CTA width is
+// chosen so that those CTAs together keep ~1280 threads (<= 48 registers each) on the SM.
+static bool line_plan(unsigned m, unsigned *C, unsigned *threads, size_t *smem)
+{
+    *smem = 2 * (size_t)(m + 1) * sizeof(double);
+    if (*smem > 200 * 1024) return false;
+    unsigned resident = (unsigned)((220 * 1024) / (*smem + 1024));
+    if (resident < 1) resident = 1;
+    if (resident > 16) resident = 16;
+    unsigned want = 1280 / resident;
+    if (want > 1024) want = 1024;
+    if (want < 64) want = 64;
+    unsigned c = (m + want - 1) / want;
+    if (c < 3 && m > 32) c = 3;
+    c |= 1u;
+    unsigned chunks = (m + c - 1) / c;
+    *C = c;
+    *threads = ((chunks + 31) / 32) * 32;
+    return *threads <= 1024;
+}
+
+template <bool NINE>
+static cudaError_t launch_linex(unsigned C, unsigned nl, unsigned threads, size_t smem, cudaStream_t st, const double *so,
+                                const double *qf, double *q, const double *sor, unsigned II, unsigned JJ, unsigned jbeg)
+{
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k_linex_block<NINE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    k_linex_block<NINE><<<nl, threads, smem, st>>>(so, qf, q, sor, II, JJ, jbeg, C);
+    return cudaSuccess;
+}
+
+static cudaError_t launch_liney(unsigned C, unsigned nl, unsigned threads, size_t smem, cudaStream_t st, double *B,
+                                const double *sor, unsigned II, unsigned JJ, unsigned ibeg)
+{
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k_liney_block, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    k_liney_block<<<nl, threads, smem, st>>>(B, sor, II, JJ, ibeg, C);
+    return cudaSuccess;
+}
+
+// ---- warp-per-line fallback (lines too long for shared memory) ---------------
 // One warp per line.  v holds the right-hand side on entry (positions 1..n-2,
 // 0-based, contiguous) and the solution on exit.  D, L as stored by the setup.
 __device__ __forceinline__ void warp_ldl_solve(double *v, const double *__restrict__ D,
@@ -232,7 +440,13 @@ extern "C" int bmgx2_relax_lines_x(int k, const double *so, const double *qf, do
         unsigned jbeg = fwd ? 3 - a : 2 + a;  // DOWN: odd lines (3,5,..) first (relax_lines_x.f90:83-99)
         if (jbeg > jj - 1) continue;
         unsigned nl = (jj - 1 - jbeg) / 2 + 1;
-        if (k < kf || ifd != 1)
+        const bool nine = (k < kf || ifd != 1);
+        unsigned lg, threads; size_t smem;
+        if (line_plan(ii - 2, &lg, &threads, &smem)) {
+            cudaError_t e = nine ? launch_linex<true>(lg, nl, threads, smem, (cudaStream_t)s, so, qf, q, sor, ii, jj, jbeg)
+                                 : launch_linex<false>(lg, nl, threads, smem, (cudaStream_t)s, so, qf, q, sor, ii, jj, jbeg);
+            if (e != cudaSuccess) return bmgx_set_cuda_error(e, "relax_lines_x/attr");
+        } else if (nine)
             k_relax_lines_x<true><<<cdiv((size_t)nl * 32, 128), 128, 0, (cudaStream_t)s>>>(so, qf, q, sor, ii, jj, jbeg);
         else
             k_relax_lines_x<false><<<cdiv((size_t)nl * 32, 128), 128, 0, (cudaStream_t)s>>>(so, qf, q, sor, ii, jj, jbeg);
@@ -259,7 +473,12 @@ extern "C" int bmgx2_relax_lines_y(int k, const double *so, const double *qf, do
         if (k < kf || ifd != 1) k_lines_y_rhs<true><<<g, 256, 0, st>>>(so, qf, q, b, ii, jj, ibeg);
         else k_lines_y_rhs<false><<<g, 256, 0, st>>>(so, qf, q, b, ii, jj, ibeg);
         BMGX_LAUNCH_CHECK("relax_lines_y/rhs");
-        k_lines_y_solve<<<cdiv((size_t)nl * 32, 128), 128, 0, st>>>(b, sor, ii, jj, ibeg);
+        unsigned lg, threads; size_t smem;
+        if (line_plan(jj - 2, &lg, &threads, &smem)) {
+            cudaError_t e = launch_liney(lg, nl, threads, smem, st, b, sor, ii, jj, ibeg);
+            if (e != cudaSuccess) return bmgx_set_cuda_error(e, "relax_lines_y/attr");
+        } else
+            k_lines_y_solve<<<cdiv((size_t)nl * 32, 128), 128, 0, st>>>(b, sor, ii, jj, ibeg);
         BMGX_LAUNCH_CHECK("relax_lines_y/solve");
         k_lines_y_scatter<<<g, 256, 0, st>>>(b, q, ii, jj, ibeg);
         BMGX_LAUNCH_CHECK("relax_lines_y/scatter");

@@ -1,0 +1,209 @@
+// bmgx3_relax_fused.cu -- 3D 7-point red-black Gauss-Seidel, BOTH colours in ONE pass over
+// memory (out of place: q_in -> q_out).
+//
+// Same arithmetic as k3_relax_colour<true> (bmgx3_stencil.cu; reference
+// src/3d/ftn/BMG3_SymStd_relax_GS.f90:142-177), same term order, -fmad=false => bitwise the
+// oracle's result.  Points of one colour are independent, so the schedule is free:
+//
+//   * a CTA owns a tile of R7_OX x R7_OY columns (plus a halo of 2 on each side whose values
+//     are recomputed, never stored) and a band of planes, and walks up the planes;
+//   * the iterate lives in a shared-memory ring of 5 planes; per step p the first colour is
+//     relaxed on plane p (it needs only old values of planes p-1, p, p+1), then the second
+//     colour on plane p-1 (whose six neighbours are now final), then plane p-1 is stored;
+//   * a thread owns two (column pair, row) items.  In plane p one column of a pair has the
+//     first colour, the other the second, and the roles swap from plane to plane, so the
+//     thread loads the coefficients of BOTH columns of plane p together (full sectors),
+//     uses one column's set at once and carries the other column's set in registers to the
+//     next step, where that column gets its second-colour update;
+//   * tiles overlap by the halo and bands by two planes, so CTAs are independent: no
+//     inter-CTA ordering, no atomics.
+//
+// Algorithmic traffic 56 B/point (PW, PS, B, SOR, QF, Q read + Q write); the per-colour
+// kernels move 2x that (every array is pulled once per colour, half of each sector unused).
+#include "bmgx3_common.cuh"
+
+#define R7_SX 64
+#define R7_SY 16
+#define R7_NT 256
+#define R7_OX (R7_SX - 4)
+#define R7_OY (R7_SY - 4)
+#define R7_RING 5
+
+namespace {
+
+struct G7 {
+    const double *pw, *ps, *kb, *sor, *qf;
+    int II, JJ, KK;
+};
+
+__device__ __forceinline__ double ld7(const double *__restrict__ a, int i, int j, int k, int II, int JJ, int KK)
+{
+    return (i >= 1 && i <= II && j >= 1 && j <= JJ && k >= 1 && k <= KK)
+               ? __ldg(a + ((size_t)(k - 1) * JJ + (j - 1)) * II + (i - 1)) : 0.0;
+}
+
+// coefficients of one column of one plane that its update needs (the coupling to the plane
+// above is stored in that plane and joins later)
+struct Col7 { double pw, pwe, ps, psn, kbd, sor, qf; };
+
+// FIRST_ODD: the first colour is (i+j+k) odd (DOWN sweep); else even (UP)
+template <bool FIRST_ODD>
+__global__ void __launch_bounds__(R7_NT, 2)
+k3_relax7_fused(G7 g, const double *__restrict__ qin, double *__restrict__ qout, int band_h)
+{
+    __shared__ double ring[R7_RING][R7_SY][R7_SX];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int II = g.II, JJ = g.JJ, KK = g.KK;
+    const int gi0 = 1 + (int)blockIdx.x * R7_OX - 2, gj0 = 1 + (int)blockIdx.y * R7_OY - 2;
+    const int kb = 1 + (int)blockIdx.z * band_h, ke = min(KK, kb + band_h - 1);
+    constexpr int pF = FIRST_ODD ? 1 : 0;
+
+    auto load_plane = [&](int p, double (&v)[4]) {
+#pragma unroll
+        for (int n = 0; n < 4; n++) {
+            const int e = t + n * R7_NT, ly = e >> 6, lx = e & 63;
+            v[n] = ld7(qin, gi0 + lx, gj0 + ly, p, II, JJ, KK);
+        }
+    };
+    auto put_plane = [&](int slot, const double (&v)[4]) {
+#pragma unroll
+        for (int n = 0; n < 4; n++) {
+            const int e = t + n * R7_NT;
+            ring[slot][e >> 6][e & 63] = v[n];
+        }
+    };
+
+    // ring slot of plane p: (p - (kb - 2)) mod 5, tracked incrementally
+    int s_m2 = 0, s_m1 = 1, s_0 = 2, s_p1 = 3, s_p2 = 4;   // slots of planes p-2, p-1, p, p+1, p+2 for p = kb-1... see below
+    {
+        // iteration p = kb-1 needs planes kb-2, kb-1, kb; (kb-3 is never read)
+        double v[4];
+        load_plane(kb - 2, v); put_plane(s_m1, v);
+        load_plane(kb - 1, v); put_plane(s_0, v);
+        load_plane(kb, v);     put_plane(s_p1, v);
+    }
+    // items: rows ly = w and w + 8, column pair (2 lane, 2 lane + 1)
+    const int c0 = gi0 + 2 * lane;
+    Col7 sv[2];          // second-colour column set of plane p-1
+    double kbc[2][2];    // KB(c0,p), KB(c1,p)
+#pragma unroll
+    for (int n = 0; n < 2; n++) {
+        const int gj = gj0 + w + 8 * n;
+        sv[n] = Col7{0, 0, 0, 0, 0, 0, 0};
+        kbc[n][0] = ld7(g.kb, c0, gj, kb - 1, II, JJ, KK);
+        kbc[n][1] = ld7(g.kb, c0 + 1, gj, kb - 1, II, JJ, KK);
+    }
+    __syncthreads();
+
+    for (int p = kb - 1; p <= ke + 1; p++) {
+        // ---- loads of this step: coefficients of plane p (both columns), KB of plane p+1, iterate plane p+2
+        double pw0[2], pw1[2], pw2[2], ps0[2], ps1[2], pn0[2], pn1[2], kn0[2], kn1[2], so0[2], so1[2], qf0[2], qf1[2];
+#pragma unroll
+        for (int n = 0; n < 2; n++) {
+            const int gj = gj0 + w + 8 * n;
+            pw0[n] = ld7(g.pw, c0, gj, p, II, JJ, KK);
+            pw1[n] = ld7(g.pw, c0 + 1, gj, p, II, JJ, KK);
+            pw2[n] = ld7(g.pw, c0 + 2, gj, p, II, JJ, KK);
+            ps0[n] = ld7(g.ps, c0, gj, p, II, JJ, KK);
+            ps1[n] = ld7(g.ps, c0 + 1, gj, p, II, JJ, KK);
+            pn0[n] = ld7(g.ps, c0, gj + 1, p, II, JJ, KK);
+            pn1[n] = ld7(g.ps, c0 + 1, gj + 1, p, II, JJ, KK);
+            kn0[n] = ld7(g.kb, c0, gj, p + 1, II, JJ, KK);
+            kn1[n] = ld7(g.kb, c0 + 1, gj, p + 1, II, JJ, KK);
+            so0[n] = ld7(g.sor, c0, gj, p, II, JJ, KK);
+            so1[n] = ld7(g.sor, c0 + 1, gj, p, II, JJ, KK);
+            qf0[n] = ld7(g.qf, c0, gj, p, II, JJ, KK);
+            qf1[n] = ld7(g.qf, c0 + 1, gj, p, II, JJ, KK);
+        }
+        double nxt[4];
+        load_plane(p + 2, nxt);
+
+        const bool pin = p >= 2 && p <= KK - 1;
+        bool a0[2];
+        // ---- first colour on plane p
+#pragma unroll
+        for (int n = 0; n < 2; n++) {
+            const int ly = w + 8 * n, gj = gj0 + ly;
+            a0[n] = (((c0 + gj + p) & 1) == pF);
+            const int lx = 2 * lane + (a0[n] ? 0 : 1), ca = c0 + (a0[n] ? 0 : 1);
+            if (pin && gj >= 2 && gj <= JJ - 1 && ca >= 2 && ca <= II - 1 && lx >= 1 && lx <= R7_SX - 2 && ly >= 1
+                && ly <= R7_SY - 2) {
+                const double cw = a0[n] ? pw0[n] : pw1[n], ce = a0[n] ? pw1[n] : pw2[n];
+                const double cs = a0[n] ? ps0[n] : ps1[n], cn = a0[n] ? pn0[n] : pn1[n];
+                const double cd = a0[n] ? kbc[n][0] : kbc[n][1], cu = a0[n] ? kn0[n] : kn1[n];
+                const double f = a0[n] ? qf0[n] : qf1[n], r = a0[n] ? so0[n] : so1[n];
+                const double v = f + cw * ring[s_0][ly][lx - 1] + cn * ring[s_0][ly + 1][lx] + ce * ring[s_0][ly][lx + 1]
+                                 + cs * ring[s_0][ly - 1][lx] + cd * ring[s_m1][ly][lx] + cu * ring[s_p1][ly][lx];
+                ring[s_0][ly][lx] = v * r;
+            }
+        }
+        __syncthreads();
+        // ---- second colour on plane p-1 (same columns), coefficients carried from the previous step
+        const bool bin = p - 1 >= max(2, kb) && p - 1 <= min(KK - 1, ke);
+#pragma unroll
+        for (int n = 0; n < 2; n++) {
+            const int ly = w + 8 * n, gj = gj0 + ly;
+            const int lx = 2 * lane + (a0[n] ? 0 : 1), ca = c0 + (a0[n] ? 0 : 1);
+            if (bin && gj >= 2 && gj <= JJ - 1 && ca >= 2 && ca <= II - 1 && lx >= 2 && lx <= R7_SX - 3 && ly >= 2
+                && ly <= R7_SY - 3) {
+                const double cu = a0[n] ? kbc[n][0] : kbc[n][1];
+                const double v = sv[n].qf + sv[n].pw * ring[s_m1][ly][lx - 1] + sv[n].psn * ring[s_m1][ly + 1][lx]
+                                 + sv[n].pwe * ring[s_m1][ly][lx + 1] + sv[n].ps * ring[s_m1][ly - 1][lx]
+                                 + sv[n].kbd * ring[s_m2][ly][lx] + cu * ring[s_0][ly][lx];
+                ring[s_m1][ly][lx] = v * sv[n].sor;
+            }
+            // the other column of plane p gets its second-colour update in the next step
+            if (a0[n]) sv[n] = Col7{pw1[n], pw2[n], ps1[n], pn1[n], kbc[n][1], so1[n], qf1[n]};
+            else sv[n] = Col7{pw0[n], pw1[n], ps0[n], pn0[n], kbc[n][0], so0[n], qf0[n]};
+            kbc[n][0] = kn0[n];
+            kbc[n][1] = kn1[n];
+        }
+        put_plane(s_p2, nxt);   // slot of plane p-3: last read by the previous step
+        __syncthreads();
+        // ---- plane p-1 is final: store the tile's own columns (ghost ring included as loaded)
+        if (p - 1 >= kb && p - 1 <= ke) {
+#pragma unroll
+            for (int n = 0; n < 4; n++) {
+                const int e = t + n * R7_NT, ly = e >> 6, lx = e & 63;
+                const int gi = gi0 + lx, gj = gj0 + ly;
+                if (lx >= 2 && lx <= R7_SX - 3 && ly >= 2 && ly <= R7_SY - 3 && gi >= 1 && gi <= II && gj >= 1 && gj <= JJ)
+                    qout[((size_t)(p - 2) * JJ + (gj - 1)) * II + (gi - 1)] = ring[s_m1][ly][lx];
+            }
+        }
+        // rotate: plane p+1 becomes plane p
+        const int freed = s_m2;
+        s_m2 = s_m1; s_m1 = s_0; s_0 = s_p1; s_p1 = s_p2; s_p2 = freed;
+    }
+}
+
+}  // namespace
+
+// Out-of-place form of bmgx3_relax_GS for the 7-point operator (ifd == 1): reads q_in, writes
+// the relaxed iterate (interior + copied ghost layer) to q_out.
+extern "C" int bmgx3_relax_GS_oop(int kg, const double *so, const double *qf, const double *q_in, double *q_out,
+                                  const double *sor, bmgx_len ii, bmgx_len jj, bmgx_len kk, int ifd, int nstncl,
+                                  int nsorv, int irelax_sym, int updown, int jpn, bmgx_stream_t s)
+{
+    (void)kg; (void)nstncl; (void)nsorv;
+    if (q_in == q_out) return bmgx_set_error(BMGX_ERR_ARG, "relax_GS3_oop: q_in aliases q_out");
+    if (ifd != 1) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_GS3_oop: 7-point operators only");
+    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_GS3_oop: periodic BCs not supported");
+    if (ii < 1 || jj < 1 || kk < 1) return BMGX_OK;
+    const bool up = (updown == BMGX_UP) || (irelax_sym == BMGX_RELAX_NONSYM);
+    const size_t pl = (size_t)ii * jj * kk;
+    G7 g;
+    g.pw = so + (KPW - 1) * pl; g.ps = so + (KPS - 1) * pl; g.kb = so + (KB - 1) * pl;
+    g.sor = sor + (MSOR - 1) * pl; g.qf = qf; g.II = (int)ii; g.JJ = (int)jj; g.KK = (int)kk;
+    const unsigned ntx = cdiv(ii, R7_OX), nty = cdiv(jj, R7_OY);
+    // about four resident waves (148 SMs x 2 CTAs) of equal bands
+    unsigned nb = (4 * 296 + ntx * nty - 1) / (ntx * nty);
+    if (nb < 1) nb = 1;
+    unsigned band_h = (kk + nb - 1) / nb;
+    if (band_h < 8) band_h = 8;
+    dim3 grid(ntx, nty, cdiv(kk, band_h));
+    // DOWN: pts = 1 first, i.e. (i+j+k) odd (relax_GS.f90:144-154); UP: even first
+    if (!up) k3_relax7_fused<true><<<grid, R7_NT, 0, (cudaStream_t)s>>>(g, q_in, q_out, (int)band_h);
+    else k3_relax7_fused<false><<<grid, R7_NT, 0, (cudaStream_t)s>>>(g, q_in, q_out, (int)band_h);
+    BMGX_LAUNCH_CHECK("relax_GS3_oop");
+    return BMGX_OK;
+}

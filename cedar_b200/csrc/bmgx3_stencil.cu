@@ -16,7 +16,7 @@ struct G3 {
 // qf + sum over the neighbours of so*q, in the order of relax_GS.f90:104-131 /
 // residual.f90:74-100 (27-point) or 162-168 / 108-114 (7-point)
 template <bool SEVEN>
-__device__ __forceinline__ double nbr_sum(const G3 &g, const double *__restrict__ q, double qf, size_t c)
+__device__ __forceinline__ double nbr_sum(const G3 &g, const double *q, double qf, size_t c)
 {
     const size_t II = g.II, PJ = (size_t)g.II * g.JJ, pl = g.pl;
     const double *so = g.so;
@@ -77,6 +77,31 @@ k3_relax_colour(G3 g, const double *__restrict__ qf, double *q, const double *__
     q[c] = nbr_sum<SEVEN>(g, q, qf[c], c) * sor[(size_t)(MSOR - 1) * g.pl + c];
 }
 
+// 27-point: the two colours of one (j,k) row parity -- they differ only in the parity of
+// i and are consecutive in the sweep order -- in ONE launch.  A CTA owns whole rows, so the
+// second colour sees the first colour's new values of its own row after a barrier; all other
+// neighbours (rows j+-1, planes k+-1) belong to colours that this launch does not touch.
+// Both colours of a row pull the same sectors of every coefficient array (the second pass
+// from L1/L2), so each launch moves half the DRAM bytes of two single-colour launches.
+__global__ void __launch_bounds__(1024)
+k3_relax_xpair(G3 g, const double *__restrict__ qf, double *q, const double *__restrict__ sor, int ifirst, int j0,
+               int k0)
+{
+    const int j = j0 + 2 * blockIdx.y, k = k0 + 2 * blockIdx.z;
+    const size_t row = ((size_t)(k - 1) * g.JJ + (j - 1)) * g.II;
+    const double *rs = sor + (size_t)(MSOR - 1) * g.pl;
+    const int i1 = ifirst + 2 * threadIdx.x, i2 = (ifirst == 2 ? 3 : 2) + 2 * threadIdx.x;
+    if (i1 <= g.II - 1) {
+        const size_t c = row + (i1 - 1);
+        q[c] = nbr_sum<false>(g, q, qf[c], c) * rs[c];
+    }
+    __syncthreads();
+    if (i2 <= g.II - 1) {
+        const size_t c = row + (i2 - 1);
+        q[c] = nbr_sum<false>(g, q, qf[c], c) * rs[c];
+    }
+}
+
 }  // namespace
 
 extern "C" int bmgx3_SETUP_recip(const double *so, double *sor, bmgx_len nx, bmgx_len ny, bmgx_len nz, int nstncl,
@@ -116,7 +141,21 @@ extern "C" int bmgx3_relax_GS(int kg, const double *so, const double *qf, double
     const bool up = (updown == BMGX_UP) || (irelax_sym == BMGX_RELAX_NONSYM);
     const int I1 = ii - 1, J1 = jj - 1, K1 = kk - 1;
     if (ifd != 1) {
-        // 8 colours; UP runs pts = 1..8, DOWN 8..1 (relax_GS.f90:82-96)
+        // 8 colours; UP runs pts = 1..8, DOWN 8..1 (relax_GS.f90:82-96).  Colours 2n-1 and 2n share
+        // (j0,k0) and are adjacent in both orders: one launch per pair when a row fits one CTA
+        const int npair = (I1 - 2) / 2 + 1;   // points of the larger x colour per row
+        if (npair <= 1024) {
+            for (int n = 0; n < 4; n++) {
+                const int pr = up ? n : 3 - n;                    // pair index: pts = 2 pr + 1, 2 pr + 2
+                const int j0 = 2 + pr % 2, k0 = 2 + pr / 2;
+                if (j0 > J1 || k0 > K1) continue;
+                const int ifirst = up ? 2 : 3;                    // UP: pts odd (i0 = 2) first; DOWN: pts even (i0 = 3)
+                dim3 grid(1, (J1 - j0) / 2 + 1, (K1 - k0) / 2 + 1);
+                k3_relax_xpair<<<grid, ((npair + 31) / 32) * 32, 0, st>>>(g, qf, q, sor, ifirst, j0, k0);
+                BMGX_LAUNCH_CHECK("relax_GS3/27 pair");
+            }
+            return BMGX_OK;
+        }
         for (int n = 0; n < 8; n++) {
             int pts = up ? 1 + n : 8 - n;
             int i0 = 2 + (pts - 1) % 2, j0 = 2 + ((pts - 1) / 2) % 2, k0 = 2 + ((pts - 1) / 4) % 2;

@@ -213,6 +213,15 @@ int bmgx3_relax_GS(int kg, const bmgx_real *so, const bmgx_real *qf, bmgx_real *
                    const bmgx_real *sor, bmgx_len ii, bmgx_len jj, bmgx_len kk, int ifd, int nstncl,
                    int nsorv, int irelax_sym, int updown, int jpn, bmgx_stream_t s);
 
+/* Out-of-place form of the same sweep for the 7-point operator (ifd == 1; B200-native fast
+ * path): reads q_in, writes the relaxed iterate (interior + copied ghost layer) to q_out; both
+ * colours in ONE pass over memory.  q_in and q_out must not alias.  27-point operators
+ * (ifd != 1) return BMGX_ERR_UNSUPPORTED: use bmgx3_relax_GS. */
+int bmgx3_relax_GS_oop(int kg, const bmgx_real *so, const bmgx_real *qf, const bmgx_real *q_in,
+                       bmgx_real *q_out, const bmgx_real *sor, bmgx_len ii, bmgx_len jj, bmgx_len kk,
+                       int ifd, int nstncl, int nsorv, int irelax_sym, int updown, int jpn,
+                       bmgx_stream_t s);
+
 /* BMG3_SymStd_residual(kg, nog, ifd, q, qf, so, res, ii, jj, kk, nstncl),
  * include/cedar/3d/residual.h:9-12 */
 int bmgx3_residual(int kg, int nog, int ifd, const bmgx_real *q, const bmgx_real *qf,

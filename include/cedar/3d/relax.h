@@ -4,6 +4,8 @@
 #ifndef CEDAR_3D_RELAX_H
 #define CEDAR_3D_RELAX_H
 
+#include <map>
+#include <tuple>
 #include <type_traits>
 
 #include <cedar/3d/types.h>
@@ -34,10 +36,24 @@ public:
 		int updown = cdir == cycle::Dir::UP ? BMGX_UP : BMGX_DOWN;
 		int ibc;
 		bmgx_get_bc(params->per_mask(), &ibc);
+		if (ifd == 1) {
+			// 7-point: both colours in one pass over memory, out of place into a scratch array of
+			// the same shape, then exchange the two device buffers (as cdr2::rbgs does)
+			auto &tmp = scratch[std::make_tuple(x.len(0), x.len(1), x.len(2))];
+			if (tmp.size() != x.size()) tmp = grid_func(x.shape(0), x.shape(1), x.shape(2));
+			const real_t *xin = x.cdev();
+			gpu::check(bmgx3_relax_GS_oop(1, so.cdev(), b.cdev(), xin, tmp.dev(), sor.cdev(), so.len(0), so.len(1),
+			                              so.len(2), ifd, stencil_ndirs<sten>::value, 2, BMGX_RELAX_SYM, updown, ibc,
+			                              gpu::stream()), "relax_GS3_oop");
+			x.swap_device(tmp);
+			return;
+		}
 		gpu::check(bmgx3_relax_GS(1, so.cdev(), b.cdev(), x.dev(), sor.cdev(), so.len(0), so.len(1), so.len(2), ifd,
 		                          stencil_ndirs<sten>::value, 2, BMGX_RELAX_SYM, updown, ibc, gpu::stream()),
 		           "relax_GS3");
 	}
+private:
+	std::map<std::tuple<len_t, len_t, len_t>, grid_func> scratch;
 };
 
 }}

@@ -44,11 +44,18 @@ def test_residual_relax(cuda, abi, nx, ny, nz, full):
     d_sor = cuda.zeros(sor.shape, dtype=cuda.float64, device="cuda")
     abi.check(abi.lib.bmgx3_SETUP_recip(ptr(d_so), ptr(d_sor), II, JJ, KK, nst, 2, None))
     assert_bitwise(host(d_sor), sor, "SETUP_recip3")
+    d_q2 = cuda.full_like(d_q, 7.0)
     for updown in (0, 1, 0):
         assert L.orc3_relax_gs(1, P(so), P(b), P(q), P(sor), II, JJ, KK, ifd, nst, 2, 1, updown, 0) == 0
+        if not full:
+            # single-pass out-of-place form first (reads d_q), then the in-place one
+            abi.check(abi.lib.bmgx3_relax_GS_oop(1, ptr(d_so), ptr(d_b), ptr(d_q), ptr(d_q2), ptr(d_sor), II, JJ, KK, ifd,
+                                                 nst, 2, 1, updown, 0, None))
         abi.check(abi.lib.bmgx3_relax_GS(1, ptr(d_so), ptr(d_b), ptr(d_q), ptr(d_sor), II, JJ, KK, ifd, nst, 2, 1,
                                          updown, 0, None))
         assert_bitwise(host(d_q), q, f"relax_GS3 updown={updown}")
+        if not full:
+            assert_bitwise(host(d_q2), q, f"relax_GS3_oop updown={updown}")
 
 
 @pytest.mark.parametrize("full", [False, True])

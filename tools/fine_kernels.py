@@ -139,6 +139,11 @@ def table3(n, reps, warm, out):
         K = []
         K.append((f"relax_GS {tag}", 136 if full else 56,
                   lambda i: L.bmgx3_relax_GS(1, P(so), P(b), P(q), P(sor), II, II, II, ifd, nst, 2, 1, i & 1, 0, None)))
+        if not full:
+            q2 = rnd(II, II, II)
+            bufs = [q, q2]
+            K.append((f"relax_GS_oop {tag} (fused sweep)", 56,
+                      lambda i: L.bmgx3_relax_GS_oop(1, P(so), P(b), P(bufs[i & 1]), P(bufs[(i + 1) & 1]), P(sor), II, II, II, ifd, nst, 2, 1, i & 1, 0, None)))
         K.append((f"residual {tag}", 136 if full else 56,
                   lambda i: L.bmgx3_residual(1, 1, ifd, P(q), P(b), P(so), P(r), II, II, II, nst, None)))
         if full:
