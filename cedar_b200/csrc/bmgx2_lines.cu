@@ -198,11 +198,24 @@ __device__ __forceinline__ void block_ldl_solve(double *sv, const double *se, co
     __syncthreads();
     block_bidiag<false>(sv, se, m, C, wsum, wpre);
     __syncthreads();
-#pragma unroll 4
-    for (unsigned p = 1 + threadIdx.x; p <= m; p += blockDim.x) sv[p - 1] = sv[p - 1] / __ldg(D + p);
+    for (unsigned p0 = 1 + threadIdx.x; p0 <= m; p0 += 4 * blockDim.x) {
+        double d[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) { const unsigned p = p0 + u * blockDim.x; d[u] = __ldg(D + (p <= m ? p : 1)); }
+#pragma unroll
+        for (int u = 0; u < 4; u++) { const unsigned p = p0 + u * blockDim.x; if (p <= m) sv[p - 1] = sv[p - 1] / d[u]; }
+    }
     __syncthreads();
     block_bidiag<true>(sv, se, m, C, wsum, wpre);
     __syncthreads();
+}
+
+// pull n doubles starting at base into L2 (one request per 32-byte sector, no destination
+// register, never waited on): the demand loads that follow are scheduled by ptxas in small
+// groups, each group paying one full memory latency -- after the prefetch that is an L2 hit
+__device__ __forceinline__ void l2_prefetch_row(const double *base, unsigned n)
+{
+    for (unsigned o = 4 * threadIdx.x; o < n; o += 4 * blockDim.x) asm volatile("prefetch.global.L2 [%0];" ::"l"(base + o));
 }
 
 // x-lines: one CTA per line j of one colour (rows j-1, j+1 belong to the other colour
@@ -221,15 +234,38 @@ k_linex_block(const double *__restrict__ so, const double *__restrict__ qf, doub
     const double *ks = so + (KS - 1) * pl, *ksw = so + (KSW - 1) * pl, *knw = so + (KNW - 1) * pl;
     const size_t row = (size_t)(j - 1) * II;
     const double *Lf = sor + pl + row;
-#pragma unroll 2
-    for (unsigned i = 1 + threadIdx.x; i <= m; i += blockDim.x) {  // 0-based i = position
-        const size_t c = row + i;
-        double r = __ldg(qf + c) + __ldg(ks + c) * q[c - II] + __ldg(ks + c + II) * q[c + II];
-        if (NINE)
-            r = r + __ldg(ksw + c) * q[c - II - 1] + __ldg(knw + c + 1) * q[c - II + 1]
-                + __ldg(knw + c + II) * q[c + II - 1] + __ldg(ksw + c + II + 1) * q[c + II + 1];
-        sv[i - 1] = r;
-        se[i - 1] = __ldg(Lf + i);
+    l2_prefetch_row(qf + row, II); l2_prefetch_row(q + row - II, II); l2_prefetch_row(q + row + II, II);
+    l2_prefetch_row(ks + row, 2 * II);
+    if (NINE) { l2_prefetch_row(ksw + row, 2 * II); l2_prefetch_row(knw + row, 2 * II); }
+    l2_prefetch_row(Lf, II); l2_prefetch_row(sor + row, II);
+    // rows j-1 and j+1 are not written by this launch: every operand is a read-only global load,
+    // issued for two positions at once before any of them is consumed (the loop is latency bound)
+    const double *qs = q + row - II, *qn = q + row + II;
+    for (unsigned i0 = 1 + threadIdx.x; i0 <= m; i0 += 2 * blockDim.x) {  // 0-based i = position
+        double r[2], l[2];
+        double v[2][NINE ? 13 : 5];
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+            const unsigned i = i0 + u * blockDim.x;
+            const bool ok = i <= m;
+            const size_t c = row + (ok ? i : 1);
+            const unsigned ii = ok ? i : 1;
+            v[u][0] = __ldg(qf + c); v[u][1] = __ldg(ks + c); v[u][2] = __ldg(qs + ii);
+            v[u][3] = __ldg(ks + c + II); v[u][4] = __ldg(qn + ii);
+            if (NINE) {
+                v[u][5] = __ldg(ksw + c); v[u][6] = __ldg(qs + ii - 1); v[u][7] = __ldg(knw + c + 1);
+                v[u][8] = __ldg(qs + ii + 1); v[u][9] = __ldg(knw + c + II); v[u][10] = __ldg(qn + ii - 1);
+                v[u][11] = __ldg(ksw + c + II + 1); v[u][12] = __ldg(qn + ii + 1);
+            }
+            l[u] = __ldg(Lf + ii);
+        }
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+            r[u] = v[u][0] + v[u][1] * v[u][2] + v[u][3] * v[u][4];
+            if (NINE) r[u] = r[u] + v[u][5] * v[u][6] + v[u][7] * v[u][8] + v[u][9] * v[u][10] + v[u][11] * v[u][12];
+            const unsigned i = i0 + u * blockDim.x;
+            if (i <= m) { sv[i - 1] = r[u]; se[i - 1] = l[u]; }
+        }
     }
     block_ldl_solve(sv, se, sor + row, m, C, wsum, wpre);
     for (unsigned i = 1 + threadIdx.x; i <= m; i += blockDim.x) q[row + i] = sv[i - 1];
@@ -247,10 +283,20 @@ k_liney_block(double *__restrict__ B, const double *__restrict__ sor, unsigned I
     const unsigned i = ibeg + 2 * blockIdx.x;  // F-index
     const size_t row = (size_t)(i - 1) * JJ;
     const double *Lf = sor + (size_t)II * JJ + row;
-#pragma unroll 4
-    for (unsigned p = 1 + threadIdx.x; p <= m; p += blockDim.x) {
-        sv[p - 1] = B[row + p];
-        se[p - 1] = __ldg(Lf + p);
+    l2_prefetch_row(B + row, JJ); l2_prefetch_row(Lf, JJ); l2_prefetch_row(sor + row, JJ);
+    for (unsigned p0 = 1 + threadIdx.x; p0 <= m; p0 += 4 * blockDim.x) {
+        double bv[4], lv[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const unsigned p = p0 + u * blockDim.x, pp = p <= m ? p : 1;
+            bv[u] = __ldcg(B + row + pp);
+            lv[u] = __ldg(Lf + pp);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const unsigned p = p0 + u * blockDim.x;
+            if (p <= m) { sv[p - 1] = bv[u]; se[p - 1] = lv[u]; }
+        }
     }
     block_ldl_solve(sv, se, sor + row, m, C, wsum, wpre);
     for (unsigned p = 1 + threadIdx.x; p <= m; p += blockDim.x) B[row + p] = sv[p - 1];

@@ -188,7 +188,7 @@ __device__ __forceinline__ double ptap_entry(const Ci3 &W, const Slab &S, int ic
 }
 
 // storage points (2..IIC-1, 2..JJC-1, planes ka..kb)
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 3)
 k3_ptap(Ci3 W, Slab S, double *__restrict__ soc, int ka)
 {
     const int ic = blockIdx.x * blockDim.x + threadIdx.x + 2, jc = blockIdx.y * blockDim.y + threadIdx.y + 2,

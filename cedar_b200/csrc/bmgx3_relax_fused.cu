@@ -36,12 +36,6 @@ struct G7 {
     int II, JJ, KK;
 };
 
-__device__ __forceinline__ double ld7(const double *__restrict__ a, int i, int j, int k, int II, int JJ, int KK)
-{
-    return (i >= 1 && i <= II && j >= 1 && j <= JJ && k >= 1 && k <= KK)
-               ? __ldg(a + ((size_t)(k - 1) * JJ + (j - 1)) * II + (i - 1)) : 0.0;
-}
-
 // coefficients of one column of one plane that its update needs (the coupling to the plane
 // above is stored in that plane and joins later)
 struct Col7 { double pw, pwe, ps, psn, kbd, sor, qf; };
@@ -58,12 +52,22 @@ k3_relax7_fused(G7 g, const double *__restrict__ qin, double *__restrict__ qout,
     const int kb = 1 + (int)blockIdx.z * band_h, ke = min(KK, kb + band_h - 1);
     constexpr int pF = FIRST_ODD ? 1 : 0;
 
-    auto load_plane = [&](int p, double (&v)[4]) {
+    // addressing is hoisted out of the plane loop: per thread four iterate elements and two
+    // (column pair, row) items, each an in-plane offset plus validity masks; a plane adds PJ
+    const long long PJ = (long long)II * JJ;
+    long long eoff[4];
+    bool eok[4];
 #pragma unroll
-        for (int n = 0; n < 4; n++) {
-            const int e = t + n * R7_NT, ly = e >> 6, lx = e & 63;
-            v[n] = ld7(qin, gi0 + lx, gj0 + ly, p, II, JJ, KK);
-        }
+    for (int n = 0; n < 4; n++) {
+        const int e = t + n * R7_NT, gi = gi0 + (e & 63), gj = gj0 + (e >> 6);
+        eok[n] = gi >= 1 && gi <= II && gj >= 1 && gj <= JJ;
+        eoff[n] = eok[n] ? (long long)(gj - 1) * II + (gi - 1) : 0;
+    }
+    auto load_plane = [&](int p, double (&v)[4]) {
+        const bool pok = p >= 1 && p <= KK;
+        const double *src = qin + (long long)(p - 1) * PJ;
+#pragma unroll
+        for (int n = 0; n < 4; n++) v[n] = (pok && eok[n]) ? __ldg(src + eoff[n]) : 0.0;
     };
     auto put_plane = [&](int slot, const double (&v)[4]) {
 #pragma unroll
@@ -73,10 +77,10 @@ k3_relax7_fused(G7 g, const double *__restrict__ qin, double *__restrict__ qout,
         }
     };
 
-    // ring slot of plane p: (p - (kb - 2)) mod 5, tracked incrementally
-    int s_m2 = 0, s_m1 = 1, s_0 = 2, s_p1 = 3, s_p2 = 4;   // slots of planes p-2, p-1, p, p+1, p+2 for p = kb-1... see below
+    // ring slots of planes p-2, p-1, p, p+1, p+2, rotated once per step
+    int s_m2 = 0, s_m1 = 1, s_0 = 2, s_p1 = 3, s_p2 = 4;
     {
-        // iteration p = kb-1 needs planes kb-2, kb-1, kb; (kb-3 is never read)
+        // step p = kb-1 needs planes kb-2, kb-1, kb (kb-3 is never read)
         double v[4];
         load_plane(kb - 2, v); put_plane(s_m1, v);
         load_plane(kb - 1, v); put_plane(s_0, v);
@@ -84,39 +88,65 @@ k3_relax7_fused(G7 g, const double *__restrict__ qin, double *__restrict__ qout,
     }
     // items: rows ly = w and w + 8, column pair (2 lane, 2 lane + 1)
     const int c0 = gi0 + 2 * lane;
+    const bool k0 = c0 >= 1 && c0 <= II, k1 = c0 + 1 >= 1 && c0 + 1 <= II, k2 = c0 + 2 >= 1 && c0 + 2 <= II;
+    long long ioff[2];
+    bool rok[2], rnok[2];
     Col7 sv[2];          // second-colour column set of plane p-1
     double kbc[2][2];    // KB(c0,p), KB(c1,p)
 #pragma unroll
     for (int n = 0; n < 2; n++) {
         const int gj = gj0 + w + 8 * n;
+        rok[n] = gj >= 1 && gj <= JJ;
+        rnok[n] = gj + 1 >= 1 && gj + 1 <= JJ;
+        ioff[n] = (long long)(gj - 1) * II + (c0 - 1);
         sv[n] = Col7{0, 0, 0, 0, 0, 0, 0};
-        kbc[n][0] = ld7(g.kb, c0, gj, kb - 1, II, JJ, KK);
-        kbc[n][1] = ld7(g.kb, c0 + 1, gj, kb - 1, II, JJ, KK);
+        const bool pok = kb - 1 >= 1 && kb - 1 <= KK;
+        const double *kp = g.kb + (long long)(kb - 2) * PJ + ioff[n];
+        kbc[n][0] = (pok && rok[n] && k0) ? __ldg(kp) : 0.0;
+        kbc[n][1] = (pok && rok[n] && k1) ? __ldg(kp + 1) : 0.0;
     }
     __syncthreads();
 
     for (int p = kb - 1; p <= ke + 1; p++) {
         // ---- loads of this step: coefficients of plane p (both columns), KB of plane p+1, iterate plane p+2
         double pw0[2], pw1[2], pw2[2], ps0[2], ps1[2], pn0[2], pn1[2], kn0[2], kn1[2], so0[2], so1[2], qf0[2], qf1[2];
+        const bool pok = p >= 1 && p <= KK, pnok = p + 1 >= 1 && p + 1 <= KK;
+        const long long po = (long long)(p - 1) * PJ;
 #pragma unroll
         for (int n = 0; n < 2; n++) {
-            const int gj = gj0 + w + 8 * n;
-            pw0[n] = ld7(g.pw, c0, gj, p, II, JJ, KK);
-            pw1[n] = ld7(g.pw, c0 + 1, gj, p, II, JJ, KK);
-            pw2[n] = ld7(g.pw, c0 + 2, gj, p, II, JJ, KK);
-            ps0[n] = ld7(g.ps, c0, gj, p, II, JJ, KK);
-            ps1[n] = ld7(g.ps, c0 + 1, gj, p, II, JJ, KK);
-            pn0[n] = ld7(g.ps, c0, gj + 1, p, II, JJ, KK);
-            pn1[n] = ld7(g.ps, c0 + 1, gj + 1, p, II, JJ, KK);
-            kn0[n] = ld7(g.kb, c0, gj, p + 1, II, JJ, KK);
-            kn1[n] = ld7(g.kb, c0 + 1, gj, p + 1, II, JJ, KK);
-            so0[n] = ld7(g.sor, c0, gj, p, II, JJ, KK);
-            so1[n] = ld7(g.sor, c0 + 1, gj, p, II, JJ, KK);
-            qf0[n] = ld7(g.qf, c0, gj, p, II, JJ, KK);
-            qf1[n] = ld7(g.qf, c0 + 1, gj, p, II, JJ, KK);
+            const long long o = po + ioff[n];
+            const bool r = pok && rok[n], rn = pok && rnok[n], ru = pnok && rok[n];
+            pw0[n] = (r && k0) ? __ldg(g.pw + o) : 0.0;
+            pw1[n] = (r && k1) ? __ldg(g.pw + o + 1) : 0.0;
+            pw2[n] = (r && k2) ? __ldg(g.pw + o + 2) : 0.0;
+            ps0[n] = (r && k0) ? __ldg(g.ps + o) : 0.0;
+            ps1[n] = (r && k1) ? __ldg(g.ps + o + 1) : 0.0;
+            pn0[n] = (rn && k0) ? __ldg(g.ps + o + II) : 0.0;
+            pn1[n] = (rn && k1) ? __ldg(g.ps + o + II + 1) : 0.0;
+            kn0[n] = (ru && k0) ? __ldg(g.kb + o + PJ) : 0.0;
+            kn1[n] = (ru && k1) ? __ldg(g.kb + o + PJ + 1) : 0.0;
+            so0[n] = (r && k0) ? __ldg(g.sor + o) : 0.0;
+            so1[n] = (r && k1) ? __ldg(g.sor + o + 1) : 0.0;
+            qf0[n] = (r && k0) ? __ldg(g.qf + o) : 0.0;
+            qf1[n] = (r && k1) ? __ldg(g.qf + o + 1) : 0.0;
         }
         double nxt[4];
         load_plane(p + 2, nxt);
+        // the next step's coefficient sectors are requested now (no register, never waited on), so that
+        // its loads -- consumed straight away -- find them in L2 instead of paying the DRAM latency
+        if (p + 1 <= KK) {
+#pragma unroll
+            for (int n = 0; n < 2; n++) {
+                if (rok[n] && k0) {
+                    const long long o = po + PJ + ioff[n];
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(g.pw + o));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(g.ps + o));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(g.sor + o));
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(g.qf + o));
+                    if (p + 2 <= KK) asm volatile("prefetch.global.L2 [%0];" ::"l"(g.kb + o + PJ));
+                }
+            }
+        }
 
         const bool pin = p >= 2 && p <= KK - 1;
         bool a0[2];
@@ -165,9 +195,8 @@ k3_relax7_fused(G7 g, const double *__restrict__ qin, double *__restrict__ qout,
 #pragma unroll
             for (int n = 0; n < 4; n++) {
                 const int e = t + n * R7_NT, ly = e >> 6, lx = e & 63;
-                const int gi = gi0 + lx, gj = gj0 + ly;
-                if (lx >= 2 && lx <= R7_SX - 3 && ly >= 2 && ly <= R7_SY - 3 && gi >= 1 && gi <= II && gj >= 1 && gj <= JJ)
-                    qout[((size_t)(p - 2) * JJ + (gj - 1)) * II + (gi - 1)] = ring[s_m1][ly][lx];
+                if (lx >= 2 && lx <= R7_SX - 3 && ly >= 2 && ly <= R7_SY - 3 && eok[n])
+                    qout[(long long)(p - 2) * PJ + eoff[n]] = ring[s_m1][ly][lx];
             }
         }
         // rotate: plane p+1 becomes plane p
