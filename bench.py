@@ -35,6 +35,10 @@ import numpy as np  # noqa: E402
 
 METRIC = "MDOF/s per V-cycle (fine-grid unknowns / V-cycle time)"
 BYTES_PER_PT = {"relax9": 64, "relax5": 48}  # algorithmic bytes per fine point per sweep
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel at 4097^2, from the
+# `ncu --set full` capture summarised in profiles/r01_fine2d_ncu_full_summary.csv (k_relax9_fused<0>: 968.93 MB
+# read + 125.03 MB written; k_relax5_fused<0>: 696.12 + 121.11).  Only quoted for the size it was captured at.
+NCU_TRAFFIC_4097 = {"relax9": 1093.96e6, "relax5": 817.23e6}
 
 
 def parse():
@@ -418,7 +422,9 @@ def main():
             "roofline": {"bound": "hbm", "kernel": "k_relax9_fused / k_relax5_fused: fine-level point-GS sweep, all colours in one launch (bmgx2_relax_GS_oop)",
                          "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                          "peak_source": peak_src, "ms_per_launch": per_sweep_ms, "launches_per_sweep": sweep_launches,
-                         "algorithmic_bytes": alg_bytes, "traffic": None},
+                         "algorithmic_bytes": alg_bytes,
+                         "traffic": (NCU_TRAFFIC_4097["relax9" if a.gallery == "fe" else "relax5"] if n == 4097 else None),
+                         "traffic_source": "ncu --set full, profiles/r01_fine2d_ncu_full_summary.csv (bytes per launch)"},
         }
         # whole-cycle roofline: SURVEY 8(d) 360 B/pt (9-pt V(1,1)) / 312 (5-pt fine)
         cyc_bytes = (360 if a.gallery == "fe" else 312) * dofs if (a.pre, a.post) == (1, 1) and a.relaxation == "point" else None

@@ -38,44 +38,62 @@ extern "C" int bmgx2_restrict(const double *q, double *qc, const double *ci, bmg
     return BMGX_OK;
 }
 
-// One thread per fine interior point.  The reference walks coarse cells and
-// touches the 4 fine points of each; per fine point that is:
+// The reference walks coarse cells and touches the 4 fine points of each; per fine point that is:
 //   C-point (i even, j even):  Q += QC
 //   x-edge  (i odd,  j even):  Q = (Q + (LR*QC(ic,jc) + LL*QC(ic-1,jc))) + RES
 //   y-edge  (i even, j odd ):  Q = (Q + (LA*QC(ic,jc) + LB*QC(ic,jc-1))) + RES
 //   centre  (i odd,  j odd ):  Q = (Q + (LSW*QC(ic-1,jc-1)+LNW*QC(ic-1,jc)+LNE*QC(ic,jc)+LSE*QC(ic,jc-1))) + RES
 // with (ic,jc) the coarse point up-right of the fine point, and RES already
 // divided by the diagonal (the division is stored back: persistent side effect).
+// One thread per coarse cell (ic,jc) = the fine points i in {2ic-3, 2ic-2}, j in {2jc-3, 2jc-2}
+// (centre, y-edge / x-edge, C-point): no divergence, 24 independent loads in flight per thread.
 __global__ void __launch_bounds__(256)
 k_interp_add(double *__restrict__ q, const double *__restrict__ qc, double *__restrict__ res,
              const double *__restrict__ so, const double *__restrict__ ci,
              unsigned IIC, unsigned JJC, unsigned IIF, unsigned JJF)
 {
-    unsigned i = blockIdx.x * blockDim.x + threadIdx.x + 2;
-    unsigned j = blockIdx.y * blockDim.y + threadIdx.y + 2;
-    if (i > IIF - 1 || j > JJF - 1) return;
-    size_t f = IX2(IIF, i, j);
-    size_t pc = (size_t)IIC * JJC;
-    double r = res[f] / so[f];  // SO(i,j,KO): KO is plane 0
-    res[f] = r;
-    unsigned ic = (i + 1) / 2 + 1, jc = (j + 1) / 2 + 1;  // i even: i/2+1 ; i odd: (i+1)/2+1
-    size_t cc = IX2(IIC, ic, jc);
-    bool io = i & 1, jo = j & 1;
-    double qv = q[f];
-    if (!io && !jo) {
-        qv = qv + qc[cc];
-    } else if (io && !jo) {
-        double a = ci[(LR - 1) * pc + cc] * qc[cc] + ci[(LL - 1) * pc + cc] * qc[cc - 1];
-        qv = qv + a + r;
-    } else if (!io && jo) {
-        double a = ci[(LA - 1) * pc + cc] * qc[cc] + ci[(LB - 1) * pc + cc] * qc[cc - IIC];
-        qv = qv + a + r;
-    } else {
-        double a = ci[(LSW - 1) * pc + cc] * qc[cc - IIC - 1] + ci[(LNW - 1) * pc + cc] * qc[cc - 1]
-                   + ci[(LNE - 1) * pc + cc] * qc[cc] + ci[(LSE - 1) * pc + cc] * qc[cc - IIC];
-        qv = qv + a + r;
+    const unsigned ic = blockIdx.x * blockDim.x + threadIdx.x + 2;
+    const unsigned jc = blockIdx.y * blockDim.y + threadIdx.y + 2;
+    if (ic > IIF / 2 + 1 || jc > JJF / 2 + 1) return;
+    const unsigned i0 = 2 * ic - 3, i1 = i0 + 1, j0 = 2 * jc - 3, j1 = j0 + 1;   // i0, j0 odd
+    const bool xi0 = i0 >= 2, xi1 = i1 <= IIF - 1, yj0 = j0 >= 2, yj1 = j1 <= JJF - 1;
+    const size_t pc = (size_t)IIC * JJC;
+    const size_t cc = IX2(IIC, ic, jc);
+    const size_t f00 = IX2(IIF, i0, j0), f10 = f00 + 1, f01 = f00 + IIF, f11 = f01 + 1;
+    const bool p00 = xi0 && yj0, p10 = xi1 && yj0, p01 = xi0 && yj1, p11 = xi1 && yj1;
+    // loads first (all independent)
+    const double r00 = p00 ? res[f00] : 0.0, r10 = p10 ? res[f10] : 0.0, r01 = p01 ? res[f01] : 0.0,
+                 r11 = p11 ? res[f11] : 0.0;
+    const double d00 = p00 ? __ldg(so + f00) : 1.0, d10 = p10 ? __ldg(so + f10) : 1.0, d01 = p01 ? __ldg(so + f01) : 1.0,
+                 d11 = p11 ? __ldg(so + f11) : 1.0;
+    const double q00 = p00 ? q[f00] : 0.0, q10 = p10 ? q[f10] : 0.0, q01 = p01 ? q[f01] : 0.0, q11 = p11 ? q[f11] : 0.0;
+    const double c11 = __ldg(qc + cc), c01 = __ldg(qc + cc - 1), c10 = __ldg(qc + cc - IIC), c00 = __ldg(qc + cc - IIC - 1);
+    const double lr = __ldg(ci + (LR - 1) * pc + cc), ll = __ldg(ci + (LL - 1) * pc + cc);
+    const double la = __ldg(ci + (LA - 1) * pc + cc), lb = __ldg(ci + (LB - 1) * pc + cc);
+    const double lsw = __ldg(ci + (LSW - 1) * pc + cc), lnw = __ldg(ci + (LNW - 1) * pc + cc);
+    const double lne = __ldg(ci + (LNE - 1) * pc + cc), lse = __ldg(ci + (LSE - 1) * pc + cc);
+    if (p00) {   // cell centre (i odd, j odd)
+        const double r = r00 / d00;
+        res[f00] = r;
+        const double a = lsw * c00 + lnw * c01 + lne * c11 + lse * c10;
+        q[f00] = q00 + a + r;
     }
-    q[f] = qv;
+    if (p10) {   // y-edge (i even, j odd)
+        const double r = r10 / d10;
+        res[f10] = r;
+        const double a = la * c11 + lb * c10;
+        q[f10] = q10 + a + r;
+    }
+    if (p01) {   // x-edge (i odd, j even)
+        const double r = r01 / d01;
+        res[f01] = r;
+        const double a = lr * c11 + ll * c01;
+        q[f01] = q01 + a + r;
+    }
+    if (p11) {   // C-point
+        res[f11] = r11 / d11;
+        q[f11] = q11 + c11;
+    }
 }
 
 extern "C" int bmgx2_interp_add(double *q, const double *qc, double *res, const double *so, const double *ci,
@@ -85,7 +103,7 @@ extern "C" int bmgx2_interp_add(double *q, const double *qc, double *res, const 
     (void)nstncl;
     if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "interp_add: periodic BCs not supported");
     if (iif < 3 || jjf < 3) return BMGX_OK;
-    dim3 b(128, 2), g(cdiv(iif - 2, 128), cdiv(jjf - 2, 2));
+    dim3 b(64, 4), g(cdiv(iif / 2, 64), cdiv(jjf / 2, 4));
     k_interp_add<<<g, b, 0, (cudaStream_t)s>>>(q, qc, res, so, ci, iic, jjc, iif, jjf);
     BMGX_LAUNCH_CHECK("interp_add");
     return BMGX_OK;
