@@ -26,6 +26,8 @@ SIGNATURES = {
     "bmgx_launch_count": (C.c_ulonglong, []),
     "bmgx_stream_is_capturing": (_i, [_p, C.POINTER(_i)]),
     "bmgx_get_bc": (None, [_i, C.POINTER(_i)]),
+    "bmgx_set_batch": (_i, [_u]),
+    "bmgx_get_batch": (_u, []),
     "bmgx_fill": (_i, [_p, _z, _d, _p]),
     "bmgx_norm_work_len": (_z, []),
     "bmgx2_sumsq": (_i, [_p, _u, _u, _p, _p, _p]),

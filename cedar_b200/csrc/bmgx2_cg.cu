@@ -99,8 +99,10 @@ extern "C" int bmgx2_SETUP_cg_LU(const double *so, bmgx_len ii, bmgx_len jj, int
 __global__ void k_solve_cg(double *q, const double *__restrict__ qf, unsigned II, unsigned JJ,
                            const double *__restrict__ abd, double *bbd, unsigned nabd1)
 {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (threadIdx.x != 0) return;
     int I1 = II - 1, J1 = JJ - 1;
+    q += (size_t)blockIdx.x * II * JJ; qf += (size_t)blockIdx.x * II * JJ;   // batch entry
+    bbd += (size_t)blockIdx.x * (I1 - 1) * (J1 - 1);
     int kd = I1, kplus1 = kd + 1;
     int n = 0;
     for (int j = 2; j <= J1; j++)
@@ -132,7 +134,7 @@ extern "C" int bmgx2_SOLVE_cg(double *q, const double *qf, bmgx_len ii, bmgx_len
 {
     (void)nabd2;
     if (jpn != BMGX_BCs_definite) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SOLVE_cg: only definite, non-periodic");
-    k_solve_cg<<<1, 32, 0, (cudaStream_t)s>>>(q, qf, ii, jj, abd, bbd, nabd1);
+    k_solve_cg<<<bmgx_batch(), 32, 0, (cudaStream_t)s>>>(q, qf, ii, jj, abd, bbd, nabd1);
     BMGX_LAUNCH_CHECK("SOLVE_cg");
     return BMGX_OK;
 }

@@ -231,6 +231,7 @@ k_linex_block(const double *__restrict__ so, const double *__restrict__ qf, doub
     double *sv = lsm, *se = lsm + m + 1;
     const unsigned j = jbeg + 2 * blockIdx.x;  // F-index
     const size_t pl = (size_t)II * JJ;
+    q += blockIdx.y * pl; qf += blockIdx.y * pl;   // batch entry
     const double *ks = so + (KS - 1) * pl, *ksw = so + (KSW - 1) * pl, *knw = so + (KNW - 1) * pl;
     const size_t row = (size_t)(j - 1) * II;
     const double *Lf = sor + pl + row;
@@ -283,6 +284,7 @@ k_liney_block(double *__restrict__ B, const double *__restrict__ sor, unsigned I
     const unsigned i = ibeg + 2 * blockIdx.x;  // F-index
     const size_t row = (size_t)(i - 1) * JJ;
     const double *Lf = sor + (size_t)II * JJ + row;
+    B += (size_t)blockIdx.y * II * JJ;   // batch entry
     l2_prefetch_row(B + row, JJ); l2_prefetch_row(Lf, JJ); l2_prefetch_row(sor + row, JJ);
     for (unsigned p0 = 1 + threadIdx.x; p0 <= m; p0 += 4 * blockDim.x) {
         double bv[4], lv[4];
@@ -334,7 +336,7 @@ static cudaError_t launch_linex(unsigned C, unsigned nl, unsigned threads, size_
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    k_linex_block<NINE><<<nl, threads, smem, st>>>(so, qf, q, sor, II, JJ, jbeg, C);
+    k_linex_block<NINE><<<dim3(nl, bmgx_batch()), threads, smem, st>>>(so, qf, q, sor, II, JJ, jbeg, C);
     return cudaSuccess;
 }
 
@@ -347,7 +349,7 @@ static cudaError_t launch_liney(unsigned C, unsigned nl, unsigned threads, size_
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    k_liney_block<<<nl, threads, smem, st>>>(B, sor, II, JJ, ibeg, C);
+    k_liney_block<<<dim3(nl, bmgx_batch()), threads, smem, st>>>(B, sor, II, JJ, ibeg, C);
     return cudaSuccess;
 }
 
@@ -421,6 +423,7 @@ k_lines_y_rhs(const double *__restrict__ so, const double *__restrict__ qf, cons
     // tile: 32 lines (i = ibeg + 2*(bx*32 + tx)) x 32 positions j
     unsigned tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
     size_t pl = (size_t)II * JJ;
+    qf += blockIdx.z * pl; q += blockIdx.z * pl; B += blockIdx.z * pl;   // batch entry
     const double *kw = so + (KW - 1) * pl, *ksw = so + (KSW - 1) * pl, *knw = so + (KNW - 1) * pl;
     unsigned i = ibeg + 2 * (blockIdx.x * 32 + tx);  // F-index
     for (unsigned r = ty; r < 32; r += 8) {
@@ -461,6 +464,7 @@ k_lines_y_scatter(const double *__restrict__ B, double *__restrict__ q, unsigned
 {
     __shared__ double tile[32][33];
     unsigned tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    B += (size_t)blockIdx.z * II * JJ; q += (size_t)blockIdx.z * II * JJ;   // batch entry
     for (unsigned r = ty; r < 32; r += 8) {
         unsigned il = ibeg + 2 * (blockIdx.x * 32 + r);
         unsigned j = 2 + blockIdx.y * 32 + tx;
@@ -492,7 +496,9 @@ extern "C" int bmgx2_relax_lines_x(int k, const double *so, const double *qf, do
             cudaError_t e = nine ? launch_linex<true>(lg, nl, threads, smem, (cudaStream_t)s, so, qf, q, sor, ii, jj, jbeg)
                                  : launch_linex<false>(lg, nl, threads, smem, (cudaStream_t)s, so, qf, q, sor, ii, jj, jbeg);
             if (e != cudaSuccess) return bmgx_set_cuda_error(e, "relax_lines_x/attr");
-        } else if (nine)
+        } else if (bmgx_batch() > 1)
+            return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_x: lines too long for the batched path");
+        else if (nine)
             k_relax_lines_x<true><<<cdiv((size_t)nl * 32, 128), 128, 0, (cudaStream_t)s>>>(so, qf, q, sor, ii, jj, jbeg);
         else
             k_relax_lines_x<false><<<cdiv((size_t)nl * 32, 128), 128, 0, (cudaStream_t)s>>>(so, qf, q, sor, ii, jj, jbeg);
@@ -515,7 +521,7 @@ extern "C" int bmgx2_relax_lines_y(int k, const double *so, const double *qf, do
         unsigned ibeg = fwd ? 3 - a : 2 + a;
         if (ibeg > ii - 1) continue;
         unsigned nl = (ii - 1 - ibeg) / 2 + 1;
-        dim3 g(cdiv(nl, 32), cdiv(jj - 2, 32));
+        dim3 g(cdiv(nl, 32), cdiv(jj - 2, 32), bmgx_batch());
         if (k < kf || ifd != 1) k_lines_y_rhs<true><<<g, 256, 0, st>>>(so, qf, q, b, ii, jj, ibeg);
         else k_lines_y_rhs<false><<<g, 256, 0, st>>>(so, qf, q, b, ii, jj, ibeg);
         BMGX_LAUNCH_CHECK("relax_lines_y/rhs");
@@ -523,7 +529,9 @@ extern "C" int bmgx2_relax_lines_y(int k, const double *so, const double *qf, do
         if (line_plan(jj - 2, &lg, &threads, &smem)) {
             cudaError_t e = launch_liney(lg, nl, threads, smem, st, b, sor, ii, jj, ibeg);
             if (e != cudaSuccess) return bmgx_set_cuda_error(e, "relax_lines_y/attr");
-        } else
+        } else if (bmgx_batch() > 1)
+            return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_y: lines too long for the batched path");
+        else
             k_lines_y_solve<<<cdiv((size_t)nl * 32, 128), 128, 0, st>>>(b, sor, ii, jj, ibeg);
         BMGX_LAUNCH_CHECK("relax_lines_y/solve");
         k_lines_y_scatter<<<g, 256, 0, st>>>(b, q, ii, jj, ibeg);

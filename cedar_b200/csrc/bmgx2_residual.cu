@@ -12,6 +12,7 @@ k_residual(const double *__restrict__ so, const double *__restrict__ qf, const d
     if (i > II - 1 || j > JJ - 1) return;
     size_t c = IX2(II, i, j);
     size_t pl = (size_t)II * JJ;
+    qf += blockIdx.z * pl; q += blockIdx.z * pl; res += blockIdx.z * pl;   // batch entry
     const double *ko = so, *kw = so + (KW - 1) * pl, *ks = so + (KS - 1) * pl;
     double acc = qf[c] + kw[c] * q[c - 1] + kw[c + 1] * q[c + 1] + ks[c] * q[c - II] + ks[c + II] * q[c + II];
     if (NINE) {
@@ -28,7 +29,7 @@ extern "C" int bmgx2_residual(int k, const double *so, const double *qf, const d
 {
     (void)nstncl; (void)ibc; (void)irelax; (void)irelax_sym; (void)updown;
     if (ii < 3 || jj < 3) return BMGX_OK;
-    dim3 b(128, 2), g(cdiv(ii - 2, 128), cdiv(jj - 2, 2));
+    dim3 b(128, 2), g(cdiv(ii - 2, 128), cdiv(jj - 2, 2), bmgx_batch());
     if (k < kf || ifd != 1)
         k_residual<true><<<g, b, 0, (cudaStream_t)s>>>(so, qf, q, res, ii, jj);
     else

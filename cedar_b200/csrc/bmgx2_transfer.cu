@@ -5,13 +5,14 @@
 
 __global__ void __launch_bounds__(256)
 k_restrict(const double *__restrict__ q, double *__restrict__ qc, const double *__restrict__ ci,
-           unsigned Nx, unsigned Nxc, unsigned Nyc)
+           unsigned Nx, unsigned Ny, unsigned Nxc, unsigned Nyc)
 {
     unsigned ic = blockIdx.x * blockDim.x + threadIdx.x + 2;
     unsigned jc = blockIdx.y * blockDim.y + threadIdx.y + 2;
     if (ic > Nxc - 1 || jc > Nyc - 1) return;
     unsigned i = 2 * (ic - 1), j = 2 * (jc - 1);
     size_t pc = (size_t)Nxc * Nyc;
+    q += (size_t)blockIdx.z * Nx * Ny; qc += blockIdx.z * pc;   // batch entry
     size_t cc = IX2(Nxc, ic, jc);
     size_t f = IX2(Nx, i, j);
     double r = ci[(LNE - 1) * pc + cc] * q[f - Nx - 1]
@@ -29,11 +30,10 @@ k_restrict(const double *__restrict__ q, double *__restrict__ qc, const double *
 extern "C" int bmgx2_restrict(const double *q, double *qc, const double *ci, bmgx_len nx, bmgx_len ny,
                               bmgx_len nxc, bmgx_len nyc, int jpn, bmgx_stream_t s)
 {
-    (void)ny;
     if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "restrict: periodic BCs not supported");
     if (nxc < 3 || nyc < 3) return BMGX_OK;
-    dim3 b(64, 4), g(cdiv(nxc - 2, 64), cdiv(nyc - 2, 4));
-    k_restrict<<<g, b, 0, (cudaStream_t)s>>>(q, qc, ci, nx, nxc, nyc);
+    dim3 b(64, 4), g(cdiv(nxc - 2, 64), cdiv(nyc - 2, 4), bmgx_batch());
+    k_restrict<<<g, b, 0, (cudaStream_t)s>>>(q, qc, ci, nx, ny, nxc, nyc);
     BMGX_LAUNCH_CHECK("restrict");
     return BMGX_OK;
 }
@@ -59,6 +59,7 @@ k_interp_add(double *__restrict__ q, const double *__restrict__ qc, double *__re
     const bool xi0 = i0 >= 2, xi1 = i1 <= IIF - 1, yj0 = j0 >= 2, yj1 = j1 <= JJF - 1;
     const size_t pc = (size_t)IIC * JJC;
     const size_t cc = IX2(IIC, ic, jc);
+    q += (size_t)blockIdx.z * IIF * JJF; res += (size_t)blockIdx.z * IIF * JJF; qc += blockIdx.z * pc;   // batch entry
     const size_t f00 = IX2(IIF, i0, j0), f10 = f00 + 1, f01 = f00 + IIF, f11 = f01 + 1;
     const bool p00 = xi0 && yj0, p10 = xi1 && yj0, p01 = xi0 && yj1, p11 = xi1 && yj1;
     // loads first (all independent)
@@ -103,7 +104,7 @@ extern "C" int bmgx2_interp_add(double *q, const double *qc, double *res, const 
     (void)nstncl;
     if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "interp_add: periodic BCs not supported");
     if (iif < 3 || jjf < 3) return BMGX_OK;
-    dim3 b(64, 4), g(cdiv(iif / 2, 64), cdiv(jjf / 2, 4));
+    dim3 b(64, 4), g(cdiv(iif / 2, 64), cdiv(jjf / 2, 4), bmgx_batch());
     k_interp_add<<<g, b, 0, (cudaStream_t)s>>>(q, qc, res, so, ci, iic, jjc, iif, jjf);
     BMGX_LAUNCH_CHECK("interp_add");
     return BMGX_OK;

@@ -25,6 +25,7 @@ __global__ void __launch_bounds__(256) k3_plane_copy(Map m, double *x3, double *
 {
     const int u = blockIdx.x * blockDim.x + threadIdx.x + 1, v = blockIdx.y + 1;
     if (u > m.n1()) return;
+    m.ipl += 2 * blockIdx.z; x2 += (size_t)blockIdx.z * m.n1() * m.n2();   // batch entry: every other plane
     int i, j, k;
     m.ijk(u, v, i, j, k);
     const size_t c3 = IX3(m.II, m.JJ, i, j, k), c2 = IX2(m.n1(), u, v);
@@ -61,6 +62,7 @@ k3_plane_rhs(Map m, Op3 A, const double *__restrict__ x, const double *__restric
 {
     const int u = blockIdx.x * blockDim.x + threadIdx.x + 2, v = blockIdx.y + 2;
     if (u > m.n1() - 1) return;
+    m.ipl += 2 * blockIdx.z; b2 += (size_t)blockIdx.z * m.n1() * m.n2();   // batch entry: every other plane
     int i, j, k;
     m.ijk(u, v, i, j, k);
     double r = b[IX3(m.II, m.JJ, i, j, k)];
@@ -83,10 +85,11 @@ k3_plane_rhs(Map m, Op3 A, const double *__restrict__ x, const double *__restric
     b2[IX2(m.n1(), u, v)] = r;
 }
 
-int check_plane(const Map &m, const char *what)
+// nb > 1 (batch context): planes ipl, ipl+2, ... must all exist
+int check_plane(const Map &m, const char *what, unsigned nb = 1)
 {
     const int n = m.dir == 0 ? m.KK : (m.dir == 1 ? m.JJ : m.II);
-    if (m.dir < 0 || m.dir > 2 || m.ipl < 1 || m.ipl > n) return bmgx_set_error(BMGX_ERR_ARG, what);
+    if (m.dir < 0 || m.dir > 2 || m.ipl < 1 || m.ipl + 2 * ((int)nb - 1) > n) return bmgx_set_error(BMGX_ERR_ARG, what);
     return BMGX_OK;
 }
 
@@ -97,8 +100,8 @@ extern "C" int bmgx3_plane_copy(double *x3, double *x2, bmgx_len ii, bmgx_len jj
                                 int to2d, bmgx_stream_t s)
 {
     Map m{dir, (int)ipl, (int)ii, (int)jj, (int)kk};
-    if (check_plane(m, "plane_copy: bad plane")) return BMGX_ERR_ARG;
-    dim3 g(cdiv(m.n1(), 256), m.n2());
+    if (check_plane(m, "plane_copy: bad plane", bmgx_batch())) return BMGX_ERR_ARG;
+    dim3 g(cdiv(m.n1(), 256), m.n2(), bmgx_batch());
     k3_plane_copy<<<g, 256, 0, (cudaStream_t)s>>>(m, x3, x2, to2d);
     BMGX_LAUNCH_CHECK("plane_copy");
     return BMGX_OK;
@@ -121,10 +124,10 @@ extern "C" int bmgx3_plane_rhs(const double *so, const double *x, const double *
                                bmgx_len kk, int nstncl, int dir, bmgx_len ipl, bmgx_stream_t s)
 {
     Map m{dir, (int)ipl, (int)ii, (int)jj, (int)kk};
-    if (check_plane(m, "plane_rhs: bad plane")) return BMGX_ERR_ARG;
+    if (check_plane(m, "plane_rhs: bad plane", bmgx_batch())) return BMGX_ERR_ARG;
     if (m.n1() < 3 || m.n2() < 3) return BMGX_OK;
     Op3 A(so, ii, jj, kk);
-    dim3 g(cdiv(m.n1() - 2, 256), m.n2() - 2);
+    dim3 g(cdiv(m.n1() - 2, 256), m.n2() - 2, bmgx_batch());
     cudaStream_t st = (cudaStream_t)s;
     const bool seven = nstncl != 14;
 #define LAUNCH(SV, D) k3_plane_rhs<SV, D><<<g, 256, 0, st>>>(m, A, x, b, b2)

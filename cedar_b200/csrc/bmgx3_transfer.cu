@@ -35,42 +35,51 @@ k3_restrict(const double *__restrict__ q, double *__restrict__ qc, const double 
 //   coarse-plane points (k even) add `a + RES` with the weighted sum `a` formed
 //   first (f90:100-150); points between coarse planes (k odd) add term by term
 //   (f90:153-230).
+// One thread per x-pair of fine points (i0 = 2ic-3 odd, i1 = 2ic-2 even) of a fine row (j,k): both share
+// the coarse point (ic,jc,kc) their weights are stored at; the (j,k) parities are uniform per warp, so
+// there is no divergence and twice the loads are in flight.
 __global__ void __launch_bounds__(128)
 k3_interp_add(double *__restrict__ q, const double *__restrict__ qc, const double *__restrict__ so,
               double *__restrict__ res, const double *__restrict__ ci, int IIC, int JJC, int KKC, int IIF, int JJF)
 {
-    int i = blockIdx.x * blockDim.x + threadIdx.x + 2, j = blockIdx.y * blockDim.y + threadIdx.y + 2, k = blockIdx.z + 2;
-    if (i > IIF - 1 || j > JJF - 1) return;
-    const size_t f = ((size_t)(k - 1) * JJF + (j - 1)) * IIF + (i - 1);
+    const int ic = blockIdx.x * blockDim.x + threadIdx.x + 2, j = blockIdx.y * blockDim.y + threadIdx.y + 2,
+              k = blockIdx.z + 2;
+    if (ic > IIF / 2 + 1 || j > JJF - 1) return;
+    const int i0 = 2 * ic - 3, i1 = i0 + 1;
+    const bool v0 = i0 >= 2, v1 = i1 <= IIF - 1;
+    const size_t f0 = ((size_t)(k - 1) * JJF + (j - 1)) * IIF + (i0 - 1), f1 = f0 + 1;
     const size_t pc = (size_t)IIC * JJC * KKC, X = 1, Y = IIC, Z = (size_t)IIC * JJC;
-    const int ic = (i + 1) / 2 + 1, jc = (j + 1) / 2 + 1, kc = (k + 1) / 2 + 1;
+    const int jc = (j + 1) / 2 + 1, kc = (k + 1) / 2 + 1;
     const size_t cc = ((size_t)(kc - 1) * JJC + (jc - 1)) * IIC + (ic - 1);
-    const double r = res[f] / so[f];   // so(i,j,k,kp): plane 0
-    res[f] = r;
-    const bool px = i & 1, py = j & 1, pz = k & 1;
-#define CI(l) ci[(size_t)((l)-1) * pc + cc]
-    double v = q[f];
+    const double n0 = v0 ? res[f0] : 0.0, n1 = v1 ? res[f1] : 0.0;
+    const double d0 = v0 ? __ldg(so + f0) : 1.0, d1 = v1 ? __ldg(so + f1) : 1.0;   // so(i,j,k,kp): plane 0
+    double w0 = v0 ? q[f0] : 0.0, w1 = v1 ? q[f1] : 0.0;
+    const double r0 = n0 / d0, r1 = n1 / d1;
+    const bool py = j & 1, pz = k & 1;
+#define CI(l) __ldg(ci + (size_t)((l)-1) * pc + cc)
+#define QC(o) __ldg(qc + cc - (o))
     if (!pz) {
-        if (!px && !py) v = v + qc[cc];
-        else if (px && !py) { double a = CI(LXYR) * qc[cc] + CI(LXYL) * qc[cc - X]; v = v + a + r; }
-        else if (!px && py) { double a = CI(LXYA) * qc[cc] + CI(LXYB) * qc[cc - Y]; v = v + a + r; }
-        else {
-            double a = CI(LXYSW) * qc[cc - X - Y] + CI(LXYNW) * qc[cc - X] + CI(LXYNE) * qc[cc] + CI(LXYSE) * qc[cc - Y];
-            v = v + a + r;
+        if (!py) {
+            { double a = CI(LXYR) * QC(0) + CI(LXYL) * QC(X); w0 = w0 + a + r0; }
+            w1 = w1 + QC(0);
+        } else {
+            { double a = CI(LXYSW) * QC(X + Y) + CI(LXYNW) * QC(X) + CI(LXYNE) * QC(0) + CI(LXYSE) * QC(Y); w0 = w0 + a + r0; }
+            { double a = CI(LXYA) * QC(0) + CI(LXYB) * QC(Y); w1 = w1 + a + r1; }
         }
     } else {
-        if (!px && !py) v = v + CI(LXZA) * qc[cc] + CI(LXZB) * qc[cc - Z] + r;
-        else if (!px && py)
-            v = v + CI(LYZNW) * qc[cc] + CI(LYZNE) * qc[cc - Y] + CI(LYZSW) * qc[cc - Z] + CI(LYZSE) * qc[cc - Y - Z] + r;
-        else if (px && !py)
-            v = v + CI(LXZNW) * qc[cc - X] + CI(LXZNE) * qc[cc] + CI(LXZSW) * qc[cc - X - Z] + CI(LXZSE) * qc[cc - Z] + r;
-        else
-            v = v + CI(LTNW) * qc[cc - X] + CI(LTNE) * qc[cc] + CI(LTSW) * qc[cc - X - Y] + CI(LTSE) * qc[cc - Y]
-                + CI(LBNW) * qc[cc - X - Z] + CI(LBNE) * qc[cc - Z] + CI(LBSW) * qc[cc - X - Y - Z]
-                + CI(LBSE) * qc[cc - Y - Z] + r;
+        if (!py) {
+            w0 = w0 + CI(LXZNW) * QC(X) + CI(LXZNE) * QC(0) + CI(LXZSW) * QC(X + Z) + CI(LXZSE) * QC(Z) + r0;
+            w1 = w1 + CI(LXZA) * QC(0) + CI(LXZB) * QC(Z) + r1;
+        } else {
+            w0 = w0 + CI(LTNW) * QC(X) + CI(LTNE) * QC(0) + CI(LTSW) * QC(X + Y) + CI(LTSE) * QC(Y)
+                 + CI(LBNW) * QC(X + Z) + CI(LBNE) * QC(Z) + CI(LBSW) * QC(X + Y + Z) + CI(LBSE) * QC(Y + Z) + r0;
+            w1 = w1 + CI(LYZNW) * QC(0) + CI(LYZNE) * QC(Y) + CI(LYZSW) * QC(Z) + CI(LYZSE) * QC(Y + Z) + r1;
+        }
     }
 #undef CI
-    q[f] = v;
+#undef QC
+    if (v0) { res[f0] = r0; q[f0] = w0; }
+    if (v1) { res[f1] = r1; q[f1] = w1; }
 }
 
 }  // namespace
@@ -94,7 +103,7 @@ extern "C" int bmgx3_interp_add(double *q, const double *qc, const double *so, d
     (void)nstncl;
     if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "interp_add3: periodic BCs not supported");
     if (iif < 3 || jjf < 3 || kkf < 3) return BMGX_OK;
-    dim3 b(64, 2), g(cdiv(iif - 2, 64), cdiv(jjf - 2, 2), kkf - 2);
+    dim3 b(32, 4), g(cdiv(iif / 2, 32), cdiv(jjf - 2, 4), kkf - 2);
     k3_interp_add<<<g, b, 0, (cudaStream_t)s>>>(q, qc, so, res, ci, iic, jjc, kkc, iif, jjf);
     BMGX_LAUNCH_CHECK("interp_add3");
     return BMGX_OK;

@@ -19,6 +19,8 @@ enum { MSOR = 2 };
 int bmgx_set_cuda_error(cudaError_t e, const char *where);
 int bmgx_set_error(int code, const char *msg);
 void bmgx_count_launch(unsigned n = 1);
+// batch context (bmgx_set_batch): number of grid functions the batch-aware entry points process per call
+unsigned bmgx_batch();
 
 #define BMGX_LAUNCH_CHECK(where)                                          \
     do {                                                                  \

@@ -23,6 +23,17 @@ extern "C" const char *bmgx_version(void) { return "bmgx 0.1 (sm_100a)"; }
 extern "C" const char *bmgx_last_error(void) { return g_err; }
 extern "C" unsigned long long bmgx_launch_count(void) { return g_launches.load(); }
 
+// batch context, per host thread (the host layer is single threaded per solver)
+static thread_local unsigned g_batch = 1;
+unsigned bmgx_batch() { return g_batch; }
+extern "C" int bmgx_set_batch(unsigned nb)
+{
+    if (nb < 1 || nb > 65535) return bmgx_set_error(BMGX_ERR_ARG, "set_batch: 1 <= nb <= 65535");
+    g_batch = nb;
+    return BMGX_OK;
+}
+extern "C" unsigned bmgx_get_batch(void) { return g_batch; }
+
 // src/2d/ftn/BMG_get_bc.f90:13-22
 extern "C" void bmgx_get_bc(int per_mask, int *ibc)
 {

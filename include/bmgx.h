@@ -82,6 +82,19 @@ int bmgx_graph_end(bmgx_stream_t s, void **graph_exec);
 int bmgx_graph_launch(void *graph_exec, bmgx_stream_t s);
 int bmgx_graph_destroy(void *graph_exec);
 
+/* ---- batch context ---------------------------------------------------------
+ * Plane relaxation solves many independent 2D problems with ONE operator (the planes of
+ * a colour).  bmgx_set_batch(nb) makes the batch-aware entry points below treat every
+ * grid-function argument (q, qf, res, the line scratch b, bbd) as nb arrays stored back to
+ * back (stride = the array's own size, e.g. ii*jj doubles) and process all of them in one
+ * launch; operator-like arguments (so, sor, ci, abd) are shared.  Batch-aware:
+ * bmgx2_relax_lines_x/_y, bmgx2_residual, bmgx2_restrict, bmgx2_interp_add, bmgx2_SOLVE_cg,
+ * and bmgx3_plane_copy / bmgx3_plane_rhs, which then stage planes ipl, ipl+2, ... (one per
+ * batch entry).  Every other entry point ignores the context.  Per host thread; read when a
+ * call is enqueued (so it is baked into a captured CUDA graph); reset with bmgx_set_batch(1). */
+int bmgx_set_batch(unsigned nb);
+unsigned bmgx_get_batch(void);
+
 /* ---- utilities used by the host layer (grid_func::set / lp_norm) ---------- */
 /* array<>::set(v) over n doubles */
 int bmgx_fill(bmgx_real *a, size_t n, bmgx_real v, bmgx_stream_t s);

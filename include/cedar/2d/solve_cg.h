@@ -25,6 +25,8 @@ public:
 	void run(grid_func &x, const grid_func &b, const grid_func &ABD, real_t *bbd) override
 	{
 		(void)bbd;
+		// batch context (plane relaxation): one packed right-hand side per batch entry
+		if (bbd_dev.size() < static_cast<std::size_t>(ABD.len(1)) * bmgx_get_batch()) bbd_dev.set_batch(bmgx_get_batch());
 		int ibc;
 		bmgx_get_bc(params->per_mask(), &ibc);
 		gpu::check(bmgx2_SOLVE_cg(x.dev(), b.cdev(), x.len(0), x.len(1), ABD.cdev(), bbd_dev.dev(), ABD.len(0),

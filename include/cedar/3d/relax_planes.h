@@ -18,6 +18,8 @@
 #ifndef CEDAR_3D_RELAX_PLANES_H
 #define CEDAR_3D_RELAX_PLANES_H
 
+#include <algorithm>
+#include <array>
 #include <map>
 #include <memory>
 #include <type_traits>
@@ -45,6 +47,22 @@ template <class sten2> struct plane_solver
 	std::unique_ptr<cdr2::solver<sten2>> slv;
 	cdr2::grid_func x2, b2;
 	len_t nplanes = 0;
+	// batched path: all planes of one colour go through the 2D cycle together (one launch per
+	// kernel for the whole colour).  The level arrays of `slv` then hold `nbmax` grid functions
+	// each, and each colour has its own staging arrays (so that the 2D cycle's captured graphs,
+	// keyed by these pointers, keep their own batch size).
+	bool batched = false;
+	len_t nbmax = 1;
+	std::array<cdr2::grid_func, 2> bx2, bb2;
+};
+
+// resets the batch context of libbmgx when it goes out of scope
+struct batch_guard
+{
+	explicit batch_guard(unsigned nb) { gpu::check(bmgx_set_batch(nb), "set_batch"); }
+	~batch_guard() { bmgx_set_batch(1); }
+	batch_guard(const batch_guard &) = delete;
+	batch_guard &operator=(const batch_guard &) = delete;
 };
 
 template <relax_dir rdir> class planes : public kernels::plane_relax<stypes, rdir>
@@ -80,6 +98,27 @@ private:
 		ps->slv = std::make_unique<cdr2::solver<sten2>>(*ps->so2, this->params->plane_config);
 		ps->x2 = cdr2::grid_func(n1, n2);
 		ps->b2 = cdr2::grid_func(n1, n2);
+		// Batch the planes of a colour when the plane solve is ONE V-cycle with line relaxation
+		// (the default plane_config) -- the kernels of that cycle are batch aware (include/bmgx.h);
+		// key "plane-batch": false in the plane config keeps the plane-by-plane path
+		const auto &st = ps->slv->get_settings();
+		using rt = ml_settings::relax_type;
+		const bool lines = st.relaxation == rt::line_x || st.relaxation == rt::line_y || st.relaxation == rt::line_xy;
+		const bool fits = std::max(n1, n2) + 2 <= 12000;   // a line must fit the shared-memory line solver
+		ps->batched = lines && fits && st.maxiter == 1 && st.cycle == ml_settings::cycle_type::v
+		              && this->params->plane_config->template get<bool>("plane-batch", true) && ps->nplanes > 1;
+		if (ps->batched) {
+			ps->nbmax = (ps->nplanes + 1) / 2;
+			auto &lv = ps->slv->levels;
+			for (std::size_t l = 0; l < lv.size(); l++) {
+				if (l == 0) { auto &L = lv.template get<sten2>(0); L.x.set_batch(ps->nbmax); L.b.set_batch(ps->nbmax); L.res.set_batch(ps->nbmax); }
+				else { auto &L = lv.get(l); L.x.set_batch(ps->nbmax); L.b.set_batch(ps->nbmax); L.res.set_batch(ps->nbmax); }
+			}
+			for (int c = 0; c < 2; c++) {
+				ps->bx2[c] = cdr2::grid_func(n1, n2); ps->bx2[c].set_batch(ps->nbmax);
+				ps->bb2[c] = cdr2::grid_func(n1, n2); ps->bb2[c].set_batch(ps->nbmax);
+			}
+		}
 		return ps;
 	}
 
@@ -92,6 +131,21 @@ private:
 		const int nst = stencil_ndirs<sten3>::value;
 		const bool single_cycle = ps.slv->get_settings().maxiter == 1;
 		for (int ipl_beg = lstart; ipl_beg != lend; ipl_beg += lstride) {
+			if (ps.batched) {
+				if (static_cast<len_t>(ipl_beg) > ps.nplanes) continue;
+				const unsigned cnt = (ps.nplanes - ipl_beg) / 2 + 1;   // planes ipl_beg, ipl_beg+2, ...
+				auto &x2 = ps.bx2[ipl_beg - 1];
+				auto &b2 = ps.bb2[ipl_beg - 1];
+				batch_guard bg(cnt);
+				gpu::check(bmgx3_plane_copy(x.dev(), x2.dev(), x.len(0), x.len(1), x.len(2), pd::code, ipl_beg + 1, 1,
+				                            gpu::stream()), "plane copy32 (batch)");
+				gpu::check(bmgx3_plane_rhs(so.cdev(), x.cdev(), b.cdev(), b2.dev(), x.len(0), x.len(1), x.len(2), nst,
+				                           pd::code, ipl_beg + 1, gpu::stream()), "plane rhs (batch)");
+				ps.slv->vcycle(x2, b2);
+				gpu::check(bmgx3_plane_copy(x.dev(), x2.dev(), x.len(0), x.len(1), x.len(2), pd::code, ipl_beg + 1, 0,
+				                            gpu::stream()), "plane copy23 (batch)");
+				continue;
+			}
 			for (len_t ipl = ipl_beg; ipl <= ps.nplanes; ipl += 2) {
 				// Fortran-style plane index ipl+1 (ipl counts interior planes from 1)
 				gpu::check(bmgx3_plane_copy(x.dev(), ps.x2.dev(), x.len(0), x.len(1), x.len(2), pd::code, ipl + 1, 1,

@@ -108,6 +108,14 @@ public:
 		buf.resize(n * sizeof(data_type));
 	}
 	std::size_t size() const { return buf.bytes() / sizeof(data_type); }
+	// storage for nb arrays of this shape back to back (the batch context of include/bmgx.h);
+	// shape, len() and indexing keep describing ONE array; contents become all zero
+	void set_batch(std::size_t nb)
+	{
+		std::size_t n = 1;
+		for (unsigned short i = 0; i < ND; i++) n *= extents[i];
+		buf.resize(n * nb * sizeof(data_type));
+	}
 
 	template <typename... T> data_type &operator()(T... args)
 	{

@@ -198,3 +198,48 @@ def test_periodic_is_refused(cuda, abi):
     d = cuda.zeros((5, 6, 6), dtype=cuda.float64, device="cuda")
     st = abi.lib.bmgx2_relax_GS(1, ptr(d), ptr(d[0]), ptr(d[1]), ptr(d), 6, 6, 1, 0, 5, 2, 1, 0, 2, None)
     assert st == 2 and b"periodic" in abi.lib.bmgx_last_error()
+
+
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(7, 5), (37, 64), (130, 97)])
+def test_batch_context(cuda, abi, nx, ny, nine):
+    """bmgx_set_batch(nb): the batch-aware entry points process nb grid functions stored back
+    to back with one shared operator -- bitwise what nb separate calls give."""
+    rng = np.random.default_rng(nx * 13 + ny + nine)
+    nb = 3
+    so = random_op2(nx, ny, nine, rng)
+    nst, ifd = so.shape[0], ifd_of(nine)
+    II, JJ = nx + 2, ny + 2
+    nxc, nyc = coarse_n(nx), coarse_n(ny)
+    IIC, JJC = nxc + 2, nyc + 2
+    d_so = dev(cuda, so)
+    d_sorx = cuda.zeros((2, JJ, II), dtype=cuda.float64, device="cuda")
+    d_sory = cuda.zeros((2, II, JJ), dtype=cuda.float64, device="cuda")
+    abi.check(abi.lib.bmgx2_SETUP_lines_x(ptr(d_so), ptr(d_sorx), II, JJ, nst, 0, None))
+    abi.check(abi.lib.bmgx2_SETUP_lines_y(ptr(d_so), ptr(d_sory), II, JJ, nst, 0, None))
+    ci = dev(cuda, rng.uniform(0.1, 0.5, size=(8, JJC, IIC)))
+    q = np.stack([random_gf(nx, ny, rng) for _ in range(nb)]); b = np.stack([random_gf(nx, ny, rng) for _ in range(nb)])
+    qc = np.stack([random_gf(nxc, nyc, rng) for _ in range(nb)])
+
+    def run(batched):
+        d_q, d_b, d_qc = dev(cuda, q), dev(cuda, b), dev(cuda, qc)
+        d_r = cuda.zeros_like(d_q); d_w = cuda.zeros_like(d_q); d_rc = cuda.zeros_like(d_qc)
+        groups = [(slice(None), nb)] if batched else [(slice(k, k + 1), 1) for k in range(nb)]
+        for sl, n in groups:
+            abi.check(abi.lib.bmgx_set_batch(n))
+            try:
+                Q, B, R, W, QC, RC = d_q[sl], d_b[sl], d_r[sl], d_w[sl], d_qc[sl], d_rc[sl]
+                abi.check(abi.lib.bmgx2_relax_lines_x(1, ptr(d_so), ptr(B), ptr(Q), ptr(d_sorx), ptr(W), II, JJ, 1, ifd, nst, 1, 0, 0, None))
+                abi.check(abi.lib.bmgx2_relax_lines_y(1, ptr(d_so), ptr(B), ptr(Q), ptr(d_sory), ptr(W), II, JJ, 1, ifd, nst, 1, 0, 0, None))
+                abi.check(abi.lib.bmgx2_residual(0, ptr(d_so), ptr(B), ptr(Q), ptr(R), II, JJ, 0, ifd, nst, 0, 0, 0, 0, None))
+                abi.check(abi.lib.bmgx2_restrict(ptr(R), ptr(RC), ptr(ci), II, JJ, IIC, JJC, 0, None))
+                abi.check(abi.lib.bmgx2_interp_add(ptr(Q), ptr(QC), ptr(R), ptr(d_so), ptr(ci), IIC, JJC, II, JJ, nst, 0, None))
+            finally:
+                abi.check(abi.lib.bmgx_set_batch(1))
+        return host(d_q), host(d_r), host(d_rc)
+
+    one = run(False)
+    many = run(True)
+    for a, c, what in zip(one, many, ("q", "res", "coarse rhs")):
+        assert_bitwise(c, a, f"batch context: {what}")
+    assert abi.lib.bmgx_get_batch() == 1
