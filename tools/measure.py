@@ -71,3 +71,5 @@ if __name__ == "__main__":
     if "planes" in which:
         run3("poisson", 129, "plane-xyz")
         run3("fe", 129, "plane-xyz")
+        run3("poisson", 257, "plane-xyz")
+        run3("poisson", 513, "plane-xyz")
