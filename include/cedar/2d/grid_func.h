@@ -5,6 +5,7 @@
 #define CEDAR_2D_CORE_GRIDFUNC_H
 
 #include <cmath>
+#include <fstream>
 #include <iostream>
 
 #include <cedar/types.h>

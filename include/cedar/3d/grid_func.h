@@ -5,6 +5,7 @@
 #define CEDAR_3D_GRID_FUNC_H
 
 #include <cmath>
+#include <fstream>
 #include <iostream>
 
 #include <cedar/types.h>

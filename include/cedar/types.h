@@ -61,6 +61,10 @@ private:
 	T b, e;
 };
 
+// the reference's AlignedVector (types.h:46-47, a 16-byte aligned std::vector); operator new already
+// aligns doubles to 16 bytes on this platform
+template <class T> using AlignedVector = std::vector<T>;
+
 template <class T> range_t<T> range(T to) { return range_t<T>(T(), to); }
 template <class T> range_t<T> range(T from, T to) { return range_t<T>(from, to); }
 
