@@ -157,6 +157,12 @@ class CudaKernels:
         self._ck(self.L.bmgx2_SETUP_interp_OI_stage(self._p(A), None, self._p(P), ii, jj, iic, jjc,
                                                     1 if nst == 3 else 0, nst, 0, 0, stage, self.s))
 
+    def relax_oop(self, A, b, x, xout, sor, updown):
+        """one whole sweep, all colours in a single pass over memory (out of place)"""
+        nst, jj, ii = A.shape
+        self._ck(self.L.bmgx2_relax_GS_oop(1, self._p(A), self._p(b), self._p(x), self._p(xout), self._p(sor), ii, jj, 1,
+                                           1 if nst == 3 else 0, nst, 2, 1, updown, 0, self.s))
+
     def galerkin(self, A, Ac, P):
         nst, jj, ii = A.shape
         _, jjc, iic = P.shape
@@ -261,7 +267,8 @@ class DistSolver2:
     the block's own stencil entries; ghost entries are filled by the solver."""
 
     def __init__(self, so_local, nx, ny, decomp_shape, nrelax_pre=2, nrelax_post=1, agglomerate=513,
-                 min_coarse=3, ndist=None, transport=None, kernels=None, device=None, coarse_factory=None):
+                 min_coarse=3, ndist=None, transport=None, kernels=None, device=None, coarse_factory=None,
+                 fused_sweep=True, fuse_min=64):
         self.nx, self.ny = nx, ny
         self.npre, self.npost = nrelax_pre, nrelax_post
         self.nlevels = compute_num_levels(nx, ny, min_coarse)
@@ -286,9 +293,14 @@ class DistSolver2:
         self.nst = next(iter(so_local.values())).shape[0]
         self.coarse_factory = coarse_factory
         self.exchanges = 0
+        self.fused_sweep, self.fuse_min = fused_sweep, fuse_min
+        self.ext = {}
         with self._on_stream():
             self._allocate(so_local)
             self._setup()
+            if fused_sweep:
+                for lvl in range(self.ndist):
+                    self._build_ext(lvl)
 
     # -- helpers -------------------------------------------------------------
     def _on_stream(self):
@@ -457,8 +469,91 @@ class DistSolver2:
             self.coarse.vcycle(self._gx, self._gb)
         self._scatter(lvl, self._gx if g is not None else None, L.x)
 
+    # -- wide halos: one exchange per sweep instead of one per colour -----------
+    # A whole multicolour sweep changes a point only through values at most 4 lines away (9-point,
+    # 4 colours; fewer for red-black).  A block therefore keeps, for relaxation only, copies of its
+    # arrays extended by WIDE = 5 lines towards every neighbour (4 recomputed redundantly + the
+    # outermost as frozen ghost line): fill them with ONE exchange, run the single-pass fused sweep
+    # (bmgx2_relax_GS_oop) on the extended arrays, and copy the block and its ghost ring back -- the
+    # ghost ring then already holds the neighbours' new values, bit for bit, so no exchange follows.
+    # WIDE is odd so that the extended array keeps the index parity (colouring) of the global grid.
+    WIDE = 5
+
+    def _build_ext(self, lvl):
+        dec, W = self.dec, self.WIDE
+        for b in self.owned:
+            _, _, nxl, nyl = dec.extent(lvl, b)
+            if min(nxl, nyl) < max(self.fuse_min, W):
+                return                                   # small level: per-colour passes
+        E = _Level()
+        E.x2, E.off = {}, {}
+        L = self.lv[lvl]
+        for b in self.owned:
+            _, _, nxl, nyl = dec.extent(lvl, b)
+            e = [(W - 1) if dec.neighbour(b, dx, dy) is not None else 0 for dx, dy in ((-1, 0), (1, 0), (0, -1), (0, 1))]
+            jj, ii = nyl + 2 + e[2] + e[3], nxl + 2 + e[0] + e[1]
+            E.off[b] = (e[0], e[2], nxl, nyl)
+            E.A[b] = self._zeros(L.A[b].shape[0], jj, ii)
+            E.sor[b] = self._zeros(2, jj, ii)
+            E.x[b], E.x2[b], E.b[b] = self._zeros(jj, ii), self._zeros(jj, ii), self._zeros(jj, ii)
+            self._centre(E, b, E.A[b]).copy_(L.A[b])
+            self._centre(E, b, E.sor[b]).copy_(L.sor[b])
+        self.ext[lvl] = E
+        self.exchange_wide(lvl, [E.A, E.sor])
+
+    @staticmethod
+    def _centre(E, b, t):
+        ox, oy, nxl, nyl = E.off[b]
+        return t[..., oy:oy + nyl + 2, ox:ox + nxl + 2]
+
+    def exchange_wide(self, lvl, arrs_list):
+        """fill the WIDE lines beyond every neighbour side of the extended arrays with the neighbours' own
+        values: columns first, then rows over the full extended width (which carries the corners)"""
+        dec, W, E = self.dec, self.WIDE, self.ext[lvl]
+        for phase in (0, 1):
+            msgs, unpack = [], []
+            for b in self.owned:
+                ox, oy, nxl, nyl = E.off[b]
+                for sgn in (-1, 1):
+                    nb = dec.neighbour(b, sgn if phase == 0 else 0, sgn if phase == 1 else 0)
+                    if nb is None:
+                        continue
+                    if phase == 0:     # own interior rows; own first / last WIDE interior columns <-> halo columns
+                        rows = slice(oy + 1, oy + 1 + nyl)
+                        send = (rows, slice(ox + 1, ox + 1 + W) if sgn < 0 else slice(ox + 1 + nxl - W, ox + 1 + nxl))
+                        recv = (rows, slice(ox + 1 - W, ox + 1) if sgn < 0 else slice(ox + 1 + nxl, ox + 1 + nxl + W))
+                    else:              # every column of the extended array
+                        cols = slice(None)
+                        send = (slice(oy + 1, oy + 1 + W) if sgn < 0 else slice(oy + 1 + nyl - W, oy + 1 + nyl), cols)
+                        recv = (slice(oy + 1 - W, oy + 1) if sgn < 0 else slice(oy + 1 + nyl, oy + 1 + nyl + W), cols)
+                    parts = [a[b][..., send[0], send[1]] for a in arrs_list]
+                    sbuf = torch.cat([q.reshape(-1) for q in parts])
+                    rbuf = torch.empty_like(sbuf)
+                    msgs.append((b, nb, ("w", phase, sgn), sbuf, None))
+                    msgs.append((nb, b, ("w", phase, -sgn), None, rbuf))
+                    unpack.append(([a[b][..., recv[0], recv[1]] for a in arrs_list], rbuf))
+            self.T.run(msgs)
+            for views, rbuf in unpack:
+                o = 0
+                for v in views:
+                    v.copy_(rbuf[o:o + v.numel()].reshape(v.shape))
+                    o += v.numel()
+            self.exchanges += 1
+
+    def _sweep_fused(self, lvl, x, b, updown):
+        E, K = self.ext[lvl], self.K
+        for blk in self.owned:
+            self._centre(E, blk, E.x[blk]).copy_(x[blk])
+            self._centre(E, blk, E.b[blk]).copy_(b[blk])
+        self.exchange_wide(lvl, [E.x, E.b])
+        for blk in self.owned:
+            K.relax_oop(E.A[blk], E.b[blk], E.x[blk], E.x2[blk], E.sor[blk], updown)
+            x[blk].copy_(self._centre(E, blk, E.x2[blk]))
+
     # -- the cycle (include/cedar/cycle/vcycle.h:57-115) ------------------------
     def _sweep(self, lvl, x, b, updown):
+        if lvl in self.ext:
+            return self._sweep_fused(lvl, x, b, updown)
         L, K = self.lv[lvl], self.K
         npass = 2 if L.A[self.owned[0]].shape[0] == 3 else 4
         for p in range(npass):

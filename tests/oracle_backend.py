@@ -30,6 +30,12 @@ class OracleKernels:
         assert self.L.orc2_relax_gs_pass(1, P(_n(A)), P(_n(b)), P(_n(x)), P(_n(sor)), ii, jj, 1, 1 if nst == 3 else 0,
                                          nst, 2, 1, updown, 0, p) == 0
 
+    def relax_oop(self, A, b, x, xout, sor, updown):
+        nst, jj, ii = A.shape
+        xout.copy_(x)
+        assert self.L.orc2_relax_gs(1, P(_n(A)), P(_n(b)), P(_n(xout)), P(_n(sor)), ii, jj, 1, 1 if nst == 3 else 0, nst,
+                                    2, 1, updown, 0) == 0
+
     def residual(self, A, b, x, r):
         nst, jj, ii = A.shape
         self.L.orc2_residual(0, P(_n(A)), P(_n(b)), P(_n(x)), P(_n(r)), ii, jj, 0, 1 if nst == 3 else 0, nst)

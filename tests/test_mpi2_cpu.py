@@ -74,8 +74,9 @@ CASES = [(65, 65, 2, 1, True, 9), (65, 65, 2, 2, True, 9), (129, 65, 4, 2, True,
          (65, 65, 2, 2, False, 9), (200, 131, 3, 2, False, 17), (33, 33, 2, 2, True, 100)]
 
 
+@pytest.mark.parametrize("fuse_min", [8, 10 ** 9])    # wide-halo fused sweeps on every big enough level / never
 @pytest.mark.parametrize("nx,ny,px,py,nine,agg", CASES)
-def test_multiblock_equals_serial(nx, ny, px, py, nine, agg):
+def test_multiblock_equals_serial(nx, ny, px, py, nine, agg, fuse_min):
     rng = np.random.default_rng(nx + ny + nine)
     so = random_op2(nx, ny, nine, rng)
     b = random_gf(nx, ny, rng)
@@ -83,8 +84,10 @@ def test_multiblock_equals_serial(nx, ny, px, py, nine, agg):
     xr, hr, r0r = ref.solve(b, maxiter=5, tol=1e-12)
     dec = m.Decomp2(nx, ny, px, py, ndist_for(nx, ny, agg))
     sol = m.DistSolver2(m.split_blocks(so, dec), nx, ny, (px, py), 2, 1, agglomerate=agg, kernels=OracleKernels(),
-                        coarse_factory=OracleCoarse)
+                        coarse_factory=OracleCoarse, fuse_min=fuse_min)
     assert sol.nlevels == ref.nlevels and sol.ndist == dec.ndist
+    if fuse_min == 8 and sol.ndist > 0 and min(nx // px, ny // py) >= 16:
+        assert 0 in sol.ext            # the fused path is what runs on the fine level
     for lvl in range(1, sol.ndist + 1):
         assert np.array_equal(m.join_blocks(sol.lv[lvl].A, dec, lvl), ref.level_array(lvl, "A")), lvl
         Pr = ref.level_array(lvl, "P").copy()
@@ -116,7 +119,7 @@ def _worker(rank, world, port, nx, ny, px, py, nine, agg, out):
         dec = m.Decomp2(nx, ny, px, py, ndist_for(nx, ny, agg))
         T = m.DistTransport(dec)
         sol = m.DistSolver2(m.split_blocks(so, dec, blocks=[rank]), nx, ny, (px, py), 2, 1, agglomerate=agg,
-                            transport=T, kernels=OracleKernels(), coarse_factory=OracleCoarse)
+                            transport=T, kernels=OracleKernels(), coarse_factory=OracleCoarse, fuse_min=8)
         x, h, r0 = sol.solve(m.split_blocks(b, dec, blocks=[rank]), maxiter=5, tol=1e-12)
         np.save(os.path.join(out, f"x{rank}.npy"), x[rank].numpy())
         if rank == 0:
