@@ -486,7 +486,7 @@ class DistSolver2:
             if min(nxl, nyl) < max(self.fuse_min, W):
                 return                                   # small level: per-colour passes
         E = _Level()
-        E.x2, E.off = {}, {}
+        E.x2, E.off, E.b_current = {}, {}, False
         L = self.lv[lvl]
         for b in self.owned:
             _, _, nxl, nyl = dec.extent(lvl, b)
@@ -542,10 +542,15 @@ class DistSolver2:
 
     def _sweep_fused(self, lvl, x, b, updown):
         E, K = self.ext[lvl], self.K
+        arrs = [E.x]
         for blk in self.owned:
             self._centre(E, blk, E.x[blk]).copy_(x[blk])
-            self._centre(E, blk, E.b[blk]).copy_(b[blk])
-        self.exchange_wide(lvl, [E.x, E.b])
+        if not E.b_current:          # the right-hand side of a level changes once per visit: it rides along once
+            for blk in self.owned:
+                self._centre(E, blk, E.b[blk]).copy_(b[blk])
+            arrs.append(E.b)
+            E.b_current = True
+        self.exchange_wide(lvl, arrs)
         for blk in self.owned:
             K.relax_oop(E.A[blk], E.b[blk], E.x[blk], E.x2[blk], E.sor[blk], updown)
             x[blk].copy_(self._centre(E, blk, E.x2[blk]))
@@ -563,6 +568,8 @@ class DistSolver2:
 
     def _ncycle(self, lvl, x, b):
         L, Cc, K = self.lv[lvl], self.lv[lvl + 1], self.K
+        if lvl in self.ext:
+            self.ext[lvl].b_current = False
         for _ in range(self.npre):
             self._sweep(lvl, x, b, DOWN)
         for blk in self.owned:
