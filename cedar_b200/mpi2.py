@@ -506,39 +506,51 @@ class DistSolver2:
         ox, oy, nxl, nyl = E.off[b]
         return t[..., oy:oy + nyl + 2, ox:ox + nxl + 2]
 
-    def exchange_wide(self, lvl, arrs_list):
-        """fill the WIDE lines beyond every neighbour side of the extended arrays with the neighbours' own
-        values: columns first, then rows over the full extended width (which carries the corners)"""
-        dec, W, E = self.dec, self.WIDE, self.ext[lvl]
-        for phase in (0, 1):
-            msgs, unpack = [], []
-            for b in self.owned:
-                ox, oy, nxl, nyl = E.off[b]
-                for sgn in (-1, 1):
-                    nb = dec.neighbour(b, sgn if phase == 0 else 0, sgn if phase == 1 else 0)
+    def _halo(self, lvl, arrs_list, geom, W):
+        """one-phase halo exchange with all (up to 8) neighbours: the W own lines next to a side (a W x W
+        corner for the diagonal neighbours) go into the neighbour's W halo lines.  geom(b) = (ox, oy): the
+        block's own interior starts at [oy + 1, ox + 1] of its arrays."""
+        dec = self.dec
+        msgs, unpack = [], []
+
+        def span(o, n, d, recv):
+            if d == 0:
+                return slice(o + 1, o + 1 + n)
+            if recv:
+                return slice(o + 1 - W, o + 1) if d < 0 else slice(o + 1 + n, o + 1 + n + W)
+            return slice(o + 1, o + 1 + W) if d < 0 else slice(o + 1 + n - W, o + 1 + n)
+
+        for b in self.owned:
+            ox, oy = geom(b)
+            _, _, nxl, nyl = dec.extent(lvl, b)
+            for dy in (-1, 0, 1):
+                for dx in (-1, 0, 1):
+                    nb = dec.neighbour(b, dx, dy) if (dx or dy) else None
                     if nb is None:
                         continue
-                    if phase == 0:     # own interior rows; own first / last WIDE interior columns <-> halo columns
-                        rows = slice(oy + 1, oy + 1 + nyl)
-                        send = (rows, slice(ox + 1, ox + 1 + W) if sgn < 0 else slice(ox + 1 + nxl - W, ox + 1 + nxl))
-                        recv = (rows, slice(ox + 1 - W, ox + 1) if sgn < 0 else slice(ox + 1 + nxl, ox + 1 + nxl + W))
-                    else:              # every column of the extended array
-                        cols = slice(None)
-                        send = (slice(oy + 1, oy + 1 + W) if sgn < 0 else slice(oy + 1 + nyl - W, oy + 1 + nyl), cols)
-                        recv = (slice(oy + 1 - W, oy + 1) if sgn < 0 else slice(oy + 1 + nyl, oy + 1 + nyl + W), cols)
-                    parts = [a[b][..., send[0], send[1]] for a in arrs_list]
-                    sbuf = torch.cat([q.reshape(-1) for q in parts])
+                    rs, cs = span(oy, nyl, dy, False), span(ox, nxl, dx, False)
+                    sbuf = torch.cat([a[b][..., rs, cs].reshape(-1) for a in arrs_list])
                     rbuf = torch.empty_like(sbuf)
-                    msgs.append((b, nb, ("w", phase, sgn), sbuf, None))
-                    msgs.append((nb, b, ("w", phase, -sgn), None, rbuf))
-                    unpack.append(([a[b][..., recv[0], recv[1]] for a in arrs_list], rbuf))
-            self.T.run(msgs)
-            for views, rbuf in unpack:
-                o = 0
-                for v in views:
-                    v.copy_(rbuf[o:o + v.numel()].reshape(v.shape))
-                    o += v.numel()
-            self.exchanges += 1
+                    msgs.append((b, nb, ("h", dx, dy), sbuf, None))
+                    msgs.append((nb, b, ("h", -dx, -dy), None, rbuf))
+                    rr, cr = span(oy, nyl, dy, True), span(ox, nxl, dx, True)
+                    unpack.append(([a[b][..., rr, cr] for a in arrs_list], rbuf))
+        self.T.run(msgs)
+        for views, rbuf in unpack:
+            o = 0
+            for v in views:
+                v.copy_(rbuf[o:o + v.numel()].reshape(v.shape))
+                o += v.numel()
+        self.exchanges += 1
+
+    def exchange_wide(self, lvl, arrs_list):
+        """fill the WIDE lines beyond every neighbour side of the extended arrays with the neighbours' own values"""
+        E = self.ext[lvl]
+        self._halo(lvl, arrs_list, lambda b: E.off[b][:2], self.WIDE)
+
+    def exchange1(self, lvl, arrs):
+        """the standard one-line ghost exchange of grid functions, all neighbours in one phase"""
+        self._halo(lvl, [arrs], lambda b: (0, 0), 1)
 
     def _sweep_fused(self, lvl, x, b, updown):
         E, K = self.ext[lvl], self.K
@@ -564,7 +576,7 @@ class DistSolver2:
         for p in range(npass):
             for blk in self.owned:
                 K.relax_pass(L.A[blk], b[blk], x[blk], L.sor[blk], updown, p)
-            self.exchange(lvl, x)
+            self.exchange1(lvl, x)
 
     def _ncycle(self, lvl, x, b):
         L, Cc, K = self.lv[lvl], self.lv[lvl + 1], self.K
@@ -574,7 +586,7 @@ class DistSolver2:
             self._sweep(lvl, x, b, DOWN)
         for blk in self.owned:
             K.residual(L.A[blk], b[blk], x[blk], L.res[blk])
-        self.exchange(lvl, L.res)
+        self.exchange1(lvl, L.res)
         for blk in self.owned:
             K.restrict(L.res[blk], Cc.b[blk], Cc.P[blk])
             Cc.x[blk].zero_()
@@ -582,10 +594,10 @@ class DistSolver2:
             self._coarse_solve()
         else:
             self._ncycle(lvl + 1, Cc.x, Cc.b)
-        self.exchange(lvl + 1, Cc.x)
+        self.exchange1(lvl + 1, Cc.x)
         for blk in self.owned:
             K.interp_add(x[blk], Cc.x[blk], L.res[blk], L.A[blk], Cc.P[blk])
-        self.exchange(lvl, x)
+        self.exchange1(lvl, x)
         for _ in range(self.npost):
             self._sweep(lvl, x, b, UP)
 
