@@ -41,15 +41,30 @@ k_setup_lines(const double *__restrict__ so_d, const double *__restrict__ so_o, 
     if (l > nlines - 2) return;
     const double *pd = so_d + l * sl, *po = so_o + l * sl;
     double *D = sor + (size_t)l * dl, *L = sor + plane + (size_t)l * dl;
-    // DPTTRF(n-2, D(1..), L(2..)) on d(p)=diag(p), e(p)=-off(p+1)
+    // DPTTRF(n-2, D(1..), L(2..)) on d(p)=diag(p), e(p)=-off(p+1).  The recurrence is sequential, its operands
+    // are not: they are fetched 16 positions ahead so that the chain never waits for memory
     double d = pd[(size_t)1 * sp];
-    for (unsigned p = 1; p + 1 <= n - 2; p++) {
-        double ei = -po[(size_t)(p + 1) * sp];
-        double dn = pd[(size_t)(p + 1) * sp];
-        D[p] = d;
-        double e = ei / d;
-        L[p + 1] = e;
-        d = dn - e * ei;
+    constexpr unsigned U = 16;
+    for (unsigned p0 = 1; p0 + 1 <= n - 2; p0 += U) {
+        double eo[U], dn[U];
+#pragma unroll
+        for (unsigned u = 0; u < U; u++) {
+            const unsigned p = p0 + u;
+            const bool ok = p + 1 <= n - 2;
+            eo[u] = ok ? __ldg(po + (size_t)(p + 1) * sp) : 0.0;
+            dn[u] = ok ? __ldg(pd + (size_t)(p + 1) * sp) : 0.0;
+        }
+#pragma unroll
+        for (unsigned u = 0; u < U; u++) {
+            const unsigned p = p0 + u;
+            if (p + 1 <= n - 2) {
+                const double ei = -eo[u];
+                D[p] = d;
+                const double e = ei / d;
+                L[p + 1] = e;
+                d = dn[u] - e * ei;
+            }
+        }
     }
     D[n - 2] = d;
     L[1] = -po[(size_t)1 * sp];  // SOR(2,j,2) = -SO(2,j,KW): stored, never used by the solve
