@@ -8,8 +8,11 @@ kernels.  Default workload = BASELINE.json configs[1]: 2D 9-point (gallery::fe)
 4097^2, 4-colour point relaxation, V(1,1).
 
   value   MDOF/s, device-resident (b, x and the hierarchy already in HBM)
-  e2e     MDOF/s through the host-buffer API: b and x copied H2D from pinned
-          memory and x copied D2H inside every timed step
+  e2e     MDOF/s through the host-buffer API (include/cedar_capi.h): a stream
+          of right-hand sides in pinned host memory; every timed step uploads
+          its b and downloads its x (x0 = 0), copies overlapped with the
+          cycles of the neighbouring steps; e2e.single_call = one synchronous
+          call at a time (no overlap)
   setup   one-off Galerkin setup time (interpolation + RAP on every level)
   solve   full solve to `tol` (iterations, ms)
   roofline   the dominant kernel (fine-level point-GS sweep) timed alone
@@ -373,20 +376,36 @@ def main():
     barrier()
 
     # ---- end to end through the host-buffer API ----------------------------
+    # (a) a stream of right-hand sides through cdr2_solver_vcycle_batch: every step uploads its b from pinned host
+    #     memory and downloads its x (x0 = 0, so there is no x to upload); the copies of step k+1 / k-1 overlap the
+    #     cycle of step k on separate streams.  A ring of 4 pinned b/x pairs stands for the stream.
+    ring = 4
+    pbs, pxs = sol.pinned_grid_funcs(ring), sol.pinned_grid_funcs(ring)
+    for k in range(ring):
+        pbs[k][...] = b
+    bl = [pbs[k % ring] for k in range(a.steps)]
+    xl = [pxs[k % ring] for k in range(a.steps)]
+    sol.vcycle_batch(bl[:ring], xl[:ring])          # warm-up (allocates the staging buffers and streams)
+    barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    sol.vcycle_batch(bl, xl)                          # returns when the last x has arrived on the host
+    ms_e2e = (time.perf_counter() - t0) / a.steps * 1e3
+    # (b) one right-hand side at a time (latency of a single synchronous call): H2D b, cycle, D2H x
     hb, hx = sol.buffers()
     hb[...] = b
     for _ in range(2):
-        hx[...] = 0.0
-        sol.vcycle_pinned()
+        sol.vcycle0_pinned()
     barrier()
-    t_e2e = 0.0
+    t_one = 0.0
     for _ in range(a.steps):
-        hx[...] = 0.0            # host-side reset of the iterate, outside the timed region
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        sol.vcycle_pinned()      # H2D b, H2D x, cycle, D2H x (synchronises)
-        t_e2e += time.perf_counter() - t0
-    ms_e2e = t_e2e / a.steps * 1e3
+        sol.vcycle0_pinned()
+        t_one += time.perf_counter() - t0
+    ms_one = t_one / a.steps * 1e3
+    e2e_check = float(np.max(np.abs(pxs[(a.steps - 1) % ring] - hx)))   # same b, same x0: must be identical
+    del pbs, pxs, bl, xl
     bytes_gf = (n + 2) * (n + 2) * 8
 
     # ---- full solve to tol (device resident) -------------------------------
@@ -412,8 +431,12 @@ def main():
             "config": dict(workload(a), parallelism=("1 GPU" if world == 1 else
                                                      f"{world} independent replicas (one {n}^2 problem per GPU)")),
             "e2e": {"value": world * dofs / (ms_e2e * 1e-3) / 1e6, "unit": "MDOF/s", "ms_per_step": ms_e2e,
-                    "h2d_bytes_per_step": 2 * bytes_gf, "d2h_bytes_per_step": bytes_gf,
-                    "call": "cdr2_solver_vcycle_pinned (pinned host b,x -> device -> x back)"},
+                    "h2d_bytes_per_step": bytes_gf, "d2h_bytes_per_step": bytes_gf,
+                    "call": "cdr2_solver_vcycle_batch: a stream of right-hand sides in pinned host memory, x0 = 0; every "
+                            "step uploads its b and downloads its x, copies overlapped with the neighbouring steps' cycles",
+                    "single_call": {"ms_per_step": ms_one, "value": world * dofs / (ms_one * 1e-3) / 1e6,
+                                    "call": "cdr2_solver_vcycle0_pinned (synchronous: H2D b, cycle, D2H x)"},
+                    "max_abs_diff_batch_vs_single": e2e_check},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "setup": {"ms": setup_first_s * 1e3, "what": "operator upload + interpolation + Galerkin RAP on all levels "

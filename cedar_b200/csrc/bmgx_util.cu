@@ -192,6 +192,7 @@ extern "C" int bmgx_device_sync(void) { RT(cudaDeviceSynchronize(), "bmgx_device
 extern "C" int bmgx_event_create(void **ev) { RT(cudaEventCreate((cudaEvent_t *)ev), "bmgx_event_create"); }
 extern "C" int bmgx_event_destroy(void *ev) { RT(cudaEventDestroy((cudaEvent_t)ev), "bmgx_event_destroy"); }
 extern "C" int bmgx_event_record(void *ev, bmgx_stream_t s) { RT(cudaEventRecord((cudaEvent_t)ev, (cudaStream_t)s), "bmgx_event_record"); }
+extern "C" int bmgx_stream_wait_event(bmgx_stream_t s, void *ev) { RT(cudaStreamWaitEvent((cudaStream_t)s, (cudaEvent_t)ev, 0), "bmgx_stream_wait_event"); }
 extern "C" int bmgx_event_sync(void *ev) { RT(cudaEventSynchronize((cudaEvent_t)ev), "bmgx_event_sync"); }
 extern "C" int bmgx_event_elapsed_ms(void *a, void *b, float *ms) { RT(cudaEventElapsedTime(ms, (cudaEvent_t)a, (cudaEvent_t)b), "bmgx_event_elapsed_ms"); }
 

@@ -156,6 +156,13 @@ void dual_buffer::swap_device(dual_buffer &o)
 	hvalid = o.hvalid = false;
 }
 
+void dual_buffer::zero_device()
+{
+	if (!d) gpu::check(bmgx_malloc(&d, nbytes), "array alloc");
+	gpu::check(bmgx_memset0(d, nbytes, gpu::stream()), "array zero");
+	dvalid = true; hvalid = false;
+}
+
 void dual_buffer::zero()
 {
 	if (d && (dvalid || !h)) {

@@ -36,12 +36,47 @@ lib.cdr2_solve_host.argtypes = [C.c_int, C.c_uint, C.c_uint, _dp, _dp, _dp, C.c_
 lib.cdr2_solver_buffers.argtypes = [C.c_void_p, C.POINTER(_dp), C.POINTER(_dp)]
 lib.cdr2_solver_vcycle_pinned.argtypes = [C.c_void_p]
 lib.cdr2_solver_solve_pinned.argtypes = [C.c_void_p, _dp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double)]
+lib.cdr2_solver_vcycle0_pinned.argtypes = [C.c_void_p]
+lib.cdr2_solver_vcycle_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(_dp), C.POINTER(_dp)]
+lib.cdr_pinned_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
+lib.cdr_pinned_free.argtypes = [C.c_void_p]
 lib.cdr_set_log.argtypes = [C.c_char_p]
 lib.cdr2_solver_vcycle_dev.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
 
 
 class CedarError(RuntimeError):
     pass
+
+
+class PinnedArrays:
+    """float64 arrays in pinned host memory (cdr_pinned_alloc); ``arrays`` are numpy views, valid while this
+    object lives."""
+
+    def __init__(self, n, shape):
+        self.ptrs, self.arrays = [], []
+        count = int(np.prod(shape))
+        for _ in range(n):
+            p = C.c_void_p()
+            if lib.cdr_pinned_alloc(C.byref(p), count * 8) != 0:
+                raise CedarError(lib.cdr_last_error().decode())
+            self.ptrs.append(p)
+            a = np.ctypeslib.as_array(C.cast(p, _dp), shape=(count,)).reshape(shape)
+            a[...] = 0.0
+            self.arrays.append(a)
+
+    def __iter__(self):
+        return iter(self.arrays)
+
+    def __getitem__(self, i):
+        return self.arrays[i]
+
+    def __len__(self):
+        return len(self.arrays)
+
+    def __del__(self):
+        for p in self.ptrs:
+            lib.cdr_pinned_free(p)
+        self.ptrs = []
 
 
 def _check(rc):
@@ -149,6 +184,25 @@ class Solver2:
     def vcycle_pinned(self):
         """upload b, x from the pinned buffers; one cycle; download x"""
         _check(lib.cdr2_solver_vcycle_pinned(self.h))
+
+    def vcycle0_pinned(self):
+        """upload b from the pinned buffer; x0 = 0 on the device; one cycle; download x"""
+        _check(lib.cdr2_solver_vcycle0_pinned(self.h))
+
+    def pinned_grid_funcs(self, n):
+        """n pinned host arrays of the solver's grid-function shape (freed with the returned owner)"""
+        shape = (self.op.ny + 2, self.op.nx + 2)
+        return PinnedArrays(n, shape)
+
+    def vcycle_batch(self, bs, xs):
+        """One cycle from x0 = 0 for each right-hand side of ``bs``, results into ``xs`` (lists of C-contiguous
+        float64 arrays, ideally from pinned_grid_funcs); copies of consecutive right-hand sides overlap the cycles."""
+        n = len(bs)
+        assert len(xs) == n
+        pb = (_dp * n)(*[_P(a) for a in bs])
+        px = (_dp * n)(*[_P(a) for a in xs])
+        _check(lib.cdr2_solver_vcycle_batch(self.h, n, pb, px))
+        return xs
 
     def solve_pinned(self, maxiter_cap=1000):
         hist = np.zeros(maxiter_cap)

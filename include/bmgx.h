@@ -75,6 +75,7 @@ int bmgx_event_create(void **ev);
 int bmgx_event_destroy(void *ev);
 int bmgx_event_record(void *ev, bmgx_stream_t s);
 int bmgx_event_sync(void *ev);
+int bmgx_stream_wait_event(bmgx_stream_t s, void *ev);   /* work enqueued on s after this call waits for ev */
 int bmgx_event_elapsed_ms(void *start, void *stop, float *ms);
 /* CUDA-graph capture of a sequence of bmgx calls (one V-cycle) */
 int bmgx_graph_begin(bmgx_stream_t s);

@@ -45,6 +45,7 @@ public:
 	const void *dev_ro() const;           // valid device copy
 	void swap_device(dual_buffer &o);     // both end up device-valid, host stale
 	void zero();                          // all zero, wherever the data lives
+	void zero_device();                   // all zero on the device (a memset on the stream), host marked stale
 	bool on_device() const { return dvalid; }
 	const void *raw_dev() const { return d; }
 	// While a recorder is installed (CUDA-graph capture of a cycle) every
@@ -144,6 +145,7 @@ public:
 	// device pointers
 	data_type *dev() { return static_cast<data_type *>(buf.dev_rw()); }
 	const data_type *cdev() const { return static_cast<const data_type *>(buf.dev_ro()); }
+	void zero_device() { buf.zero_device(); }
 	void swap_device(aarray &o)
 	{
 		assert(size() == o.size());

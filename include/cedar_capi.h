@@ -61,6 +61,18 @@ int cdr2_solver_vcycle_dev(cdr2_solver *solver, const double *b_dev, double *x_d
 int cdr2_solver_buffers(cdr2_solver *solver, double **b, double **x);
 int cdr2_solver_vcycle_pinned(cdr2_solver *solver);
 int cdr2_solver_solve_pinned(cdr2_solver *solver, double *hist, int hist_cap, int *niter, double *res0);
+/* zero initial guess (what multilevel::solve(b) of the reference starts from, include/cedar/multilevel.h:278-286):
+ * uploads b only, clears x on the device, one cycle, downloads x into the pinned buffer */
+int cdr2_solver_vcycle0_pinned(cdr2_solver *solver);
+
+/* A stream of right-hand sides.  For k < nrhs: one cycle from a zero initial guess on b[k], result in x[k]
+ * (host pointers, (nx+2)(ny+2) doubles each).  The upload of b[k+1], the cycle on b[k] and the download of x[k-1]
+ * run concurrently (two copy streams, two device staging buffers each way), provided the host arrays are pinned
+ * (cdr_pinned_alloc); pageable arrays work but serialise.  Returns when x[nrhs-1] has arrived.  Every x[k] is
+ * identical to what cdr2_solver_vcycle0_pinned gives for b[k]. */
+int cdr2_solver_vcycle_batch(cdr2_solver *solver, int nrhs, const double *const *b, double *const *x);
+int cdr_pinned_alloc(void **p, size_t bytes);
+int cdr_pinned_free(void *p);
 
 /* device-resident timing: keeps b and x on the GPU, runs `warmup` + `n` cycles
  * (x reset to 0 before each), returns the mean device time per cycle in ms

@@ -115,3 +115,36 @@ def test_fcycle_runs(cs):
     # the reference's F-cycle restarts from x = 0 on every call (fcycle.h:77-78), so
     # repeating it is idempotent: one FMG pass reaches a few percent and stays there
     assert h[0] < 0.05 and abs(h[-1] - h[0]) <= 1e-12
+
+
+@pytest.mark.parametrize("graph", [True, False])
+def test_vcycle_batch_matches_single_calls(cs, graph):
+    """A stream of right-hand sides through cdr2_solver_vcycle_batch (copies overlapped with the cycles on
+    separate streams) gives, for every right-hand side, exactly the V-cycle of the oracle from x0 = 0."""
+    nx, ny = 257, 200
+    so = oracle.gallery2("fe", nx, ny)
+    ref = oracle.Solver2(so, "point", 1, 1)
+    sol = cs.Solver2(cs.Operator2(so), relaxation="point", nrelax_pre=1, nrelax_post=1, cuda_graph=graph)
+    nrhs = 7
+    rng = np.random.default_rng(77)
+    bs = sol.pinned_grid_funcs(nrhs)
+    xs = sol.pinned_grid_funcs(nrhs)
+    for k in range(nrhs):
+        bs[k][1:-1, 1:-1] = rng.standard_normal((ny, nx))
+        xs[k][...] = 123.0            # must be overwritten, not used as an initial guess
+    sol.vcycle_batch(list(bs), list(xs))
+    hb, hx = sol.buffers()
+    for k in range(nrhs):
+        xr = np.zeros_like(bs[k])
+        ref.vcycle(xr, bs[k].copy())
+        assert_bitwise(xs[k], xr, f"rhs {k}")
+        hb[...] = bs[k]
+        hx[...] = 55.0
+        sol.vcycle0_pinned()
+        assert_bitwise(hx, xr, f"vcycle0 rhs {k}")
+    # pageable host arrays are accepted too
+    b2 = [np.array(bs[k]) for k in range(3)]
+    x2 = [np.empty_like(b2[k]) for k in range(3)]
+    sol.vcycle_batch(b2, x2)
+    for k in range(3):
+        assert_bitwise(x2[k], xs[k], f"pageable rhs {k}")
