@@ -243,22 +243,34 @@ def run_multi(a, torch, dist, world, rank, local):
     ms_dev = sum(s.elapsed_time(e) for s, e in zip(e0, e1)) / a.steps
     launches = sol.K.launches - l0
     exchanges = sol.exchanges - ex0
-    # end to end: local b and x from pinned host memory, local x back, every step
-    t_e2e = 0.0
+    # end to end (a): a stream of right-hand sides, this rank's block of each from pinned host memory and its block
+    # of the solution back, every step; copies overlapped with the neighbouring steps' cycles (x0 = 0: no x upload)
+    ring = 2
+    bhs = [bh] + [bh.clone().pin_memory() for _ in range(ring - 1)]
+    xhs = [xh] + [torch.zeros_like(bh).pin_memory() for _ in range(ring - 1)]
+    bl = [bhs[k % ring] for k in range(a.steps)]
+    xl = [xhs[k % ring] for k in range(a.steps)]
+    sol.vcycle_stream(x, b, bl[:3], xl[:3], graphed=not a.no_graph)
+    barrier()
+    t0 = time.perf_counter()
+    sol.vcycle_stream(x, b, bl, xl, graphed=not a.no_graph)
+    ms_e2e = (time.perf_counter() - t0) / a.steps * 1e3
+    # (b) one right-hand side at a time: H2D b, cycle, D2H x, synchronous
+    t_one = 0.0
     for i in range(a.steps + 2):
-        xh.zero_()
         barrier()
         t0 = time.perf_counter()
         with torch.cuda.stream(sol.stream):
             b[rank].copy_(bh, non_blocking=True)
-            x[rank].copy_(xh, non_blocking=True)
+            x[rank].zero_()
         cycle(x, b)
         with torch.cuda.stream(sol.stream):
             xh.copy_(x[rank], non_blocking=True)
         sol.stream.synchronize()
         if i >= 2:
-            t_e2e += time.perf_counter() - t0
-    ms_e2e = t_e2e / a.steps * 1e3
+            t_one += time.perf_counter() - t0
+    ms_one = t_one / a.steps * 1e3
+    e2e_check = float((xhs[(a.steps - 1) % ring] - xh).abs().max())
     # full solve to tol
     barrier()
     t0 = time.perf_counter()
@@ -266,9 +278,9 @@ def run_multi(a, torch, dist, world, rank, local):
     torch.cuda.synchronize()
     ms_solve = (time.perf_counter() - t0) * 1e3
     clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([ms_dev, ms_e2e, ms_solve], dtype=torch.float64, device="cuda")
+    t = torch.tensor([ms_dev, ms_e2e, ms_solve, ms_one, e2e_check], dtype=torch.float64, device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_dev, ms_e2e, ms_solve = [float(v) for v in t.tolist()]
+    ms_dev, ms_e2e, ms_solve, ms_one, e2e_check = [float(v) for v in t.tolist()]
     if rank == 0:
         peaks = {}
         try:
@@ -289,8 +301,13 @@ def run_multi(a, torch, dist, world, rank, local):
                                       f"levels <= {a.agglomerate} agglomerated on rank 0",
                        "l2": "inputs larger than L2 (each block's fine level is > 1 GB)"},
             "e2e": {"value": dofs / (ms_e2e * 1e-3) / 1e6, "unit": "MDOF/s", "ms_per_step": ms_e2e,
-                    "h2d_bytes_per_step": 2 * loc * world, "d2h_bytes_per_step": loc * world,
-                    "call": "DistSolver2.vcycle on pinned host blocks (b, x H2D; x D2H) per rank"},
+                    "h2d_bytes_per_step": loc * world, "d2h_bytes_per_step": loc * world,
+                    "call": "DistSolver2.vcycle_stream: a stream of right-hand sides, every rank's block of b from pinned "
+                            "host memory and its block of x back per step (x0 = 0), copies overlapped with the "
+                            "neighbouring steps' cycles",
+                    "single_call": {"ms_per_step": ms_one, "value": dofs / (ms_one * 1e-3) / 1e6,
+                                    "call": "H2D b block, DistSolver2.vcycle, D2H x block, synchronous"},
+                    "max_abs_diff_batch_vs_single": e2e_check},
             "gpu_launches": int(launches), "ghost_exchanges_per_step": exchanges / a.steps,
             "clocks": clocks,
             "setup": {"ms": setup_s * 1e3, "what": "block upload + distributed interpolation/Galerkin setup + agglomerated serial setup"},

@@ -28,6 +28,7 @@ CPU tests of the host logic inject ``tests/oracle_backend.py`` explicitly.
 """
 import ctypes as C
 import math
+import types
 
 import numpy as np
 import torch
@@ -639,6 +640,47 @@ class DistSolver2:
             g.replay()
         self.K.launches += self._graph_cost[0]
         self.exchanges += self._graph_cost[1]
+
+    def vcycle_stream(self, x, b, bhs, xhs, graphed=True):
+        """A stream of right-hand sides from and to pinned host memory (this rank's block of each): for every
+        pair (bh, xh) one cycle from x0 = 0 on bh, the result in xh.  The upload of the next right-hand side and
+        the download of the previous solution run on their own streams while the cycle (kernels + NCCL ghost
+        exchanges) runs on the solver's; device staging is double-buffered each way.  Host-API counterpart of
+        cdr2_solver_vcycle_batch (include/cedar_capi.h) for the block-decomposed solver; all ranks call it with
+        the same number of pairs."""
+        (r,) = self.owned
+        st = getattr(self, "_stage", None)
+        if st is None:
+            st = self._stage = types.SimpleNamespace(
+                up=torch.cuda.Stream(), down=torch.cuda.Stream(),
+                db=[torch.empty_like(b[r]) for _ in range(2)], dx=[torch.empty_like(x[r]) for _ in range(2)],
+                b_ready=[torch.cuda.Event() for _ in range(2)], b_free=[torch.cuda.Event() for _ in range(2)],
+                x_ready=[torch.cuda.Event() for _ in range(2)], x_free=[torch.cuda.Event() for _ in range(2)])
+        cyc = self.vcycle_graphed if graphed else self.vcycle
+        for k, (bh, xh) in enumerate(zip(bhs, xhs)):
+            q = k & 1
+            with torch.cuda.stream(st.up):
+                if k >= 2:
+                    st.up.wait_event(st.b_free[q])
+                st.db[q].copy_(bh, non_blocking=True)
+                st.b_ready[q].record()
+            with torch.cuda.stream(self.stream):
+                self.stream.wait_event(st.b_ready[q])
+                b[r].copy_(st.db[q])
+                st.b_free[q].record()
+                x[r].zero_()
+            cyc(x, b)
+            with torch.cuda.stream(self.stream):
+                if k >= 2:
+                    self.stream.wait_event(st.x_free[q])
+                st.dx[q].copy_(x[r])
+                st.x_ready[q].record()
+            with torch.cuda.stream(st.down):
+                st.down.wait_event(st.x_ready[q])
+                xh.copy_(st.dx[q], non_blocking=True)
+                st.x_free[q].record()
+        st.down.synchronize()
+        self.stream.synchronize()
 
     def _norm(self, arrs):
         tot = self._zeros(1)

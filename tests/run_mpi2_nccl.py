@@ -2,6 +2,7 @@
 serial GPU solver on the same problem -- solution bitwise, history to 1e-10.
     python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 tests/run_mpi2_nccl.py"""
 import os
+import threading
 import sys
 
 import numpy as np
@@ -47,8 +48,36 @@ def main():
         if rank == 0:
             print(f"{nx}x{ny} {px}x{py} ndist={nd}: bitwise={bool(flag.item())} hist={h}", flush=True)
         ok = ok and bool(flag.item())
+        # a stream of right-hand sides through vcycle_stream == the same cycles one call at a time
+        bl = {rank: torch.from_numpy(np.ascontiguousarray(m.split_blocks(b, dec, blocks=[rank])[rank])).cuda()}
+        xl = {rank: torch.zeros_like(bl[rank])}
+        bhs = [(bl[rank] * (k + 1)).cpu().pin_memory() for k in range(5)]
+        xhs = [torch.full_like(h_, 7.0).pin_memory() for h_ in bhs]
+        for graphed in (False, True):
+            sol.vcycle_stream(xl, bl, bhs, xhs, graphed=graphed)
+            good = True
+            for k in range(5):
+                with torch.cuda.stream(sol.stream):
+                    bl[rank].copy_(bhs[k], non_blocking=True)
+                    xl[rank].zero_()
+                sol.vcycle(xl, bl)
+                torch.cuda.synchronize()
+                good = good and torch.equal(xl[rank].cpu(), xhs[k])
+            flag = torch.tensor([int(good)], device="cuda")
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if rank == 0:
+                print(f"  vcycle_stream graphed={graphed}: bitwise={bool(flag.item())}", flush=True)
+            ok = ok and bool(flag.item())
+        # captured graphs hold NCCL work: release them before the process group goes away
+        if hasattr(sol, "_graphs"):
+            sol._graphs.clear()
+        torch.cuda.synchronize()
+        dist.barrier()
     if rank == 0:
         print("MPI2 NCCL OK" if ok else "MPI2 NCCL FAILED", flush=True)
+    killer = threading.Timer(20.0, lambda: os._exit(0 if ok else 1))   # never let teardown hang the run
+    killer.daemon = True
+    killer.start()
     dist.destroy_process_group()
     sys.exit(0 if ok else 1)
 
