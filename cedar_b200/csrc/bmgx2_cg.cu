@@ -99,6 +99,7 @@ extern "C" int bmgx2_SETUP_cg_LU(const double *so, bmgx_len ii, bmgx_len jj, int
 __global__ void k_solve_cg(double *q, const double *__restrict__ qf, unsigned II, unsigned JJ,
                            const double *__restrict__ abd, double *bbd, unsigned nabd1)
 {
+    pdl_wait();
     if (threadIdx.x != 0) return;
     int I1 = II - 1, J1 = JJ - 1;
     q += (size_t)blockIdx.x * II * JJ; qf += (size_t)blockIdx.x * II * JJ;   // batch entry
@@ -134,7 +135,7 @@ extern "C" int bmgx2_SOLVE_cg(double *q, const double *qf, bmgx_len ii, bmgx_len
 {
     (void)nabd2;
     if (jpn != BMGX_BCs_definite) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SOLVE_cg: only definite, non-periodic");
-    k_solve_cg<<<bmgx_batch(), 32, 0, (cudaStream_t)s>>>(q, qf, ii, jj, abd, bbd, nabd1);
+    launch_pdl(k_solve_cg, dim3(bmgx_batch()), dim3(32), 0, (cudaStream_t)s, q, qf, ii, jj, abd, bbd, nabd1);
     BMGX_LAUNCH_CHECK("SOLVE_cg");
     return BMGX_OK;
 }

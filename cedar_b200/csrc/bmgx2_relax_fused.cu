@@ -120,6 +120,7 @@ template <bool ODDFIRST>
 __global__ void __launch_bounds__(RF_NT, 4)
 k_relax9_fused(Grid g, const double *__restrict__ qin, double *__restrict__ qout, int band_h)
 {
+    pdl_wait();
     __shared__ double ring[RF_RING][RF_W + 2];
     const int t = threadIdx.x;
     const int II = g.II, JJ = g.JJ, I1 = II - 1, J1 = JJ - 1;
@@ -175,6 +176,7 @@ template <bool BLACKFIRST>
 __global__ void __launch_bounds__(RF_NT, 4)
 k_relax5_fused(Grid g, const double *__restrict__ qin, double *__restrict__ qout, int band_h)
 {
+    pdl_wait();
     __shared__ double ring[RF_RING][RF_W + 2];
     const int t = threadIdx.x;
     const int II = g.II, JJ = g.JJ, I1 = II - 1, J1 = JJ - 1;
@@ -262,11 +264,11 @@ extern "C" int bmgx2_relax_GS_oop(int k, const double *so, const double *qf, con
     dim3 grid(nstrips, (jj + band_h - 1) / band_h);
     cudaStream_t st = (cudaStream_t)s;
     if (nine) {
-        if (fwd) k_relax9_fused<false><<<grid, RF_NT, 0, st>>>(g, q_in, q_out, (int)band_h);
-        else k_relax9_fused<true><<<grid, RF_NT, 0, st>>>(g, q_in, q_out, (int)band_h);
+        if (fwd) launch_pdl(k_relax9_fused<false>, grid, dim3(RF_NT), 0, st, g, q_in, q_out, (int)band_h);
+        else launch_pdl(k_relax9_fused<true>, grid, dim3(RF_NT), 0, st, g, q_in, q_out, (int)band_h);
     } else {
-        if (fwd) k_relax5_fused<false><<<grid, RF_NT, 0, st>>>(g, q_in, q_out, (int)band_h);
-        else k_relax5_fused<true><<<grid, RF_NT, 0, st>>>(g, q_in, q_out, (int)band_h);
+        if (fwd) launch_pdl(k_relax5_fused<false>, grid, dim3(RF_NT), 0, st, g, q_in, q_out, (int)band_h);
+        else launch_pdl(k_relax5_fused<true>, grid, dim3(RF_NT), 0, st, g, q_in, q_out, (int)band_h);
     }
     BMGX_LAUNCH_CHECK("relax_GS_oop");
     return BMGX_OK;

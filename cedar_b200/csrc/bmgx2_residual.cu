@@ -7,6 +7,7 @@ __global__ void __launch_bounds__(256)
 k_residual(const double *__restrict__ so, const double *__restrict__ qf, const double *__restrict__ q,
            double *__restrict__ res, unsigned II, unsigned JJ)
 {
+    pdl_wait();
     unsigned i = blockIdx.x * blockDim.x + threadIdx.x + 2;
     unsigned j = blockIdx.y * blockDim.y + threadIdx.y + 2;
     if (i > II - 1 || j > JJ - 1) return;
@@ -31,9 +32,9 @@ extern "C" int bmgx2_residual(int k, const double *so, const double *qf, const d
     if (ii < 3 || jj < 3) return BMGX_OK;
     dim3 b(128, 2), g(cdiv(ii - 2, 128), cdiv(jj - 2, 2), bmgx_batch());
     if (k < kf || ifd != 1)
-        k_residual<true><<<g, b, 0, (cudaStream_t)s>>>(so, qf, q, res, ii, jj);
+        launch_pdl(k_residual<true>, g, b, 0, (cudaStream_t)s, so, qf, q, res, ii, jj);
     else
-        k_residual<false><<<g, b, 0, (cudaStream_t)s>>>(so, qf, q, res, ii, jj);
+        launch_pdl(k_residual<false>, g, b, 0, (cudaStream_t)s, so, qf, q, res, ii, jj);
     BMGX_LAUNCH_CHECK("residual");
     return BMGX_OK;
 }

@@ -7,6 +7,7 @@ __global__ void __launch_bounds__(256)
 k_restrict(const double *__restrict__ q, double *__restrict__ qc, const double *__restrict__ ci,
            unsigned Nx, unsigned Ny, unsigned Nxc, unsigned Nyc)
 {
+    pdl_wait();
     unsigned ic = blockIdx.x * blockDim.x + threadIdx.x + 2;
     unsigned jc = blockIdx.y * blockDim.y + threadIdx.y + 2;
     if (ic > Nxc - 1 || jc > Nyc - 1) return;
@@ -33,7 +34,7 @@ extern "C" int bmgx2_restrict(const double *q, double *qc, const double *ci, bmg
     if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "restrict: periodic BCs not supported");
     if (nxc < 3 || nyc < 3) return BMGX_OK;
     dim3 b(64, 4), g(cdiv(nxc - 2, 64), cdiv(nyc - 2, 4), bmgx_batch());
-    k_restrict<<<g, b, 0, (cudaStream_t)s>>>(q, qc, ci, nx, ny, nxc, nyc);
+    launch_pdl(k_restrict, g, b, 0, (cudaStream_t)s, q, qc, ci, nx, ny, nxc, nyc);
     BMGX_LAUNCH_CHECK("restrict");
     return BMGX_OK;
 }
@@ -52,6 +53,7 @@ k_interp_add(double *__restrict__ q, const double *__restrict__ qc, double *__re
              const double *__restrict__ so, const double *__restrict__ ci,
              unsigned IIC, unsigned JJC, unsigned IIF, unsigned JJF)
 {
+    pdl_wait();
     const unsigned ic = blockIdx.x * blockDim.x + threadIdx.x + 2;
     const unsigned jc = blockIdx.y * blockDim.y + threadIdx.y + 2;
     if (ic > IIF / 2 + 1 || jc > JJF / 2 + 1) return;
@@ -105,7 +107,7 @@ extern "C" int bmgx2_interp_add(double *q, const double *qc, double *res, const 
     if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "interp_add: periodic BCs not supported");
     if (iif < 3 || jjf < 3) return BMGX_OK;
     dim3 b(64, 4), g(cdiv(iif / 2, 64), cdiv(jjf / 2, 4), bmgx_batch());
-    k_interp_add<<<g, b, 0, (cudaStream_t)s>>>(q, qc, res, so, ci, iic, jjc, iif, jjf);
+    launch_pdl(k_interp_add, g, b, 0, (cudaStream_t)s, q, qc, res, so, ci, iic, jjc, iif, jjf);
     BMGX_LAUNCH_CHECK("interp_add");
     return BMGX_OK;
 }

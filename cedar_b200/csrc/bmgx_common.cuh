@@ -29,6 +29,30 @@ unsigned bmgx_batch();
         bmgx_count_launch();                                              \
     } while (0)
 
+// Programmatic dependent launch for the chains of small kernels on the coarse levels of a cycle: a kernel launched
+// through launch_pdl may become resident while its predecessor on the stream is still running; it executes
+// pdl_wait() before it touches memory (the predecessor has then completed and its writes are visible), so the
+// launch latency of kernel N+1 is paid while kernel N runs.  Captured into CUDA graphs as programmatic edges.
+// Every kernel launched this way calls pdl_wait() first (completion of N+1 then implies completion of N).
+// Opt-in: BMGX_PDL=1 in the environment (default: plain stream order; pdl_wait() is then a no-op).
+bool bmgx_pdl_enabled();
+template <typename... P, typename... A>
+static inline void launch_pdl(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A &&...args)
+{
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = bmgx_pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kern, static_cast<A &&>(args)...);
+}
+__device__ __forceinline__ void pdl_wait()
+{
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+
 static inline bool bmgx_nonperiodic(int jpn) { return jpn == BMGX_BCs_definite || jpn == BMGX_BCs_indef_nonper; }
 static inline unsigned cdiv(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
 
