@@ -7,6 +7,7 @@
 #include <cedar_capi.h>
 #include <cedar/2d/solver.h>
 #include <cedar/2d/gallery.h>
+#include "batch_stage.h"
 
 using namespace cedar;
 using namespace cedar::cdr2;
@@ -20,37 +21,6 @@ struct cdr2_operator
 	std::unique_ptr<stencil_op<five_pt>> five;
 	std::unique_ptr<stencil_op<nine_pt>> nine;
 	unsigned nx, ny;
-};
-
-// device staging for cdr2_solver_vcycle_batch: right-hand sides arrive in db[], solutions leave from dx[]
-struct batch_stage
-{
-	void *db[2] = {nullptr, nullptr}, *dx[2] = {nullptr, nullptr};
-	bmgx_stream_t up = nullptr, down = nullptr;
-	void *b_ready[2] = {}, *b_free[2] = {}, *x_ready[2] = {}, *x_free[2] = {};
-	bool live = false;
-	void init(size_t bytes)
-	{
-		if (live) return;
-		for (int q = 0; q < 2; q++) {
-			gpu::check(bmgx_malloc(&db[q], bytes), "batch staging");
-			gpu::check(bmgx_malloc(&dx[q], bytes), "batch staging");
-			gpu::check(bmgx_event_create(&b_ready[q]), "event"); gpu::check(bmgx_event_create(&b_free[q]), "event");
-			gpu::check(bmgx_event_create(&x_ready[q]), "event"); gpu::check(bmgx_event_create(&x_free[q]), "event");
-		}
-		gpu::check(bmgx_stream_create(&up), "stream"); gpu::check(bmgx_stream_create(&down), "stream");
-		live = true;
-	}
-	~batch_stage()
-	{
-		if (!live) return;
-		for (int q = 0; q < 2; q++) {
-			bmgx_free(db[q]); bmgx_free(dx[q]);
-			bmgx_event_destroy(b_ready[q]); bmgx_event_destroy(b_free[q]);
-			bmgx_event_destroy(x_ready[q]); bmgx_event_destroy(x_free[q]);
-		}
-		bmgx_stream_destroy(up); bmgx_stream_destroy(down);
-	}
 };
 
 struct cdr2_solver
@@ -261,32 +231,8 @@ int cdr2_solver_vcycle0_pinned(cdr2_solver *s)
 int cdr2_solver_vcycle_batch(cdr2_solver *s, int nrhs, const double *const *b, double *const *x)
 {
 	return guard([&] {
-		const size_t bytes = s->b.size() * sizeof(double);
-		batch_stage &st = s->stage;
-		st.init(bytes);
-		bmgx_stream_t cs = gpu::stream();
-		for (int k = 0; k < nrhs; k++) {
-			const int q = k & 1;
-			// upload stream: b[k] into its staging slot once the cycle two steps back has taken the slot's contents
-			if (k >= 2) gpu::check(bmgx_stream_wait_event(st.up, st.b_free[q]), "batch wait");
-			gpu::check(bmgx_memcpy_h2d(st.db[q], b[k], bytes, st.up), "batch upload");
-			gpu::check(bmgx_event_record(st.b_ready[q], st.up), "batch record");
-			// compute stream: the solver's own b and x (the cycle's CUDA graph is bound to their device buffers)
-			gpu::check(bmgx_stream_wait_event(cs, st.b_ready[q]), "batch wait");
-			gpu::check(bmgx_memcpy_d2d(s->b.dev(), st.db[q], bytes, cs), "batch b");
-			gpu::check(bmgx_event_record(st.b_free[q], cs), "batch record");
-			s->x.zero_device();
-			if (s->s5) s->s5->vcycle(s->x, s->b); else s->s9->vcycle(s->x, s->b);
-			if (k >= 2) gpu::check(bmgx_stream_wait_event(cs, st.x_free[q]), "batch wait");
-			gpu::check(bmgx_memcpy_d2d(st.dx[q], s->x.cdev(), bytes, cs), "batch x");
-			gpu::check(bmgx_event_record(st.x_ready[q], cs), "batch record");
-			// download stream
-			gpu::check(bmgx_stream_wait_event(st.down, st.x_ready[q]), "batch wait");
-			gpu::check(bmgx_memcpy_d2h(x[k], st.dx[q], bytes, st.down), "batch download");
-			gpu::check(bmgx_event_record(st.x_free[q], st.down), "batch record");
-		}
-		gpu::check(bmgx_stream_sync(st.down), "batch sync");
-		gpu::check(bmgx_stream_sync(cs), "batch sync");
+		run_batch(s->stage, s->b, s->x, nrhs, b, x,
+		          [&] { if (s->s5) s->s5->vcycle(s->x, s->b); else s->s9->vcycle(s->x, s->b); });
 	});
 }
 

@@ -6,6 +6,7 @@
 #include <cedar_capi.h>
 #include <cedar/3d/solver.h>
 #include <cedar/3d/gallery.h>
+#include "batch_stage.h"
 
 using namespace cedar;
 using namespace cedar::cdr3;
@@ -26,6 +27,7 @@ struct cdr3_solver
 	std::unique_ptr<solver<seven_pt>> s7;
 	std::unique_ptr<solver<xxvii_pt>> s27;
 	grid_func b, x;
+	batch_stage stage;
 	template <class F> auto each(F &&f) { return s7 ? f(*s7) : f(*s27); }
 };
 
@@ -202,6 +204,23 @@ int cdr3_solver_vcycle_pinned(cdr3_solver *s)
 		s->b.data(); s->x.data();
 		s->each([&](auto &sv) { sv.vcycle(s->x, s->b); return 0; });
 		s->x.cdata();
+	});
+}
+
+int cdr3_solver_vcycle0_pinned(cdr3_solver *s)
+{
+	return guard([&] {
+		s->b.data();
+		s->x.zero_device();
+		s->each([&](auto &sv) { sv.vcycle(s->x, s->b); return 0; });
+		s->x.cdata();
+	});
+}
+
+int cdr3_solver_vcycle_batch(cdr3_solver *s, int nrhs, const double *const *b, double *const *x)
+{
+	return guard([&] {
+		run_batch(s->stage, s->b, s->x, nrhs, b, x, [&] { s->each([&](auto &sv) { sv.vcycle(s->x, s->b); return 0; }); });
 	});
 }
 

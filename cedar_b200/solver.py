@@ -257,6 +257,8 @@ lib.cdr3_solver_solve.argtypes = [_vp, _dp, _dp, _dp, C.c_int, C.POINTER(C.c_int
 lib.cdr3_solver_vcycle.argtypes = [_vp, _dp, _dp]
 lib.cdr3_solver_buffers.argtypes = [_vp, C.POINTER(_dp), C.POINTER(_dp)]
 lib.cdr3_solver_vcycle_pinned.argtypes = [_vp]
+lib.cdr3_solver_vcycle0_pinned.argtypes = [_vp]
+lib.cdr3_solver_vcycle_batch.argtypes = [_vp, C.c_int, C.POINTER(_dp), C.POINTER(_dp)]
 lib.cdr3_solver_time_vcycles.argtypes = [_vp, _dp, C.c_int, C.c_int, C.POINTER(C.c_float)]
 lib.cdr3_solver_time_solves.argtypes = [_vp, _dp, C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int)]
 
@@ -337,6 +339,22 @@ class Solver3:
 
     def vcycle_pinned(self):
         _check(lib.cdr3_solver_vcycle_pinned(self.h))
+
+    def vcycle0_pinned(self):
+        """upload b from the pinned buffer; x0 = 0 on the device; one cycle; download x"""
+        _check(lib.cdr3_solver_vcycle0_pinned(self.h))
+
+    def pinned_grid_funcs(self, n):
+        return PinnedArrays(n, (self.op.nz + 2, self.op.ny + 2, self.op.nx + 2))
+
+    def vcycle_batch(self, bs, xs):
+        """3D counterpart of Solver2.vcycle_batch"""
+        n = len(bs)
+        assert len(xs) == n
+        pb = (_dp * n)(*[_P(a) for a in bs])
+        px = (_dp * n)(*[_P(a) for a in xs])
+        _check(lib.cdr3_solver_vcycle_batch(self.h, n, pb, px))
+        return xs
 
     def time_vcycles(self, b, warmup=3, n=10):
         ms = C.c_float()

@@ -106,6 +106,8 @@ int cdr3_solver_solve(cdr3_solver *solver, const double *b, double *x, double *h
 int cdr3_solver_vcycle(cdr3_solver *solver, const double *b, double *x);
 int cdr3_solver_buffers(cdr3_solver *solver, double **b, double **x);
 int cdr3_solver_vcycle_pinned(cdr3_solver *solver);
+int cdr3_solver_vcycle0_pinned(cdr3_solver *solver);   /* x0 = 0: uploads b only */
+int cdr3_solver_vcycle_batch(cdr3_solver *solver, int nrhs, const double *const *b, double *const *x);
 int cdr3_solver_time_vcycles(cdr3_solver *solver, const double *b, int warmup, int n, float *ms_per_cycle);
 int cdr3_solver_time_solves(cdr3_solver *solver, const double *b, int warmup, int n, float *ms_per_solve, int *niter);
 

@@ -14,7 +14,7 @@ from tests.util import (assert_bitwise, coarse_n, dev, host, ptr, random_gf, ran
 
 pytestmark = pytest.mark.gpu
 
-SIZES = [(1, 1), (2, 3), (3, 3), (7, 5), (16, 16), (31, 31), (37, 64), (130, 97), (400, 257), (1030, 301), (245, 30), (246, 33), (247, 18)]
+SIZES = [(1, 1), (2, 3), (3, 3), (7, 5), (16, 16), (31, 31), (37, 64), (58, 58), (58, 59), (1, 40), (40, 1), (130, 97), (400, 257), (1030, 301), (245, 30), (246, 33), (247, 18)]
 
 
 @pytest.fixture(scope="module")
