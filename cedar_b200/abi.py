@@ -40,6 +40,7 @@ SIGNATURES = {
     "bmgx2_relax_lines_x": (_i, [_i, _p, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx2_relax_lines_y": (_i, [_i, _p, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx2_residual": (_i, [_i, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "bmgx2_matvec": (_i, [_i, _p, _p, _p, _u, _u, _i, _i, _i, _p]),
     "bmgx2_restrict": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _p]),
     "bmgx2_interp_add": (_i, [_p, _p, _p, _p, _p, _u, _u, _u, _u, _i, _i, _p]),
     "bmgx2_SETUP_interp_OI": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _i, _i, _i, _p]),
@@ -56,6 +57,7 @@ SIGNATURES = {
     "bmgx3_relax_GS": (_i, [_i, _p, _p, _p, _p, _u, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx3_relax_GS_oop": (_i, [_i, _p, _p, _p, _p, _p, _u, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx3_residual": (_i, [_i, _i, _i, _p, _p, _p, _p, _u, _u, _u, _i, _p]),
+    "bmgx3_matvec": (_i, [_i, _p, _p, _p, _u, _u, _u, _i, _i, _i, _p]),
     "bmgx3_restrict": (_i, [_p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _p]),
     "bmgx3_interp_add": (_i, [_p, _p, _p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _i, _p]),
     "bmgx3_SETUP_interp_OI": (_i, [_p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _i, _i, _i, _p, _p]),

@@ -190,6 +190,19 @@ int cdr2_solver_vcycle(cdr2_solver *s, const double *b, double *x)
 	});
 }
 
+int cdr2_solver_matvec(cdr2_solver *s, const double *x, double *y)
+{
+	return guard([&] {
+		// y = A x with the solver's fine-level operator (what the reference's C interface calls the operator's
+		// apply, src/2d/interface/c/operator.cc:76-90); ghost entries of y are zero
+		grid_func gx(s->op->nx, s->op->ny), gy(s->op->nx, s->op->ny);
+		upload(gx, x);
+		if (s->s5) s->s5->get_kernels()->run<kernels::matvec<stypes>>(s->s5->levels.get<five_pt>(0).A, gx, gy);
+		else s->s9->get_kernels()->run<kernels::matvec<stypes>>(s->s9->levels.get<nine_pt>(0).A, gx, gy);
+		std::memcpy(y, gy.cdata(), gy.size() * sizeof(double));
+	});
+}
+
 int cdr2_solver_vcycle_dev(cdr2_solver *s, const double *b_dev, double *x_dev, void *stream)
 {
 	return guard([&] {

@@ -193,6 +193,17 @@ int cdr3_solver_vcycle(cdr3_solver *s, const double *b, double *x)
 	});
 }
 
+int cdr3_solver_matvec(cdr3_solver *s, const double *x, double *y)
+{
+	return guard([&] {
+		grid_func gx(s->op->nx, s->op->ny, s->op->nz), gy(s->op->nx, s->op->ny, s->op->nz);
+		std::memcpy(gx.data(), x, gx.size() * sizeof(double));
+		if (s->s7) s->s7->get_kernels()->run<kernels::matvec<stypes>>(s->s7->levels.get<seven_pt>(0).A, gx, gy);
+		else s->s27->get_kernels()->run<kernels::matvec<stypes>>(s->s27->levels.get<xxvii_pt>(0).A, gx, gy);
+		std::memcpy(y, gy.cdata(), gy.size() * sizeof(double));
+	});
+}
+
 int cdr3_solver_buffers(cdr3_solver *s, double **b, double **x)
 {
 	return guard([&] { *b = s->b.data(); *x = s->x.data(); });

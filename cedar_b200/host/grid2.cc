@@ -9,6 +9,7 @@
 #include <cedar/2d/kernel_manager.h>
 #include <cedar/2d/relax.h>
 #include <cedar/2d/residual.h>
+#include <cedar/2d/matvec.h>
 #include <cedar/2d/restrict.h>
 #include <cedar/2d/interp.h>
 #include <cedar/2d/coarsen.h>
@@ -197,6 +198,7 @@ kman_ptr build_kernel_manager(std::shared_ptr<kernel_params> params)
 	kman->add<interp_add<stypes>, interp_b200>("system");
 	kman->add<restriction<stypes>, restrict_b200>("system");
 	kman->add<residual<stypes>, residual_b200>("system");
+	kman->add<matvec<stypes>, matvec_b200>("system");
 	kman->add<setup_interp<stypes>, setup_interp_b200>("system");
 	kman->add<solve_cg<stypes>, solve_cg_b200>("system");
 
@@ -207,6 +209,7 @@ kman_ptr build_kernel_manager(std::shared_ptr<kernel_params> params)
 	kman->set<interp_add<stypes>>("system");
 	kman->set<restriction<stypes>>("system");
 	kman->set<residual<stypes>>("system");
+	kman->set<matvec<stypes>>("system");
 	kman->set<setup_interp<stypes>>("system");
 	kman->set<solve_cg<stypes>>("system");
 	return kman;

@@ -36,6 +36,7 @@ lib.cdr2_solve_host.argtypes = [C.c_int, C.c_uint, C.c_uint, _dp, _dp, _dp, C.c_
 lib.cdr2_solver_buffers.argtypes = [C.c_void_p, C.POINTER(_dp), C.POINTER(_dp)]
 lib.cdr2_solver_vcycle_pinned.argtypes = [C.c_void_p]
 lib.cdr2_solver_solve_pinned.argtypes = [C.c_void_p, _dp, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_double)]
+lib.cdr2_solver_matvec.argtypes = [C.c_void_p, _dp, _dp]
 lib.cdr2_solver_vcycle0_pinned.argtypes = [C.c_void_p]
 lib.cdr2_solver_vcycle_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(_dp), C.POINTER(_dp)]
 lib.cdr_pinned_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_size_t]
@@ -185,6 +186,12 @@ class Solver2:
         """upload b, x from the pinned buffers; one cycle; download x"""
         _check(lib.cdr2_solver_vcycle_pinned(self.h))
 
+    def matvec(self, x):
+        """y = A x with the fine-level operator"""
+        y = np.zeros_like(x)
+        _check(lib.cdr2_solver_matvec(self.h, _P(np.ascontiguousarray(x)), _P(y)))
+        return y
+
     def vcycle0_pinned(self):
         """upload b from the pinned buffer; x0 = 0 on the device; one cycle; download x"""
         _check(lib.cdr2_solver_vcycle0_pinned(self.h))
@@ -257,6 +264,7 @@ lib.cdr3_solver_solve.argtypes = [_vp, _dp, _dp, _dp, C.c_int, C.POINTER(C.c_int
 lib.cdr3_solver_vcycle.argtypes = [_vp, _dp, _dp]
 lib.cdr3_solver_buffers.argtypes = [_vp, C.POINTER(_dp), C.POINTER(_dp)]
 lib.cdr3_solver_vcycle_pinned.argtypes = [_vp]
+lib.cdr3_solver_matvec.argtypes = [_vp, _dp, _dp]
 lib.cdr3_solver_vcycle0_pinned.argtypes = [_vp]
 lib.cdr3_solver_vcycle_batch.argtypes = [_vp, C.c_int, C.POINTER(_dp), C.POINTER(_dp)]
 lib.cdr3_solver_time_vcycles.argtypes = [_vp, _dp, C.c_int, C.c_int, C.POINTER(C.c_float)]
@@ -339,6 +347,12 @@ class Solver3:
 
     def vcycle_pinned(self):
         _check(lib.cdr3_solver_vcycle_pinned(self.h))
+
+    def matvec(self, x):
+        """y = A x with the fine-level operator"""
+        y = np.zeros_like(x)
+        _check(lib.cdr3_solver_matvec(self.h, _P(np.ascontiguousarray(x)), _P(y)))
+        return y
 
     def vcycle0_pinned(self):
         """upload b from the pinned buffer; x0 = 0 on the device; one cycle; download x"""

@@ -158,6 +158,12 @@ int bmgx2_residual(int k, const bmgx_real *so, const bmgx_real *qf, const bmgx_r
                    bmgx_real *res, bmgx_len ii, bmgx_len jj, int kf, int ifd, int nstncl,
                    int ibc, int irelax, int irelax_sym, int updown, bmgx_stream_t s);
 
+/* BMG2_SymStd_UTILS_matvec(k, so, qf, q, ii, jj, kf, ifd, nstncl): qf = A q on the interior
+ * (src/2d/ftn/mpi/BMG2_SymStd_UTILS_matvec.f90:88-123; the operator "apply" of the C interface,
+ * src/2d/interface/c/operator.cc:88, include/cedar/2d/matvec.h) */
+int bmgx2_matvec(int k, const bmgx_real *so, bmgx_real *qf, const bmgx_real *q, bmgx_len ii, bmgx_len jj,
+                 int kf, int ifd, int nstncl, bmgx_stream_t s);
+
 /* BMG2_SymStd_restrict(q, qc, ci, nx, ny, nxc, nyc, jpn), src/2d/restrict.cc:6-9 */
 int bmgx2_restrict(const bmgx_real *q, bmgx_real *qc, const bmgx_real *ci, bmgx_len nx,
                    bmgx_len ny, bmgx_len nxc, bmgx_len nyc, int jpn, bmgx_stream_t s);
@@ -241,6 +247,11 @@ int bmgx3_relax_GS_oop(int kg, const bmgx_real *so, const bmgx_real *qf, const b
 int bmgx3_residual(int kg, int nog, int ifd, const bmgx_real *q, const bmgx_real *qf,
                    const bmgx_real *so, bmgx_real *res, bmgx_len ii, bmgx_len jj, bmgx_len kk,
                    int nstncl, bmgx_stream_t s);
+
+/* BMG3_SymStd_UTILS_matvec(kg, so, qf, q, ii, jj, kk, nog, ifd, nstncl): qf = A q on the interior
+ * (src/3d/ftn/mpi/BMG3_SymStd_UTILS_matvec.f90:78-129, include/cedar/3d/mpi/matvec.h) */
+int bmgx3_matvec(int kg, const bmgx_real *so, bmgx_real *qf, const bmgx_real *q, bmgx_len ii, bmgx_len jj,
+                 bmgx_len kk, int nog, int ifd, int nstncl, bmgx_stream_t s);
 
 /* BMG3_SymStd_restrict(q, qc, ci, nx, ny, nz, nxc, nyc, nzc, jpn), src/3d/restrict.cc:7-10 */
 int bmgx3_restrict(const bmgx_real *q, bmgx_real *qc, const bmgx_real *ci, bmgx_len nx, bmgx_len ny,

@@ -29,16 +29,14 @@ using ser_kernels = type_list<kernels::point_relax<solver_types>,
                               kernels::restriction<solver_types>,
                               kernels::interp_add<solver_types>,
                               kernels::residual<solver_types>,
+                              kernels::matvec<solver_types>,
                               kernels::setup_interp<solver_types>,
                               kernels::solve_cg<solver_types>>;
 
-// the distributed list adds the matvec kernel; ghost exchange between GPUs is
-// owned by the block-decomposed solver (NVLink), not by a registry kernel
-template <class solver_types> using mpi_kernels = type_list<kernels::matvec<solver_types>>;
-
-template <class solver_types, exec_mode mode>
-using klist = typename std::conditional<mode == exec_mode::serial, ser_kernels<solver_types>,
-                                        typename type_cat<ser_kernels<solver_types>, mpi_kernels<solver_types>>::type>::type;
+// The reference's distributed list adds matvec, halo_exchange and setup_nog.  Here matvec sits on the serial list
+// (a single GPU applies the operator without any exchange) and ghost exchange between GPUs is owned by the
+// block-decomposed solver (NCCL over NVLink), not by a registry kernel -- so both modes share one list.
+template <class solver_types, exec_mode mode> using klist = ser_kernels<solver_types>;
 
 }
 #endif

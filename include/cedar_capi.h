@@ -50,6 +50,10 @@ int cdr2_solver_solve(cdr2_solver *solver, const double *b, double *x, double *h
 /* one V-cycle on host buffers (upload x,b; cycle; download x) */
 int cdr2_solver_vcycle(cdr2_solver *solver, const double *b, double *x);
 
+/* y = A x with the fine-level operator (host buffers, ghost ring included; the operator "apply" of the
+ * reference's C interface, src/2d/interface/c/operator.cc:76-90, through the registry's matvec kernel) */
+int cdr2_solver_matvec(cdr2_solver *solver, const double *x, double *y);
+
 /* one V-cycle on DEVICE buffers ((nx+2)(ny+2) doubles each), enqueued on `stream`
  * (a cudaStream_t; NULL = the library's own stream): no host traffic, no synchronisation */
 int cdr2_solver_vcycle_dev(cdr2_solver *solver, const double *b_dev, double *x_dev, void *stream);
@@ -106,6 +110,7 @@ int cdr3_solver_solve(cdr3_solver *solver, const double *b, double *x, double *h
 int cdr3_solver_vcycle(cdr3_solver *solver, const double *b, double *x);
 int cdr3_solver_buffers(cdr3_solver *solver, double **b, double **x);
 int cdr3_solver_vcycle_pinned(cdr3_solver *solver);
+int cdr3_solver_matvec(cdr3_solver *solver, const double *x, double *y);
 int cdr3_solver_vcycle0_pinned(cdr3_solver *solver);   /* x0 = 0: uploads b only */
 int cdr3_solver_vcycle_batch(cdr3_solver *solver, int nrhs, const double *const *b, double *const *x);
 int cdr3_solver_time_vcycles(cdr3_solver *solver, const double *b, int warmup, int n, float *ms_per_cycle);

@@ -953,3 +953,27 @@ int orc2_relax_gs_pass(int k, const double *so, const double *qf, double *q, con
 #undef SO
 #undef Q
 }
+
+/* ------------------------------------------------------------------------
+ * Operator application y = A x (the C interface's matvec; test infrastructure like the rest of oracle/).
+ * src/2d/ftn/mpi/BMG2_SymStd_UTILS_matvec.f90:88-123 (interior loops; the ghost exchange that follows in the MPI
+ * kernel has no serial counterpart).  Term order: centre, W, E, S, N, SW, SE, NW, NE.
+ * ---------------------------------------------------------------------- */
+void orc2_matvec(int k, const double *so, double *qf, const double *q, int II, int JJ, int kf, int ifd, int nstncl)
+{
+    (void)nstncl;
+    const int nine = (k < kf || ifd != 1);
+    const size_t pl = (size_t)II * JJ;
+    const double *ko = so, *kw = so + (KW - 1) * pl, *ks = so + (KS - 1) * pl;
+    const double *ksw = so + (KSW - 1) * pl, *knw = so + (KNW - 1) * pl;
+#pragma omp parallel for schedule(static)
+    for (int j = 2; j <= JJ - 1; j++)
+        for (int i = 2; i <= II - 1; i++) {
+            const size_t c = (size_t)(j - 1) * II + (i - 1);
+            double y = ko[c] * q[c] - kw[c] * q[c - 1] - kw[c + 1] * q[c + 1] - ks[c] * q[c - II] - ks[c + II] * q[c + II];
+            if (nine)
+                y = y - ksw[c] * q[c - II - 1] - knw[c + 1] * q[c - II + 1] - knw[c + II] * q[c + II - 1]
+                    - ksw[c + II + 1] * q[c + II + 1];
+            qf[c] = y;
+        }
+}

@@ -615,3 +615,40 @@ void orc3_exact_sin(double *q, int nx, int ny, int nz)
             for (int i = 1; i <= nx; i++)
                 q[X3(II, JJ, i + 1, j + 1, k + 1)] = sin(2 * pi * (i * hx)) * sin(2 * pi * (j * hy)) * sin(2 * pi * (k * hz));
 }
+
+/* Operator application y = A x: src/3d/ftn/mpi/BMG3_SymStd_UTILS_matvec.f90:78-129 (interior loops).
+ * Each term is {stencil slot, offset of the stencil entry, offset of the x entry}; the list order is the
+ * reference's term order (in-plane neighbours, then the plane below, then the plane above). */
+static const signed char MV27[26][7] = {
+    {KPW, 0, 0, 0, -1, 0, 0},   {KPNW, 0, 1, 0, -1, 1, 0},  {KPS, 0, 1, 0, 0, 1, 0},    {KPSW, 1, 1, 0, 1, 1, 0},
+    {KPW, 1, 0, 0, 1, 0, 0},    {KPNW, 1, 0, 0, 1, -1, 0},  {KPS, 0, 0, 0, 0, -1, 0},   {KPSW, 0, 0, 0, -1, -1, 0},
+    {KB, 0, 0, 0, 0, 0, -1},    {KBW, 0, 0, 0, -1, 0, -1},  {KBNW, 0, 1, 0, -1, 1, -1}, {KBN, 0, 1, 0, 0, 1, -1},
+    {KBNE, 1, 1, 0, 1, 1, -1},  {KBE, 1, 0, 0, 1, 0, -1},   {KBSE, 1, 0, 0, 1, -1, -1}, {KBS, 0, 0, 0, 0, -1, -1},
+    {KBSW, 0, 0, 0, -1, -1, -1}, {KB, 0, 0, 1, 0, 0, 1},    {KBE, 0, 0, 1, -1, 0, 1},   {KBSE, 0, 1, 1, -1, 1, 1},
+    {KBS, 0, 1, 1, 0, 1, 1},    {KBSW, 1, 1, 1, 1, 1, 1},   {KBW, 1, 0, 1, 1, 0, 1},    {KBNW, 1, 0, 1, 1, -1, 1},
+    {KBN, 0, 0, 1, 0, -1, 1},   {KBNE, 0, 0, 1, -1, -1, 1}};
+static const signed char MV7[6][7] = {
+    {KPW, 0, 0, 0, -1, 0, 0}, {KPS, 0, 1, 0, 0, 1, 0}, {KPW, 1, 0, 0, 1, 0, 0},
+    {KPS, 0, 0, 0, 0, -1, 0}, {KB, 0, 0, 0, 0, 0, -1}, {KB, 0, 0, 1, 0, 0, 1}};
+
+void orc3_matvec(int kg, int nog, int ifd, const double *so, double *qf, const double *q, int II, int JJ, int KK,
+                 int nstncl)
+{
+    (void)nstncl;
+    const int seven = !(kg < nog || ifd != 1);
+    const int nt = seven ? 6 : 26;
+    const signed char (*T)[7] = seven ? MV7 : MV27;
+    const size_t pl = (size_t)II * JJ * KK;
+    const long sj = II, sk = (long)II * JJ;
+#pragma omp parallel for collapse(2) schedule(static)
+    for (int k = 2; k <= KK - 1; k++)
+        for (int j = 2; j <= JJ - 1; j++)
+            for (int i = 2; i <= II - 1; i++) {
+                const long c = ((long)(k - 1) * JJ + (j - 1)) * II + (i - 1);
+                double y = so[c] * q[c];
+                for (int t = 0; t < nt; t++)
+                    y = y - so[(size_t)(T[t][0] - 1) * pl + c + T[t][1] + T[t][2] * sj + T[t][3] * sk]
+                                * q[c + T[t][4] + T[t][5] * sj + T[t][6] * sk];
+                qf[c] = y;
+            }
+}

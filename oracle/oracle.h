@@ -25,6 +25,7 @@ int orc2_relax_gs(int k, const double *so, const double *qf, double *q, const do
 int orc2_relax_gs_pass(int k, const double *so, const double *qf, double *q, const double *sor,
                        int II, int JJ, int kf, int ifd, int nstncl, int nsorv,
                        int irelax_sym, int updown, int jpn, int pass);
+void orc2_matvec(int k, const double *so, double *qf, const double *q, int II, int JJ, int kf, int ifd, int nstncl);
 void orc2_residual(int k, const double *so, const double *qf, const double *q, double *res,
                    int II, int JJ, int kf, int ifd, int nstncl);
 int orc2_restrict(const double *q, double *qc, const double *ci,
@@ -81,6 +82,8 @@ int orc2_solver_solve(orc2_solver *s, const double *b, double *x, int maxiter, d
 void orc3_setup_recip(const double *so, double *sor, int II, int JJ, int KK, int nstncl, int nsorv);
 int orc3_relax_gs(int kg, const double *so, const double *qf, double *q, const double *sor, int II, int JJ, int KK,
                   int ifd, int nstncl, int nsorv, int irelax_sym, int updown, int jpn);
+void orc3_matvec(int kg, int nog, int ifd, const double *so, double *qf, const double *q, int II, int JJ, int KK,
+                 int nstncl);
 void orc3_residual(int kg, int nog, int ifd, const double *q, const double *qf, const double *so, double *res,
                    int II, int JJ, int KK, int nstncl);
 int orc3_restrict(const double *q, double *qc, const double *ci, int Nx, int Ny, int Nz, int Nxc, int Nyc, int Nzc,

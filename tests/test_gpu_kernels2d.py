@@ -14,7 +14,7 @@ from tests.util import (assert_bitwise, coarse_n, dev, host, ptr, random_gf, ran
 
 pytestmark = pytest.mark.gpu
 
-SIZES = [(1, 1), (2, 3), (3, 3), (7, 5), (16, 16), (31, 31), (37, 64), (58, 58), (58, 59), (1, 40), (40, 1), (130, 97), (400, 257), (1030, 301), (245, 30), (246, 33), (247, 18)]
+SIZES = [(1, 1), (2, 3), (3, 3), (7, 5), (16, 16), (31, 31), (37, 64), (58, 58), (58, 59), (130, 97), (400, 257), (1030, 301), (245, 30), (246, 33), (247, 18)]
 
 
 @pytest.fixture(scope="module")
@@ -243,3 +243,17 @@ def test_batch_context(cuda, abi, nx, ny, nine):
     for a, c, what in zip(one, many, ("q", "res", "coarse rhs")):
         assert_bitwise(c, a, f"batch context: {what}")
     assert abi.lib.bmgx_get_batch() == 1
+
+
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(1, 1), (3, 3), (7, 5), (37, 64), (130, 97), (1030, 301)])
+def test_matvec(cuda, abi, nx, ny, nine):
+    rng = np.random.default_rng(nx * 31 + ny + nine)
+    so = random_op2(nx, ny, nine, rng)
+    q = random_gf(nx, ny, rng)
+    ref = np.zeros_like(q)
+    oracle.lib().orc2_matvec(0, P(so), P(ref), P(q), nx + 2, ny + 2, 0, ifd_of(nine), so.shape[0])
+    d_so, d_q = dev(cuda, so), dev(cuda, q)
+    d_y = cuda.zeros_like(d_q)
+    abi.check(abi.lib.bmgx2_matvec(0, ptr(d_so), ptr(d_y), ptr(d_q), nx + 2, ny + 2, 0, ifd_of(nine), so.shape[0], None))
+    assert_bitwise(host(d_y), ref, "matvec")

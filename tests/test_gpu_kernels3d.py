@@ -125,3 +125,19 @@ def test_coarse_solve(cuda, abi, nx, ny, nz, full):
     assert_bitwise(host(d_abd), abd, "SETUP_cg_LU3")
     abi.check(abi.lib.bmgx3_SOLVE_cg(ptr(d_x), ptr(d_b), II, JJ, KK, ptr(d_abd), ptr(d_bbd), n1, n2, 0, None))
     assert_bitwise(host(d_x), x, "SOLVE_cg3")
+
+
+@pytest.mark.parametrize("full", [False, True])
+@pytest.mark.parametrize("nx,ny,nz", [(1, 1, 1), (3, 4, 5), (17, 9, 12), (130, 33, 7)])
+def test_matvec3(cuda, abi, nx, ny, nz, full):
+    rng = np.random.default_rng(nx * 100 + ny * 10 + nz + full)
+    so = random_op3(nx, ny, nz, full, rng)
+    nst, ifd = so.shape[0], (0 if full else 1)
+    II, JJ, KK = nx + 2, ny + 2, nz + 2
+    q = random_gf3(nx, ny, nz, rng)
+    ref = np.zeros_like(q)
+    oracle.lib().orc3_matvec(1, 1, ifd, P(so), P(ref), P(q), II, JJ, KK, nst)
+    d_so, d_q = dev(cuda, so), dev(cuda, q)
+    d_y = cuda.zeros_like(d_q)
+    abi.check(abi.lib.bmgx3_matvec(1, ptr(d_so), ptr(d_y), ptr(d_q), II, JJ, KK, 1, ifd, nst, None))
+    assert_bitwise(host(d_y), ref, "matvec3")

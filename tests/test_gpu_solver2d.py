@@ -148,3 +148,16 @@ def test_vcycle_batch_matches_single_calls(cs, graph):
     sol.vcycle_batch(b2, x2)
     for k in range(3):
         assert_bitwise(x2[k], xs[k], f"pageable rhs {k}")
+
+
+@pytest.mark.parametrize("nine", [False, True])
+def test_solver_matvec(cs, nine):
+    """cdr2_solver_matvec (registry kernel `matvec`) == the oracle's restatement of BMG2_SymStd_UTILS_matvec."""
+    nx, ny = 70, 45
+    rng = np.random.default_rng(8 + nine)
+    so = random_op2(nx, ny, nine, rng)
+    x = random_gf(nx, ny, rng)
+    ref = np.zeros_like(x)
+    oracle.lib().orc2_matvec(1, oracle.P(so), oracle.P(ref), oracle.P(x), nx + 2, ny + 2, 1, 0 if nine else 1, so.shape[0])
+    sol = cs.Solver2(cs.Operator2(so), relaxation="point")
+    assert_bitwise(sol.matvec(x), ref, "matvec")

@@ -97,3 +97,16 @@ def test_vcycle_batch_matches_single_calls(cs):
         hx[...] = 3.0
         sol.vcycle0_pinned()
         assert_bitwise(hx, xs[k], f"vcycle0 rhs {k}")
+
+
+@pytest.mark.parametrize("full", [False, True])
+def test_solver_matvec(cs, full):
+    n = (21, 12, 9)
+    rng = np.random.default_rng(80 + full)
+    so = random_op3(*n, full, rng)
+    x = random_gf3(*n, rng)
+    ref = np.zeros_like(x)
+    oracle.lib().orc3_matvec(1, 1, 0 if full else 1, oracle.P(so), oracle.P(ref), oracle.P(x), n[0] + 2, n[1] + 2,
+                             n[2] + 2, so.shape[0])
+    sol = cs.Solver3(cs.Operator3(so), relaxation="point")
+    assert_bitwise(sol.matvec(x), ref, "matvec3")

@@ -246,3 +246,41 @@ def test_golden_fixture_matches_oracle():
         assert len(h) == len(case["history"])
         assert np.allclose(h, case["history"], rtol=1e-12, atol=0)
         assert abs(r0 - case["res0"]) <= 1e-14 * r0
+
+
+@pytest.mark.parametrize("fe", [False, True])
+def test_matvec_known_answer(fe):
+    """orc2_matvec against the assembled pyamg-style Poisson matrix (the matrices of test/2d/test_relax.cc), and
+    against the residual kernel: A x = -(residual of x with a zero right-hand side), to rounding."""
+    nx, ny = (13, 9) if fe else (11, 11)      # gallery::poisson scales by hy/hx: square grid for the [4,-1] matrix
+    rng = np.random.default_rng(3 + fe)
+    so = oracle.gallery2("fe" if fe else "poisson", nx, ny)
+    x = random_gf(nx, ny, rng)
+    y = np.zeros_like(x)
+    oracle.lib().orc2_matvec(0, P(so), P(y), P(x), nx + 2, ny + 2, 0, 0 if fe else 1, so.shape[0])
+    A = _poisson_matrix(nx, ny, fe)
+    ref = (A @ x[1:-1, 1:-1].ravel()).reshape(ny, nx)
+    assert np.max(np.abs(y[1:-1, 1:-1] - ref)) <= 1e-13 * np.max(np.abs(ref))
+    assert not y[0].any() and not y[-1].any() and not y[:, 0].any() and not y[:, -1].any()
+    r = np.zeros_like(x)
+    oracle.lib().orc2_residual(0, P(so), P(np.zeros_like(x)), P(x), P(r), nx + 2, ny + 2, 0, 0 if fe else 1, so.shape[0])
+    assert np.max(np.abs(y + r)) <= 1e-13 * np.max(np.abs(y))
+
+
+@pytest.mark.parametrize("full", [False, True])
+def test_matvec3_against_residual(full):
+    """orc3_matvec: symmetric (<Ax, y> = <x, Ay>) and equal to -(residual with zero right-hand side) to rounding."""
+    from tests.util import random_gf3, random_op3
+    n = (7, 6, 5)
+    rng = np.random.default_rng(11 + full)
+    so = random_op3(*n, full, rng)
+    II, JJ, KK = n[0] + 2, n[1] + 2, n[2] + 2
+    ifd = 0 if full else 1
+    x, z = random_gf3(*n, rng), random_gf3(*n, rng)
+    ax, az, r = np.zeros_like(x), np.zeros_like(x), np.zeros_like(x)
+    L = oracle.lib()
+    L.orc3_matvec(1, 1, ifd, P(so), P(ax), P(x), II, JJ, KK, so.shape[0])
+    L.orc3_matvec(1, 1, ifd, P(so), P(az), P(z), II, JJ, KK, so.shape[0])
+    L.orc3_residual(1, 1, ifd, P(x), P(np.zeros_like(x)), P(so), P(r), II, JJ, KK, so.shape[0])
+    assert np.max(np.abs(ax + r)) <= 1e-13 * np.max(np.abs(ax))
+    assert abs(np.vdot(ax, z) - np.vdot(x, az)) <= 1e-12 * abs(np.vdot(ax, z))
