@@ -377,7 +377,6 @@ def main():
                      cuda_graph=not a.no_graph)
     torch.cuda.synchronize()
     setup_first_s = time.perf_counter() - t0
-
     # ---- device-resident V-cycles: value -----------------------------------
     sampler = ClockSampler(local)
     if rank == 0:
