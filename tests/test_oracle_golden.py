@@ -284,3 +284,24 @@ def test_matvec3_against_residual(full):
     L.orc3_residual(1, 1, ifd, P(x), P(np.zeros_like(x)), P(so), P(r), II, JJ, KK, so.shape[0])
     assert np.max(np.abs(ax + r)) <= 1e-13 * np.max(np.abs(ax))
     assert abs(np.vdot(ax, z) - np.vdot(x, az)) <= 1e-12 * abs(np.vdot(ax, z))
+
+
+def test_hetero_generator_c3b():
+    """cedar_b200.gallery (config C3(b), SURVEY 8(d)): constant coefficients reproduce gallery::diag_diffusion, the
+    operator is an M-matrix with zero interior row sums, and BoxMG with line-xy relaxation converges on jumps of 1e6."""
+    from cedar_b200 import gallery
+    so = gallery.fv_diffusion5(np.full((9, 13), 1.0), np.full((9, 13), 1e-4))
+    ref = oracle.gallery2("diag_diffusion", 13, 9, 1.0, 1e-4)
+    assert np.allclose(so, ref, rtol=1e-15, atol=0)
+    nx = ny = 96
+    so = gallery.hetero5(nx, ny, nblk=8)
+    assert so.shape == (3, ny + 2, nx + 2) and (so >= 0).all()
+    assert not so[:, 0].any() and not so[:, -1].any() and not so[:, :, 0].any() and not so[:, :, -1].any()
+    assert not so[1, :, 1].any() and not so[2, 1, :].any()          # boundary edges are not stored in W / S
+    assert so[0].max() / so[0][1:-1, 1:-1].min() > 1e4               # the jumps are there
+    c, w, s = so
+    rowsum = c[2:-2, 2:-2] - w[2:-2, 2:-2] - w[2:-2, 3:-1] - s[2:-2, 2:-2] - s[3:-1, 2:-2]
+    assert np.max(np.abs(rowsum)) <= 1e-12 * c.max()
+    b = oracle.rhs_sin2(nx, ny)
+    x, h, _ = oracle.Solver2(so, "line-xy", 1, 1).solve(b, maxiter=20, tol=1e-10)
+    assert h[-1] < 1e-10 and len(h) <= 16, h

@@ -24,7 +24,11 @@ def rhs(shape):
 
 def run2(gallery, n, relax, pre=1, post=1, bpp=None):
     dy = 1e-4 if gallery == "diag_diffusion" else 1.0
-    op = cs.Operator2(gallery=gallery, nx=n, ny=n, dx=1.0, dy=dy)
+    if gallery == "hetero5":       # config C3(b): checkerboard coefficient, jumps up to 1e6 (cedar_b200/gallery.py)
+        from cedar_b200 import gallery as gal
+        op = cs.Operator2(gal.hetero5(n, n))
+    else:
+        op = cs.Operator2(gallery=gallery, nx=n, ny=n, dx=1.0, dy=dy)
     torch.cuda.synchronize(); t0 = time.perf_counter()
     sol = cs.Solver2(op, relaxation=relax, nrelax_pre=pre, nrelax_post=post, maxiter=30, tol=1e-10)
     torch.cuda.synchronize(); setup = time.perf_counter() - t0
@@ -63,6 +67,8 @@ if __name__ == "__main__":
         run2("diag_diffusion", 8193, "line-y")
         run2("diag_diffusion", 8193, "line-xy")
         run2("fe", 8193, "line-xy")
+        run2("hetero5", 8193, "line-xy")
+        run2("hetero5", 8193, "point")
     if "c4" in which:
         run3("poisson", 257, "point", bpp=335)
         run3("fe", 257, "point", bpp=575)
