@@ -9,8 +9,9 @@
  *
  * Every function keeps the loop order and the floating-point expression order
  * of the Fortran routine it cites, so that the CUDA kernels (compiled with
- * -fmad=false) can be compared bit for bit.  Non-periodic branches only
- * (periodic boundary conditions are a "next" row of SURVEY.md section 8(f)).
+ * -fmad=false) can be compared bit for bit.  Non-periodic branches, plus the
+ * periodic branch of point relaxation (the first brick of SURVEY.md section 8(f).2;
+ * the other periodic branches are not restated yet).
  *
  * Parity pin: the multilevel driver in ml2.c built on these kernels reproduces
  * the residual history printed in the reference README.md:52-63 (see
@@ -168,7 +169,6 @@ int orc2_relax_gs(int k, const double *so, const double *qf, double *q, const do
                   int irelax_sym, int updown, int jpn)
 {
     (void)nstncl; (void)nsorv;
-    if (jpn != 0 && jpn != -4) return -1;
     int J1 = JJ - 1, I1 = II - 1;
     int lstart, lend, lstride;
     if (irelax_sym == 0 || (updown == 0 && irelax_sym == 1)) {
@@ -180,6 +180,44 @@ int orc2_relax_gs(int k, const double *so, const double *qf, double *q, const do
 #define Q(i, j) A2(q, II, i, j)
 #define QF(i, j) A2(qf, II, i, j)
 #define SOR(i, j, kk) A3(sor, II, JJ, i, j, kk)
+    const int ipn = jpn < 0 ? -jpn : jpn;
+    if (ipn != 0 && ipn != 4) {
+        /* BMG2_SymStd_relax_GS.f90:139-224, periodic: same updates; the x ghosts of a row are refreshed after
+         * each colour of that row (Q(1,J)=Q(I1,J), Q(II,J)=Q(2,J)) when periodic in x (|jpn| = 2, 3), the y ghost
+         * rows only ONCE, after the whole sweep, when periodic in y (|jpn| = 1, 3) -- so the first and last
+         * interior rows see the previous sweep's wrap.  Literal loop order. */
+        const int perx = (ipn == 2 || ipn == 3), pery = (ipn == 1 || ipn == 3);
+        if (k < kf || ifd != 1) {
+            for (int jbeg = lstart; jbeg != lend + lstride; jbeg += lstride) {
+                int jend = 2 * ((J1 - jbeg) / 2) + jbeg;
+                for (int j = jbeg; j <= jend; j += 2)
+                    for (int ibeg = lstart; ibeg != lend + lstride; ibeg += lstride) {
+                        int iend = 2 * ((I1 - ibeg) / 2) + ibeg;
+                        for (int i = ibeg; i <= iend; i += 2)
+                            Q(i, j) = (QF(i, j) + SO(i, j, KW) * Q(i - 1, j) + SO(i + 1, j, KW) * Q(i + 1, j)
+                                       + SO(i, j, KS) * Q(i, j - 1) + SO(i, j + 1, KS) * Q(i, j + 1)
+                                       + SO(i, j, KSW) * Q(i - 1, j - 1) + SO(i + 1, j, KNW) * Q(i + 1, j - 1)
+                                       + SO(i, j + 1, KNW) * Q(i - 1, j + 1) + SO(i + 1, j + 1, KSW) * Q(i + 1, j + 1))
+                                      * SOR(i, j, MSOR);
+                        if (perx) { Q(1, j) = Q(I1, j); Q(II, j) = Q(2, j); }
+                    }
+            }
+        } else {
+            for (int jo = lstart; jo != lend + lstride; jo += lstride)
+                for (int j = 2; j <= J1; j++) {
+                    int ibeg = (j + jo) % 2 + 2;
+                    int iend = 2 * ((I1 - ibeg) / 2) + ibeg;
+                    for (int i = ibeg; i <= iend; i += 2)
+                        Q(i, j) = (QF(i, j) + SO(i, j, KW) * Q(i - 1, j) + SO(i + 1, j, KW) * Q(i + 1, j)
+                                   + SO(i, j, KS) * Q(i, j - 1) + SO(i, j + 1, KS) * Q(i, j + 1))
+                                  * SOR(i, j, MSOR);
+                    if (perx) { Q(1, j) = Q(I1, j); Q(II, j) = Q(2, j); }
+                }
+        }
+        if (pery)
+            for (int i = 1; i <= II; i++) { Q(i, 1) = Q(i, J1); Q(i, JJ) = Q(i, 2); }
+        return 0;
+    }
     if (k < kf || ifd != 1) {
         for (int jbeg = lstart; jbeg != lend + lstride; jbeg += lstride) {
             int jend = 2 * ((J1 - jbeg) / 2) + jbeg;

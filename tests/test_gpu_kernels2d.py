@@ -195,8 +195,12 @@ def test_sumsq(cuda, abi, nx, ny):
 
 
 def test_periodic_is_refused(cuda, abi):
+    """entry points whose periodic branch is not built yet refuse the boundary code instead of guessing
+    (in-place point relaxation has it: test_relax_gs_periodic)"""
     d = cuda.zeros((5, 6, 6), dtype=cuda.float64, device="cuda")
-    st = abi.lib.bmgx2_relax_GS(1, ptr(d), ptr(d[0]), ptr(d[1]), ptr(d), 6, 6, 1, 0, 5, 2, 1, 0, 2, None)
+    st = abi.lib.bmgx2_relax_GS_oop(1, ptr(d), ptr(d[0]), ptr(d[1]), ptr(d[2]), ptr(d), 6, 6, 1, 0, 5, 2, 1, 0, 2, None)
+    assert st == 2 and b"periodic" in abi.lib.bmgx_last_error()
+    st = abi.lib.bmgx2_restrict(ptr(d[0]), ptr(d[1]), ptr(d), 6, 6, 4, 4, 2, None)
     assert st == 2 and b"periodic" in abi.lib.bmgx_last_error()
 
 
@@ -257,3 +261,26 @@ def test_matvec(cuda, abi, nx, ny, nine):
     d_y = cuda.zeros_like(d_q)
     abi.check(abi.lib.bmgx2_matvec(0, ptr(d_so), ptr(d_y), ptr(d_q), nx + 2, ny + 2, 0, ifd_of(nine), so.shape[0], None))
     assert_bitwise(host(d_y), ref, "matvec")
+
+
+@pytest.mark.parametrize("jpn", [1, 2, 3, -3])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(1, 1), (4, 4), (7, 5), (37, 64), (400, 257)])
+def test_relax_gs_periodic(cuda, abi, nx, ny, nine, jpn):
+    """Periodic branch of point relaxation (BMG2_SymStd_relax_GS.f90:139-224; oracle pinned against the reference's
+    own kernel in tests/test_ref_parity_cpu.py): x ghosts per colour pass, y ghost rows once per sweep; bitwise."""
+    rng = np.random.default_rng(nx * 131 + ny * 7 + nine + 10 * abs(jpn))
+    II, JJ = nx + 2, ny + 2
+    nst = 5 if nine else 3
+    so = 10.0 ** rng.uniform(-1, 1, size=(nst, JJ, II))     # periodic operators carry couplings in the ghost layer
+    so[0] = so[1:].sum(axis=0) * 2.5 + 1.0
+    b, q = rng.standard_normal((JJ, II)), rng.standard_normal((JJ, II))
+    sor = np.zeros((2, JJ, II))
+    L = oracle.lib()
+    L.orc2_setup_recip(P(so), P(sor), II, JJ, nst, 2)
+    d_so, d_q, d_b, d_sor = dev(cuda, so), dev(cuda, q), dev(cuda, b), dev(cuda, sor)
+    for sweep, updown in enumerate((0, 1, 1, 0)):
+        assert L.orc2_relax_gs(1, P(so), P(b), P(q), P(sor), II, JJ, 1, ifd_of(nine), nst, 2, 1, updown, jpn) == 0
+        abi.check(abi.lib.bmgx2_relax_GS(1, ptr(d_so), ptr(d_b), ptr(d_q), ptr(d_sor), II, JJ, 1, ifd_of(nine), nst, 2,
+                                         1, updown, jpn, None))
+        assert_bitwise(host(d_q), q, f"periodic relax_GS sweep {sweep}")

@@ -93,3 +93,30 @@ def test_2d_coarse_solve_bitwise_vs_reference(nx, ny, nine):
     L.orc2_solve_cg(P(x1), P(b), II, JJ, P(a1), P(w1), n1, n2, 0)
     R.BMG2_SymStd_SOLVE_cg(P(x2), P(b), II, JJ, P(a2), P(w2), n1, n2, 0)
     assert np.array_equal(x1, x2)
+
+
+@pytest.mark.parametrize("jpn", [1, 2, 3, -1, -2, -3])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(3, 3), (4, 4), (8, 6), (7, 5), (16, 17), (37, 64)])
+def test_periodic_point_relaxation_bitwise_vs_reference(nx, ny, nine, jpn):
+    """Periodic branch of BMG2_SymStd_relax_GS (f90:139-224): x ghosts refreshed per row and colour, y ghost rows once
+    per sweep.  Ghosts deliberately start inconsistent with the interior: the reference does not fix them up front."""
+    R, L = ref.lib(), oracle.lib()
+    rng = np.random.default_rng(nx * 131 + ny * 7 + nine + 10 * abs(jpn))
+    II, JJ = nx + 2, ny + 2
+    nst, ifd = (5, 0) if nine else (3, 1)
+    # periodic operators carry couplings in the ghost layer too
+    so = 10.0 ** rng.uniform(-1, 1, size=(nst, JJ, II))
+    so[0] = so[1:].sum(axis=0) * 2.5 + 1.0
+    b = rng.standard_normal((JJ, II))
+    q = rng.standard_normal((JJ, II))
+    s1, s2 = np.zeros((2, JJ, II)), np.zeros((2, JJ, II))
+    L.orc2_setup_recip(P(so), P(s1), II, JJ, nst, 2)
+    R.BMG2_SymStd_SETUP_recip(P(so), P(s2), II, JJ, nst, 2)
+    assert np.array_equal(s1, s2)
+    q1, q2 = q.copy(), q.copy()
+    for ud in (0, 1, 1, 0):
+        assert L.orc2_relax_gs(1, P(so), P(b), P(q1), P(s1), II, JJ, 1, ifd, nst, 2, 1, ud, jpn) == 0
+        R.BMG2_SymStd_relax_GS(1, P(so), P(b), P(q2), P(s2), II, JJ, 1, ifd, nst, 2, 1, ud, jpn)
+        assert np.array_equal(q1, q2)
+    assert not np.array_equal(q1, q)
