@@ -265,7 +265,7 @@ def test_matvec(cuda, abi, nx, ny, nine):
 
 @pytest.mark.parametrize("jpn", [1, 2, 3, -3])
 @pytest.mark.parametrize("nine", [False, True])
-@pytest.mark.parametrize("nx,ny", [(1, 1), (4, 4), (7, 5), (37, 64), (400, 257)])
+@pytest.mark.parametrize("nx,ny", [(2, 3), (4, 4), (7, 5), (37, 64), (400, 257)])
 def test_relax_gs_periodic(cuda, abi, nx, ny, nine, jpn):
     """Periodic branch of point relaxation (BMG2_SymStd_relax_GS.f90:139-224; oracle pinned against the reference's
     own kernel in tests/test_ref_parity_cpu.py): x ghosts per colour pass, y ghost rows once per sweep; bitwise."""
