@@ -55,22 +55,6 @@ k_relax_colour(const double *__restrict__ so, const double *__restrict__ qf, dou
 // Periodic boundaries (BMG2_SymStd_relax_GS.f90:139-224): the reference refreshes the x ghosts of a row after each
 // colour of that row and the y ghost rows once, after the whole sweep.  One colour never reads its own rows' x
 // ghosts written in the same pass, so refreshing them for all rows of the pass right after the pass is the same.
-__global__ void __launch_bounds__(128) k_wrap_x(double *q, unsigned II, unsigned jbeg, unsigned jstep, unsigned nrow)
-{
-    unsigned r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= nrow) return;
-    double *row = q + (size_t)(jbeg + jstep * r - 1) * II;
-    row[0] = row[II - 2];       // Q(1,J)  = Q(I1,J)
-    row[II - 1] = row[1];       // Q(II,J) = Q(2,J)
-}
-__global__ void __launch_bounds__(128) k_wrap_y(double *q, unsigned II, unsigned JJ)
-{
-    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= II) return;
-    q[i] = q[(size_t)(JJ - 2) * II + i];                 // Q(I,1)  = Q(I,J1)
-    q[(size_t)(JJ - 1) * II + i] = q[(size_t)II + i];    // Q(I,JJ) = Q(I,2)
-}
-
 // passes: bit n set = run the n-th colour pass of the sweep (9-point: 4 passes, 5-point: 2)
 static int relax_gs_passes(int k, const double *so, const double *qf, double *q, const double *sor, bmgx_len ii,
                            bmgx_len jj, int kf, int ifd, int irelax_sym, int updown, int jpn, unsigned passes,
@@ -100,8 +84,7 @@ static int relax_gs_passes(int k, const double *so, const double *qf, double *q,
                 k_relax_colour<true><<<g, 128, 0, st>>>(so, qf, q, sor, ii, jj, ibeg, jbeg, 2, 0);
                 BMGX_LAUNCH_CHECK("relax_GS/9");
                 if (perx) {
-                    k_wrap_x<<<cdiv(nrow, 128), 128, 0, st>>>(q, ii, jbeg, 2, nrow);
-                    BMGX_LAUNCH_CHECK("relax_GS/9 wrap x");
+                    if (bmgx_wrap_x(q, ii, jbeg, 2, nrow, st)) return BMGX_ERR_CUDA;
                 }
             }
         }
@@ -114,14 +97,12 @@ static int relax_gs_passes(int k, const double *so, const double *qf, double *q,
             k_relax_colour<false><<<g, 128, 0, st>>>(so, qf, q, sor, ii, jj, 0, 2, 1, jo);
             BMGX_LAUNCH_CHECK("relax_GS/5");
             if (perx) {
-                k_wrap_x<<<cdiv(J1 - 1, 128), 128, 0, st>>>(q, ii, 2, 1, J1 - 1);
-                BMGX_LAUNCH_CHECK("relax_GS/5 wrap x");
+                if (bmgx_wrap_x(q, ii, 2, 1, J1 - 1, st)) return BMGX_ERR_CUDA;
             }
         }
     }
     if (pery) {
-        k_wrap_y<<<cdiv(ii, 128), 128, 0, st>>>(q, ii, jj);
-        BMGX_LAUNCH_CHECK("relax_GS wrap y");
+        if (bmgx_wrap_y(q, ii, jj, st)) return BMGX_ERR_CUDA;
     }
     return BMGX_OK;
 }

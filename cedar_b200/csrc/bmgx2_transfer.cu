@@ -31,7 +31,17 @@ k_restrict(const double *__restrict__ q, double *__restrict__ qc, const double *
 extern "C" int bmgx2_restrict(const double *q, double *qc, const double *ci, bmgx_len nx, bmgx_len ny,
                               bmgx_len nxc, bmgx_len nyc, int jpn, bmgx_stream_t s)
 {
-    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "restrict: periodic BCs not supported");
+    if (!bmgx_nonperiodic(jpn)) {
+        // BMG2_SymStd_restrict.f90:96-111: refresh the fine vector's ghost layer first (the "const" argument is
+        // mutated, as in the reference): y rows, then x columns, each only for the N/2+1 coarsening
+        const int ipn = jpn < 0 ? -jpn : jpn;
+        if (ipn < 1 || ipn > 3) return bmgx_set_error(BMGX_ERR_ARG, "restrict: unknown boundary code");
+        if (bmgx_batch() != 1) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "restrict: periodic BCs not supported in a batch");
+        if (nx < 3 || ny < 3) return BMGX_OK;
+        double *qm = const_cast<double *>(q);
+        if ((ipn == 1 || ipn == 3) && ny / 2 + 1 == nyc && bmgx_wrap_y(qm, nx, ny, (cudaStream_t)s)) return BMGX_ERR_CUDA;
+        if ((ipn == 2 || ipn == 3) && nx / 2 + 1 == nxc && bmgx_wrap_x(qm, nx, 1, 1, ny, (cudaStream_t)s)) return BMGX_ERR_CUDA;
+    }
     if (nxc < 3 || nyc < 3) return BMGX_OK;
     dim3 b(64, 4), g(cdiv(nxc - 2, 64), cdiv(nyc - 2, 4), bmgx_batch());
     launch_pdl(k_restrict, g, b, 0, (cudaStream_t)s, q, qc, ci, nx, ny, nxc, nyc);

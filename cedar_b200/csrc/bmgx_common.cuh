@@ -53,6 +53,11 @@ __device__ __forceinline__ void pdl_wait()
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
+// periodic ghost refresh: Q(1,J)=Q(I1,J), Q(II,J)=Q(2,J) on rows jbeg, jbeg+jstep, ... (nrow of them);
+// Q(I,1)=Q(I,J1), Q(I,JJ)=Q(I,2) on every column
+int bmgx_wrap_x(double *q, unsigned ii, unsigned jbeg, unsigned jstep, unsigned nrow, cudaStream_t st);
+int bmgx_wrap_y(double *q, unsigned ii, unsigned jj, cudaStream_t st);
+
 static inline bool bmgx_nonperiodic(int jpn) { return jpn == BMGX_BCs_definite || jpn == BMGX_BCs_indef_nonper; }
 static inline unsigned cdiv(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
 

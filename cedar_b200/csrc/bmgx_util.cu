@@ -202,6 +202,37 @@ extern "C" int bmgx_device_sync(void) { RT(cudaDeviceSynchronize(), "bmgx_device
 extern "C" int bmgx_event_create(void **ev) { RT(cudaEventCreate((cudaEvent_t *)ev), "bmgx_event_create"); }
 extern "C" int bmgx_event_destroy(void *ev) { RT(cudaEventDestroy((cudaEvent_t)ev), "bmgx_event_destroy"); }
 extern "C" int bmgx_event_record(void *ev, bmgx_stream_t s) { RT(cudaEventRecord((cudaEvent_t)ev, (cudaStream_t)s), "bmgx_event_record"); }
+// periodic ghost refresh of a 2D grid function (used by the periodic branches of relax_GS and restrict)
+__global__ void __launch_bounds__(128) k_wrap_x(double *q, unsigned II, unsigned jbeg, unsigned jstep, unsigned nrow)
+{
+    unsigned r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= nrow) return;
+    double *row = q + (size_t)(jbeg + jstep * r - 1) * II;
+    row[0] = row[II - 2];       // Q(1,J)  = Q(I1,J)
+    row[II - 1] = row[1];       // Q(II,J) = Q(2,J)
+}
+__global__ void __launch_bounds__(128) k_wrap_y(double *q, unsigned II, unsigned JJ)
+{
+    unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= II) return;
+    q[i] = q[(size_t)(JJ - 2) * II + i];                 // Q(I,1)  = Q(I,J1)
+    q[(size_t)(JJ - 1) * II + i] = q[(size_t)II + i];    // Q(I,JJ) = Q(I,2)
+}
+
+int bmgx_wrap_x(double *q, unsigned ii, unsigned jbeg, unsigned jstep, unsigned nrow, cudaStream_t st)
+{
+    if (nrow == 0) return BMGX_OK;
+    k_wrap_x<<<cdiv(nrow, 128), 128, 0, st>>>(q, ii, jbeg, jstep, nrow);
+    BMGX_LAUNCH_CHECK("wrap x");
+    return BMGX_OK;
+}
+int bmgx_wrap_y(double *q, unsigned ii, unsigned jj, cudaStream_t st)
+{
+    k_wrap_y<<<cdiv(ii, 128), 128, 0, st>>>(q, ii, jj);
+    BMGX_LAUNCH_CHECK("wrap y");
+    return BMGX_OK;
+}
+
 bool bmgx_pdl_enabled()
 {
     // measured on the 4097^2 V(1,1) cycle: 1.172 -> 1.168 ms; the coarse-level tail is bound by the kernels'

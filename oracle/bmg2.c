@@ -317,11 +317,22 @@ void orc2_residual(int k, const double *so, const double *qf, const double *q, d
 int orc2_restrict(const double *q, double *qc, const double *ci,
                   int Nx, int Ny, int Nxc, int Nyc, int jpn)
 {
-    if (jpn != 0 && jpn != -4) return -1;
-    (void)Ny;
 #define CI(i, j, kk) A3(ci, Nxc, Nyc, i, j, kk)
 #define Q(i, j) A2(q, Nx, i, j)
 #define QC(i, j) A2(qc, Nxc, i, j)
+    const int ipn = jpn < 0 ? -jpn : jpn;
+    if (ipn != 0 && ipn != 4) {
+        /* BMG2_SymStd_restrict.f90:96-111, periodic: the ghost layer of the FINE vector is refreshed first (the
+         * argument is mutated, as in the reference) -- y rows, then x columns, each only when that direction is
+         * periodic and the coarse grid is the "even" coarsening N/2+1 of the fine one -- then the same stencil. */
+        double *qm = (double *)q;
+#define QM(i, j) A2(qm, Nx, i, j)
+        if ((ipn == 1 || ipn == 3) && Ny / 2 + 1 == Nyc)
+            for (int i = 1; i <= Nx; i++) { QM(i, 1) = QM(i, Ny - 1); QM(i, Ny) = QM(i, 2); }
+        if ((ipn == 2 || ipn == 3) && Nx / 2 + 1 == Nxc)
+            for (int j = 1; j <= Ny; j++) { QM(1, j) = QM(Nx - 1, j); QM(Nx, j) = QM(2, j); }
+#undef QM
+    }
 #pragma omp parallel for schedule(static)
     for (int jc = 2; jc <= Nyc - 1; jc++) {
         int j = 2 * (jc - 1);

@@ -200,7 +200,7 @@ def test_periodic_is_refused(cuda, abi):
     d = cuda.zeros((5, 6, 6), dtype=cuda.float64, device="cuda")
     st = abi.lib.bmgx2_relax_GS_oop(1, ptr(d), ptr(d[0]), ptr(d[1]), ptr(d[2]), ptr(d), 6, 6, 1, 0, 5, 2, 1, 0, 2, None)
     assert st == 2 and b"periodic" in abi.lib.bmgx_last_error()
-    st = abi.lib.bmgx2_restrict(ptr(d[0]), ptr(d[1]), ptr(d), 6, 6, 4, 4, 2, None)
+    st = abi.lib.bmgx2_interp_add(ptr(d[0]), ptr(d[1]), ptr(d[2]), ptr(d), ptr(d), 4, 4, 6, 6, 5, 2, None)
     assert st == 2 and b"periodic" in abi.lib.bmgx_last_error()
 
 
@@ -284,3 +284,22 @@ def test_relax_gs_periodic(cuda, abi, nx, ny, nine, jpn):
         abi.check(abi.lib.bmgx2_relax_GS(1, ptr(d_so), ptr(d_b), ptr(d_q), ptr(d_sor), II, JJ, 1, ifd_of(nine), nst, 2,
                                          1, updown, jpn, None))
         assert_bitwise(host(d_q), q, f"periodic relax_GS sweep {sweep}")
+
+
+@pytest.mark.parametrize("jpn", [1, 2, 3, -3])
+@pytest.mark.parametrize("nx,ny", [(4, 4), (8, 6), (7, 5), (64, 38), (400, 258)])
+def test_restrict_periodic(cuda, abi, nx, ny, jpn):
+    """Periodic branch of restriction (BMG2_SymStd_restrict.f90:96-128): ghost refresh of the fine vector (argument
+    mutated) for the N/2+1 coarsening, then the same stencil; coarse result and fine vector bitwise."""
+    rng = np.random.default_rng(nx * 17 + ny + 100 * abs(jpn))
+    II, JJ = nx + 2, ny + 2
+    iic, jjc = II // 2 + 1, JJ // 2 + 1
+    ci = rng.uniform(0, 1, size=(8, jjc, iic))
+    q = rng.standard_normal((JJ, II))
+    ref = np.zeros((jjc, iic))
+    d_q, d_ci = dev(cuda, q), dev(cuda, ci)
+    d_c = cuda.zeros((jjc, iic), dtype=cuda.float64, device="cuda")
+    assert oracle.lib().orc2_restrict(P(q), P(ref), P(ci), II, JJ, iic, jjc, jpn) == 0
+    abi.check(abi.lib.bmgx2_restrict(ptr(d_q), ptr(d_c), ptr(d_ci), II, JJ, iic, jjc, jpn, None))
+    assert_bitwise(host(d_c), ref, "periodic restrict")
+    assert_bitwise(host(d_q), q, "fine vector after the ghost refresh")

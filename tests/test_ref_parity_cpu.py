@@ -120,3 +120,23 @@ def test_periodic_point_relaxation_bitwise_vs_reference(nx, ny, nine, jpn):
         R.BMG2_SymStd_relax_GS(1, P(so), P(b), P(q2), P(s2), II, JJ, 1, ifd, nst, 2, 1, ud, jpn)
         assert np.array_equal(q1, q2)
     assert not np.array_equal(q1, q)
+
+
+@pytest.mark.parametrize("jpn", [1, 2, 3, -1, -2, -3])
+@pytest.mark.parametrize("nx,ny", [(4, 4), (8, 6), (7, 5), (16, 17), (37, 64), (64, 38)])
+def test_periodic_restrict_bitwise_vs_reference(nx, ny, jpn):
+    """Periodic branch of BMG2_SymStd_restrict (f90:96-128): refreshes the fine vector's ghost layer (mutating its
+    argument) when the coarse grid is the N/2+1 coarsening, then applies the same stencil."""
+    R, L = ref.lib(), oracle.lib()
+    rng = np.random.default_rng(nx * 17 + ny + 100 * abs(jpn))
+    II, JJ = nx + 2, ny + 2
+    for iic, jjc in [(II // 2 + 1, JJ // 2 + 1), (coarse_n(nx) + 2, coarse_n(ny) + 2)]:
+        if 2 * (iic - 1) > II or 2 * (jjc - 1) > JJ:
+            continue            # the stencil must stay inside the fine array
+        ci = rng.uniform(0, 1, size=(8, jjc, iic))
+        q = rng.standard_normal((JJ, II))
+        q1, q2 = q.copy(), q.copy()
+        c1, c2 = np.zeros((jjc, iic)), np.zeros((jjc, iic))
+        assert L.orc2_restrict(P(q1), P(c1), P(ci), II, JJ, iic, jjc, jpn) == 0
+        R.BMG2_SymStd_restrict(P(q2), P(c2), P(ci), II, JJ, iic, jjc, jpn)
+        assert np.array_equal(c1, c2) and np.array_equal(q1, q2)
