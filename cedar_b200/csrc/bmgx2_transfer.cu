@@ -114,10 +114,19 @@ extern "C" int bmgx2_interp_add(double *q, const double *qc, double *res, const 
                                 bmgx_stream_t s)
 {
     (void)nstncl;
-    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "interp_add: periodic BCs not supported");
+    const bool periodic = !bmgx_nonperiodic(jpn);
+    const int ipn = jpn < 0 ? -jpn : jpn;
+    if (periodic && (ipn < 1 || ipn > 3)) return bmgx_set_error(BMGX_ERR_ARG, "interp_add: unknown boundary code");
+    if (periodic && bmgx_batch() != 1)
+        return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "interp_add: periodic BCs not supported in a batch");
     if (iif < 3 || jjf < 3) return BMGX_OK;
     dim3 b(64, 4), g(cdiv(iif / 2, 64), cdiv(jjf / 2, 4), bmgx_batch());
     launch_pdl(k_interp_add, g, b, 0, (cudaStream_t)s, q, qc, res, so, ci, iic, jjc, iif, jjf);
     BMGX_LAUNCH_CHECK("interp_add");
+    if (periodic) {
+        // BMG2_SymStd_interp_add.f90:143-165: ghost layer of the corrected vector, y rows first, then x columns
+        if ((ipn == 1 || ipn == 3) && bmgx_wrap_y(q, iif, jjf, (cudaStream_t)s)) return BMGX_ERR_CUDA;
+        if ((ipn == 2 || ipn == 3) && bmgx_wrap_x(q, iif, 1, 1, jjf, (cudaStream_t)s)) return BMGX_ERR_CUDA;
+    }
     return BMGX_OK;
 }

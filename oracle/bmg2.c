@@ -363,7 +363,6 @@ int orc2_interp_add(double *q, const double *qc, double *res, const double *so, 
                     int IIC, int JJC, int IIF, int JJF, int nstncl, int jpn)
 {
     (void)nstncl;
-    if (jpn != 0 && jpn != -4) return -1;
     int JJF1 = JJF - 1, IIF1 = IIF - 1;
     int IICF = (IIF - 2) / 2 + 3, JJCF = (JJF - 2) / 2 + 3;
     int IICF1 = IICF - 1, JJCF1 = JJCF - 1;
@@ -405,6 +404,15 @@ int orc2_interp_add(double *q, const double *qc, double *res, const double *so, 
                 + CI(ic, jc, LNE) * QC(ic, jc) + CI(ic, jc, LSE) * QC(ic, jc - 1);
             Q(i - 1, j - 1) = Q(i - 1, j - 1) + a + RES(i - 1, j - 1);
         }
+    }
+    {
+        /* BMG2_SymStd_interp_add.f90:143-165, periodic: the ghost layer of the corrected fine vector is refreshed
+         * at the end, y rows first, then x columns */
+        const int ipn = jpn < 0 ? -jpn : jpn;
+        if (ipn == 1 || ipn == 3)
+            for (int i = 1; i <= IIF; i++) { Q(i, 1) = Q(i, JJF1); Q(i, JJF) = Q(i, 2); }
+        if (ipn == 2 || ipn == 3)
+            for (int j = 1; j <= JJF; j++) { Q(1, j) = Q(IIF1, j); Q(IIF, j) = Q(2, j); }
     }
     return 0;
 #undef CI

@@ -200,7 +200,7 @@ def test_periodic_is_refused(cuda, abi):
     d = cuda.zeros((5, 6, 6), dtype=cuda.float64, device="cuda")
     st = abi.lib.bmgx2_relax_GS_oop(1, ptr(d), ptr(d[0]), ptr(d[1]), ptr(d[2]), ptr(d), 6, 6, 1, 0, 5, 2, 1, 0, 2, None)
     assert st == 2 and b"periodic" in abi.lib.bmgx_last_error()
-    st = abi.lib.bmgx2_interp_add(ptr(d[0]), ptr(d[1]), ptr(d[2]), ptr(d), ptr(d), 4, 4, 6, 6, 5, 2, None)
+    st = abi.lib.bmgx2_SETUP_lines_x(ptr(d), ptr(d), 6, 6, 5, 2, None)
     assert st == 2 and b"periodic" in abi.lib.bmgx_last_error()
 
 
@@ -303,3 +303,33 @@ def test_restrict_periodic(cuda, abi, nx, ny, jpn):
     abi.check(abi.lib.bmgx2_restrict(ptr(d_q), ptr(d_c), ptr(d_ci), II, JJ, iic, jjc, jpn, None))
     assert_bitwise(host(d_c), ref, "periodic restrict")
     assert_bitwise(host(d_q), q, "fine vector after the ghost refresh")
+
+
+@pytest.mark.parametrize("jpn", [1, 2, 3, -3])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(4, 4), (8, 6), (7, 5), (37, 64), (400, 258)])
+def test_interp_add_periodic(cuda, abi, nx, ny, nine, jpn):
+    """Periodic branch of interpolate-and-add (BMG2_SymStd_interp_add.f90:143-165): same correction, then the ghost
+    layer of the fine vector refreshed; fine vector and scaled residual bitwise."""
+    rng = np.random.default_rng(nx * 19 + ny + nine + 100 * abs(jpn))
+    II, JJ = nx + 2, ny + 2
+    iic, jjc = II // 2 + 1 + II % 2, JJ // 2 + 1 + JJ % 2        # N/2+1 coarsening (even N), (N+1)/2+1 (odd N)
+    nst = 5 if nine else 3
+    so = 10.0 ** rng.uniform(-1, 1, size=(nst, JJ, II))
+    so[0] = so[1:].sum(axis=0) * 2.5 + 1.0
+    ci = rng.uniform(0, 1, size=(8, jjc, iic))
+    v = rng.standard_normal((jjc, iic))
+    q, r = rng.standard_normal((JJ, II)), rng.standard_normal((JJ, II))
+    # a direction that is not periodic keeps the zero ghost layer every Cedar array has (include/cedar/array.h:65);
+    # the reference's loops run over those ghost cells too on even grids, adding zeros
+    if abs(jpn) == 1:
+        for a in (q, r, v):
+            a[:, 0] = a[:, -1] = 0.0
+    if abs(jpn) == 2:
+        for a in (q, r, v):
+            a[0, :] = a[-1, :] = 0.0
+    d_q, d_r, d_so, d_ci, d_v = dev(cuda, q), dev(cuda, r), dev(cuda, so), dev(cuda, ci), dev(cuda, v)
+    assert oracle.lib().orc2_interp_add(P(q), P(v), P(r), P(so), P(ci), iic, jjc, II, JJ, nst, jpn) == 0
+    abi.check(abi.lib.bmgx2_interp_add(ptr(d_q), ptr(d_v), ptr(d_r), ptr(d_so), ptr(d_ci), iic, jjc, II, JJ, nst, jpn, None))
+    assert_bitwise(host(d_q), q, "periodic interp_add")
+    assert_bitwise(host(d_r), r, "scaled residual")

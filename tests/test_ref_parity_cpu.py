@@ -140,3 +140,25 @@ def test_periodic_restrict_bitwise_vs_reference(nx, ny, jpn):
         assert L.orc2_restrict(P(q1), P(c1), P(ci), II, JJ, iic, jjc, jpn) == 0
         R.BMG2_SymStd_restrict(P(q2), P(c2), P(ci), II, JJ, iic, jjc, jpn)
         assert np.array_equal(c1, c2) and np.array_equal(q1, q2)
+
+
+@pytest.mark.parametrize("jpn", [1, 2, 3, -1, -2, -3])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(4, 4), (8, 6), (7, 5), (16, 17), (37, 64)])
+def test_periodic_interp_add_bitwise_vs_reference(nx, ny, nine, jpn):
+    """Periodic branch of BMG2_SymStd_interp_add (f90:143-165): the same correction, then the ghost layer of the
+    fine vector refreshed (y rows, then x columns)."""
+    R, L = ref.lib(), oracle.lib()
+    rng = np.random.default_rng(nx * 19 + ny + nine + 100 * abs(jpn))
+    II, JJ = nx + 2, ny + 2
+    iic, jjc = (II - 2) // 2 + 3, (JJ - 2) // 2 + 3          # IICF, JJCF: what the loops of the kernel span
+    nst = 5 if nine else 3
+    so = 10.0 ** rng.uniform(-1, 1, size=(nst, JJ, II))
+    so[0] = so[1:].sum(axis=0) * 2.5 + 1.0
+    ci = rng.uniform(0, 1, size=(8, jjc, iic))
+    v = rng.standard_normal((jjc, iic))
+    q, r = rng.standard_normal((JJ, II)), rng.standard_normal((JJ, II))
+    qa, qb, ra, rb = q.copy(), q.copy(), r.copy(), r.copy()
+    assert L.orc2_interp_add(P(qa), P(v), P(ra), P(so), P(ci), iic, jjc, II, JJ, nst, jpn) == 0
+    R.BMG2_SymStd_interp_add(P(qb), P(v), P(rb), P(so), P(ci), iic, jjc, II, JJ, nst, jpn)
+    assert np.array_equal(qa, qb) and np.array_equal(ra, rb)
