@@ -291,11 +291,22 @@ extern "C" int bmgx2_SETUP_ITLI_ex(const double *so, double *soc, const double *
                                    bmgx_len IIC, bmgx_len JJC, int ifd, int nstncl, int ipn, bmgx_stream_t s)
 {
     (void)nstncl;
-    if (!bmgx_nonperiodic(ipn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SETUP_ITLI_ex: periodic BCs not supported");
+    const bool periodic = !bmgx_nonperiodic(ipn);
+    const int apn = ipn < 0 ? -ipn : ipn;
+    if (periodic && (apn < 1 || apn > 3)) return bmgx_set_error(BMGX_ERR_ARG, "SETUP_ITLI_ex: unknown boundary code");
     if (IIC < 3 || JJC < 3) return BMGX_OK;
     dim3 b(32, 4), g(cdiv(IIC - 2, 32), cdiv(JJC - 2, 4));
     if (ifd != 1) k_itli<true><<<g, b, 0, (cudaStream_t)s>>>(so, soc, ci, IIF, JJF, IIC, JJC);
     else k_itli<false><<<g, b, 0, (cudaStream_t)s>>>(so, soc, ci, IIF, JJF, IIC, JJC);
     BMGX_LAUNCH_CHECK("SETUP_ITLI_ex");
+    if (periodic) {
+        // BMG2_SymStd_SETUP_ITLI_ex.f90:216-247 / 333-364: ghost layer of all five planes of the coarse operator,
+        // y rows first, then x columns
+        const size_t pc = (size_t)IIC * JJC;
+        for (int kk = 0; kk < 5; kk++)
+            if ((apn == 1 || apn == 3) && bmgx_wrap_y(soc + kk * pc, IIC, JJC, (cudaStream_t)s)) return BMGX_ERR_CUDA;
+        for (int kk = 0; kk < 5; kk++)
+            if ((apn == 2 || apn == 3) && bmgx_wrap_x(soc + kk * pc, IIC, 1, 1, JJC, (cudaStream_t)s)) return BMGX_ERR_CUDA;
+    }
     return BMGX_OK;
 }

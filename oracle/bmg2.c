@@ -590,7 +590,7 @@ int orc2_setup_itli_ex(const double *so, double *soc, const double *ci,
                        int IIF, int JJF, int IIC, int JJC, int ifd, int nstncl, int ipn)
 {
     (void)nstncl;
-    if (ipn != 0 && ipn != -4) return -1;
+    ipn = ipn < 0 ? -ipn : ipn;
     int IIC1 = IIC - 1, JJC1 = JJC - 1;
 #define SO(i, j, kk) A3(so, IIF, JJF, i, j, kk)
 #define CI(i, j, kk) A3(ci, IIC, JJC, i, j, kk)
@@ -766,6 +766,16 @@ int orc2_setup_itli_ex(const double *so, double *soc, const double *ci,
                                   - CI(ic, jc, LA) * cs - CI(ic + 1, jc, LNW) * cse;
             }
         }
+    }
+    if (ipn != 0 && ipn != 4) {
+        /* BMG2_SymStd_SETUP_ITLI_ex.f90:216-247 and 333-364, periodic: the ghost layer of every plane of the coarse
+         * operator is refreshed -- y rows first (row JJC <- row 2, row 1 <- row JJC-1), then x columns */
+        if (ipn == 1 || ipn == 3)
+            for (int kk = KO; kk <= KNW; kk++)
+                for (int ic = 1; ic <= IIC; ic++) { SOC(ic, JJC, kk) = SOC(ic, 2, kk); SOC(ic, 1, kk) = SOC(ic, JJC1, kk); }
+        if (ipn == 2 || ipn == 3)
+            for (int kk = KO; kk <= KNW; kk++)
+                for (int jc = 1; jc <= JJC; jc++) { SOC(IIC, jc, kk) = SOC(2, jc, kk); SOC(1, jc, kk) = SOC(IIC1, jc, kk); }
     }
     return 0;
 #undef SO

@@ -333,3 +333,23 @@ def test_interp_add_periodic(cuda, abi, nx, ny, nine, jpn):
     abi.check(abi.lib.bmgx2_interp_add(ptr(d_q), ptr(d_v), ptr(d_r), ptr(d_so), ptr(d_ci), iic, jjc, II, JJ, nst, jpn, None))
     assert_bitwise(host(d_q), q, "periodic interp_add")
     assert_bitwise(host(d_r), r, "scaled residual")
+
+
+@pytest.mark.parametrize("jpn", [1, 2, 3, -3])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(4, 4), (8, 6), (7, 5), (37, 64), (400, 258)])
+def test_galerkin_periodic(cuda, abi, nx, ny, nine, jpn):
+    """Periodic branch of the Galerkin coarse operator (BMG2_SymStd_SETUP_ITLI_ex.f90:216-247, 333-364): same
+    products, then the ghost layer of the five coarse planes refreshed; bitwise."""
+    rng = np.random.default_rng(nx * 23 + ny + nine + 100 * abs(jpn))
+    II, JJ = nx + 2, ny + 2
+    iic, jjc = II // 2 + 1 + II % 2, JJ // 2 + 1 + JJ % 2
+    nst = 5 if nine else 3
+    so = 10.0 ** rng.uniform(-1, 1, size=(nst, JJ, II))
+    so[0] = so[1:].sum(axis=0) * 2.5 + 1.0
+    ci = rng.uniform(0, 1, size=(8, jjc, iic))
+    soc = np.zeros((5, jjc, iic))
+    d_so, d_ci, d_soc = dev(cuda, so), dev(cuda, ci), dev(cuda, soc)
+    assert oracle.lib().orc2_setup_itli_ex(P(so), P(soc), P(ci), II, JJ, iic, jjc, ifd_of(nine), nst, jpn) == 0
+    abi.check(abi.lib.bmgx2_SETUP_ITLI_ex(ptr(d_so), ptr(d_soc), ptr(d_ci), II, JJ, iic, jjc, ifd_of(nine), nst, jpn, None))
+    assert_bitwise(host(d_soc), soc, "periodic SETUP_ITLI_ex")

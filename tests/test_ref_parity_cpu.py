@@ -162,3 +162,24 @@ def test_periodic_interp_add_bitwise_vs_reference(nx, ny, nine, jpn):
     assert L.orc2_interp_add(P(qa), P(v), P(ra), P(so), P(ci), iic, jjc, II, JJ, nst, jpn) == 0
     R.BMG2_SymStd_interp_add(P(qb), P(v), P(rb), P(so), P(ci), iic, jjc, II, JJ, nst, jpn)
     assert np.array_equal(qa, qb) and np.array_equal(ra, rb)
+
+
+@pytest.mark.parametrize("jpn", [1, 2, 3, -1, -2, -3])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(4, 4), (8, 6), (7, 5), (16, 17), (37, 64)])
+def test_periodic_galerkin_bitwise_vs_reference(nx, ny, nine, jpn):
+    """Periodic branch of BMG2_SymStd_SETUP_ITLI_ex (f90:216-247, 333-364): the same Galerkin products, then the ghost
+    layer of all five planes of the coarse operator refreshed."""
+    R, L = ref.lib(), oracle.lib()
+    rng = np.random.default_rng(nx * 23 + ny + nine + 100 * abs(jpn))
+    II, JJ = nx + 2, ny + 2
+    iic, jjc = II // 2 + 1 + II % 2, JJ // 2 + 1 + JJ % 2
+    nst, ifd = (5, 0) if nine else (3, 1)
+    so = 10.0 ** rng.uniform(-1, 1, size=(nst, JJ, II))
+    so[0] = so[1:].sum(axis=0) * 2.5 + 1.0
+    ci = rng.uniform(0, 1, size=(8, jjc, iic))
+    c1 = rng.standard_normal((5, jjc, iic))
+    c2 = c1.copy()
+    assert L.orc2_setup_itli_ex(P(so), P(c1), P(ci), II, JJ, iic, jjc, ifd, nst, jpn) == 0
+    R.BMG2_SymStd_SETUP_ITLI_ex(P(so), P(c2), P(ci), II, JJ, iic, jjc, ifd, nst, jpn)
+    assert np.array_equal(c1, c2)
