@@ -183,3 +183,23 @@ def test_periodic_galerkin_bitwise_vs_reference(nx, ny, nine, jpn):
     assert L.orc2_setup_itli_ex(P(so), P(c1), P(ci), II, JJ, iic, jjc, ifd, nst, jpn) == 0
     R.BMG2_SymStd_SETUP_ITLI_ex(P(so), P(c2), P(ci), II, JJ, iic, jjc, ifd, nst, jpn)
     assert np.array_equal(c1, c2)
+
+
+@pytest.mark.parametrize("ibc", [1, 2, 3])
+@pytest.mark.parametrize("nine", [False, True])
+def test_residual_has_no_periodic_branch(nine, ibc):
+    """BMG2_SymStd_residual ignores its boundary code (f90:87-119 is the whole kernel): with a periodic code and
+    non-zero ghost values the reference gives what the restatement gives with code 0 -- the periodic cycle relies
+    on the ghost refreshes of relaxation / restriction / interpolation alone."""
+    R, L = ref.lib(), oracle.lib()
+    nx, ny = 9, 6
+    rng = np.random.default_rng(5 + nine + 10 * ibc)
+    II, JJ = nx + 2, ny + 2
+    nst, ifd = (5, 0) if nine else (3, 1)
+    so = 10.0 ** rng.uniform(-1, 1, size=(nst, JJ, II))
+    q, b = rng.standard_normal((JJ, II)), rng.standard_normal((JJ, II))
+    r1, r2 = np.zeros_like(q), np.zeros_like(q)
+    L.orc2_residual(0, P(so), P(b), P(q), P(r1), II, JJ, 0, ifd, nst)
+    R.BMG2_SymStd_residual(ref.ip(0), P(so), P(b), P(q), P(r2), ref.ip(II), ref.ip(JJ), ref.ip(0), ref.ip(ifd),
+                           ref.ip(nst), ref.ip(ibc), ref.ip(0), ref.ip(1), ref.ip(0))
+    assert np.array_equal(r1, r2)
