@@ -218,6 +218,56 @@ int bmgx2_SETUP_interp_OI_stage(const bmgx_real *so, const bmgx_real *soc, bmgx_
 int bmgx2_line_copy(bmgx_real *a, bmgx_len ii, bmgx_len jj, int nplanes, unsigned plane_mask,
                     int dir, bmgx_len index, bmgx_real *buf, int to_buf, bmgx_stream_t s);
 
+/* ---- peer-memory ghost exchange of the block-decomposed path (cedar_b200/csrc/bmgx2_halo.cu) ----
+ * Replaces kernels::halo_exchange (include/cedar/kernels/halo_exchange.h:22-31; MSG/Tausch + MPI in
+ * src/2d/mpi/halo.cc): every rank keeps its arrays in one device allocation, the ranks open each other's
+ * allocations once through CUDA IPC, and one exchange is ONE kernel that signals, waits for the ranks it
+ * reads from and pulls the halo rectangles out of their arrays over NVLink. */
+#define BMGX_IPC_HANDLE_BYTES 64
+int bmgx_ipc_export(void *devptr, void *handle64);            /* cudaIpcGetMemHandle of a bmgx_malloc'd block */
+int bmgx_ipc_open(const void *handle64, void **devptr);       /* maps a peer's block (enables peer access) */
+int bmgx_ipc_close(void *devptr);
+/* one rectangle of an exchange: rows x cols doubles from src (in rank src_rank's allocation, as mapped in
+ * this process) to dst (local); pitches in doubles */
+typedef struct {
+    const bmgx_real *src;
+    bmgx_real *dst;
+    uint32_t rows, cols;
+    uint64_t src_pitch, dst_pitch;
+    int32_t src_rank, reserved;
+} bmgx_seg;
+/* One exchange step.  my_sync: this rank's sync block (world + 3 zero-initialised 64-bit words at a fixed place of
+ * its allocation: flags[world], exchange counter, CTA counter, error word); peer_sync_dev: DEVICE array of
+ * `world` pointers to the sync blocks of all ranks (own included) as mapped here.  phase: 1 = signal, 2 = wait
+ * + pull, 3 = both (one rank per process).  wait_all != 0: wait for every rank, not only the ranks read from.
+ * nseg may be 0 (a pure synchronisation step).  A wait longer than timeout_s stores 1 + rank in the error word
+ * and carries on instead of hanging.  max_chunks: CTAs per rectangle (1..64). */
+int bmgx_halo_step(const bmgx_seg *segs_dev, int nseg, int max_chunks, void *const *peer_sync_dev, void *my_sync,
+                   int me, int world, int phase, int wait_all, double timeout_s, bmgx_stream_t s);
+/* rectangle copies (pitches in doubles): device to device (a kernel), host <-> device (cudaMemcpy2DAsync) */
+int bmgx_copy2d(bmgx_real *dst, size_t dpitch, const bmgx_real *src, size_t spitch, bmgx_len cols, bmgx_len rows,
+                bmgx_stream_t s);
+int bmgx_memcpy2d_h2d(bmgx_real *dst, size_t dpitch, const bmgx_real *src, size_t spitch, bmgx_len cols,
+                      bmgx_len rows, bmgx_stream_t s);
+int bmgx_memcpy2d_d2h(bmgx_real *dst, size_t dpitch, const bmgx_real *src, size_t spitch, bmgx_len cols,
+                      bmgx_len rows, bmgx_stream_t s);
+/* deterministic sum of squares of a rows x cols window (a block's own points inside its halo-extended array);
+ * work: >= bmgx_sumsq_win_work_len() doubles */
+size_t bmgx_sumsq_win_work_len(void);
+int bmgx2_sumsq_win(const bmgx_real *q, size_t pitch, bmgx_len cols, bmgx_len rows, bmgx_real *work, bmgx_real *out,
+                    bmgx_stream_t s);
+/* *out = v[0] + ... + v[n-1] in index order (the rank-ordered fold of the partial norms: same bits on every rank) */
+int bmgx_sum_ordered(const bmgx_real *v, int n, bmgx_real *out, bmgx_stream_t s);
+/* bmgx2_restrict / bmgx2_interp_add (non-periodic) with the COARSE arrays (qc, ci) given as a window of a larger
+ * array: pointers to the window's first entry, row pitch cpitch and plane stride cplane in doubles.  The fine
+ * arrays are plain.  Used by the block-decomposed path, whose coarse arrays carry wider halos than the fine
+ * array's coarsening reaches. */
+int bmgx2_restrict_v(const bmgx_real *q, bmgx_real *qc, const bmgx_real *ci, bmgx_len nx, bmgx_len ny, bmgx_len nxc,
+                     bmgx_len nyc, size_t cpitch, size_t cplane, bmgx_stream_t s);
+int bmgx2_interp_add_v(bmgx_real *q, const bmgx_real *qc, bmgx_real *res, const bmgx_real *so, const bmgx_real *ci,
+                       bmgx_len iic, bmgx_len jjc, bmgx_len iif, bmgx_len jjf, size_t cpitch, size_t cplane,
+                       bmgx_stream_t s);
+
 /* ---- 3D ------------------------------------------------------------------
  * Arrays: Q(II,JJ,KK), SO(II,JJ,KK,NStncl) with NStncl = 4 (seven_pt: p,pw,ps,b)
  * or 14 (xxvii_pt), SOR(II,JJ,KK,2), CI(IIC,JJC,KKC,26); slot order of

@@ -1,0 +1,330 @@
+// cedar/2d/mpi/plan.h -- block decomposition and exchange schedule of the multi-GPU 2D solver.
+//
+// Host-only (no device code): the decomposition of the reference's cdr2::mpi::solver
+// (include/cedar/2d/mpi/solver.h:104 setup_space, include/cedar/decomp.h:59-86 grid_decomp,
+// include/cedar/mpi/block_partition.h:14-17) and the ORDER of kernels and ghost exchanges of one
+// setup / one V-cycle / one residual norm, as a flat list of operations.  The CUDA executor
+// (cedar_b200/host/dist2.cc) runs the list with the C-ABI kernels and peer-memory exchanges; the CPU
+// tests run the very same list with the oracle's kernels over gloo (tests/dist_plan_sim.py).
+//
+// Deep halos instead of an exchange per colour.  The reference exchanges one ghost line after every
+// colour of a sweep, after the residual and after the interpolation
+// (src/2d/ftn/mpi/BMG2_SymStd_relax_GS.f90:126,171, BMG2_SymStd_residual.f90, BMG2_SymStd_interp_add.f90).
+// Here every array of a block carries W lines of its neighbours (W odd, so the global colouring is
+// kept; the outermost line plays the role of the ghost ring) and every kernel simply runs over the
+// whole extended array, recomputing the neighbours' values it needs.  Each kernel consumes a known
+// number of lines of validity (a 4-colour sweep 4, a residual 1, a restriction halves it, ...); the
+// planner tracks, per array, how many halo lines still hold exactly the values the neighbour holds and
+// inserts an exchange only when a kernel would otherwise produce a wrong OWN value.  With W = 15 a
+// V(1,1) cycle needs ONE exchange per level (the restricted right-hand side) instead of twelve; the
+// result is bit for bit the serial solver's (every recomputed value is computed from the same operands
+// in the same order as on its owner).
+#ifndef CEDAR_2D_MPI_PLAN_H
+#define CEDAR_2D_MPI_PLAN_H
+
+#include <algorithm>
+#include <array>
+#include <map>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace cedar { namespace cdr2 { namespace mpi {
+
+// include/cedar/decomp.h:59-86: prime factors, largest first, onto the currently longest dimension
+inline std::array<int, 2> grid_decomp(std::array<long, 2> n, int nprocs)
+{
+	std::vector<int> fac;
+	for (int p = 2, m = nprocs; m > 1; p++)
+		while (m % p == 0) { fac.push_back(p); m /= p; }
+	std::sort(fac.rbegin(), fac.rend());
+	std::array<int, 2> dec{1, 1};
+	for (int f : fac) {
+		int ind = n[1] > n[0] ? 1 : 0;
+		dec[ind] *= f;
+		n[ind] /= f;
+	}
+	return dec;
+}
+
+inline int coarse_n(int n) { return (n - 1) / 2 + 1; }   // include/cedar/2d/solver.h:86-87
+
+inline int compute_num_levels(int nx, int ny, int min_coarse = 3)   // include/cedar/2d/solver.h:57-73
+{
+	for (int ng = 1;; ng++)
+		if (std::min((nx - 1) / (1 << ng) + 1, (ny - 1) / (1 << ng) + 1) < min_coarse) return ng;
+}
+
+// array slots of a level
+enum arr { X0 = 0, X1 = 1, B = 2, RES = 3, A = 4, SOR = 5, P = 6, NARR = 7 };
+
+// geometry of one block on one level: own points and the halo-extended array that holds them
+struct block_geom
+{
+	int x0, y0, nx, ny;       // first own point (0-based global interior index) and own counts
+	int wl, wr, wb, wt;       // lines beyond the own points on each side: W towards a neighbour, 1 at the boundary
+	int ii, jj;               // array extents: nx + wl + wr, ny + wb + wt (the own points start at [wb][wl], 0-based)
+};
+
+struct decomp
+{
+	int gnx, gny, px, py, ndist, nlevels, W;
+	std::vector<std::array<int, 2>> gn;                 // global size per level
+	std::vector<std::array<std::vector<int>, 2>> lo;    // lo[lvl][dim][coord], with the end as sentinel
+
+	decomp(int gnx, int gny, int px, int py, int ndist, int W)
+	    : gnx(gnx), gny(gny), px(px), py(py), ndist(ndist), nlevels(compute_num_levels(gnx, gny)), W(W)
+	{
+		if (W < 1 || W % 2 == 0) throw std::invalid_argument("halo width must be odd");
+		if (ndist < 1 || ndist > nlevels - 1) throw std::invalid_argument("need 1 <= distributed levels < levels");
+		gn.push_back({gnx, gny});
+		for (int l = 0; l < ndist; l++) gn.push_back({coarse_n(gn.back()[0]), coarse_n(gn.back()[1])});
+		// block boundaries on coarse points of every distributed level (multiples of 2^ndist)
+		const int al = 1 << ndist;
+		lo.resize(ndist + 1);
+		for (int l = 0; l <= ndist; l++)
+			for (int d = 0; d < 2; d++) {
+				const int n0 = d == 0 ? gnx : gny, p = d == 0 ? px : py;
+				for (int c = 0; c < p; c++) lo[l][d].push_back(((int)((long)c * n0 / p) / al * al) >> l);
+				lo[l][d].push_back(gn[l][d]);
+			}
+		for (int d = 0; d < 2; d++)
+			for (int c = 0; c < (d == 0 ? px : py); c++)
+				if (lo[ndist][d][c + 1] - lo[ndist][d][c] < std::max(W, 2) && (px * py > 1))
+					throw std::invalid_argument("blocks smaller than the halo width on the coarsest distributed level");
+	}
+	int nblocks() const { return px * py; }
+	int neighbour(int b, int dx, int dy) const
+	{
+		const int cx = b % px + dx, cy = b / px + dy;   // x fastest, like the reference's topology
+		return (cx < 0 || cx >= px || cy < 0 || cy >= py) ? -1 : cy * px + cx;
+	}
+	block_geom geom(int lvl, int b) const
+	{
+		const int cx = b % px, cy = b / px;
+		block_geom g;
+		g.x0 = lo[lvl][0][cx]; g.nx = lo[lvl][0][cx + 1] - g.x0;
+		g.y0 = lo[lvl][1][cy]; g.ny = lo[lvl][1][cy + 1] - g.y0;
+		g.wl = cx > 0 ? W : 1; g.wr = cx + 1 < px ? W : 1;
+		g.wb = cy > 0 ? W : 1; g.wt = cy + 1 < py ? W : 1;
+		g.ii = g.nx + g.wl + g.wr; g.jj = g.ny + g.wb + g.wt;
+		return g;
+	}
+	// window of the level lvl+1 array that the serial transfer kernels see as "the coarse grid" of the whole
+	// level-lvl array: first entry (0-based) and extents
+	void coarse_window(int lvl, int b, int &ox, int &oy, int &iic, int &jjc) const
+	{
+		const block_geom f = geom(lvl, b);
+		ox = (f.wl - 1) / 2; oy = (f.wb - 1) / 2;
+		iic = (f.ii - 3) / 2 + 3; jjc = (f.jj - 3) / 2 + 3;
+	}
+};
+
+enum class op_kind { exchange, sync, sweep, residual, restrict_, zero, gather, coarse, scatter, interp, copy, sumsq, norm,
+                     recip, setup_interp, galerkin, gather_op, setup_coarse };
+
+struct plan_op
+{
+	op_kind kind;
+	int lvl = 0;
+	int a = 0, b = 0;           // array slots (meaning depends on kind)
+	int dir = 0;                // sweep direction (0 = down, 1 = up)
+	std::vector<int> arrays;    // exchange: the slots that travel
+	bool wait_all = false;
+};
+
+inline const char *op_name(op_kind k)
+{
+	static const char *n[] = {"exchange", "sync", "sweep", "residual", "restrict", "zero", "gather", "coarse", "scatter",
+	                          "interp", "copy", "sumsq", "norm", "recip", "setup_interp", "galerkin", "gather_op",
+	                          "setup_coarse"};
+	return n[(int)k];
+}
+
+// Builds operation lists.  `ncol0` = colours of the finest operator's sweep (2 five-point, 4 nine-point);
+// coarse operators are nine-point.
+class planner
+{
+public:
+	planner(int ndist, int W, int ncol0, int npre, int npost) : ndist(ndist), W(W), ncol0(ncol0), npre(npre), npost(npost)
+	{
+		if (npre + npost < 1) throw std::invalid_argument("a cycle needs at least one sweep");
+		// a whole 4-colour sweep over the extended array must leave the own points exact: colour c is exact out to line
+		// W - 1 - (c - 1), so W - 4 >= 0 and W odd
+		if (W < 5 || W % 2 == 0) throw std::invalid_argument("halo width must be odd and at least 5");
+	}
+
+	// interpolation + Galerkin operators of the distributed levels, agglomerated operator
+	std::vector<plan_op> setup()
+	{
+		begin();
+		exchange(0, {A}, true);
+		for (int l = 0; l < ndist; l++) {
+			push(op_kind::recip, l);
+			push(op_kind::setup_interp, l);          // writes P of level l+1 (own points + what the halo allows)
+			exchange(l + 1, {P}, false);
+			push(op_kind::galerkin, l);              // writes A of level l+1
+			exchange(l + 1, {A}, false);
+		}
+		gather(op_kind::gather_op, ndist, A);
+		push(op_kind::setup_coarse, ndist);
+		return take();
+	}
+
+	// one V-cycle on (X0, B) of level 0; own values of both must be current, halos need not be
+	std::vector<plan_op> cycle()
+	{
+		begin();
+		cur.assign(ndist + 1, X0);
+		val.assign(ndist + 1, std::array<int, 4>{0, 0, 0, 0});
+		exchange(0, {X0, B}, true);
+		ncycle(0);
+		if (cur[0] != X0) { before_write(0, X0); push(op_kind::copy, 0, cur[0], X0); }
+		return take();
+	}
+
+	// res = b - A x on level 0 and the global sum of squares of its own points (every rank gets the same bits)
+	std::vector<plan_op> norm()
+	{
+		begin();
+		val.assign(ndist + 1, std::array<int, 4>{0, 0, 0, 0});
+		exchange(0, {X0, B}, true);
+		push(op_kind::residual, 0, X0);
+		push(op_kind::sumsq, 0, RES);
+		plan_op o; o.kind = op_kind::norm; o.wait_all = true;
+		ops.push_back(o); step++; last_all = step;
+		return take();
+	}
+
+	int exchanges(const std::vector<plan_op> &p) const
+	{
+		int n = 0;
+		for (auto &o : p) n += o.kind == op_kind::exchange || o.kind == op_kind::sync || o.kind == op_kind::gather
+		                       || o.kind == op_kind::gather_op || o.kind == op_kind::norm;
+		return n;
+	}
+
+	static std::string to_json(const std::vector<plan_op> &p)
+	{
+		std::ostringstream s;
+		s << "[";
+		for (std::size_t i = 0; i < p.size(); i++) {
+			const plan_op &o = p[i];
+			s << (i ? "," : "") << "{\"op\":\"" << op_name(o.kind) << "\",\"lvl\":" << o.lvl << ",\"a\":" << o.a << ",\"b\":" << o.b
+			  << ",\"dir\":" << o.dir << ",\"wait_all\":" << (o.wait_all ? "true" : "false") << ",\"arrays\":[";
+			for (std::size_t k = 0; k < o.arrays.size(); k++) s << (k ? "," : "") << o.arrays[k];
+			s << "]}";
+		}
+		s << "]";
+		return s.str();
+	}
+
+private:
+	static constexpr int INF = 1 << 20;
+	int ndist, W, ncol0, npre, npost;
+	std::vector<plan_op> ops;
+	std::vector<std::array<int, 4>> val;   // X0, X1, B, RES: halo lines that hold the neighbours' exact values
+	std::vector<int> cur;                  // slot that holds the iterate of each level
+	long step = 0, last_all = 0;
+	std::map<std::pair<int, int>, std::pair<long, bool>> pulled;   // (lvl, slot) -> exchange step that read it, by all ranks?
+
+	void begin() { ops.clear(); pulled.clear(); step = 0; last_all = 0; }
+	std::vector<plan_op> take() { std::vector<plan_op> r; r.swap(ops); return r; }
+	void push(op_kind k, int lvl, int a = 0, int b = 0, int dir = 0)
+	{
+		plan_op o; o.kind = k; o.lvl = lvl; o.a = a; o.b = b; o.dir = dir;
+		ops.push_back(o);
+	}
+	void exchange(int lvl, std::vector<int> arrays, bool wait_all)
+	{
+		plan_op o; o.kind = op_kind::exchange; o.lvl = lvl; o.arrays = arrays; o.wait_all = wait_all;
+		ops.push_back(o);
+		step++;
+		if (wait_all) last_all = step;
+		for (int a : arrays) {
+			pulled[{lvl, a}] = {step, false};
+			if (a < 4 && !val.empty()) val[lvl][a] = W;
+		}
+	}
+	void gather(op_kind k, int lvl, int a)
+	{
+		plan_op o; o.kind = k; o.lvl = lvl; o.a = a; o.wait_all = true;
+		ops.push_back(o);
+		step++; last_all = step;
+		pulled[{lvl, a}] = {step, true};
+	}
+	// A region other ranks read in exchange step s may be overwritten only after a later step has waited for them:
+	// a rank publishes step s+1 after its reads of step s (cedar_b200/csrc/bmgx2_halo.cu).
+	void before_write(int lvl, int a)
+	{
+		auto it = pulled.find({lvl, a});
+		if (it == pulled.end()) return;
+		const bool ok = it->second.second ? last_all > it->second.first : step > it->second.first;
+		pulled.erase(it);
+		if (ok) return;
+		plan_op o; o.kind = op_kind::sync; o.wait_all = true;
+		ops.push_back(o);
+		step++; last_all = step;
+	}
+	int ncol(int lvl) const { return lvl == 0 ? ncol0 : 4; }
+
+	void sweep(int l, int dir)
+	{
+		const int nc = ncol(l), src = cur[l], dst = src == X0 ? X1 : X0;
+		std::vector<int> need;
+		if (std::min(val[l][src] - 1, W - 1) - (nc - 1) < 0) need.push_back(src);
+		if (val[l][B] - (nc - 1) < 0) need.push_back(B);
+		if (!need.empty()) exchange(l, need, false);
+		before_write(l, dst);
+		push(op_kind::sweep, l, src, dst, dir);
+		// first colour: needs the old iterate one line further out and the right-hand side; never beyond line W - 1 (the
+		// outermost line is the frozen ring); every further colour needs the previous colours one line further out
+		val[l][dst] = std::min(std::min(val[l][src] - 1, val[l][B]), W - 1) - (nc - 1);
+		cur[l] = dst;
+	}
+	void residual(int l)
+	{
+		const int x = cur[l];
+		std::vector<int> need;
+		if (val[l][x] - 1 < 1) need.push_back(x);
+		if (val[l][B] < 1) need.push_back(B);
+		if (!need.empty()) exchange(l, need, false);
+		before_write(l, RES);
+		push(op_kind::residual, l, x);
+		val[l][RES] = std::min(std::min(val[l][x] - 1, val[l][B]), W - 1);
+	}
+	void ncycle(int l)
+	{
+		for (int i = 0; i < npre; i++) sweep(l, 0);
+		residual(l);
+		before_write(l + 1, B);
+		push(op_kind::restrict_, l);
+		if (l + 1 == ndist) {
+			gather(op_kind::gather, ndist, B);
+			push(op_kind::coarse, ndist);
+			before_write(ndist, X0);
+			push(op_kind::scatter, ndist, X0);
+			val[ndist][X0] = W;
+			cur[ndist] = X0;
+		} else {
+			exchange(l + 1, {B}, false);
+			before_write(l + 1, X0);
+			push(op_kind::zero, l + 1, X0);
+			val[l + 1][X0] = INF;
+			cur[l + 1] = X0;
+			ncycle(l + 1);
+		}
+		// interpolate and add: fine halo line k needs the coarse iterate out to line (k + 1) / 2 + 1 at most
+		const int x = cur[l], xc = cur[l + 1];
+		if (val[l + 1][xc] < 1) exchange(l + 1, {xc}, false);
+		before_write(l, x);
+		before_write(l, RES);
+		push(op_kind::interp, l, x, xc);
+		val[l][x] = std::min(std::min(val[l][x], val[l][RES]), std::min(2 * val[l + 1][xc] - 1, W));
+		for (int i = 0; i < npost; i++) sweep(l, 1);
+	}
+};
+
+}}}
+#endif

@@ -91,6 +91,46 @@ int cdr2_solve_host(int nstencil, unsigned nx, unsigned ny, const double *so, co
                     const char *config_json, double *hist, int hist_cap, int *niter);
 
 
+/* ---- block-decomposed 2D solver across GPUs (cdr2::mpi::solver of the reference, include/cedar/2d/mpi/solver.h) ----
+ * One process per GPU (or several blocks in one process on one GPU).  The global nx x ny grid is cut into px x py
+ * blocks (block id = cy*px + cx, include/cedar/decomp.h); each process creates the solver with the ids it owns,
+ * uploads the own entries of its blocks' operators, hands the others its IPC handles (the caller moves these bytes
+ * between the processes: one all-gather), connects, and runs setup.  Ghost exchanges then go through peer memory
+ * over NVLink (include/bmgx.h, bmgx_halo_step); collective calls (setup, vcycle, solve, time_vcycles,
+ * vcycle_stream) must be made by all processes in the same order.  Point relaxation; results are bit for bit
+ * those of the serial cdr2::solver on the global problem.  Levels of global size <= agglomerate are solved
+ * replicated on every rank.  halo_width: odd, lines of the neighbours every array carries (15 = one exchange per
+ * level per V(1,1) cycle). */
+typedef struct cdr2_dist cdr2_dist;
+int cdr2_dist_create(unsigned nx, unsigned ny, int px, int py, int nstencil, int nowned, const int *owned_blocks,
+                     int nrelax_pre, int nrelax_post, int agglomerate, int halo_width, int cuda_graph, cdr2_dist **out);
+void cdr2_dist_destroy(cdr2_dist *d);
+int cdr2_dist_info(cdr2_dist *d, int *ndist, int *nlevels, int *halo_width, int *exchanges_per_cycle, int *ops_per_cycle);
+/* first own point (0-based global interior index) and own counts of a block on a distributed level */
+int cdr2_dist_block_extent(cdr2_dist *d, int lvl, int block, int *x0, int *y0, int *nx, int *ny);
+/* handles: nblocks * 64 bytes indexed by block id; export fills the entries of the owned blocks */
+int cdr2_dist_export_handles(cdr2_dist *d, void *handles);
+int cdr2_dist_connect(cdr2_dist *d, const void *handles);
+/* own entries of a block's fine operator: host array (nstencil, nyl+2, nxl+2) in Cedar layout, ghost ring ignored */
+int cdr2_dist_set_operator(cdr2_dist *d, int block, const double *so);
+int cdr2_dist_setup(cdr2_dist *d);
+/* grid functions of a block, host arrays (nyl+2, nxl+2), own points only; which = "x" | "b" (download also "res") */
+int cdr2_dist_upload(cdr2_dist *d, int block, const char *which, const double *host);
+int cdr2_dist_download(cdr2_dist *d, int block, const char *which, double *host);
+/* own points of a level array -> host (planes, nyl, nxl); which = "A" | "P" | "SOR" | "x" | "b" | "res" */
+int cdr2_dist_level_array(cdr2_dist *d, int block, int lvl, const char *which, double *out);
+/* one V-cycle on the resident x, b (enqueued; cdr2_dist_sync waits and reports exchange time-outs) */
+int cdr2_dist_vcycle(cdr2_dist *d);
+int cdr2_dist_sync(cdr2_dist *d);
+int cdr2_dist_solve(cdr2_dist *d, int maxiter, double tol, double *hist, int hist_cap, int *niter, double *res0);
+int cdr2_dist_time_vcycles(cdr2_dist *d, int warmup, int n, float *ms_per_cycle);
+int cdr2_dist_vcycle_stream(cdr2_dist *d, int nrhs, const double *const *b, double *const *x);
+/* host-only views of the schedule (no device needed): operation list as JSON, block geometry
+ * (x0,y0,nx,ny, wl,wr,wb,wt, coarse window ox,oy,iic,jjc) */
+int cdr2_dist_plan_json(unsigned nx, unsigned ny, int px, int py, int nstencil, int nrelax_pre, int nrelax_post,
+                        int agglomerate, int halo_width, const char *what, char *out, size_t cap, int *ndist);
+int cdr2_dist_geometry(unsigned nx, unsigned ny, int px, int py, int ndist, int halo_width, int lvl, int block, int *out12);
+
 /* ---- 3D (cdr3::solver): same protocol; nstencil = 4 (seven_pt) or 14 (xxvii_pt),
  * arrays (nx+2)(ny+2)(nz+2)[ndirs] ---- */
 typedef struct cdr3_operator cdr3_operator;

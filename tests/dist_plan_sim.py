@@ -1,0 +1,280 @@
+"""TEST INFRASTRUCTURE: runs the operation lists of include/cedar/2d/mpi/plan.h (the schedule the CUDA
+executor cedar_b200/host/dist2.cc runs on the GPUs) with the CPU oracle's kernels on numpy arrays, so that
+the planner -- halo widths, validity tracking, where the exchanges go, coarse windows, agglomeration -- is
+checked on CPU: all blocks in one process, or one block per rank over torch.distributed/gloo.  The plan and
+the block geometry come from the product library (host-only entry points cdr2_dist_plan_json /
+cdr2_dist_geometry); the arithmetic is the oracle's.  Never imported by the product."""
+import numpy as np
+
+import oracle
+from oracle import P
+import cedar_b200.dist2 as d2
+
+X0, X1, B, RES, A, SOR, PI = range(7)
+NPL = {X0: 1, X1: 1, B: 1, RES: 1, SOR: 2, PI: 8}
+
+
+class PlanSim:
+    def __init__(self, nx, ny, px, py, so_blocks, pre=1, post=1, agglomerate=33, halo=15, dist=None, poison=True):
+        """so_blocks: {block: (nst, nyl+2, nxl+2)} own entries of the blocks this process owns"""
+        self.L = oracle.lib()
+        self.nx, self.ny, self.px, self.py, self.W = nx, ny, px, py, halo
+        self.pre, self.post, self.dist = pre, post, dist
+        self.owned = sorted(so_blocks)
+        self.nst = next(iter(so_blocks.values())).shape[0]
+        kw = dict(nst=self.nst, pre=pre, post=post, agglomerate=agglomerate, halo=halo)
+        self.p_setup, self.nd = d2.plan(nx, ny, px, py, what="setup", **kw)
+        self.p_cycle, _ = d2.plan(nx, ny, px, py, what="cycle", **kw)
+        self.p_norm, _ = d2.plan(nx, ny, px, py, what="norm", **kw)
+        self.nb = px * py
+        self.g = {(l, b): d2.geometry(nx, ny, px, py, self.nd, halo, l, b) for l in range(self.nd + 1) for b in range(self.nb)}
+        self.gn = [(nx, ny)]
+        for _ in range(self.nd):
+            self.gn.append(((self.gn[-1][0] - 1) // 2 + 1, (self.gn[-1][1] - 1) // 2 + 1))
+        self.nlevels = 1
+        while min((nx - 1) // (1 << self.nlevels) + 1, (ny - 1) // (1 << self.nlevels) + 1) >= 3:
+            self.nlevels += 1
+        # arrays; halos start as NaN so that any use of a never-exchanged halo value shows up in the own points
+        fill = np.nan if poison else 0.0
+        self.a = {}
+        for l in range(self.nd + 1):
+            for b in self.owned:
+                g = self.g[l, b]
+                for s in range(7):
+                    if s == PI and l == 0:
+                        continue
+                    npl = (self.nst if l == 0 else 5) if s == A else NPL[s]
+                    arr = np.full((npl, g["jj"], g["ii"]), fill)
+                    self.a[l, b, s] = arr
+        for b in self.owned:
+            g = self.g[0, b]
+            self._own(0, b, A)[...] = so_blocks[b][:, 1:-1, 1:-1]
+            for s in (X0, B):
+                self._own(0, b, s)[...] = 0.0
+        self._clean_boundary()
+        self.red = {b: 0.0 for b in self.owned}
+        self.tmpP, self.tmpA = {}, {}
+        self.coarse = {}
+        self.exchanges = 0
+        self.run(self.p_setup)
+
+    # -- helpers ----------------------------------------------------------------
+    def _own(self, l, b, s):
+        g = self.g[l, b]
+        return self.a[l, b, s][:, g["wb"]:g["wb"] + g["ny"], g["wl"]:g["wl"] + g["nx"]]
+
+    def _clean_boundary(self):
+        """the ghost ring at the physical boundary is zero, as in the serial arrays"""
+        for (l, b, s), arr in self.a.items():
+            g = self.g[l, b]
+            if g["wl"] == 1: arr[:, :, 0] = 0.0
+            if g["wr"] == 1: arr[:, :, -1] = 0.0
+            if g["wb"] == 1: arr[:, 0, :] = 0.0
+            if g["wt"] == 1: arr[:, -1, :] = 0.0
+
+    def _neighbour(self, b, dx, dy):
+        cx, cy = b % self.px + dx, b // self.px + dy
+        return None if (cx < 0 or cx >= self.px or cy < 0 or cy >= self.py) else cy * self.px + cx
+
+    def _rects(self, l, b):
+        """(neighbour, my destination slices, its source slices) of a ghost exchange"""
+        g, W = self.g[l, b], self.W
+        for dy in (-1, 0, 1):
+            for dx in (-1, 0, 1):
+                nb = self._neighbour(b, dx, dy) if (dx or dy) else None
+                if nb is None:
+                    continue
+                h = self.g[l, nb]
+                if dx < 0: dc, sc = slice(0, W), slice(h["wl"] + h["nx"] - W, h["wl"] + h["nx"])
+                elif dx > 0: dc, sc = slice(g["wl"] + g["nx"], g["wl"] + g["nx"] + W), slice(h["wl"], h["wl"] + W)
+                else: dc, sc = slice(g["wl"], g["wl"] + g["nx"]), slice(h["wl"], h["wl"] + h["nx"])
+                if dy < 0: dr, sr = slice(0, W), slice(h["wb"] + h["ny"] - W, h["wb"] + h["ny"])
+                elif dy > 0: dr, sr = slice(g["wb"] + g["ny"], g["wb"] + g["ny"] + W), slice(h["wb"], h["wb"] + W)
+                else: dr, sr = slice(g["wb"], g["wb"] + g["ny"]), slice(h["wb"], h["wb"] + h["ny"])
+                yield nb, (dr, dc), (sr, sc), (dx, dy)
+
+    def _exchange(self, l, slots):
+        self.exchanges += 1
+        if self.dist is None:
+            snap = {(b, s): self.a[l, b, s].copy() for b in self.owned for s in slots}
+            for b in self.owned:
+                for nb, (dr, dc), (sr, sc), _ in self._rects(l, b):
+                    for s in slots:
+                        self.a[l, b, s][:, dr, dc] = snap[nb, s][:, sr, sc]
+            return
+        import torch
+        dist = self.dist
+        (b,) = self.owned
+        ops, recvs = [], []
+        # what I send to nb is what nb's _rects asks of me: the mirror rectangle
+        for nb, (dr, dc), _, (dx, dy) in self._rects(l, b):
+            for (nb2, _, (sr, sc), (dx2, dy2)) in self._rects(l, nb):
+                if nb2 == b and (dx2, dy2) == (-dx, -dy):
+                    sbuf = torch.from_numpy(np.concatenate([self.a[l, b, s][:, sr, sc].reshape(-1) for s in slots]))
+                    ops.append(dist.P2POp(dist.isend, sbuf, nb))
+            n = sum(self.a[l, b, s][:, dr, dc].size for s in slots)
+            rbuf = torch.empty(n, dtype=torch.float64)
+            ops.append(dist.P2POp(dist.irecv, rbuf, nb))
+            recvs.append((rbuf, dr, dc))
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+        for rbuf, dr, dc in recvs:
+            o = 0
+            r = rbuf.numpy()
+            for s in slots:
+                v = self.a[l, b, s][:, dr, dc]
+                v[...] = r[o:o + v.size].reshape(v.shape)
+                o += v.size
+
+    def _gather(self, l, s):
+        """own points of every block -> a global array with zero ghost ring, on every rank"""
+        gx, gy = self.gn[l]
+        npl = self.a[l, self.owned[0], s].shape[0]
+        out = np.zeros((npl, gy + 2, gx + 2))
+        parts = {b: np.ascontiguousarray(self._own(l, b, s)) for b in self.owned}
+        if self.dist is not None:
+            allp = [None] * self.dist.get_world_size()
+            self.dist.all_gather_object(allp, parts)
+            parts = {k: v for p in allp for k, v in p.items()}
+        for b, v in parts.items():
+            g = self.g[l, b]
+            out[:, 1 + g["y0"]:1 + g["y0"] + g["ny"], 1 + g["x0"]:1 + g["x0"] + g["nx"]] = v
+        return out
+
+    # -- the executor -------------------------------------------------------------
+    def run(self, plan):
+        for o in plan:
+            getattr(self, "op_" + o["op"])(o)
+
+    def op_exchange(self, o):
+        self._exchange(o["lvl"], o["arrays"])
+
+    def op_sync(self, o):
+        self.exchanges += 1
+
+    def _each(self, o):
+        for b in self.owned:
+            yield b, self.g[o["lvl"], b]
+
+    def _ifd(self, l):
+        return 1 if (l == 0 and self.nst == 3) else 0
+
+    def _nstl(self, l):
+        return self.nst if l == 0 else 5
+
+    def op_sweep(self, o):
+        l = o["lvl"]
+        for b, g in self._each(o):
+            src, dst = self.a[l, b, o["a"]], self.a[l, b, o["b"]]
+            dst[...] = src
+            assert self.L.orc2_relax_gs(1, P(self.a[l, b, A]), P(self.a[l, b, B]), P(dst), P(self.a[l, b, SOR]), g["ii"], g["jj"], 1,
+                                        self._ifd(l), self._nstl(l), 2, 1, o["dir"], 0) == 0
+
+    def op_residual(self, o):
+        l = o["lvl"]
+        for b, g in self._each(o):
+            self.L.orc2_residual(0, P(self.a[l, b, A]), P(self.a[l, b, B]), P(self.a[l, b, o["a"]]), P(self.a[l, b, RES]), g["ii"],
+                                 g["jj"], 0, self._ifd(l), self._nstl(l))
+
+    def _window(self, l, b, s):
+        g = self.g[l, b]
+        return self.a[l + 1, b, s][:, g["oy"]:g["oy"] + g["jjc"], g["ox"]:g["ox"] + g["iic"]]
+
+    def op_restrict(self, o):
+        l = o["lvl"]
+        for b, g in self._each(o):
+            bc = np.ascontiguousarray(self._window(l, b, B))
+            pw = np.ascontiguousarray(self._window(l, b, PI))
+            assert self.L.orc2_restrict(P(self.a[l, b, RES]), P(bc), P(pw), g["ii"], g["jj"], g["iic"], g["jjc"], 0) == 0
+            self._window(l, b, B)[:, 1:-1, 1:-1] = bc[:, 1:-1, 1:-1]
+
+    def op_interp(self, o):
+        l = o["lvl"]
+        for b, g in self._each(o):
+            xc = np.ascontiguousarray(self._window(l, b, o["b"]))
+            pw = np.ascontiguousarray(self._window(l, b, PI))
+            assert self.L.orc2_interp_add(P(self.a[l, b, o["a"]]), P(xc), P(self.a[l, b, RES]), P(self.a[l, b, A]), P(pw), g["iic"],
+                                          g["jjc"], g["ii"], g["jj"], self._nstl(l), 0) == 0
+
+    def op_zero(self, o):
+        for b, _ in self._each(o):
+            self.a[o["lvl"], b, o["a"]][...] = 0.0
+
+    def op_copy(self, o):
+        for b, _ in self._each(o):
+            self.a[o["lvl"], b, o["b"]][...] = self.a[o["lvl"], b, o["a"]]
+
+    def op_gather(self, o):
+        self.exchanges += 1
+        self.GB = self._gather(self.nd, B)[0]
+
+    def op_coarse(self, o):
+        self.GX = np.zeros_like(self.GB)
+        self.csol.vcycle(self.GX, self.GB)
+
+    def op_scatter(self, o):
+        l = o["lvl"]
+        for b, g in self._each(o):
+            r0, c0 = g["y0"] + 1 - g["wb"], g["x0"] + 1 - g["wl"]
+            self.a[l, b, o["a"]][0] = self.GX[r0:r0 + g["jj"], c0:c0 + g["ii"]]
+
+    def op_recip(self, o):
+        l = o["lvl"]
+        for b, g in self._each(o):
+            self.L.orc2_setup_recip(P(self.a[l, b, A]), P(self.a[l, b, SOR]), g["ii"], g["jj"], self._nstl(l), 2)
+
+    def op_setup_interp(self, o):
+        l = o["lvl"]
+        for b, g in self._each(o):
+            pw = np.zeros((8, g["jjc"], g["iic"]))
+            for stage in (1, 2):
+                assert self.L.orc2_setup_interp_oi_stage(P(self.a[l, b, A]), None, P(pw), g["ii"], g["jj"], g["iic"], g["jjc"],
+                                                         self._ifd(l), self._nstl(l), 0, 0, stage) == 0
+            self.tmpP[b] = pw
+            self._window(l, b, PI)[...] = pw
+
+    def op_galerkin(self, o):
+        l = o["lvl"]
+        for b, g in self._each(o):
+            ac = np.zeros((5, g["jjc"], g["iic"]))
+            assert self.L.orc2_setup_itli_ex(P(self.a[l, b, A]), P(ac), P(self.tmpP[b]), g["ii"], g["jj"], g["iic"], g["jjc"],
+                                             self._ifd(l), self._nstl(l), 0) == 0
+            self._window(l, b, A)[...] = ac
+
+    def op_gather_op(self, o):
+        self.exchanges += 1
+        self.GA = self._gather(self.nd, A)
+
+    def op_setup_coarse(self, o):
+        self.csol = oracle.Solver2(self.GA, "point", self.pre, self.post, num_levels=self.nlevels - self.nd)
+        assert self.csol.nlevels == self.nlevels - self.nd
+
+    def op_sumsq(self, o):
+        for b, _ in self._each(o):
+            self.red[b] = float((self._own(o["lvl"], b, o["a"]) ** 2).sum())
+
+    def op_norm(self, o):
+        self.exchanges += 1
+        parts = dict(self.red)
+        if self.dist is not None:
+            allp = [None] * self.dist.get_world_size()
+            self.dist.all_gather_object(allp, parts)
+            parts = {k: v for p in allp for k, v in p.items()}
+        self.norm2 = sum(parts[b] for b in sorted(parts))
+
+    # -- user level ---------------------------------------------------------------
+    def set(self, b, slot, local):
+        self._own(0, b, slot)[0] = local[1:-1, 1:-1]
+
+    def get(self, b, slot=X0):
+        g = self.g[0, b]
+        out = np.zeros((g["ny"] + 2, g["nx"] + 2))
+        out[1:-1, 1:-1] = self._own(0, b, slot)[0]
+        return out
+
+    def vcycle(self):
+        self.run(self.p_cycle)
+
+    def norm(self):
+        self.run(self.p_norm)
+        return float(np.sqrt(self.norm2))
