@@ -50,6 +50,18 @@ SIGNATURES = {
     "bmgx2_relax_GS_pass": (_i, [_i, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx2_SETUP_interp_OI_stage": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _i, _i, _i, _i, _p]),
     "bmgx2_line_copy": (_i, [_p, _u, _u, _i, _u, _i, _u, _p, _i, _p]),
+    "bmgx_ipc_export": (_i, [_p, _p]),
+    "bmgx_ipc_open": (_i, [_p, C.POINTER(_p)]),
+    "bmgx_ipc_close": (_i, [_p]),
+    "bmgx_halo_step": (_i, [_p, _i, _i, _p, _p, _i, _i, _i, _i, _d, _p]),
+    "bmgx_copy2d": (_i, [_p, _z, _p, _z, _u, _u, _p]),
+    "bmgx_memcpy2d_h2d": (_i, [_p, _z, _p, _z, _u, _u, _p]),
+    "bmgx_memcpy2d_d2h": (_i, [_p, _z, _p, _z, _u, _u, _p]),
+    "bmgx_sumsq_win_work_len": (_z, []),
+    "bmgx2_sumsq_win": (_i, [_p, _z, _u, _u, _p, _p, _p]),
+    "bmgx_sum_ordered": (_i, [_p, _i, _p, _p]),
+    "bmgx2_restrict_v": (_i, [_p, _p, _p, _u, _u, _u, _u, _z, _z, _p]),
+    "bmgx2_interp_add_v": (_i, [_p, _p, _p, _p, _p, _u, _u, _u, _u, _z, _z, _p]),
     "bmgx3_plane_copy": (_i, [_p, _p, _u, _u, _u, _i, _u, _i, _p]),
     "bmgx3_plane_coeff": (_i, [_p, _p, _u, _u, _u, _i, _i, _u, _p]),
     "bmgx3_plane_rhs": (_i, [_p, _p, _p, _p, _u, _u, _u, _i, _i, _u, _p]),
@@ -72,6 +84,12 @@ for _name, (_res, _args) in SIGNATURES.items():
         _f = getattr(lib, _name)
         _f.restype = _res
         _f.argtypes = _args
+
+
+class Seg(C.Structure):
+    """bmgx_seg of include/bmgx.h"""
+    _fields_ = [("src", _p), ("dst", _p), ("rows", C.c_uint32), ("cols", C.c_uint32), ("src_pitch", C.c_uint64),
+                ("dst_pitch", C.c_uint64), ("src_rank", C.c_int32), ("reserved", C.c_int32)]
 
 
 class BmgxError(RuntimeError):

@@ -86,17 +86,17 @@ struct cdr2_dist
 		size_t o = off_red() + ALIGN_D;
 		for (int l = 0; l <= dec->ndist; l++) {
 			const block_geom g = dec->geom(l, b);
-			const size_t pl = up((size_t)g.ii * g.jj);
+			const size_t pl = (size_t)g.ii * g.jj;   // planes of an array are contiguous, as the serial kernels expect
 			for (int s = 0; s < NARR; s++) {
 				if (l == lvl && s == a) return o;
 				if (s == P && l == 0) continue;
-				o += (size_t)planes(l, s) * pl;
+				o += up((size_t)planes(l, s) * pl);
 			}
 		}
 		return o;
 	}
 	size_t arena_doubles(int b) const { return off_arr(b, dec->ndist + 1, 0); }
-	size_t plane_stride(int b, int lvl) const { const block_geom g = dec->geom(lvl, b); return up((size_t)g.ii * g.jj); }
+	size_t plane_stride(int b, int lvl) const { const block_geom g = dec->geom(lvl, b); return (size_t)g.ii * g.jj; }
 	double *ptr(int b, int lvl, int a, int plane = 0) const
 	{
 		return reinterpret_cast<double *>(base[b]) + off_arr(b, lvl, a) + (size_t)plane * plane_stride(b, lvl);

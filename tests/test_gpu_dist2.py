@@ -1,0 +1,193 @@
+"""GPU tests of the peer-memory block-decomposed solver (cedar_b200/host/dist2.cc, cdr2_dist_* of
+include/cedar_capi.h; exchange kernel cedar_b200/csrc/bmgx2_halo.cu) through the C API:
+  * the exchange kernel alone (signal / wait / pull, counters, time-out instead of a hang);
+  * the windowed transfer kernels against the plain ones, bitwise;
+  * several blocks on ONE GPU must reproduce the serial GPU solver and the CPU oracle BITWISE (hierarchy,
+    cycles eager and replayed from the captured graph, solve history);
+  * with >= 2 GPUs the same check runs one rank per GPU (tests/run_dist2_ranks.py under torchrun)."""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import oracle
+from tests.util import assert_bitwise, dev, host, ptr, random_gf, random_op2, coarse_n
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _segs(torch, abi, lst):
+    arr = (abi.Seg * len(lst))()
+    for k, (src, dst, rows, cols, sp, dp, r) in enumerate(lst):
+        arr[k] = abi.Seg(src, dst, rows, cols, sp, dp, r, 0)
+    t = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8).cuda()
+    return t
+
+
+def test_halo_step_kernel(cuda):
+    """two 'ranks' in one process: counters advance, rectangles arrive, a missing signal times out with an error word"""
+    import cedar_b200.abi as abi
+    torch = cuda
+    world = 2
+    sync = [torch.zeros(world + 3, dtype=torch.int64, device="cuda") for _ in range(world)]
+    peers = torch.tensor([s.data_ptr() for s in sync], dtype=torch.int64, device="cuda")
+    rng = np.random.default_rng(5)
+    a = [dev(torch, rng.standard_normal((40, 50))) for _ in range(world)]
+    h = [dev(torch, np.zeros((40, 50))) for _ in range(world)]
+    # rank r pulls a 7 x 9 window of the other rank's array into its own h
+    tabs = []
+    for r in range(world):
+        o = 1 - r
+        tabs.append(_segs(torch, abi, [(a[o].data_ptr() + (3 * 50 + 4) * 8, h[r].data_ptr() + (10 * 50 + 20) * 8, 7, 9, 50, 50, o),
+                                      (a[o].data_ptr(), h[r].data_ptr(), 1, 50, 50, 50, o)]))
+    for it in range(3):
+        for r in range(world):
+            abi.check(abi.lib.bmgx_halo_step(None, 0, 1, ptr(peers), ptr(sync[r]), r, world, 1, 0, 5.0, None))
+        for r in range(world):
+            abi.check(abi.lib.bmgx_halo_step(ptr(tabs[r]), 2, 4, ptr(peers), ptr(sync[r]), r, world, 2, it & 1, 5.0, None))
+    torch.cuda.synchronize()
+    for r in range(world):
+        s = host(sync[r])
+        assert list(s[:world]) == [3, 3] and s[world] == 3 and s[world + 1] == 0 and s[world + 2] == 0, s
+        o = 1 - r
+        assert_bitwise(host(h[r])[10:17, 20:29], host(a[o])[3:10, 4:13], "window")
+        assert_bitwise(host(h[r])[0], host(a[o])[0], "row")
+    # rank 0 waits for a signal rank 1 never sends: error word = 1 + rank, no hang
+    abi.check(abi.lib.bmgx_halo_step(ptr(tabs[0]), 2, 4, ptr(peers), ptr(sync[0]), 0, world, 2, 0, 0.2, None))
+    torch.cuda.synchronize()
+    assert host(sync[0])[world + 2] == 2
+
+
+@pytest.mark.parametrize("nine", [True, False])
+def test_windowed_transfer_kernels(cuda, nine):
+    """bmgx2_restrict_v / bmgx2_interp_add_v on a window of a larger coarse array == the plain kernels"""
+    import cedar_b200.abi as abi
+    torch = cuda
+    L = abi.lib
+    nx, ny = 131, 86
+    nxc, nyc = coarse_n(nx), coarse_n(ny)
+    rng = np.random.default_rng(11)
+    so = random_op2(nx, ny, nine, rng)
+    nst = so.shape[0]
+    ci = rng.uniform(0, 1, size=(8, nyc + 2, nxc + 2))
+    res = random_gf(nx, ny, rng, ghosts_zero=False)
+    q = random_gf(nx, ny, rng, ghosts_zero=False)
+    qc = random_gf(nxc, nyc, rng, ghosts_zero=False)
+    # plain
+    d_res, d_ci, d_qc0 = dev(torch, res), dev(torch, ci), dev(torch, np.zeros_like(qc))
+    abi.check(L.bmgx2_restrict(ptr(d_res), ptr(d_qc0), ptr(d_ci), nx + 2, ny + 2, nxc + 2, nyc + 2, 0, None))
+    d_q, d_r2, d_so, d_qc = dev(torch, q), dev(torch, res), dev(torch, so), dev(torch, qc)
+    abi.check(L.bmgx2_interp_add(ptr(d_q), ptr(d_qc), ptr(d_r2), ptr(d_so), ptr(d_ci), nxc + 2, nyc + 2, nx + 2, ny + 2, nst, 0, None))
+    # windowed: the coarse arrays sit at (oy, ox) of wider arrays with their own pitch and plane stride
+    oy, ox, JJ, II = 3, 5, nyc + 2 + 9, nxc + 2 + 11
+    big_ci = rng.standard_normal((8, JJ, II)); big_ci[:, oy:oy + nyc + 2, ox:ox + nxc + 2] = ci
+    big_qc = rng.standard_normal((JJ, II)); big_qc[oy:oy + nyc + 2, ox:ox + nxc + 2] = qc
+    big_out = np.full((JJ, II), 7.0)
+    off = (oy * II + ox) * 8
+    w_ci, w_qc, w_out = dev(torch, big_ci), dev(torch, big_qc), dev(torch, big_out)
+    abi.check(L.bmgx2_restrict_v(ptr(d_res), C.c_void_p(w_out.data_ptr() + off), C.c_void_p(w_ci.data_ptr() + off), nx + 2, ny + 2,
+                                 nxc + 2, nyc + 2, II, II * JJ, None))
+    got = host(w_out)
+    assert_bitwise(got[oy + 1:oy + nyc + 1, ox + 1:ox + nxc + 1], host(d_qc0)[1:-1, 1:-1], "restrict_v")
+    mask = np.ones_like(got, dtype=bool); mask[oy + 1:oy + nyc + 1, ox + 1:ox + nxc + 1] = False
+    assert (got[mask] == 7.0).all()          # nothing outside the window's interior is written
+    v_q, v_r = dev(torch, q), dev(torch, res)
+    abi.check(L.bmgx2_interp_add_v(ptr(v_q), C.c_void_p(w_qc.data_ptr() + off), ptr(v_r), ptr(d_so), C.c_void_p(w_ci.data_ptr() + off),
+                                   nxc + 2, nyc + 2, nx + 2, ny + 2, II, II * JJ, None))
+    assert_bitwise(host(v_q), host(d_q), "interp_add_v q")
+    assert_bitwise(host(v_r), host(d_r2), "interp_add_v res")
+    # window sum of squares and ordered fold
+    work = torch.zeros(L.bmgx_sumsq_win_work_len() + 2, dtype=torch.float64, device="cuda")
+    out = torch.zeros(1, dtype=torch.float64, device="cuda")
+    abi.check(L.bmgx2_sumsq_win(C.c_void_p(w_qc.data_ptr() + off), II, nxc + 2, nyc + 2, ptr(work), ptr(out), None))
+    assert abs(float(out.item()) - (qc ** 2).sum()) <= 1e-12 * (qc ** 2).sum()
+
+
+def _join(parts, ext, nx, ny):
+    first = next(iter(parts.values()))
+    g = np.zeros(first.shape[:-2] + (ny + 2, nx + 2))
+    for b, t in parts.items():
+        x0, y0, nxl, nyl = ext[b]
+        g[..., 1 + y0:1 + y0 + nyl, 1 + x0:1 + x0 + nxl] = t
+    return g
+
+
+CASES = [(257, 257, 2, 2, True, 33, 15, 1, 1), (513, 257, 4, 2, True, 65, 15, 1, 1), (300, 210, 2, 2, False, 33, 7, 2, 1),
+         (1025, 1025, 2, 1, True, 129, 15, 1, 1), (513, 513, 2, 2, True, 65, 5, 2, 2), (385, 641, 1, 3, True, 65, 9, 1, 2)]
+
+
+@pytest.mark.parametrize("nx,ny,px,py,nine,agg,halo,pre,post", CASES)
+def test_blocks_on_one_gpu_equal_serial(cuda, nx, ny, px, py, nine, agg, halo, pre, post):
+    import cedar_b200.dist2 as d2
+    import cedar_b200.solver as cs
+    rng = np.random.default_rng(nx + ny + nine + halo)
+    so = random_op2(nx, ny, nine, rng)
+    b = random_gf(nx, ny, rng)
+    ref = oracle.Solver2(so, "point", pre, post)
+    ser = cs.Solver2(cs.Operator2(so), relaxation="point", nrelax_pre=pre, nrelax_post=post, maxiter=6, tol=1e-30)
+    l0 = cs.gpu_launches()
+    sol = d2.DistSolver2(nx, ny, (px, py), nst=so.shape[0], nrelax_pre=pre, nrelax_post=post, agglomerate=agg, halo=halo)
+    nb = px * py
+    ext = {k: sol.extent(0, k) for k in range(nb)}
+    for k, v in d2.split_blocks(so, ext).items():
+        sol.set_operator(k, v)
+    sol.setup()
+    assert sol.nlevels == ref.nlevels and sol.ndist >= 1
+    for lvl in range(1, sol.ndist + 1):
+        extl = {k: sol.extent(lvl, k) for k in range(nb)}
+        gx, gy = ref.level_shape(lvl)
+        for name in ("A", "P"):
+            want = ref.level_array(lvl, name).copy()
+            want[:, 0, :] = 0; want[:, -1, :] = 0; want[:, :, 0] = 0; want[:, :, -1] = 0
+            assert_bitwise(_join({k: sol.level_array(k, lvl, name) for k in range(nb)}, extl, gx, gy), want, f"{name} level {lvl}")
+    # cycles: eager (2), captured, replayed -- every one bitwise the oracle's
+    xr = np.zeros_like(b)
+    for k, v in d2.split_blocks(b, ext).items():
+        sol.upload(k, "b", v)
+        sol.upload(k, "x", np.zeros_like(v))
+    for it in range(5):
+        ref.vcycle(xr, b)
+        sol.vcycle()
+        x = _join({k: sol.download(k)[1:-1, 1:-1] for k in range(nb)}, ext, nx, ny)
+        assert_bitwise(x, xr, f"cycle {it}")
+    # solve from x = 0: history against the serial GPU solver and the oracle
+    for k, v in d2.split_blocks(b, ext).items():
+        sol.upload(k, "x", np.zeros_like(v))
+    h, r0 = sol.solve(maxiter=6, tol=1e-30)
+    xs, hs, r0s = ser.solve(b)
+    xo, ho, r0o = ref.solve(b, maxiter=6, tol=1e-30)
+    x = _join({k: sol.download(k)[1:-1, 1:-1] for k in range(nb)}, ext, nx, ny)
+    assert_bitwise(x, xo, "solve vs oracle")
+    assert_bitwise(x, xs, "solve vs serial GPU solver")
+    assert len(h) == len(ho) and np.allclose(h, ho, rtol=1e-10, atol=0) and abs(r0 - r0o) <= 1e-12 * r0o
+    assert cs.gpu_launches() > l0
+    sol.close()
+
+
+def test_stream_of_right_hand_sides_single_block_process(cuda):
+    """vcycle_stream needs one block per process: refused with several"""
+    import cedar_b200.dist2 as d2
+    import cedar_b200.solver as cs
+    sol = d2.DistSolver2(257, 257, (2, 1), agglomerate=33)
+    ext = {k: sol.extent(0, k) for k in range(2)}
+    for k in range(2):
+        sol.set_operator(k, d2.gallery_fe_block((257, 257), ext[k]))
+    sol.setup()
+    with pytest.raises(cs.CedarError):
+        sol.vcycle_stream([np.zeros((259, 130))], [np.zeros((259, 130))])
+    sol.close()
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_ranks_equal_serial(cuda, world):
+    if cuda.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr",
+           "127.0.0.1", "--master-port", "29541", os.path.join(ROOT, "tests", "run_dist2_ranks.py")]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "DIST2 RANKS OK" in r.stdout
