@@ -36,6 +36,7 @@ lib.cdr2_dist_sync.argtypes = [C.c_void_p]
 lib.cdr2_dist_solve.argtypes = [C.c_void_p, C.c_int, C.c_double, _dp, C.c_int, _ip, _dp]
 lib.cdr2_dist_time_vcycles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float)]
 lib.cdr2_dist_vcycle_stream.argtypes = [C.c_void_p, C.c_int, C.POINTER(_dp), C.POINTER(_dp)]
+lib.cdr2_dist_profile_ops.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int, _ip]
 lib.cdr2_dist_plan_json.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.c_char_p, C.c_char_p, C.c_size_t, _ip]
 lib.cdr2_dist_geometry.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _ip]
@@ -109,6 +110,7 @@ class DistSolver2:
                  cuda_graph=True, comm=None):
         px, py = decomp_shape
         self.nx, self.ny, self.px, self.py, self.nst, self.comm = nx, ny, px, py, nst, comm
+        self.pre, self.post, self.agglomerate = nrelax_pre, nrelax_post, agglomerate
         nb = px * py
         if blocks is None:
             blocks = [comm.rank] if comm is not None else list(range(nb))
@@ -188,6 +190,15 @@ class DistSolver2:
         ms = C.c_float()
         _check(lib.cdr2_dist_time_vcycles(self.h, warmup, n, C.byref(ms)))
         return ms.value
+
+    def profile_ops(self, n=5):
+        """[(operation dict, ms)] for one cycle: eager, host-synchronised per operation (diagnostic)"""
+        ops, _ = plan(self.nx, self.ny, self.px, self.py, self.nst, self.pre, self.post, self.agglomerate, self.halo, "cycle")
+        out = (C.c_float * len(ops))()
+        m = C.c_int()
+        _check(lib.cdr2_dist_profile_ops(self.h, n, out, len(ops), C.byref(m)))
+        assert m.value == len(ops)
+        return list(zip(ops, list(out)))
 
     def vcycle_stream(self, bs, xs):
         n = len(bs)

@@ -217,6 +217,20 @@ int cdr2_solver_vcycle_dev(cdr2_solver *s, const double *b_dev, double *x_dev, v
 	});
 }
 
+int cdr2_solver_resident_ptrs(cdr2_solver *s, double **b_dev, double **x_dev)
+{
+	return guard([&] { *b_dev = s->b.dev(); *x_dev = s->x.dev(); });
+}
+
+int cdr2_solver_vcycle_resident(cdr2_solver *s, void *stream)
+{
+	return guard([&] {
+		gpu::stream_guard on_callers_stream(stream);
+		s->b.dev(); s->x.dev();    // the caller wrote the device buffers
+		if (s->s5) s->s5->vcycle(s->x, s->b); else s->s9->vcycle(s->x, s->b);
+	});
+}
+
 int cdr2_solver_buffers(cdr2_solver *s, double **b, double **x)
 {
 	return guard([&] { *b = s->b.data(); *x = s->x.data(); });

@@ -43,7 +43,8 @@ struct dist_block
 	std::vector<block_geom> g;
 	cdr2_operator *cop = nullptr;
 	cdr2_solver *csol = nullptr;
-	double *GB = nullptr, *GX = nullptr, *GA = nullptr;   // global arrays of the agglomerated level
+	double *GB = nullptr, *GX = nullptr;   // the replicated solver's own b and (current) x: global arrays of the agglomerated level
+	double *GA = nullptr;                  // setup: the gathered operator of that level
 	double *tmpP = nullptr, *tmpA = nullptr;              // setup: contiguous coarse windows
 	double *work = nullptr, *red_all = nullptr, *norm_out = nullptr;
 	std::map<std::string, seg_table> segs;
@@ -124,7 +125,7 @@ void upload_segs(seg_table &t, const std::vector<bmgx_seg> &v, bmgx_stream_t s)
 	t.n = (int)v.size();
 	size_t big = 0;
 	for (auto &sg : v) big = std::max(big, (size_t)sg.rows * sg.cols);
-	t.chunks = (int)std::min<size_t>(32, std::max<size_t>(1, big / 4096));
+	t.chunks = (int)std::min<size_t>(64, std::max<size_t>(1, (big + 1023) / 1024));   // 256 threads x 4 loads in flight
 	if (t.n == 0) return;
 	check(bmgx_malloc((void **)&t.dev, v.size() * sizeof(bmgx_seg)), "segment table");
 	check(bmgx_memcpy_h2d(t.dev, v.data(), v.size() * sizeof(bmgx_seg), s), "segment table upload");
@@ -194,7 +195,7 @@ seg_table &table(cdr2_dist &d, dist_block &K, const plan_op &o)
 	const int nd = d.dec->ndist;
 	switch (o.kind) {
 	case op_kind::exchange: v = exchange_segs(d, o.lvl, K.id, o.arrays); break;
-	case op_kind::gather: v = gather_segs(d, nd, o.a, K.GB); break;
+	case op_kind::gather: v = gather_segs(d, nd, o.a, K.GB); break;   // GB = the replicated solver's own right-hand side
 	case op_kind::gather_op: v = gather_segs(d, nd, A, K.GA); break;
 	case op_kind::norm:
 		for (int q = 0; q < d.nblocks(); q++) {
@@ -275,9 +276,15 @@ void run_op(cdr2_dist &d, const plan_op &o)
 			check(bmgx_memcpy_d2d(d.ptr(b, l, o.b), d.ptr(b, l, o.a), (size_t)g.ii * g.jj * 8, s), "copy");
 			break;
 		case op_kind::coarse: {
+			// the replicated serial solver works on its own device buffers: the gather wrote its b; clear its x, cycle,
+			// and remember where its iterate ended up (the fused relaxation ping-pongs x with a scratch array)
 			const size_t n = (size_t)(dec.gn[nd][0] + 2) * (dec.gn[nd][1] + 2);
-			check(bmgx_memset0(K.GX, n * 8, s), "coarse x0");
-			if (cdr2_solver_vcycle_dev(K.csol, K.GB, K.GX, s)) throw std::runtime_error(std::string("agglomerated cycle: ") + cdr_last_error());
+			double *cb = nullptr, *cx = nullptr;
+			if (cdr2_solver_resident_ptrs(K.csol, &cb, &cx)) throw std::runtime_error(cdr_last_error());
+			if (cb != K.GB) throw std::logic_error("replicated solver moved its right-hand side");
+			check(bmgx_memset0(cx, n * 8, s), "coarse x0");
+			if (cdr2_solver_vcycle_resident(K.csol, s)) throw std::runtime_error(std::string("agglomerated cycle: ") + cdr_last_error());
+			if (cdr2_solver_resident_ptrs(K.csol, &cb, &K.GX)) throw std::runtime_error(cdr_last_error());
 			break;
 		}
 		case op_kind::scatter: {
@@ -326,6 +333,7 @@ void run_op(cdr2_dist &d, const plan_op &o)
 			                        "}, \"max-iter\": 1, \"tol\": 0, \"cuda-graph\": false, \"num-levels\": " + std::to_string(nl) + "}}";
 			if (cdr2_solver_create(K.cop, cfg.c_str(), &K.csol)) throw std::runtime_error(cdr_last_error());
 			if (cdr2_solver_nlevels(K.csol) != nl) throw std::runtime_error("agglomerated solver: unexpected number of levels");
+			if (cdr2_solver_resident_ptrs(K.csol, &K.GB, &K.GX)) throw std::runtime_error(cdr_last_error());
 			break;
 		}
 		default: throw std::logic_error("unknown plan operation");
@@ -410,9 +418,7 @@ int cdr2_dist_create(unsigned gnx, unsigned gny, int px, int py, int nstencil, i
 			d->base[K.id] = K.arena;
 			const int ndl = d->dec->ndist;
 			const size_t gn = (size_t)(d->dec->gn[ndl][0] + 2) * (d->dec->gn[ndl][1] + 2);
-			check(bmgx_malloc((void **)&K.GB, gn * 8), "GB"); check(bmgx_malloc((void **)&K.GX, gn * 8), "GX");
 			check(bmgx_malloc((void **)&K.GA, gn * 5 * 8), "GA");
-			check(bmgx_memset0(K.GB, gn * 8, d->stream), "clear"); check(bmgx_memset0(K.GX, gn * 8, d->stream), "clear");
 			check(bmgx_memset0(K.GA, gn * 5 * 8, d->stream), "clear");
 			size_t wmax = 0;
 			for (int l = 0; l < ndl; l++) {
@@ -440,7 +446,7 @@ void cdr2_dist_destroy(cdr2_dist *d)
 		for (auto &kv : K.segs) if (kv.second.dev) bmgx_free(kv.second.dev);
 		if (K.csol) cdr2_solver_destroy(K.csol);
 		if (K.cop) cdr2_operator_destroy(K.cop);
-		bmgx_free(K.GB); bmgx_free(K.GX); bmgx_free(K.GA); bmgx_free(K.tmpP); bmgx_free(K.tmpA); bmgx_free(K.work);
+		bmgx_free(K.GA); bmgx_free(K.tmpP); bmgx_free(K.tmpA); bmgx_free(K.work);
 		bmgx_free(K.arena);
 	}
 	for (int q = 0; q < 2; q++) { if (d->db[q]) bmgx_free(d->db[q]); if (d->dx[q]) bmgx_free(d->dx[q]); }
@@ -662,6 +668,37 @@ int cdr2_dist_vcycle_stream(cdr2_dist *d, int nrhs, const double *const *bh, dou
 		}
 		check(bmgx_stream_sync(d->s_down), "sync");
 		check(bmgx_stream_sync(cs), "sync");
+		check_device_error(*d);
+	});
+}
+
+/* per-operation device times of one cycle (eager, one host synchronisation per operation, CUDA events around each):
+ * out[k] = ms of operation k of the cycle list (cdr2_dist_plan_json "cycle"), averaged over n cycles.  Exchange
+ * operations include the wait for the neighbours.  A diagnostic: the sum exceeds the graph-replayed cycle. */
+int cdr2_dist_profile_ops(cdr2_dist *d, int n, float *out, int cap, int *nops)
+{
+	return guard([&] {
+		if (!d->is_setup) throw std::runtime_error("cdr2_dist_setup has not run");
+		const int m = (int)d->p_cycle.size();
+		if (nops) *nops = m;
+		if (cap < m) throw std::runtime_error("profile buffer too small");
+		void *e0, *e1;
+		check(bmgx_event_create(&e0), "event"); check(bmgx_event_create(&e1), "event");
+		for (int k = 0; k < m; k++) out[k] = 0;
+		for (int it = 0; it < n + 1; it++) {
+			for (auto &K : d->blk) check(bmgx_memset0(d->ptr(K.id, 0, X0), (size_t)K.g[0].ii * K.g[0].jj * 8, d->stream), "x0");
+			for (int k = 0; k < m; k++) {
+				check(bmgx_stream_sync(d->stream), "sync");
+				check(bmgx_event_record(e0, d->stream), "record");
+				run_op(*d, d->p_cycle[k]);
+				check(bmgx_event_record(e1, d->stream), "record");
+				check(bmgx_event_sync(e1), "sync");
+				float ms = 0;
+				check(bmgx_event_elapsed_ms(e0, e1, &ms), "elapsed");
+				if (it > 0) out[k] += ms / n;
+			}
+		}
+		bmgx_event_destroy(e0); bmgx_event_destroy(e1);
 		check_device_error(*d);
 	});
 }

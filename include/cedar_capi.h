@@ -58,6 +58,13 @@ int cdr2_solver_matvec(cdr2_solver *solver, const double *x, double *y);
  * (a cudaStream_t; NULL = the library's own stream): no host traffic, no synchronisation */
 int cdr2_solver_vcycle_dev(cdr2_solver *solver, const double *b_dev, double *x_dev, void *stream);
 
+/* The solver's own device-resident b and x ((nx+2)(ny+2) doubles each) and one V-cycle on them, enqueued on `stream`:
+ * for device-side callers that fill b and x themselves (the block-decomposed solver's replicated coarse levels).
+ * The fused relaxation exchanges x's device buffer with a scratch array, so ask for the pointers again after a
+ * cycle: *x_dev is where the iterate is NOW. */
+int cdr2_solver_resident_ptrs(cdr2_solver *solver, double **b_dev, double **x_dev);
+int cdr2_solver_vcycle_resident(cdr2_solver *solver, void *stream);
+
 /* Pinned host staging buffers owned by the solver ((nx+2)(ny+2) doubles each):
  * fill *b (and *x as initial guess) in place, then call the _pinned variants,
  * which upload b and x, run on the device and download x into the same buffer
@@ -125,6 +132,8 @@ int cdr2_dist_sync(cdr2_dist *d);
 int cdr2_dist_solve(cdr2_dist *d, int maxiter, double tol, double *hist, int hist_cap, int *niter, double *res0);
 int cdr2_dist_time_vcycles(cdr2_dist *d, int warmup, int n, float *ms_per_cycle);
 int cdr2_dist_vcycle_stream(cdr2_dist *d, int nrhs, const double *const *b, double *const *x);
+/* diagnostic: device time of every operation of the cycle list, eager with a host synchronisation per operation */
+int cdr2_dist_profile_ops(cdr2_dist *d, int n, float *ms_per_op, int cap, int *nops);
 /* host-only views of the schedule (no device needed): operation list as JSON, block geometry
  * (x0,y0,nx,ny, wl,wr,wb,wt, coarse window ox,oy,iic,jjc) */
 int cdr2_dist_plan_json(unsigned nx, unsigned ny, int px, int py, int nstencil, int nrelax_pre, int nrelax_post,
