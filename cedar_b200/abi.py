@@ -46,6 +46,7 @@ SIGNATURES = {
     "bmgx2_SETUP_interp_OI": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _i, _i, _i, _p]),
     "bmgx2_SETUP_ITLI_ex": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _i, _i, _p]),
     "bmgx2_SETUP_cg_LU": (_i, [_p, _u, _u, _i, _p, _u, _u, _i, _p]),
+    "bmgx_cg_LU_info": (_i, [C.POINTER(_i), _p]),
     "bmgx2_SOLVE_cg": (_i, [_p, _p, _u, _u, _p, _p, _u, _u, _i, _p]),
     "bmgx2_relax_GS_pass": (_i, [_i, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx2_SETUP_interp_OI_stage": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _i, _i, _i, _i, _p]),

@@ -8,8 +8,14 @@
 // sequential accumulation order in one thread: the coarsest grids of the hot
 // path have 9..49 unknowns.
 #include "bmgx_common.cuh"
+#include <cstdio>
 
 #define ABD(i, j) abd[(size_t)((j)-1) * nabd1 + ((i)-1)]
+
+// INFO of the last banded Cholesky factorisation enqueued by this library (DPBTRF's INFO: 0 = ok, j > 0 = the
+// leading minor of order j is not positive definite; the reference logs "Coarse grid Cholesky decomposition
+// failed", BMG2_SymStd_SETUP_cg_LU.f90:124-131).  Read back with bmgx_cg_LU_info().
+__device__ int g_cg_info = 0;
 
 __global__ void __launch_bounds__(256)
 k_cg_assemble(const double *__restrict__ so, unsigned II, unsigned JJ, int nstncl, double *__restrict__ abd,
@@ -73,7 +79,20 @@ __global__ void __launch_bounds__(256) k_dpbtf2_upper(int n, int kd, double *abd
         }
         __syncthreads();
     }
-    if (threadIdx.x == 0 && info) *info = s_bad;
+    if (threadIdx.x == 0) { g_cg_info = s_bad; if (info) *info = s_bad; }
+}
+
+extern "C" int bmgx_cg_LU_info(int *info, bmgx_stream_t s)
+{
+    cudaError_t e = cudaStreamSynchronize((cudaStream_t)s);
+    if (e == cudaSuccess) e = cudaMemcpyFromSymbol(info, g_cg_info, sizeof(int));
+    if (e != cudaSuccess) return bmgx_set_cuda_error(e, "bmgx_cg_LU_info");
+    if (*info != 0) {
+        char msg[128];
+        snprintf(msg, sizeof(msg), "Coarse grid Cholesky decomposition failed at column %d (operator not positive definite)", *info);
+        return bmgx_set_error(BMGX_ERR_ARG, msg);
+    }
+    return BMGX_OK;
 }
 
 extern "C" int bmgx2_SETUP_cg_LU(const double *so, bmgx_len ii, bmgx_len jj, int nstncl, double *abd,

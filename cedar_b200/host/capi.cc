@@ -176,7 +176,7 @@ int cdr2_solver_solve(cdr2_solver *s, const double *b, double *x, double *hist, 
 		else { s->s9->solve(s->b, s->x); h = &s->s9->history(); if (res0) *res0 = s->s9->res0(); }
 		std::memcpy(x, s->x.cdata(), s->x.size() * sizeof(double));
 		if (niter) *niter = static_cast<int>(h->size());
-		for (int i = 0; i < hist_cap && i < static_cast<int>(h->size()); i++) hist[i] = (*h)[i];
+		for (int i = 0; hist && i < hist_cap && i < static_cast<int>(h->size()); i++) hist[i] = (*h)[i];
 	});
 }
 

@@ -193,6 +193,11 @@ int bmgx2_SETUP_cg_LU(const bmgx_real *so, bmgx_len ii, bmgx_len jj, int nstncl,
                       bmgx_real *abd, bmgx_len nabd1, bmgx_len nabd2, int ibc,
                       bmgx_stream_t s);
 
+/* INFO of the last factorisation enqueued by bmgx2_/bmgx3_SETUP_cg_LU (DPBTRF's INFO; the reference logs "Coarse grid
+ * Cholesky decomposition failed", BMG2_SymStd_SETUP_cg_LU.f90:124-131).  Synchronises the stream.  Returns
+ * BMGX_ERR_ARG with the failing column in bmgx_last_error() when *info != 0: the factor is unusable. */
+int bmgx_cg_LU_info(int *info, bmgx_stream_t s);
+
 /* BMG2_SymStd_SOLVE_cg(q, qf, ii, jj, abd, bbd, nabd1, nabd2, jpn)
  * src/2d/solve_cg.cc:6 ; bbd is DEVICE scratch of nabd2 doubles. */
 int bmgx2_SOLVE_cg(bmgx_real *q, const bmgx_real *qf, bmgx_len ii, bmgx_len jj,

@@ -17,6 +17,10 @@ public:
 		bmgx_get_bc(params->per_mask(), &ibc);
 		gpu::check(bmgx3_SETUP_cg_LU(so.cdev(), so.len(0), so.len(1), so.len(2), stencil_ndirs<sten>::value, ABD.dev(),
 		                             ABD.len(0), ABD.len(1), ibc, gpu::stream()), "SETUP_cg_LU3");
+		// DPBTRF's INFO: a half-factored ABD must not be used (the reference logs "Coarse grid Cholesky decomposition
+		// failed"); synchronises, setup phase only
+		int info = 0;
+		gpu::check(bmgx_cg_LU_info(&info, gpu::stream()), "coarse-grid Cholesky");
 		bbd_dev.reshape(ABD.len(1));
 		bbd_dev.dev();
 	}

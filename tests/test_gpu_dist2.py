@@ -191,3 +191,29 @@ def test_ranks_equal_serial(cuda, world):
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "DIST2 RANKS OK" in r.stdout
+
+
+def test_c5_operator_history_equals_oracle(cuda):
+    """BASELINE configs[4]'s operator (9-point heterogeneous, 64x64 checkerboard of D = 10^U(-3,3)) at 1025^2 on a 2x2
+    block grid: the decomposed GPU solve follows the serial CPU oracle's residual history to 1e-10 -- including its
+    shape: the L2 residual first GROWS (to ~16x) and then contracts slowly (~0.95 per V(1,1) point-relaxation cycle
+    asymptotically), so the 30-cycle 'final_rel_residual > 1' of the round-1 bench line is the operator's, not the
+    decomposition's"""
+    import cedar_b200.dist2 as d2
+    n, px, py = 1025, 2, 2
+    so = d2.gallery_hetero_block((n, n), (0, 0, n, n))
+    b = d2.rhs_sin_block((n, n), (0, 0, n, n))
+    ref = oracle.Solver2(so, "point", 1, 1)
+    xo, ho, r0o = ref.solve(b, maxiter=40, tol=1e-10)
+    sol = d2.DistSolver2(n, n, (px, py), agglomerate=129)
+    ext = {k: sol.extent(0, k) for k in range(px * py)}
+    for k in range(px * py):
+        sol.set_operator(k, d2.gallery_hetero_block((n, n), ext[k]))     # block-wise generator == cut of the global one
+        sol.upload(k, "b", d2.rhs_sin_block((n, n), ext[k]))
+    sol.setup()
+    h, r0 = sol.solve(maxiter=40, tol=1e-10)
+    assert len(h) == len(ho) == 40 and ho.max() > 5.0 and ho[-1] < ho.max()
+    assert np.allclose(h, ho, rtol=1e-10, atol=0) and abs(r0 - r0o) <= 1e-12 * r0o
+    x = _join({k: sol.download(k)[1:-1, 1:-1] for k in range(px * py)}, ext, n, n)
+    assert_bitwise(x, xo, "C5 operator, 40 cycles")
+    sol.close()

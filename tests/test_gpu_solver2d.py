@@ -184,3 +184,21 @@ def test_hetero_c3b_matches_oracle(cs, relax):
         # condition number carries the 1e6 jumps: the histories agree to 1e-10 relative down to a floor of 1e-12
         assert np.all(np.abs(h - hr) <= 1e-10 * hr + 1e-12), (h, hr)
         assert np.max(np.abs(x - xr)) <= 1e-6 * np.max(np.abs(xr))
+
+
+def test_indefinite_coarse_operator_is_reported(cs):
+    """DPBTRF INFO (BMG2_SymStd_SETUP_cg_LU.f90:124-131 logs 'Coarse grid Cholesky decomposition failed'): a
+    coarsest-grid operator that is not positive definite must fail the setup loudly, not leave a half-factored ABD"""
+    nx = ny = 5                      # one level: the fine operator IS the coarse-solve operator
+    so = oracle.gallery2("fe", nx, ny)
+    so[0, 1:-1, 1:-1] = -8.0         # negative diagonal: first pivot <= 0
+    with pytest.raises(cs.CedarError, match="Cholesky"):
+        cs.Solver2(cs.Operator2(so), relaxation="point", nrelax_pre=1, nrelax_post=1, num_levels=1)
+    # a singular one (zero row sums everywhere, pure Neumann-like): the last pivot collapses
+    so = oracle.gallery2("fe", nx, ny)
+    so[0, 1:-1, 1:-1] = 0.0
+    with pytest.raises(cs.CedarError, match="Cholesky"):
+        cs.Solver2(cs.Operator2(so), relaxation="point", nrelax_pre=1, nrelax_post=1, num_levels=1)
+    # and a good operator still sets up after the failures (the status word is reset by the next factorisation)
+    sol = cs.Solver2(cs.Operator2(oracle.gallery2("fe", nx, ny)), relaxation="point", nrelax_pre=1, nrelax_post=1, num_levels=1)
+    assert sol.nlevels == 1
