@@ -255,3 +255,33 @@ int cdr3_solver_time_solves(cdr3_solver *s, const double *b, int warmup, int n, 
 }
 
 }
+
+// One plane-relaxation sweep through the kernel registry, exactly the call sequence of the reference's own test
+// (test/3d/test_planes.cc:13-52): build_kernel_manager(conf); kman->setup<plane_relax<dir>>(so);
+// kman->run<plane_relax<dir>>(so, x, b, cdir).  Host arrays in, x out.
+template <relax_dir rdir, class OP>
+static void plane_sweep(OP &so, config &conf, grid_func &x, const grid_func &b, cycle::Dir cdir)
+{
+	auto kman = build_kernel_manager(conf);
+	kman->template setup<kernels::plane_relax<stypes, rdir>>(so);
+	kman->template run<kernels::plane_relax<stypes, rdir>>(so, x, b, cdir);
+}
+
+extern "C" int cdr3_plane_relax(cdr3_operator *op, const char *config_json, const char *dir, int updown, const double *b, double *x)
+{
+	return guard([&] {
+		auto conf = make_config(config_json);
+		grid_func gx(op->nx, op->ny, op->nz), gb(op->nx, op->ny, op->nz);
+		upload(gx, x); upload(gb, b);
+		const std::string d(dir);
+		const cycle::Dir cdir = updown ? cycle::Dir::UP : cycle::Dir::DOWN;
+		auto go = [&](auto &so) {
+			if (d == "xy") plane_sweep<relax_dir::xy>(so, *conf, gx, gb, cdir);
+			else if (d == "xz") plane_sweep<relax_dir::xz>(so, *conf, gx, gb, cdir);
+			else if (d == "yz") plane_sweep<relax_dir::yz>(so, *conf, gx, gb, cdir);
+			else throw std::runtime_error("plane direction must be xy, xz or yz");
+		};
+		if (op->seven) go(*op->seven); else go(*op->full);
+		std::memcpy(x, gx.cdata(), gx.size() * sizeof(double));
+	});
+}

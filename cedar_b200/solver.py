@@ -271,6 +271,16 @@ lib.cdr3_solver_time_vcycles.argtypes = [_vp, _dp, C.c_int, C.c_int, C.POINTER(C
 lib.cdr3_solver_time_solves.argtypes = [_vp, _dp, C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int)]
 
 
+lib.cdr3_plane_relax.argtypes = [_vp, C.c_char_p, C.c_char_p, C.c_int, _dp, _dp]
+
+
+def plane_relax3(op, direction, x, b, up=False, plane_config=None):
+    """one zebra plane sweep through the kernel registry (test/3d/test_planes.cc); x is updated in place"""
+    cfg = json.dumps({"log": ["error"], "plane-config": plane_config or {}})
+    _check(lib.cdr3_plane_relax(op.h, cfg.encode(), direction.encode(), int(up), _P(np.ascontiguousarray(b)), _P(x)))
+    return x
+
+
 class Operator3:
     """Host-side 3D stencil operator, shape (ndirs, nz+2, ny+2, nx+2); ndirs = 4 or 14."""
 

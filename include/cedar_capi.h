@@ -164,6 +164,10 @@ int cdr3_solver_vcycle0_pinned(cdr3_solver *solver);   /* x0 = 0: uploads b only
 int cdr3_solver_vcycle_batch(cdr3_solver *solver, int nrhs, const double *const *b, double *const *x);
 int cdr3_solver_time_vcycles(cdr3_solver *solver, const double *b, int warmup, int n, float *ms_per_cycle);
 int cdr3_solver_time_solves(cdr3_solver *solver, const double *b, int warmup, int n, float *ms_per_solve, int *niter);
+/* one plane-relaxation sweep (dir = "xy" | "xz" | "yz"; updown 0 = down, 1 = up) through the kernel registry, the call
+ * sequence of the reference's test/3d/test_planes.cc:13-52 (build_kernel_manager, setup<plane_relax<dir>>, run);
+ * config_json carries "plane-config" as in test/3d/test-planes-ser.json.  Host arrays; x is updated in place. */
+int cdr3_plane_relax(cdr3_operator *op, const char *config_json, const char *dir, int updown, const double *b, double *x);
 
 #ifdef __cplusplus
 }

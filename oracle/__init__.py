@@ -93,7 +93,7 @@ class Solver2:
     """Mirror of cdr2::solver<fsten> on the CPU oracle."""
 
     def __init__(self, so, relaxation="point", nrelax_pre=2, nrelax_post=1,
-                 num_levels=-1, min_coarse=3):
+                 num_levels=-1, min_coarse=3, cycle="v"):
         self.so = np.ascontiguousarray(so)
         nst, jj, ii = self.so.shape
         self.nx, self.ny = ii - 2, jj - 2
@@ -101,6 +101,8 @@ class Solver2:
                                           nrelax_pre, nrelax_post, num_levels, min_coarse)
         self.h = C.c_void_p(self.h)
         self.nlevels = lib().orc2_solver_nlevels(self.h)
+        if cycle == "f":       # include/cedar/cycle/fcycle.h
+            lib().orc2_solver_set_cycle(self.h, 1)
 
     def level_shape(self, lvl):
         nx, ny = C.c_int(), C.c_int()

@@ -31,6 +31,7 @@ struct orc2_solver {
     double *ABD, *bbd;
     int nabd1, nabd2;
     double *linebuf;
+    int fcycle;   /* 0: V-cycle (default), 1: F-cycle (cycle/fcycle.h) */
 };
 
 static double *zalloc(size_t n) { return (double *)calloc(n ? n : 1, sizeof(double)); }
@@ -198,8 +199,32 @@ static void ncycle(orc2_solver *s, int l, double *x, const double *b)
     for (int i = 0; i < s->npost; i++) relax_level(s, l, x, b, 1);
 }
 
+/* cycle/fcycle.h:49-83: fmg_cycle + fmg_cycle_helper.  The right-hand side itself is restricted down to the coarsest
+ * level, which is solved directly; on the way up every level starts from x = 0, takes the interpolated coarse
+ * solution (interp_add with a zero residual) and runs one V-cycle from that level. */
+static void fmg_cycle(orc2_solver *s, int l, double *x, const double *b)
+{
+    olevel *L = &s->lv[l];
+    int II = L->nx + 2, JJ = L->ny + 2;
+    if (l == s->nlevels - 1) {
+        orc2_solve_cg(x, b, II, JJ, s->ABD, s->bbd, s->nabd1, s->nabd2, 0);
+        return;
+    }
+    olevel *C = &s->lv[l + 1];
+    int IIC = C->nx + 2, JJC = C->ny + 2;
+    orc2_restrict(b, C->b, C->P, II, JJ, IIC, JJC, 0);
+    fmg_cycle(s, l + 1, C->x, C->b);
+    memset(x, 0, sizeof(double) * (size_t)II * JJ);
+    memset(L->res, 0, sizeof(double) * (size_t)II * JJ);
+    orc2_interp_add(x, C->x, L->res, L->A, C->P, IIC, JJC, II, JJ, L->nstncl, 0);
+    ncycle(s, l, x, b);
+}
+
+void orc2_solver_set_cycle(orc2_solver *s, int fcycle) { s->fcycle = fcycle; }
+
 void orc2_solver_vcycle(orc2_solver *s, double *x, const double *b)
 {
+    if (s->fcycle && s->nlevels > 1) { fmg_cycle(s, 0, x, b); return; }
     if (s->nlevels == 1) {
         olevel *C = &s->lv[0];
         orc2_solve_cg(x, b, C->nx + 2, C->ny + 2, s->ABD, s->bbd, s->nabd1, s->nabd2, 0);

@@ -72,6 +72,8 @@ void orc2_solver_level_shape(const orc2_solver *s, int lvl, int *nx, int *ny);
 /* which: 0=A 1=P(ci) 2=x 3=res 4=b 5=SOR0 6=SOR1 7=ABD */
 double *orc2_solver_level_ptr(orc2_solver *s, int lvl, int which);
 void orc2_solver_vcycle(orc2_solver *s, double *x, const double *b);
+/* 1: orc2_solver_vcycle / _solve run the F-cycle of include/cedar/cycle/fcycle.h:49-83 instead of the V-cycle */
+void orc2_solver_set_cycle(orc2_solver *s, int fcycle);
 /* returns #iterations done; rel_hist[i] = ||r_i||/||r_0|| after cycle i */
 int orc2_solver_solve(orc2_solver *s, const double *b, double *x, int maxiter, double tol,
                       double *rel_hist, double *res0);

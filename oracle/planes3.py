@@ -57,7 +57,10 @@ def _shift(a, off):
 class _Planes:
     """the plane solvers of one direction on one level"""
 
-    def __init__(self, so, d, plane_kw):
+    def __init__(self, so, d, plane_kw, iters=1):
+        """iters: cycles per plane visit (plane-config "max-iter", default 1; the reference's own plane test uses 50
+        with tol 1e-30, test/3d/test-planes-ser.json)"""
+        self.iters = iters
         nst = so.shape[0]
         n = so.shape[1 + _AXIS[d]] - 2
         slots = _COEFF[d][:5 if nst == 14 else 3]
@@ -82,8 +85,19 @@ class _Planes:
                     xv = _plane_int(_shift(x, off), d, ipl)
                     acc = acc + cp * xv
                 b2[1:-1, 1:-1] = acc
-                self.slv.vcycle(x2, b2)
+                for _ in range(self.iters):
+                    self.slv.vcycle(x2, b2)
                 _plane(x, d, ipl)[...] = x2
+
+
+def plane_rhs(so, x, b, d, ipl):
+    """copy_rhs (src/3d/relax_planes.cc:26-178): right-hand side of plane ipl's 2D problem, interior points"""
+    offs = (_RHS27 if so.shape[0] == 14 else _RHS7)[d]
+    acc = _plane(b, d, ipl)[1:-1, 1:-1].copy()
+    for off in offs:
+        e, s = _CPL[off]
+        acc = acc + _plane_int(_shift(so[e], s), d, ipl) * _plane_int(_shift(x, off), d, ipl)
+    return acc
 
 
 def _plane_int(a_int, d, ipl):

@@ -88,3 +88,44 @@ def test_plane_solver_matches_oracle(cs, case):
     # constant-coefficient galleries, but the Galerkin coarse operators are not plane-invariant near the
     # boundary, so deeper hierarchies (33^3: 5 levels) contract by only ~0.7 per cycle, here and in the oracle
     assert h[-1] < h[0] * (1e-2 if max(nx, ny, nz) <= 20 else 0.5)
+
+
+# ---- the reference's own plane test (test/3d/test_planes.cc:13-265) on the GPU path ---------------------------------
+from tests import planes_ref_cases as ref_planes  # noqa: E402
+
+
+@pytest.mark.parametrize("name,d,n", ref_planes.CASES)
+def test_reference_plane_cases(cs, name, d, n):
+    """SerialPlanes.XY7 ... YZ27: build_kernel_manager, setup<plane_relax<dir>>, run(DOWN) through the registry
+    (cdr3_plane_relax); even planes against the sparse direct solve to the reference's 1e-8, and the whole sweep
+    against the pinned CPU oracle (point-relaxed plane solves are bitwise kernels: 1e-12 relative)"""
+    nx, ny, nz = n
+    so = oracle.gallery3(name, nx, ny, nz)
+    x = ref_planes.index_field(nx, ny, nz)
+    b = x.copy()
+    xg = cs.plane_relax3(cs.Operator3(so), d, x.copy(), b, plane_config=ref_planes.PLANE_CONFIG)
+    assert ref_planes.check_even_planes(name, d, n, so, xg, b) < ref_planes.TOL
+    kw = ref_planes.PLANE_CONFIG["solver"]
+    pl = planes3._Planes(so, d, dict(relaxation="point", nrelax_pre=2, nrelax_post=1), iters=kw["max-iter"])
+    xo = x.copy()
+    pl.relax(so, xo, b, True)
+    assert np.max(np.abs(xg - xo)) <= 1e-12 * np.max(np.abs(xo))
+
+
+@pytest.mark.parametrize("case", [("poisson", 17, 17, 17, "plane-xyz"), ("fe", 20, 13, 17, "plane-xy"), ("fe", 17, 12, 20, "plane-yz")])
+def test_plane_solver_point_planes_tight(cs, case):
+    """with POINT relaxation inside the planes every kernel of the plane cycle is bitwise the oracle's, so the 3D solve
+    agrees to rounding of the norm only: history to 1e-10 (north_star's tolerance), iterate to 1e-12"""
+    name, nx, ny, nz, relax = case
+    so = oracle.gallery3(name, nx, ny, nz)
+    b = oracle.rhs_sin3(nx, ny, nz)
+    pk = dict(relaxation="point", nrelax_pre=2, nrelax_post=1)
+    ref = planes3.Solver3Planes(so, relax, 1, 1, plane_kw=pk)
+    xr, hr, r0r = ref.solve(b, maxiter=5, tol=1e-30)
+    import json
+    cfg = json.loads(cs.make_config(relaxation=relax, nrelax_pre=1, nrelax_post=1, maxiter=5, tol=1e-30))
+    cfg["plane-config"] = {"solver": {"relaxation": "point", "max-iter": 1, "cycle": {"nrelax-pre": 2, "nrelax-post": 1}}}
+    sol = cs.Solver3(cs.Operator3(so), config_json=json.dumps(cfg))
+    x, h, r0 = sol.solve(b)
+    assert len(h) == len(hr) and np.allclose(h, hr, rtol=1e-10, atol=0)
+    assert np.max(np.abs(x - xr)) <= 1e-12 * np.max(np.abs(xr))

@@ -106,6 +106,21 @@ def test_solve_host_end_to_end(cs):
     assert np.linalg.norm(r[1:-1, 1:-1]) <= 1.01e-10 * np.linalg.norm(b[1:-1, 1:-1])
 
 
+@pytest.mark.parametrize("case", [("poisson", 129, 129, 1, 1), ("fe", 100, 77, 2, 1), ("fe", 257, 257, 1, 1)])
+def test_fcycle_matches_oracle(cs, case):
+    """cycle type "f" (include/cedar/cycle/fcycle.h:49-83) against the oracle's F-cycle (oracle/ml2.c fmg_cycle,
+    itself checked against a Python composition of the pinned kernels): iterate bitwise, history to 1e-10"""
+    name, nx, ny, pre, post = case
+    so = oracle.gallery2(name, nx, ny)
+    b = oracle.rhs_sin2(nx, ny)
+    ref = oracle.Solver2(so, "point", pre, post, cycle="f")
+    xr, hr, r0r = ref.solve(b, maxiter=3, tol=1e-30)
+    sol = cs.Solver2(cs.Operator2(so), relaxation="point", cycle="f", nrelax_pre=pre, nrelax_post=post, maxiter=3, tol=1e-30)
+    x, h, r0 = sol.solve(b)
+    assert_bitwise(x, xr, "F-cycle iterate")
+    assert len(h) == len(hr) and np.allclose(h, hr, rtol=1e-10, atol=0) and abs(r0 - r0r) <= 1e-12 * r0r
+
+
 def test_fcycle_runs(cs):
     nx, ny = 129, 129
     so = oracle.gallery2("poisson", nx, ny)

@@ -305,3 +305,46 @@ def test_hetero_generator_c3b():
     b = oracle.rhs_sin2(nx, ny)
     x, h, _ = oracle.Solver2(so, "line-xy", 1, 1).solve(b, maxiter=20, tol=1e-10)
     assert h[-1] < 1e-10 and len(h) <= 16, h
+
+
+def test_fcycle_restatement_against_composition():
+    """oracle F-cycle (oracle/ml2.c fmg_cycle, restating include/cedar/cycle/fcycle.h:49-83) == the same control flow
+    composed in Python from the pinned pieces: restrict the right-hand side down, direct solve, and on every level
+    x = 0, interpolate-and-add with a zero residual, one V-cycle of the sub-hierarchy starting there"""
+    import oracle
+    from oracle import P
+    L = oracle.lib()
+    for name, nx, ny, pre, post in (("fe", 33, 33, 1, 1), ("poisson", 50, 37, 2, 1)):
+        so = oracle.gallery2(name, nx, ny)
+        b = oracle.rhs_sin2(nx, ny)
+        full = oracle.Solver2(so, "point", pre, post)
+        nl = full.nlevels
+
+        def fmg(l, bl):
+            A = np.ascontiguousarray(full.level_array(l, "A"))
+            if l == nl - 1:
+                x = np.zeros_like(bl)
+                oracle.Solver2(A, "point", pre, post, num_levels=1).vcycle(x, bl)
+                return x
+            Pc = np.ascontiguousarray(full.level_array(l + 1, "P"))
+            jjc, iic = Pc.shape[1:]
+            bc = np.zeros((jjc, iic))
+            jj, ii = bl.shape
+            assert L.orc2_restrict(P(bl), P(bc), P(Pc), ii, jj, iic, jjc, 0) == 0
+            xc = fmg(l + 1, bc)
+            x, res = np.zeros_like(bl), np.zeros_like(bl)
+            assert L.orc2_interp_add(P(x), P(xc), P(res), P(A), P(Pc), iic, jjc, ii, jj, A.shape[0], 0) == 0
+            sub = oracle.Solver2(A, "point", pre, post, num_levels=nl - l)
+            assert sub.nlevels == nl - l
+            sub.vcycle(x, bl)
+            return x
+
+        want = fmg(0, b)
+        f = oracle.Solver2(so, "point", pre, post, cycle="f")
+        x = np.zeros_like(b)
+        f.vcycle(x, b)
+        assert np.array_equal(x, want), name
+        # the F-cycle restarts from x = 0: calling it again gives the same bits
+        x2 = x.copy()
+        f.vcycle(x2, b)
+        assert np.array_equal(x2, x)
