@@ -48,3 +48,22 @@ def test_ser_poisson_3d_converges(cuda, tmp_path):
     assert all(b < a for a, b in zip(hist, hist[1:]))
     assert abs(float(norm)) < 1e-3, out                             # second-order error of the 65^3 grid
     assert "Finished test" in out
+
+
+CAPI = os.path.join(ROOT, "examples", "_ref", "capi-fe2d")
+
+
+@pytest.mark.skipif(not os.path.isfile(CAPI), reason="examples/_ref not built")
+@pytest.mark.parametrize("n", [65, 200])
+def test_c_application_against_the_reference_c_interface(cuda, tmp_path, n):
+    """examples/capi/fe2d.c: plain C against include/cedar/capi.h (bmg2_topo_create, bmg2_operator_create/set/apply,
+    bmg2_solver_create/run by the reference's names and argument orders, include/cedar/2d/interface/c/*.h): the
+    vertex-based signed stencil goes through the symmetric-storage conversion, apply equals the stencil, the solve
+    recovers x from b = A x"""
+    (tmp_path / "config.json").write_text('{"log": ["error"], "solver": {"relaxation": "point", "max-iter": 20, "tol": 1e-12, '
+                                          '"cycle": {"nrelax-pre": 2, "nrelax-post": 1}}}')
+    p = subprocess.run([CAPI, str(n)], cwd=tmp_path, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stdout + p.stderr
+    m = re.search(r"apply_err (\S+) solve_err (\S+)", p.stdout)
+    assert m and float(m.group(1)) < 1e-12 and float(m.group(2)) < 1e-9, p.stdout
+    assert (tmp_path / "timer.json").exists()
