@@ -65,6 +65,7 @@ def parse():
     ap.add_argument("--tol", type=float, default=1e-10)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--coarse-tail", type=int, default=None, help="solver.coarse-tail (levels of at most this size run in one kernel)")
     ap.add_argument("--replicas", action="store_true", help="N > 1: independent replicas instead of one decomposed problem")
     ap.add_argument("--agglomerate", type=int, default=513, help="N > 1: levels of this size or smaller are solved replicated")
     ap.add_argument("--halo", type=int, default=15, help="N > 1: lines of the neighbours every array carries (odd)")
@@ -651,7 +652,7 @@ def main():
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     sol = cs.Solver2(op, relaxation=a.relaxation, nrelax_pre=a.pre, nrelax_post=a.post, maxiter=100, tol=a.tol,
-                     cuda_graph=not a.no_graph)
+                     cuda_graph=not a.no_graph, coarse_tail=a.coarse_tail)
     torch.cuda.synchronize()
     setup_first_s = time.perf_counter() - t0
     # ---- device-resident V-cycles: value -----------------------------------

@@ -51,6 +51,7 @@ SIGNATURES = {
     "bmgx2_relax_GS_pass": (_i, [_i, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx2_SETUP_interp_OI_stage": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _i, _i, _i, _i, _p]),
     "bmgx2_line_copy": (_i, [_p, _u, _u, _i, _u, _i, _u, _p, _i, _p]),
+    "bmgx2_vcycle_tail": (_i, [_p, _i, _p, _p, _u, _i, _i, _p]),
     "bmgx_ipc_export": (_i, [_p, _p]),
     "bmgx_ipc_open": (_i, [_p, C.POINTER(_p)]),
     "bmgx_ipc_close": (_i, [_p]),

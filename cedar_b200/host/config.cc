@@ -231,6 +231,7 @@ void ml_settings::init(config &conf)
 	// so the "min-coarse" entry of the shipped JSON files is ignored there: same here
 	this->min_coarse = conf.get<int>("solver.min_coarse", 3);
 	this->cuda_graph = conf.get<bool>("solver.cuda-graph", true);
+	this->coarse_tail = conf.get<int>("solver.coarse-tail", 33);
 
 	auto cg_solver_str = conf.get<std::string>("solver.cg-solver", "LU");
 	if (cg_solver_str == "LU") this->coarse_solver = cg_type::lu;

@@ -204,6 +204,24 @@ int bmgx2_SOLVE_cg(bmgx_real *q, const bmgx_real *qf, bmgx_len ii, bmgx_len jj,
                    const bmgx_real *abd, bmgx_real *bbd, bmgx_len nabd1, bmgx_len nabd2,
                    int jpn, bmgx_stream_t s);
 
+/* ---- the coarse tail of a V-cycle in one launch (cedar_b200/csrc/bmgx2_tail.cu) --------------------------------
+ * Runs vcycle::ncycle (include/cedar/cycle/vcycle.h; reference cycle/vcycle.h:57-115) for `nlevels` successive
+ * nine-point levels, finest first, with point relaxation and the direct solve (bmgx2_SOLVE_cg's ABD, bbd) on the last:
+ * presmooth, residual, restrict, zero coarse x, ..., interpolate-and-add, postsmooth -- one CTA, no launches in
+ * between.  Same arithmetic as the per-level entry points (bitwise).  Entry l: so/sor (5 and 2 planes), q (iterate,
+ * in place; the caller provides q of entry 0, the others are cleared), qf (right-hand side; entries > 0 are
+ * overwritten), res (scratch), ci = interpolation between level l-1 and l (8 planes on level l's grid, unused for
+ * l = 0); ii, jj with ghost layer.  Levels are limited to BMGX_TAIL_MAX_POINTS entries. */
+#define BMGX_TAIL_MAX 8
+#define BMGX_TAIL_MAX_POINTS (160 * 160)
+typedef struct {
+    const bmgx_real *so, *sor, *ci;
+    bmgx_real *q, *qf, *res;
+    bmgx_len ii, jj;
+} bmgx_tail_level;
+int bmgx2_vcycle_tail(const bmgx_tail_level *levels, int nlevels, const bmgx_real *abd, bmgx_real *bbd, bmgx_len nabd1,
+                      int nrelax_pre, int nrelax_post, bmgx_stream_t s);
+
 /* ---- entry points of the block-decomposed (multi-GPU) 2D path ----------------
  * The reference's MPI kernels (src/2d/ftn/mpi/) exchange ghost values between the
  * colour passes of a sweep and between the stages of the interpolation setup; these

@@ -40,11 +40,49 @@ public:
 	{
 		this->kman = build_kernel_manager(*this->conf);
 		parent::setup(fop);
+		setup_tail();
 	}
 	solver(stencil_op<fsten> &fop, std::shared_ptr<config> conf) : parent::multilevel(fop, conf)
 	{
 		this->kman = build_kernel_manager(*this->conf);
 		parent::setup(fop);
+		setup_tail();
+	}
+
+	// B200 extension: hand the small levels' sub-cycle to one kernel (bmgx2_vcycle_tail, include/bmgx.h).  Point
+	// relaxation, non-periodic, V-cycle only; the first tail level is the first coarse level (>= 1, always nine-point)
+	// whose larger dimension is at most settings.coarse_tail, and at least two levels must remain.
+	void setup_tail()
+	{
+		auto &st = this->settings;
+		auto params = this->kman->get_params();
+		const std::size_t nl = this->levels.size();
+		if (st.coarse_tail <= 0 || st.relaxation != ml_settings::relax_type::point || st.cycle != ml_settings::cycle_type::v) return;
+		if (params->periodic[0] || params->periodic[1] || nl < 3) return;
+		std::size_t first = 0;
+		for (std::size_t l = 1; l + 1 < nl; l++) {
+			auto &A = this->levels.get(l).A;
+			if (std::max(A.shape(0), A.shape(1)) <= static_cast<len_t>(st.coarse_tail)
+			    && static_cast<std::size_t>(A.len(0)) * A.len(1) <= BMGX_TAIL_MAX_POINTS) { first = l; break; }
+		}
+		if (first == 0 || nl - first > BMGX_TAIL_MAX) return;
+		this->cycle->set_tail(first, [this, first, nl](grid_func &x, const grid_func &b) {
+			bmgx_tail_level lv[BMGX_TAIL_MAX];
+			for (std::size_t l = first; l < nl; l++) {
+				auto &L = this->levels.get(l);
+				bmgx_tail_level &d = lv[l - first];
+				d.so = L.A.cdev();
+				d.sor = l + 1 < nl ? L.SOR[0].cdev() : nullptr;
+				d.ci = L.P.cdev();
+				// the entry level works on the caller's x and b (the arrays the cycle above restricts into)
+				d.q = l == first ? x.dev() : L.x.dev();
+				d.qf = l == first ? const_cast<real_t *>(b.cdev()) : L.b.dev();
+				d.res = L.res.dev();
+				d.ii = L.A.len(0); d.jj = L.A.len(1);
+			}
+			gpu::check(bmgx2_vcycle_tail(lv, static_cast<int>(nl - first), this->ABD.cdev(), tail_bbd(), this->ABD.len(0),
+			                             this->settings.nrelax_pre, this->settings.nrelax_post, gpu::stream()), "vcycle_tail");
+		});
 	}
 	~solver() { delete[] this->bbd; }
 
@@ -89,6 +127,12 @@ public:
 
 	void give_op(std::unique_ptr<stencil_op<fsten>> fop) { fop_ref = std::move(fop); }
 protected:
+	real_t *tail_bbd()
+	{
+		if (tail_scratch.size() < static_cast<std::size_t>(this->ABD.len(1))) tail_scratch.reshape(this->ABD.len(1));
+		return tail_scratch.dev();
+	}
+	array<real_t, 1> tail_scratch;
 	std::unique_ptr<stencil_op<fsten>> fop_ref;
 };
 

@@ -23,6 +23,9 @@ public:
 	    : levels(levels), coarse_solver(coarse_solver) {}
 	virtual ~cycle() {}
 	void set_kernels(std::shared_ptr<manager> kregis) { this->kman = kregis; }
+	// B200 extension: the levels from `lvl` down (lvl >= 1) may be handed to one kernel that runs their whole sub-cycle
+	// (cdr2: bmgx2_vcycle_tail); x arrives zeroed, like the coarse iterate of ncycle_helper
+	void set_tail(std::size_t lvl, std::function<void(grid_func &x, const grid_func &b)> f) { tail_level = lvl; tail_solver = std::move(f); }
 	virtual void run(grid_func &x, const grid_func &b) = 0;
 	void log_residual(std::size_t lvl, const grid_func &res)
 	{
@@ -34,6 +37,8 @@ protected:
 	std::shared_ptr<manager> kman;
 	level_container &levels;
 	std::function<void(grid_func &x, const grid_func &b)> &coarse_solver;
+	std::size_t tail_level = 0;   // 0 = none
+	std::function<void(grid_func &x, const grid_func &b)> tail_solver;
 };
 
 }}

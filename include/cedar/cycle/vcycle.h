@@ -33,6 +33,8 @@ public:
 	using parent::coarse_solver;
 	using parent::log_residual;
 	using parent::kman;
+	using parent::tail_level;
+	using parent::tail_solver;
 
 	vcycle(level_container &levels, std::function<void(grid_func &, const grid_func &)> &coarse_solver,
 	       bool use_graph = true)
@@ -114,6 +116,8 @@ public:
 				kman->template run<residual>(coarse_A, coarse_x, coarse_b, coarse_residual);
 				log_residual(lvl + 1, coarse_residual);
 			}
+		} else if (tail_solver && lvl + 1 == tail_level && n == 1 && !log::info.active()) {
+			tail_solver(coarse_x, coarse_b);   // the remaining levels' sub-cycle in one launch
 		} else {
 			for (int i = 0; i < n; i++) ncycle(lvl + 1, coarse_x, coarse_b, n);
 		}

@@ -32,6 +32,10 @@ struct ml_settings
 	// B200 extension (key "solver.cuda-graph", default true): replay each
 	// V-cycle as one CUDA graph instead of ~10 launches per level
 	bool cuda_graph = true;
+	// B200 extension (key "solver.coarse-tail", default 33; 0 = off): with point relaxation, the levels whose larger
+	// dimension is at most this many unknowns run their whole sub-cycle in ONE kernel (bmgx2_vcycle_tail) instead of
+	// ~6 launches per level; same arithmetic, bit for bit
+	int coarse_tail = 33;
 };
 
 }

@@ -217,3 +217,26 @@ def test_indefinite_coarse_operator_is_reported(cs):
     # and a good operator still sets up after the failures (the status word is reset by the next factorisation)
     sol = cs.Solver2(cs.Operator2(oracle.gallery2("fe", nx, ny)), relaxation="point", nrelax_pre=1, nrelax_post=1, num_levels=1)
     assert sol.nlevels == 1
+
+
+@pytest.mark.parametrize("case", [("fe", 257, 257, 1, 1), ("poisson", 400, 300, 2, 1), ("fe", 1025, 513, 1, 2), ("fe", 130, 67, 0, 1)])
+def test_coarse_tail_kernel_is_bitwise_and_saves_launches(cs, case):
+    """solver.coarse-tail (default 33): the levels up to that size run their whole sub-cycle in ONE kernel
+    (bmgx2_vcycle_tail).  Same bits as the level-by-level cycle (coarse-tail 0) and as the oracle; fewer launches."""
+    name, nx, ny, pre, post = case
+    so = oracle.gallery2(name, nx, ny)
+    rng = np.random.default_rng(7)
+    so[0, 1:-1, 1:-1] += rng.uniform(0, 0.3, size=(ny, nx))
+    b = random_gf(nx, ny, rng)
+    ref = oracle.Solver2(so, "point", pre, post)
+    xr, hr, _ = ref.solve(b, maxiter=4, tol=1e-30)
+    out = {}
+    for tail in (0, 33, 129):
+        sol = cs.Solver2(cs.Operator2(so), relaxation="point", nrelax_pre=pre, nrelax_post=post, maxiter=4, tol=1e-30,
+                         coarse_tail=tail, cuda_graph=False)
+        l0 = cs.gpu_launches()
+        x, h, _ = sol.solve(b)
+        out[tail] = (x, h, cs.gpu_launches() - l0)
+        assert_bitwise(x, xr, f"coarse-tail {tail} vs oracle")
+        assert np.allclose(h, hr, rtol=1e-10, atol=0)
+    assert out[33][2] < out[0][2] and out[129][2] <= out[33][2], {k: v[2] for k, v in out.items()}
