@@ -69,6 +69,7 @@ def parse():
     ap.add_argument("--replicas", action="store_true", help="N > 1: independent replicas instead of one decomposed problem")
     ap.add_argument("--agglomerate", type=int, default=513, help="N > 1: levels of this size or smaller are solved replicated")
     ap.add_argument("--halo", type=int, default=15, help="N > 1: lines of the neighbours every array carries (odd)")
+    ap.add_argument("--split-min", type=int, default=512, help="N > 1: split sweeps (exchange beside the interior) where blocks are at least this wide; 0 = never")
     ap.add_argument("--global-n", type=int, default=0, help="N > 1: strong scaling on a global-n^2 grid instead of (n-1)^2 per GPU")
     ap.add_argument("--no-c5", action="store_true", help="N > 1: skip the extra 16385^2 heterogeneous (configs[4]) measurement")
     ap.add_argument("--c5-n", type=int, default=16385)
@@ -243,7 +244,7 @@ def _dist_problem(a, d2, cs, comm, rank, gnx, gny, px, py, gallery, pre, post, a
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     sol = d2.DistSolver2(gnx, gny, (px, py), nst=5, nrelax_pre=pre, nrelax_post=post, agglomerate=agglomerate, halo=halo,
-                         cuda_graph=graph, comm=comm)
+                         cuda_graph=graph, comm=comm, split_min=a.split_min)
     ext = sol.extent(0, rank)
     t1 = time.perf_counter()
     so = gen((gnx, gny), ext)
@@ -393,6 +394,8 @@ def run_multi(a, torch, dist, world, rank, local):
             "scaling": "strong" if a.global_n else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": cfg,
             "decomposition": {"blocks": f"{px}x{py}", "halo_lines": a.halo, "distributed_levels": info["ndist"],
+                              "overlap": (f"on levels with blocks >= {a.split_min} wide the ghost exchange runs on a second stream "
+                                          "beside the interior of the sweep that needs it; the frames follow") if a.split_min else "off",
                               "levels": info["nlevels"], "replicated_below": a.agglomerate,
                               "exchange": "one kernel per exchange: signal, wait, pull out of the neighbours' device memory "
                                           "(CUDA IPC over NVLink); no NCCL on the data path"},

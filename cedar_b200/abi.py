@@ -35,6 +35,7 @@ SIGNATURES = {
     "bmgx2_SETUP_recip": (_i, [_p, _p, _u, _u, _i, _i, _p]),
     "bmgx2_relax_GS": (_i, [_i, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx2_relax_GS_oop": (_i, [_i, _p, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "bmgx2_relax_GS_oop_rects": (_i, [_i, _p, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _p, _i, _p]),
     "bmgx2_SETUP_lines_x": (_i, [_p, _p, _u, _u, _i, _i, _p]),
     "bmgx2_SETUP_lines_y": (_i, [_p, _p, _u, _u, _i, _i, _p]),
     "bmgx2_relax_lines_x": (_i, [_i, _p, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
@@ -92,6 +93,11 @@ class Seg(C.Structure):
     """bmgx_seg of include/bmgx.h"""
     _fields_ = [("src", _p), ("dst", _p), ("rows", C.c_uint32), ("cols", C.c_uint32), ("src_pitch", C.c_uint64),
                 ("dst_pitch", C.c_uint64), ("src_rank", C.c_int32), ("reserved", C.c_int32)]
+
+
+class Rect(C.Structure):
+    """bmgx_rect of include/bmgx.h"""
+    _fields_ = [(n, C.c_uint32) for n in ("i0", "j0", "ni", "nj", "wi0", "wi1", "wj0", "wj1")]
 
 
 class BmgxError(RuntimeError):

@@ -19,7 +19,9 @@ _ip = C.POINTER(C.c_int)
 HANDLE_BYTES = 64
 
 lib.cdr2_dist_create.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, _ip, C.c_int, C.c_int, C.c_int,
-                                 C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+                                 C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+lib.cdr2_dist_sweep_rects.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+                                      _ip, C.c_int, _ip]
 lib.cdr2_dist_destroy.argtypes = [C.c_void_p]
 lib.cdr2_dist_destroy.restype = None
 lib.cdr2_dist_info.argtypes = [C.c_void_p, _ip, _ip, _ip, _ip, _ip]
@@ -37,7 +39,7 @@ lib.cdr2_dist_solve.argtypes = [C.c_void_p, C.c_int, C.c_double, _dp, C.c_int, _
 lib.cdr2_dist_time_vcycles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float)]
 lib.cdr2_dist_vcycle_stream.argtypes = [C.c_void_p, C.c_int, C.POINTER(_dp), C.POINTER(_dp)]
 lib.cdr2_dist_profile_ops.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int, _ip]
-lib.cdr2_dist_plan_json.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
+lib.cdr2_dist_plan_json.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                     C.c_char_p, C.c_char_p, C.c_size_t, _ip]
 lib.cdr2_dist_geometry.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _ip]
 
@@ -50,12 +52,24 @@ def _P(a):
 
 
 # ------------------------------------------------------------------ host-only views of the schedule
-def plan(nx, ny, px, py, nst=5, pre=1, post=1, agglomerate=513, halo=15, what="cycle"):
+SPLIT_MIN = 512      # default: sweeps are split (exchange beside the interior) where blocks are at least this wide
+
+
+def plan(nx, ny, px, py, nst=5, pre=1, post=1, agglomerate=513, halo=15, what="cycle", split_min=SPLIT_MIN):
     """(operation list, number of distributed levels): include/cedar/2d/mpi/plan.h; needs no device"""
     buf = C.create_string_buffer(1 << 20)
     nd = C.c_int()
-    _check(lib.cdr2_dist_plan_json(nx, ny, px, py, nst, pre, post, agglomerate, halo, what.encode(), buf, len(buf), C.byref(nd)))
+    _check(lib.cdr2_dist_plan_json(nx, ny, px, py, nst, pre, post, agglomerate, halo, split_min, what.encode(), buf, len(buf),
+                                   C.byref(nd)))
     return json.loads(buf.value.decode()), nd.value
+
+
+def sweep_rects(nx, ny, px, py, ndist, halo, lvl, block, ncolours, part):
+    """rectangles (i0, j0, ni, nj, wi0, wi1, wj0, wj1) of a split sweep: part 1 = interior, 2 = frames"""
+    out = (C.c_int * 40)()
+    n = C.c_int()
+    _check(lib.cdr2_dist_sweep_rects(nx, ny, px, py, ndist, halo, lvl, block, ncolours, part, out, 5, C.byref(n)))
+    return [tuple(out[8 * k:8 * k + 8]) for k in range(n.value)]
 
 
 def geometry(nx, ny, px, py, ndist, halo, lvl, block):
@@ -107,7 +121,7 @@ class DistSolver2:
     comm is None: every block on this process's GPU)."""
 
     def __init__(self, nx, ny, decomp_shape, nst=5, blocks=None, nrelax_pre=1, nrelax_post=1, agglomerate=513, halo=15,
-                 cuda_graph=True, comm=None):
+                 cuda_graph=True, comm=None, split_min=SPLIT_MIN):
         px, py = decomp_shape
         self.nx, self.ny, self.px, self.py, self.nst, self.comm = nx, ny, px, py, nst, comm
         self.pre, self.post, self.agglomerate = nrelax_pre, nrelax_post, agglomerate
@@ -117,8 +131,9 @@ class DistSolver2:
         self.owned = list(blocks)
         ids = (C.c_int * len(self.owned))(*self.owned)
         self.h = C.c_void_p()
+        self.split_min = split_min
         _check(lib.cdr2_dist_create(nx, ny, px, py, nst, len(self.owned), ids, nrelax_pre, nrelax_post, agglomerate, halo,
-                                    int(cuda_graph), C.byref(self.h)))
+                                    split_min, int(cuda_graph), C.byref(self.h)))
         v = [C.c_int() for _ in range(5)]
         _check(lib.cdr2_dist_info(self.h, *[C.byref(t) for t in v]))
         self.ndist, self.nlevels, self.halo, self.exchanges_per_cycle, self.ops_per_cycle = [t.value for t in v]
@@ -193,7 +208,8 @@ class DistSolver2:
 
     def profile_ops(self, n=5):
         """[(operation dict, ms)] for one cycle: eager, host-synchronised per operation (diagnostic)"""
-        ops, _ = plan(self.nx, self.ny, self.px, self.py, self.nst, self.pre, self.post, self.agglomerate, self.halo, "cycle")
+        ops, _ = plan(self.nx, self.ny, self.px, self.py, self.nst, self.pre, self.post, self.agglomerate, self.halo, "cycle",
+                      self.split_min)
         out = (C.c_float * len(ops))()
         m = C.c_int()
         _check(lib.cdr2_dist_profile_ops(self.h, n, out, len(ops), C.byref(m)))

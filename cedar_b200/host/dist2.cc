@@ -63,7 +63,9 @@ struct cdr2_dist
 	std::vector<char *> base;                    // arena of every block as mapped in this process
 	std::vector<bool> opened;                    // base[i] came from bmgx_ipc_open
 	void **peer_sync_dev = nullptr;
-	bmgx_stream_t stream = nullptr;
+	bmgx_stream_t stream = nullptr, side = nullptr;   // side: exchanges that run beside the interior sweeps
+	std::vector<void *> fork_ev, join_ev;             // one pair per asynchronous exchange of the cycle
+	bool overlap = true;
 	std::vector<plan_op> p_setup, p_cycle, p_norm;
 	void *graph = nullptr;
 	unsigned long long graph_nodes = 0;
@@ -213,17 +215,17 @@ seg_table &table(cdr2_dist &d, dist_block &K, const plan_op &o)
 	return K.segs.emplace(k, t).first->second;
 }
 
-void step(cdr2_dist &d, const plan_op &o)
+void step(cdr2_dist &d, const plan_op &o, bmgx_stream_t st)
 {
 	const int world = d.nblocks();
 	const bool local = d.blk.size() > 1;
 	if (local)
 		for (auto &K : d.blk)
-			check(bmgx_halo_step(nullptr, 0, 1, d.peer_sync_dev, K.arena, K.id, world, 1, 0, d.timeout_s, d.stream), "halo signal");
+			check(bmgx_halo_step(nullptr, 0, 1, d.peer_sync_dev, K.arena, K.id, world, 1, 0, d.timeout_s, st), "halo signal");
 	for (auto &K : d.blk) {
 		seg_table &t = table(d, K, o);
 		check(bmgx_halo_step(t.dev, t.n, t.chunks, d.peer_sync_dev, K.arena, K.id, world, local ? 2 : 3, o.wait_all ? 1 : 0,
-		                     d.timeout_s, d.stream), "halo step");
+		                     d.timeout_s, st), "halo step");
 	}
 }
 
@@ -234,8 +236,21 @@ void run_op(cdr2_dist &d, const plan_op &o)
 	const int l = o.lvl, nd = dec.ndist;
 	bmgx_stream_t s = d.stream;
 	switch (o.kind) {
+	case op_kind::join:
+		// the exchange started by the matching asynchronous operation has delivered the halos
+		if (d.overlap) check(bmgx_stream_wait_event(s, d.join_ev[o.id]), "join");
+		return;
 	case op_kind::exchange: case op_kind::sync: case op_kind::gather: case op_kind::gather_op: case op_kind::norm:
-		step(d, o);
+		if (o.async && d.overlap) {
+			// fork: the exchange kernel goes to the side stream behind everything enqueued so far; the operations up to
+			// the join (the interior of the next sweep) run beside it
+			check(bmgx_event_record(d.fork_ev[o.id], s), "fork");
+			check(bmgx_stream_wait_event(d.side, d.fork_ev[o.id]), "fork");
+			step(d, o, d.side);
+			check(bmgx_event_record(d.join_ev[o.id], d.side), "fork");
+			return;
+		}
+		step(d, o, s);
 		if (o.kind == op_kind::norm)
 			for (auto &K : d.blk) check(bmgx_sum_ordered(K.red_all, d.nblocks(), K.norm_out, s), "norm fold");
 		return;
@@ -254,8 +269,21 @@ void run_op(cdr2_dist &d, const plan_op &o)
 		}
 		switch (o.kind) {
 		case op_kind::sweep:
-			check(bmgx2_relax_GS_oop(1, d.ptr(b, l, A), d.ptr(b, l, B), d.ptr(b, l, o.a), d.ptr(b, l, o.b), d.ptr(b, l, SOR),
-			                         g.ii, g.jj, 1, ifd, nst, 2, BMGX_RELAX_SYM, o.dir ? BMGX_UP : BMGX_DOWN, 0, s), "relax_GS_oop");
+			if (o.part == 0) {
+				check(bmgx2_relax_GS_oop(1, d.ptr(b, l, A), d.ptr(b, l, B), d.ptr(b, l, o.a), d.ptr(b, l, o.b), d.ptr(b, l, SOR),
+				                         g.ii, g.jj, 1, ifd, nst, 2, BMGX_RELAX_SYM, o.dir ? BMGX_UP : BMGX_DOWN, 0, s), "relax_GS_oop");
+			} else {
+				// a split sweep: interior (own points only, beside the exchange) or the frames around it
+				const std::vector<sweep_rect> rs = sweep_rects(g, ifd ? 2 : 4, o.part);
+				bmgx_rect br[5];
+				for (std::size_t k = 0; k < rs.size(); k++)
+					br[k] = bmgx_rect{(bmgx_len)rs[k].i0, (bmgx_len)rs[k].j0, (bmgx_len)rs[k].ni, (bmgx_len)rs[k].nj,
+					                  (bmgx_len)rs[k].wi0, (bmgx_len)rs[k].wi1, (bmgx_len)rs[k].wj0, (bmgx_len)rs[k].wj1};
+				if (!rs.empty())
+					check(bmgx2_relax_GS_oop_rects(1, d.ptr(b, l, A), d.ptr(b, l, B), d.ptr(b, l, o.a), d.ptr(b, l, o.b),
+					                               d.ptr(b, l, SOR), g.ii, g.jj, 1, ifd, nst, 2, BMGX_RELAX_SYM,
+					                               o.dir ? BMGX_UP : BMGX_DOWN, 0, br, (int)rs.size(), s), "relax_GS_oop_rects");
+			}
 			break;
 		case op_kind::residual:
 			check(bmgx2_residual(0, d.ptr(b, l, A), d.ptr(b, l, B), d.ptr(b, l, o.a), d.ptr(b, l, RES), g.ii, g.jj, 0, ifd, nst,
@@ -385,7 +413,7 @@ dist_block &find(cdr2_dist &d, int b)
 extern "C" {
 
 int cdr2_dist_create(unsigned gnx, unsigned gny, int px, int py, int nstencil, int nowned, const int *owned, int nrelax_pre,
-                     int nrelax_post, int agglomerate, int halo_width, int use_graph, cdr2_dist **out)
+                     int nrelax_post, int agglomerate, int halo_width, int split_min, int use_graph, cdr2_dist **out)
 {
 	return guard([&] {
 		if (nstencil != 3 && nstencil != 5) throw std::runtime_error("nstencil must be 3 or 5");
@@ -401,12 +429,21 @@ int cdr2_dist_create(unsigned gnx, unsigned gny, int px, int py, int nstencil, i
 			try { d->dec = std::make_unique<decomp>(gnx, gny, px, py, ndist, halo_width); break; }
 			catch (std::invalid_argument &) { if (ndist <= 1) throw; }
 		}
-		d->plan = std::make_unique<planner>(d->dec->ndist, halo_width, nstencil == 3 ? 2 : 4, nrelax_pre, nrelax_post);
+		d->plan = std::make_unique<planner>(d->dec->ndist, halo_width, nstencil == 3 ? 2 : 4, nrelax_pre, nrelax_post,
+		                                    d->dec->split_levels(split_min));
 		d->p_setup = d->plan->setup(); d->p_cycle = d->plan->cycle(); d->p_norm = d->plan->norm();
+		if (const char *e = getenv("CDR_DIST_OVERLAP")) d->overlap = atoi(e) != 0;
+		for (auto &o : d->p_cycle)
+			if (o.kind == op_kind::join) {
+				void *e0 = nullptr, *e1 = nullptr;
+				check(bmgx_event_create(&e0), "event"); check(bmgx_event_create(&e1), "event");
+				d->fork_ev.push_back(e0); d->join_ev.push_back(e1);
+			}
 		const int nb = d->dec->nblocks();
 		d->sync_words = nb + 3;
 		d->base.assign(nb, nullptr); d->opened.assign(nb, false);
 		check(bmgx_stream_create(&d->stream), "stream");
+		check(bmgx_stream_create(&d->side), "stream");
 		for (int i = 0; i < nowned; i++) {
 			dist_block K;
 			K.id = owned[i];
@@ -454,6 +491,9 @@ void cdr2_dist_destroy(cdr2_dist *d)
 	if (d->s_up) bmgx_stream_destroy(d->s_up);
 	if (d->s_down) bmgx_stream_destroy(d->s_down);
 	if (d->peer_sync_dev) bmgx_free(d->peer_sync_dev);
+	for (auto e : d->fork_ev) bmgx_event_destroy(e);
+	for (auto e : d->join_ev) bmgx_event_destroy(e);
+	if (d->side) bmgx_stream_destroy(d->side);
 	if (d->stream) bmgx_stream_destroy(d->stream);
 	delete d;
 }
@@ -685,6 +725,8 @@ int cdr2_dist_profile_ops(cdr2_dist *d, int n, float *out, int cap, int *nops)
 		void *e0, *e1;
 		check(bmgx_event_create(&e0), "event"); check(bmgx_event_create(&e1), "event");
 		for (int k = 0; k < m; k++) out[k] = 0;
+		const bool was = d->overlap;
+		d->overlap = false;      // one operation at a time
 		for (int it = 0; it < n + 1; it++) {
 			for (auto &K : d->blk) check(bmgx_memset0(d->ptr(K.id, 0, X0), (size_t)K.g[0].ii * K.g[0].jj * 8, d->stream), "x0");
 			for (int k = 0; k < m; k++) {
@@ -699,13 +741,14 @@ int cdr2_dist_profile_ops(cdr2_dist *d, int n, float *out, int cap, int *nops)
 			}
 		}
 		bmgx_event_destroy(e0); bmgx_event_destroy(e1);
+		d->overlap = was;
 		check_device_error(*d);
 	});
 }
 
 /* the operation lists as JSON (host only, no device needed): what = "setup", "cycle" or "norm" */
 int cdr2_dist_plan_json(unsigned gnx, unsigned gny, int px, int py, int nstencil, int nrelax_pre, int nrelax_post,
-                        int agglomerate, int halo_width, const char *what, char *out, size_t cap, int *ndist_out)
+                        int agglomerate, int halo_width, int split_min, const char *what, char *out, size_t cap, int *ndist_out)
 {
 	return guard([&] {
 		const int nl = compute_num_levels(gnx, gny);
@@ -717,7 +760,7 @@ int cdr2_dist_plan_json(unsigned gnx, unsigned gny, int px, int py, int nstencil
 			try { dec = std::make_unique<decomp>(gnx, gny, px, py, ndist, halo_width); break; }
 			catch (std::invalid_argument &) { if (ndist <= 1) throw; }
 		}
-		planner pl(dec->ndist, halo_width, nstencil == 3 ? 2 : 4, nrelax_pre, nrelax_post);
+		planner pl(dec->ndist, halo_width, nstencil == 3 ? 2 : 4, nrelax_pre, nrelax_post, dec->split_levels(split_min));
 		const std::string w(what);
 		const std::string js = planner::to_json(w == "setup" ? pl.setup() : w == "norm" ? pl.norm() : pl.cycle());
 		if (js.size() + 1 > cap) throw std::runtime_error("plan buffer too small");
@@ -738,4 +781,19 @@ int cdr2_dist_geometry(unsigned gnx, unsigned gny, int px, int py, int ndist, in
 	});
 }
 
+}
+
+extern "C" int cdr2_dist_sweep_rects(unsigned gnx, unsigned gny, int px, int py, int ndist, int halo_width, int lvl, int block,
+                                     int ncolours, int part, int *out8, int cap, int *nrects)
+{
+	return guard([&] {
+		decomp dec(gnx, gny, px, py, ndist, halo_width);
+		const std::vector<sweep_rect> rs = sweep_rects(dec.geom(lvl, block), ncolours, part);
+		if ((int)rs.size() > cap) throw std::runtime_error("rectangle buffer too small");
+		for (std::size_t k = 0; k < rs.size(); k++) {
+			const int v[8] = {rs[k].i0, rs[k].j0, rs[k].ni, rs[k].nj, rs[k].wi0, rs[k].wi1, rs[k].wj0, rs[k].wj1};
+			std::memcpy(out8 + 8 * k, v, sizeof(v));
+		}
+		*nrects = (int)rs.size();
+	});
 }

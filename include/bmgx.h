@@ -132,6 +132,21 @@ int bmgx2_relax_GS_oop(int k, const bmgx_real *so, const bmgx_real *qf, const bm
                        int kf, int ifd, int nstncl, int nsorv, int irelax_sym, int updown,
                        int jpn, bmgx_stream_t s);
 
+/* The same out-of-place sweep restricted to rectangles of the array (at most 5 per launch): each rectangle is a
+ * sub-array [i0, i0+ni) x [j0, j0+nj) (0-based, i0 and j0 even so that the colouring by index parity is kept) that is
+ * swept as if it were a grid of its own -- its outer lines play the ghost ring and come from q_in -- and only the
+ * values inside the window [wi0, wi1] x [wj0, wj1] (1-based, inclusive, sub-array coordinates) are stored to q_out.
+ * A window whose points lie at least ncolours lines inside the sub-array (or on a side where the sub-array ends
+ * with the array) receives exactly the values of the whole-array sweep: this is how the block-decomposed path
+ * relaxes the interior of a block while its halos are still travelling, and the frames afterwards. */
+typedef struct {
+    bmgx_len i0, j0, ni, nj;
+    bmgx_len wi0, wi1, wj0, wj1;
+} bmgx_rect;
+int bmgx2_relax_GS_oop_rects(int k, const bmgx_real *so, const bmgx_real *qf, const bmgx_real *q_in, bmgx_real *q_out,
+                             const bmgx_real *sor, bmgx_len ii, bmgx_len jj, int kf, int ifd, int nstncl, int nsorv,
+                             int irelax_sym, int updown, int jpn, const bmgx_rect *rects, int nrects, bmgx_stream_t s);
+
 /* BMG2_SymStd_SETUP_lines_x / _y (so, sor, nx, ny, nstncl, jpn)
  * include/cedar/2d/relax.h:16-19; LAPACK DPTTRF is replaced on device. */
 int bmgx2_SETUP_lines_x(const bmgx_real *so, bmgx_real *sor, bmgx_len nx, bmgx_len ny,

@@ -111,6 +111,20 @@ struct decomp
 		g.ii = g.nx + g.wl + g.wr; g.jj = g.ny + g.wb + g.wt;
 		return g;
 	}
+	// leading levels on which every block has at least `split_min` own points per dimension (sweeps are split there)
+	int split_levels(int split_min) const
+	{
+		if (split_min <= 0 || px * py == 1) return 0;
+		int n = 0;
+		for (int l = 0; l < ndist; l++) {
+			for (int b = 0; b < px * py; b++) {
+				const block_geom g = geom(l, b);
+				if (std::min(g.nx, g.ny) < std::max(split_min, 4 * W)) return n;
+			}
+			n = l + 1;
+		}
+		return n;
+	}
 	// window of the level lvl+1 array that the serial transfer kernels see as "the coarse grid" of the whole
 	// level-lvl array: first entry (0-based) and extents
 	void coarse_window(int lvl, int b, int &ox, int &oy, int &iic, int &jjc) const
@@ -121,8 +135,49 @@ struct decomp
 	}
 };
 
+// Rectangles of a split sweep (bmgx2_relax_GS_oop_rects): sub-array [i0, i0+ni) x [j0, j0+nj) of the block's array
+// (0-based, even origin) and the window of it that is stored (1-based, inclusive, sub-array coordinates).
+struct sweep_rect { int i0, j0, ni, nj, wi0, wi1, wj0, wj1; };
+
+// part 1 = interior: reads only OWN points of the iterate and the right-hand side (its sub-array starts one line
+// inside the own region towards every neighbour), so it can run while the halos are being pulled; stores the points at
+// least nc lines inside that sub-array.  part 2 = frames: everything else (the halo lines and the own points next to
+// them), one rectangle per neighbour side, each with nc + 1 recomputed lines towards the interior.  Together the
+// stored windows tile the whole array and every stored value equals the whole-array sweep's: a point's value depends
+// on values at most nc lines away (nc colours), and each window keeps that distance from every sub-array edge that is
+// not an edge of the array itself.
+inline std::vector<sweep_rect> sweep_rects(const block_geom &g, int nc, int part)
+{
+	const bool L = g.wl > 1, R = g.wr > 1, B = g.wb > 1, T = g.wt > 1;
+	// interior sub-array (array coordinates, inclusive) and its stored window
+	const int s0 = L ? g.wl + 1 : 0, e0 = R ? g.wl + g.nx - 1 : g.ii - 1;
+	const int t0 = B ? g.wb + 1 : 0, f0 = T ? g.wb + g.ny - 1 : g.jj - 1;
+	const int cl = L ? s0 + nc : 0, cr = R ? e0 - nc : g.ii - 1;
+	const int rb = B ? t0 + nc : 0, rt = T ? f0 - nc : g.jj - 1;
+	if (cl > cr || rb > rt) throw std::invalid_argument("block too small to split a sweep");
+	auto rect = [](int a0, int a1, int b0, int b1, int wa0, int wa1, int wb0, int wb1) {
+		// sub-array cols [a0, a1], rows [b0, b1]; stored cols [wa0, wa1], rows [wb0, wb1] (array coordinates, inclusive)
+		sweep_rect r;
+		r.i0 = a0; r.j0 = b0; r.ni = a1 - a0 + 1; r.nj = b1 - b0 + 1;
+		r.wi0 = wa0 - a0 + 1; r.wi1 = wa1 - a0 + 1; r.wj0 = wb0 - b0 + 1; r.wj1 = wb1 - b0 + 1;
+		return r;
+	};
+	auto even_down = [](int v) { return v < 0 ? 0 : v - (v & 1); };
+	std::vector<sweep_rect> out;
+	if (part == 1) {
+		out.push_back(rect(s0, e0, t0, f0, cl, cr, rb, rt));
+		return out;
+	}
+	if (L) out.push_back(rect(0, std::min(g.ii - 1, cl + nc), 0, g.jj - 1, 0, cl - 1, 0, g.jj - 1));
+	if (R) out.push_back(rect(even_down(cr - nc), g.ii - 1, 0, g.jj - 1, cr + 1, g.ii - 1, 0, g.jj - 1));
+	const int a0 = even_down(cl - (nc + 1)), a1 = std::min(g.ii - 1, cr + nc + 1);
+	if (B) out.push_back(rect(a0, a1, 0, std::min(g.jj - 1, rb + nc), cl, cr, 0, rb - 1));
+	if (T) out.push_back(rect(a0, a1, even_down(rt - nc), g.jj - 1, cl, cr, rt + 1, g.jj - 1));
+	return out;
+}
+
 enum class op_kind { exchange, sync, sweep, residual, restrict_, zero, gather, coarse, scatter, interp, copy, sumsq, norm,
-                     recip, setup_interp, galerkin, gather_op, setup_coarse };
+                     recip, setup_interp, galerkin, gather_op, setup_coarse, join };
 
 struct plan_op
 {
@@ -132,13 +187,16 @@ struct plan_op
 	int dir = 0;                // sweep direction (0 = down, 1 = up)
 	std::vector<int> arrays;    // exchange: the slots that travel
 	bool wait_all = false;
+	bool async = false;         // exchange: runs beside the following operations until the matching `join`
+	int part = 0;               // sweep: 0 = whole array, 1 = interior, 2 = frames (sweep_rects)
+	int id = 0;                 // async exchange / join: running number of the pair within the list
 };
 
 inline const char *op_name(op_kind k)
 {
 	static const char *n[] = {"exchange", "sync", "sweep", "residual", "restrict", "zero", "gather", "coarse", "scatter",
 	                          "interp", "copy", "sumsq", "norm", "recip", "setup_interp", "galerkin", "gather_op",
-	                          "setup_coarse"};
+	                          "setup_coarse", "join"};
 	return n[(int)k];
 }
 
@@ -147,7 +205,10 @@ inline const char *op_name(op_kind k)
 class planner
 {
 public:
-	planner(int ndist, int W, int ncol0, int npre, int npost) : ndist(ndist), W(W), ncol0(ncol0), npre(npre), npost(npost)
+	// split_levels: on levels 0 .. split_levels-1 a sweep that directly follows the exchange of its operands is split:
+	// the exchange starts, the interior is relaxed meanwhile, the frames after the halos have arrived
+	planner(int ndist, int W, int ncol0, int npre, int npost, int split_levels = 0)
+	    : ndist(ndist), W(W), ncol0(ncol0), npre(npre), npost(npost), split_levels(split_levels)
 	{
 		if (npre + npost < 1) throw std::invalid_argument("a cycle needs at least one sweep");
 		// a whole 4-colour sweep over the extended array must leave the own points exact: colour c is exact out to line
@@ -181,6 +242,7 @@ public:
 		exchange(0, {X0, B}, true);
 		ncycle(0);
 		if (cur[0] != X0) { before_write(0, X0); push(op_kind::copy, 0, cur[0], X0); }
+		overlap();
 		return take();
 	}
 
@@ -212,7 +274,8 @@ public:
 		for (std::size_t i = 0; i < p.size(); i++) {
 			const plan_op &o = p[i];
 			s << (i ? "," : "") << "{\"op\":\"" << op_name(o.kind) << "\",\"lvl\":" << o.lvl << ",\"a\":" << o.a << ",\"b\":" << o.b
-			  << ",\"dir\":" << o.dir << ",\"wait_all\":" << (o.wait_all ? "true" : "false") << ",\"arrays\":[";
+			  << ",\"dir\":" << o.dir << ",\"wait_all\":" << (o.wait_all ? "true" : "false") << ",\"async\":"
+			  << (o.async ? "true" : "false") << ",\"part\":" << o.part << ",\"id\":" << o.id << ",\"arrays\":[";
 			for (std::size_t k = 0; k < o.arrays.size(); k++) s << (k ? "," : "") << o.arrays[k];
 			s << "]}";
 		}
@@ -222,7 +285,7 @@ public:
 
 private:
 	static constexpr int INF = 1 << 20;
-	int ndist, W, ncol0, npre, npost;
+	int ndist, W, ncol0, npre, npost, split_levels;
 	std::vector<plan_op> ops;
 	std::vector<std::array<int, 4>> val;   // X0, X1, B, RES: halo lines that hold the neighbours' exact values
 	std::vector<int> cur;                  // slot that holds the iterate of each level
@@ -230,6 +293,32 @@ private:
 	std::map<std::pair<int, int>, std::pair<long, bool>> pulled;   // (lvl, slot) -> exchange step that read it, by all ranks?
 
 	void begin() { ops.clear(); pulled.clear(); step = 0; last_all = 0; }
+	// exchange(l, operands of the sweep) [zero(l, x)] sweep(l)  ->  [zero] exchange(async) sweep(interior) join sweep(frames).
+	// The interior part reads own points only, the pull writes halo lines only, the zero is moved ahead of both.
+	void overlap()
+	{
+		std::vector<plan_op> out;
+		int pairs = 0;
+		for (std::size_t i = 0; i < ops.size(); i++) {
+			const plan_op &e = ops[i];
+			std::size_t k = i + 1;
+			const bool z = k < ops.size() && ops[k].kind == op_kind::zero && ops[k].lvl == e.lvl;
+			if (z) k++;
+			bool ok = e.kind == op_kind::exchange && e.lvl < split_levels && k < ops.size() && ops[k].kind == op_kind::sweep
+			          && ops[k].lvl == e.lvl && (!z || ops[i + 1].a == ops[k].a);
+			if (ok)
+				for (int a : e.arrays) ok = ok && (a == ops[k].a || a == B);
+			if (!ok) { out.push_back(e); continue; }
+			if (z) out.push_back(ops[i + 1]);
+			plan_op ex = e; ex.async = true; ex.id = pairs;
+			plan_op in = ops[k]; in.part = 1;
+			plan_op fr = ops[k]; fr.part = 2;
+			plan_op jn; jn.kind = op_kind::join; jn.lvl = e.lvl; jn.id = pairs++;
+			out.push_back(ex); out.push_back(in); out.push_back(jn); out.push_back(fr);
+			i = k;
+		}
+		ops.swap(out);
+	}
 	std::vector<plan_op> take() { std::vector<plan_op> r; r.swap(ops); return r; }
 	void push(op_kind k, int lvl, int a = 0, int b = 0, int dir = 0)
 	{

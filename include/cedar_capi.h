@@ -109,8 +109,13 @@ int cdr2_solve_host(int nstencil, unsigned nx, unsigned ny, const double *so, co
  * replicated on every rank.  halo_width: odd, lines of the neighbours every array carries (15 = one exchange per
  * level per V(1,1) cycle). */
 typedef struct cdr2_dist cdr2_dist;
+/* split_min: on the levels where every block has at least this many own points per dimension, a sweep that directly
+ * follows the exchange of its operands is split: the exchange runs on a second stream while the interior is relaxed,
+ * the frames follow when the halos have arrived (0 = never; CDR_DIST_OVERLAP=0 in the environment runs the same
+ * operation list without the second stream). */
 int cdr2_dist_create(unsigned nx, unsigned ny, int px, int py, int nstencil, int nowned, const int *owned_blocks,
-                     int nrelax_pre, int nrelax_post, int agglomerate, int halo_width, int cuda_graph, cdr2_dist **out);
+                     int nrelax_pre, int nrelax_post, int agglomerate, int halo_width, int split_min, int cuda_graph,
+                     cdr2_dist **out);
 void cdr2_dist_destroy(cdr2_dist *d);
 int cdr2_dist_info(cdr2_dist *d, int *ndist, int *nlevels, int *halo_width, int *exchanges_per_cycle, int *ops_per_cycle);
 /* first own point (0-based global interior index) and own counts of a block on a distributed level */
@@ -137,7 +142,11 @@ int cdr2_dist_profile_ops(cdr2_dist *d, int n, float *ms_per_op, int cap, int *n
 /* host-only views of the schedule (no device needed): operation list as JSON, block geometry
  * (x0,y0,nx,ny, wl,wr,wb,wt, coarse window ox,oy,iic,jjc) */
 int cdr2_dist_plan_json(unsigned nx, unsigned ny, int px, int py, int nstencil, int nrelax_pre, int nrelax_post,
-                        int agglomerate, int halo_width, const char *what, char *out, size_t cap, int *ndist);
+                        int agglomerate, int halo_width, int split_min, const char *what, char *out, size_t cap, int *ndist);
+/* rectangles of a split sweep (part 1 = interior, 2 = frames) of a block: 8 ints each (i0, j0, ni, nj, wi0, wi1, wj0, wj1),
+ * the bmgx_rect of include/bmgx.h */
+int cdr2_dist_sweep_rects(unsigned nx, unsigned ny, int px, int py, int ndist, int halo_width, int lvl, int block,
+                          int ncolours, int part, int *out8, int cap, int *nrects);
 int cdr2_dist_geometry(unsigned nx, unsigned ny, int px, int py, int ndist, int halo_width, int lvl, int block, int *out12);
 
 /* ---- 3D (cdr3::solver): same protocol; nstencil = 4 (seven_pt) or 14 (xxvii_pt),

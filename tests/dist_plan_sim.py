@@ -11,18 +11,20 @@ from oracle import P
 import cedar_b200.dist2 as d2
 
 X0, X1, B, RES, A, SOR, PI = range(7)
+A_SLOT = A
 NPL = {X0: 1, X1: 1, B: 1, RES: 1, SOR: 2, PI: 8}
 
 
 class PlanSim:
-    def __init__(self, nx, ny, px, py, so_blocks, pre=1, post=1, agglomerate=33, halo=15, dist=None, poison=True):
+    def __init__(self, nx, ny, px, py, so_blocks, pre=1, post=1, agglomerate=33, halo=15, dist=None, poison=True, split_min=0):
         """so_blocks: {block: (nst, nyl+2, nxl+2)} own entries of the blocks this process owns"""
         self.L = oracle.lib()
         self.nx, self.ny, self.px, self.py, self.W = nx, ny, px, py, halo
         self.pre, self.post, self.dist = pre, post, dist
         self.owned = sorted(so_blocks)
         self.nst = next(iter(so_blocks.values())).shape[0]
-        kw = dict(nst=self.nst, pre=pre, post=post, agglomerate=agglomerate, halo=halo)
+        kw = dict(nst=self.nst, pre=pre, post=post, agglomerate=agglomerate, halo=halo, split_min=split_min)
+        self.pending = {}
         self.p_setup, self.nd = d2.plan(nx, ny, px, py, what="setup", **kw)
         self.p_cycle, _ = d2.plan(nx, ny, px, py, what="cycle", **kw)
         self.p_norm, _ = d2.plan(nx, ny, px, py, what="norm", **kw)
@@ -147,7 +149,15 @@ class PlanSim:
             getattr(self, "op_" + o["op"])(o)
 
     def op_exchange(self, o):
+        if o["async"]:
+            # the pull runs beside the following operations: deliver it as LATE as allowed (at the join), so that an
+            # operation in between that reads a halo line sees the stale value and the comparison with the serial solve fails
+            self.pending[o["id"]] = (o["lvl"], o["arrays"])
+            return
         self._exchange(o["lvl"], o["arrays"])
+
+    def op_join(self, o):
+        self._exchange(*self.pending.pop(o["id"]))
 
     def op_sync(self, o):
         self.exchanges += 1
@@ -164,11 +174,28 @@ class PlanSim:
 
     def op_sweep(self, o):
         l = o["lvl"]
+        if o["part"]:
+            return self._sweep_rects(o)
         for b, g in self._each(o):
             src, dst = self.a[l, b, o["a"]], self.a[l, b, o["b"]]
             dst[...] = src
             assert self.L.orc2_relax_gs(1, P(self.a[l, b, A]), P(self.a[l, b, B]), P(dst), P(self.a[l, b, SOR]), g["ii"], g["jj"], 1,
                                         self._ifd(l), self._nstl(l), 2, 1, o["dir"], 0) == 0
+
+    def _sweep_rects(self, o):
+        """bmgx2_relax_GS_oop_rects: every rectangle is swept as a grid of its own (outer lines = ghost ring from the
+        input iterate), only its window is stored"""
+        l = o["lvl"]
+        nc = 2 if self._ifd(l) else 4
+        for b, g in self._each(o):
+            src, dst = self.a[l, b, o["a"]], self.a[l, b, o["b"]]
+            for (i0, j0, ni, nj, wi0, wi1, wj0, wj1) in d2.sweep_rects(self.nx, self.ny, self.px, self.py, self.nd, self.W, l, b, nc,
+                                                                       o["part"]):
+                assert i0 % 2 == 0 and j0 % 2 == 0
+                cut = lambda a: np.array(a[:, j0:j0 + nj, i0:i0 + ni], order="C", copy=True)   # a copy even when the slice is contiguous
+                A, bb, q, sor = cut(self.a[l, b, A_SLOT]), cut(self.a[l, b, B]), cut(src), cut(self.a[l, b, SOR])
+                assert self.L.orc2_relax_gs(1, P(A), P(bb), P(q), P(sor), ni, nj, 1, self._ifd(l), self._nstl(l), 2, 1, o["dir"], 0) == 0
+                dst[0, j0 + wj0 - 1:j0 + wj1, i0 + wi0 - 1:i0 + wi1] = q[0, wj0 - 1:wj1, wi0 - 1:wi1]
 
     def op_residual(self, o):
         l = o["lvl"]

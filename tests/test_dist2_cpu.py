@@ -47,13 +47,20 @@ def count(plan, *names):
 
 def test_plan_one_exchange_per_level():
     """W = 15: a V(1,1) cycle of the C5 grid needs the start exchange, one per coarser distributed level and the gather"""
-    plan, nd = d2.plan(16385, 16385, 4, 2, pre=1, post=1, agglomerate=513, halo=15)
+    plan, nd = d2.plan(16385, 16385, 4, 2, pre=1, post=1, agglomerate=513, halo=15, split_min=0)
     assert nd == 5
     assert count(plan, "exchange") == 5 and count(plan, "gather") == 1 and count(plan, "sync") == 0
     assert count(plan, "sweep") == 10 and count(plan, "residual") == 5
+    # default: on the levels with blocks >= 512 wide the exchange runs beside the interior of the sweep that needs it
+    ov, _ = d2.plan(16385, 16385, 4, 2, pre=1, post=1, agglomerate=513, halo=15)
+    assert count(ov, "exchange") == 5 and count(ov, "join") == 4 and sum(o["async"] for o in ov) == 4
+    assert count(ov, "sweep") == 14 and sum(o["part"] == 1 for o in ov) == 4 and sum(o["part"] == 2 for o in ov) == 4
+    for k, o in enumerate(ov):
+        if o["op"] == "exchange" and o["async"]:
+            assert ov[k + 1]["op"] == "sweep" and ov[k + 1]["part"] == 1 and ov[k + 2]["op"] == "join" and ov[k + 3]["part"] == 2
     # narrower halos cost more exchanges, never a wrong result (the simulator tests below)
-    p7, _ = d2.plan(16385, 16385, 4, 2, pre=1, post=1, agglomerate=513, halo=7)
-    p5, _ = d2.plan(16385, 16385, 4, 2, pre=1, post=1, agglomerate=513, halo=5)
+    p7, _ = d2.plan(16385, 16385, 4, 2, pre=1, post=1, agglomerate=513, halo=7, split_min=0)
+    p5, _ = d2.plan(16385, 16385, 4, 2, pre=1, post=1, agglomerate=513, halo=5, split_min=0)
     assert count(plan, "exchange") < count(p7, "exchange") <= count(p5, "exchange")
     # the first operation of every list waits for all ranks
     for what in ("setup", "cycle", "norm"):
@@ -65,9 +72,12 @@ def test_plan_never_overwrites_a_pulled_array_too_early():
     """an array read by the neighbours in exchange s is written again only after a later exchange"""
     for halo in (5, 7, 9, 15):
         for pre, post in ((1, 1), (2, 1), (0, 1), (2, 2), (3, 0)):
-            plan, nd = d2.plan(1025, 1025, 2, 2, pre=pre, post=post, agglomerate=65, halo=halo)
+          for split in (0, 100):
+            plan, nd = d2.plan(1025, 1025, 2, 2, pre=pre, post=post, agglomerate=65, halo=halo, split_min=split)
             step, pulled = 0, {}
             for o in plan:
+                if o["op"] == "join":
+                    continue
                 if o["op"] in ("exchange", "sync", "gather", "gather_op", "norm"):
                     step += 1
                     for a in o["arrays"]:
@@ -103,21 +113,28 @@ def join(parts, ext, nx, ny):
 
 
 CASES = [
-    # nx, ny, px, py, nine, agglomerate, halo, pre, post
-    (129, 129, 2, 2, True, 17, 15, 1, 1),
-    (129, 129, 2, 2, True, 17, 5, 1, 1),
-    (129, 97, 2, 1, True, 17, 7, 2, 1),
-    (257, 129, 4, 2, True, 33, 15, 1, 1),
-    (200, 131, 3, 2, True, 20, 9, 1, 2),
-    (129, 129, 2, 2, False, 17, 15, 1, 1),
-    (150, 100, 2, 2, False, 20, 5, 2, 2),
-    (129, 129, 1, 2, True, 33, 5, 3, 2),
-    (161, 161, 2, 2, True, 17, 11, 0, 2),
+    # nx, ny, px, py, nine, agglomerate, halo, pre, post, split_min (0 = sweeps never split)
+    (129, 129, 2, 2, True, 17, 15, 1, 1, 0),
+    (129, 129, 2, 2, True, 17, 5, 1, 1, 0),
+    (129, 97, 2, 1, True, 17, 7, 2, 1, 0),
+    (257, 129, 4, 2, True, 33, 15, 1, 1, 0),
+    (200, 131, 3, 2, True, 20, 9, 1, 2, 0),
+    (129, 129, 2, 2, False, 17, 15, 1, 1, 0),
+    (150, 100, 2, 2, False, 20, 5, 2, 2, 0),
+    (129, 129, 1, 2, True, 33, 5, 3, 2, 0),
+    (161, 161, 2, 2, True, 17, 11, 0, 2, 0),
+    # the exchange beside the interior of the sweep that needs it (delivered as late as allowed in the simulator)
+    (129, 129, 2, 2, True, 17, 15, 1, 1, 40),
+    (257, 257, 2, 2, True, 17, 5, 1, 1, 20),
+    (257, 129, 4, 2, True, 33, 7, 2, 1, 20),
+    (300, 200, 3, 2, False, 20, 5, 1, 2, 20),
+    (257, 193, 2, 1, True, 17, 9, 0, 2, 30),
+    (257, 193, 1, 2, True, 17, 9, 2, 2, 30),
 ]
 
 
-@pytest.mark.parametrize("nx,ny,px,py,nine,agg,halo,pre,post", CASES)
-def test_plan_blocks_equal_serial(nx, ny, px, py, nine, agg, halo, pre, post):
+@pytest.mark.parametrize("nx,ny,px,py,nine,agg,halo,pre,post,split", CASES)
+def test_plan_blocks_equal_serial(nx, ny, px, py, nine, agg, halo, pre, post, split):
     rng = np.random.default_rng(nx + 3 * ny + nine + halo)
     so = random_op2(nx, ny, nine, rng)
     b = random_gf(nx, ny, rng)
@@ -125,8 +142,10 @@ def test_plan_blocks_equal_serial(nx, ny, px, py, nine, agg, halo, pre, post):
     ref = oracle.Solver2(so, "point", pre, post)
     _, nd = d2.plan(nx, ny, px, py, nst=so.shape[0], pre=pre, post=post, agglomerate=agg, halo=halo)
     ext = blocks_of(nx, ny, px, py, nd, halo)
-    sim = PlanSim(nx, ny, px, py, d2.split_blocks(so, ext), pre, post, agg, halo)
+    sim = PlanSim(nx, ny, px, py, d2.split_blocks(so, ext), pre, post, agg, halo, split_min=split)
     assert sim.nlevels == ref.nlevels and sim.nd == nd and nd >= 1
+    joins = sum(o["op"] == "join" for o in sim.p_cycle)
+    assert joins == 0 if split == 0 else (joins > 0 or pre == 0)
     # hierarchy: own points of every distributed level's operator and interpolation
     for lvl in range(1, nd + 1):
         gx, gy = sim.gn[lvl]

@@ -107,6 +107,41 @@ def test_windowed_transfer_kernels(cuda, nine):
     assert abs(float(out.item()) - (qc ** 2).sum()) <= 1e-12 * (qc ** 2).sum()
 
 
+@pytest.mark.parametrize("nine", [True, False])
+@pytest.mark.parametrize("px,py,blk", [(2, 2, 0), (2, 2, 3), (3, 3, 4), (1, 2, 1), (4, 1, 2)])
+def test_split_sweep_rectangles_equal_whole_sweep(cuda, nine, px, py, blk):
+    """bmgx2_relax_GS_oop_rects with the planner's rectangles (interior, then frames; include/cedar/2d/mpi/plan.h
+    sweep_rects) stores exactly the values of the whole-array sweep, at every entry, in both sweep directions"""
+    import cedar_b200.abi as abi
+    import cedar_b200.dist2 as d2
+    torch = cuda
+    L = abi.lib
+    nx, ny, W, nd = 700, 500, 15, 1
+    g = d2.geometry(nx, ny, px, py, nd, W, 0, blk)
+    ii, jj = g["ii"], g["jj"]
+    rng = np.random.default_rng(ii + jj + nine)
+    so = random_op2(ii - 2, jj - 2, nine, rng)
+    so[1:] = rng.uniform(0.5, 1.5, size=so[1:].shape)        # the ring carries real neighbour data on a block's array
+    nst = so.shape[0]
+    b = rng.standard_normal((jj, ii))
+    x = rng.standard_normal((jj, ii))
+    d_so, d_b, d_x = dev(torch, so), dev(torch, b), dev(torch, x)
+    d_sor = torch.zeros((2, jj, ii), dtype=torch.float64, device="cuda")
+    abi.check(L.bmgx2_SETUP_recip(ptr(d_so), ptr(d_sor), ii, jj, nst, 2, None))
+    for updown in (0, 1):
+        whole = torch.zeros_like(d_x)
+        abi.check(L.bmgx2_relax_GS_oop(1, ptr(d_so), ptr(d_b), ptr(d_x), ptr(whole), ptr(d_sor), ii, jj, 1, 0 if nine else 1, nst,
+                                       2, 1, updown, 0, None))
+        out = torch.full_like(d_x, float("nan"))
+        for part in (1, 2):
+            rs = d2.sweep_rects(nx, ny, px, py, nd, W, 0, blk, 4 if nine else 2, part)
+            assert 1 <= len(rs) <= 4
+            arr = (abi.Rect * len(rs))(*[abi.Rect(*r) for r in rs])
+            abi.check(L.bmgx2_relax_GS_oop_rects(1, ptr(d_so), ptr(d_b), ptr(d_x), ptr(out), ptr(d_sor), ii, jj, 1, 0 if nine else 1,
+                                                 nst, 2, 1, updown, 0, arr, len(rs), None))
+        assert_bitwise(host(out), host(whole), f"split sweep, direction {updown}")
+
+
 def _join(parts, ext, nx, ny):
     first = next(iter(parts.values()))
     g = np.zeros(first.shape[:-2] + (ny + 2, nx + 2))
@@ -116,12 +151,15 @@ def _join(parts, ext, nx, ny):
     return g
 
 
-CASES = [(257, 257, 2, 2, True, 33, 15, 1, 1), (513, 257, 4, 2, True, 65, 15, 1, 1), (300, 210, 2, 2, False, 33, 7, 2, 1),
-         (1025, 1025, 2, 1, True, 129, 15, 1, 1), (513, 513, 2, 2, True, 65, 5, 2, 2), (385, 641, 1, 3, True, 65, 9, 1, 2)]
+CASES = [(257, 257, 2, 2, True, 33, 15, 1, 1, 0), (513, 257, 4, 2, True, 65, 15, 1, 1, 0), (300, 210, 2, 2, False, 33, 7, 2, 1, 0),
+         (1025, 1025, 2, 1, True, 129, 15, 1, 1, 0), (513, 513, 2, 2, True, 65, 5, 2, 2, 0), (385, 641, 1, 3, True, 65, 9, 1, 2, 0),
+         # exchanges beside the interior of the next sweep (second stream; split sweeps) on the larger levels
+         (1025, 1025, 2, 2, True, 129, 15, 1, 1, 100), (1025, 769, 2, 1, True, 65, 9, 2, 1, 60), (600, 900, 2, 3, False, 65, 15, 1, 1, 64),
+         (2049, 1025, 4, 2, True, 129, 15, 1, 1, 512)]
 
 
-@pytest.mark.parametrize("nx,ny,px,py,nine,agg,halo,pre,post", CASES)
-def test_blocks_on_one_gpu_equal_serial(cuda, nx, ny, px, py, nine, agg, halo, pre, post):
+@pytest.mark.parametrize("nx,ny,px,py,nine,agg,halo,pre,post,split", CASES)
+def test_blocks_on_one_gpu_equal_serial(cuda, nx, ny, px, py, nine, agg, halo, pre, post, split):
     import cedar_b200.dist2 as d2
     import cedar_b200.solver as cs
     rng = np.random.default_rng(nx + ny + nine + halo)
@@ -130,7 +168,10 @@ def test_blocks_on_one_gpu_equal_serial(cuda, nx, ny, px, py, nine, agg, halo, p
     ref = oracle.Solver2(so, "point", pre, post)
     ser = cs.Solver2(cs.Operator2(so), relaxation="point", nrelax_pre=pre, nrelax_post=post, maxiter=6, tol=1e-30)
     l0 = cs.gpu_launches()
-    sol = d2.DistSolver2(nx, ny, (px, py), nst=so.shape[0], nrelax_pre=pre, nrelax_post=post, agglomerate=agg, halo=halo)
+    sol = d2.DistSolver2(nx, ny, (px, py), nst=so.shape[0], nrelax_pre=pre, nrelax_post=post, agglomerate=agg, halo=halo,
+                         split_min=split)
+    plan, _ = d2.plan(nx, ny, px, py, so.shape[0], pre, post, agg, halo, "cycle", split)
+    assert (sum(o["op"] == "join" for o in plan) > 0) == (split > 0)
     nb = px * py
     ext = {k: sol.extent(0, k) for k in range(nb)}
     for k, v in d2.split_blocks(so, ext).items():
