@@ -69,7 +69,7 @@ def parse():
     ap.add_argument("--replicas", action="store_true", help="N > 1: independent replicas instead of one decomposed problem")
     ap.add_argument("--agglomerate", type=int, default=513, help="N > 1: levels of this size or smaller are solved replicated")
     ap.add_argument("--halo", type=int, default=15, help="N > 1: lines of the neighbours every array carries (odd)")
-    ap.add_argument("--split-min", type=int, default=512, help="N > 1: split sweeps (exchange beside the interior) where blocks are at least this wide; 0 = never")
+    ap.add_argument("--split-min", type=int, default=0, help="N > 1: split sweeps (ghost exchange beside the interior relaxation) where blocks are at least this wide; 0 = never (default: measured slower, DESIGN.md section 6)")
     ap.add_argument("--global-n", type=int, default=0, help="N > 1: strong scaling on a global-n^2 grid instead of (n-1)^2 per GPU")
     ap.add_argument("--no-c5", action="store_true", help="N > 1: skip the extra 16385^2 heterogeneous (configs[4]) measurement")
     ap.add_argument("--c5-n", type=int, default=16385)

@@ -52,7 +52,11 @@ def _P(a):
 
 
 # ------------------------------------------------------------------ host-only views of the schedule
-SPLIT_MIN = 512      # default: sweeps are split (exchange beside the interior) where blocks are at least this wide
+# Sweeps can be split so that the ghost exchange runs beside the interior relaxation (blocks at least this wide; 0 = never).
+# Default off: with one exchange per level left (deep halos) the latency it hides (~6 us per exchange) is smaller than
+# what the split costs (a frames launch + fork/join, ~15-25 us per level): 16385x8193 on 8 GPUs 1.344 ms per cycle without,
+# 1.398 ms with (profiles/r02_overlap_8gpu.txt); 2 GPUs 1.280 / 1.301 ms.
+SPLIT_MIN = 0
 
 
 def plan(nx, ny, px, py, nst=5, pre=1, post=1, agglomerate=513, halo=15, what="cycle", split_min=SPLIT_MIN):

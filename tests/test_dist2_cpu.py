@@ -51,8 +51,8 @@ def test_plan_one_exchange_per_level():
     assert nd == 5
     assert count(plan, "exchange") == 5 and count(plan, "gather") == 1 and count(plan, "sync") == 0
     assert count(plan, "sweep") == 10 and count(plan, "residual") == 5
-    # default: on the levels with blocks >= 512 wide the exchange runs beside the interior of the sweep that needs it
-    ov, _ = d2.plan(16385, 16385, 4, 2, pre=1, post=1, agglomerate=513, halo=15)
+    # split_min 512: on the levels with blocks >= 512 wide the exchange runs beside the interior of the sweep that needs it
+    ov, _ = d2.plan(16385, 16385, 4, 2, pre=1, post=1, agglomerate=513, halo=15, split_min=512)
     assert count(ov, "exchange") == 5 and count(ov, "join") == 4 and sum(o["async"] for o in ov) == 4
     assert count(ov, "sweep") == 14 and sum(o["part"] == 1 for o in ov) == 4 and sum(o["part"] == 2 for o in ov) == 4
     for k, o in enumerate(ov):
