@@ -75,6 +75,8 @@ SIGNATURES = {
     "bmgx3_matvec": (_i, [_i, _p, _p, _p, _u, _u, _u, _i, _i, _i, _p]),
     "bmgx3_restrict": (_i, [_p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _p]),
     "bmgx3_interp_add": (_i, [_p, _p, _p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _i, _p]),
+    "bmgx3_restrict_v": (_i, [_p, _p, _p, _u, _u, _u, _u, _u, _u, _z, _p]),
+    "bmgx3_interp_add_v": (_i, [_p, _p, _p, _p, _p, _u, _u, _u, _u, _u, _u, _z, _p]),
     "bmgx3_SETUP_interp_OI": (_i, [_p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _i, _i, _i, _p, _p]),
     "bmgx3_SETUP_ITLI07_ex": (_i, [_p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _p]),
     "bmgx3_SETUP_ITLI27_ex": (_i, [_p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _p]),

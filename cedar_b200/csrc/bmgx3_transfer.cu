@@ -8,11 +8,13 @@ namespace {
 
 __global__ void __launch_bounds__(128)
 k3_restrict(const double *__restrict__ q, double *__restrict__ qc, const double *__restrict__ ci, int Nx, int Ny,
-            int Nxc, int Nyc, int Nzc)
+            int Nxc, int Nyc, int Nzc, size_t pc)
 {
+    // pc: stride between the 26 weight arrays of ci (Nxc*Nyc*Nzc for a plain array; larger when ci is a window of
+    // planes of a thicker array, bmgx3_restrict_v)
     int ic = blockIdx.x * blockDim.x + threadIdx.x + 2, jc = blockIdx.y * blockDim.y + threadIdx.y + 2, kc = blockIdx.z + 2;
     if (ic > Nxc - 1 || jc > Nyc - 1) return;
-    const size_t pc = (size_t)Nxc * Nyc * Nzc, PJc = (size_t)Nxc * Nyc, PJ = (size_t)Nx * Ny;
+    const size_t PJc = (size_t)Nxc * Nyc, PJ = (size_t)Nx * Ny;
     const size_t cc = ((size_t)(kc - 1) * Nyc + (jc - 1)) * Nxc + (ic - 1);
     const size_t f = ((size_t)(2 * (kc - 1) - 1) * Ny + (2 * (jc - 1) - 1)) * Nx + (2 * (ic - 1) - 1);
 #define CI(l, off) ci[(size_t)((l)-1) * pc + cc + (off)]
@@ -40,7 +42,7 @@ k3_restrict(const double *__restrict__ q, double *__restrict__ qc, const double 
 // there is no divergence and twice the loads are in flight.
 __global__ void __launch_bounds__(128)
 k3_interp_add(double *__restrict__ q, const double *__restrict__ qc, const double *__restrict__ so,
-              double *__restrict__ res, const double *__restrict__ ci, int IIC, int JJC, int KKC, int IIF, int JJF)
+              double *__restrict__ res, const double *__restrict__ ci, int IIC, int JJC, int KKC, int IIF, int JJF, size_t pc)
 {
     const int ic = blockIdx.x * blockDim.x + threadIdx.x + 2, j = blockIdx.y * blockDim.y + threadIdx.y + 2,
               k = blockIdx.z + 2;
@@ -48,7 +50,7 @@ k3_interp_add(double *__restrict__ q, const double *__restrict__ qc, const doubl
     const int i0 = 2 * ic - 3, i1 = i0 + 1;
     const bool v0 = i0 >= 2, v1 = i1 <= IIF - 1;
     const size_t f0 = ((size_t)(k - 1) * JJF + (j - 1)) * IIF + (i0 - 1), f1 = f0 + 1;
-    const size_t pc = (size_t)IIC * JJC * KKC, X = 1, Y = IIC, Z = (size_t)IIC * JJC;
+    const size_t X = 1, Y = IIC, Z = (size_t)IIC * JJC;   // pc: stride between the weight arrays (see k3_restrict)
     const int jc = (j + 1) / 2 + 1, kc = (k + 1) / 2 + 1;
     const size_t cc = ((size_t)(kc - 1) * JJC + (jc - 1)) * IIC + (ic - 1);
     const double n0 = v0 ? res[f0] : 0.0, n1 = v1 ? res[f1] : 0.0;
@@ -91,8 +93,20 @@ extern "C" int bmgx3_restrict(const double *q, double *qc, const double *ci, bmg
     if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "restrict3: periodic BCs not supported");
     if (nxc < 3 || nyc < 3 || nzc < 3) return BMGX_OK;
     dim3 b(32, 4), g(cdiv(nxc - 2, 32), cdiv(nyc - 2, 4), nzc - 2);
-    k3_restrict<<<g, b, 0, (cudaStream_t)s>>>(q, qc, ci, nx, ny, nxc, nyc, nzc);
+    k3_restrict<<<g, b, 0, (cudaStream_t)s>>>(q, qc, ci, nx, ny, nxc, nyc, nzc, (size_t)nxc * nyc * nzc);
     BMGX_LAUNCH_CHECK("restrict3");
+    return BMGX_OK;
+}
+
+extern "C" int bmgx3_restrict_v(const double *q, double *qc, const double *ci, bmgx_len nx, bmgx_len ny, bmgx_len nz,
+                                bmgx_len nxc, bmgx_len nyc, bmgx_len nzc, size_t cstride, bmgx_stream_t s)
+{
+    (void)nz;
+    if (nxc < 3 || nyc < 3 || nzc < 3) return BMGX_OK;
+    if (cstride < (size_t)nxc * nyc * nzc) return bmgx_set_error(BMGX_ERR_ARG, "restrict3_v: weight stride smaller than the window");
+    dim3 b(32, 4), g(cdiv(nxc - 2, 32), cdiv(nyc - 2, 4), nzc - 2);
+    k3_restrict<<<g, b, 0, (cudaStream_t)s>>>(q, qc, ci, nx, ny, nxc, nyc, nzc, cstride);
+    BMGX_LAUNCH_CHECK("restrict3_v");
     return BMGX_OK;
 }
 
@@ -104,7 +118,19 @@ extern "C" int bmgx3_interp_add(double *q, const double *qc, const double *so, d
     if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "interp_add3: periodic BCs not supported");
     if (iif < 3 || jjf < 3 || kkf < 3) return BMGX_OK;
     dim3 b(32, 4), g(cdiv(iif / 2, 32), cdiv(jjf - 2, 4), kkf - 2);
-    k3_interp_add<<<g, b, 0, (cudaStream_t)s>>>(q, qc, so, res, ci, iic, jjc, kkc, iif, jjf);
+    k3_interp_add<<<g, b, 0, (cudaStream_t)s>>>(q, qc, so, res, ci, iic, jjc, kkc, iif, jjf, (size_t)iic * jjc * kkc);
     BMGX_LAUNCH_CHECK("interp_add3");
+    return BMGX_OK;
+}
+
+extern "C" int bmgx3_interp_add_v(double *q, const double *qc, const double *so, double *res, const double *ci,
+                                  bmgx_len iic, bmgx_len jjc, bmgx_len kkc, bmgx_len iif, bmgx_len jjf, bmgx_len kkf,
+                                  size_t cstride, bmgx_stream_t s)
+{
+    if (iif < 3 || jjf < 3 || kkf < 3) return BMGX_OK;
+    if (cstride < (size_t)iic * jjc * kkc) return bmgx_set_error(BMGX_ERR_ARG, "interp_add3_v: weight stride smaller than the window");
+    dim3 b(32, 4), g(cdiv(iif / 2, 32), cdiv(jjf - 2, 4), kkf - 2);
+    k3_interp_add<<<g, b, 0, (cudaStream_t)s>>>(q, qc, so, res, ci, iic, jjc, kkc, iif, jjf, cstride);
+    BMGX_LAUNCH_CHECK("interp_add3_v");
     return BMGX_OK;
 }

@@ -285,3 +285,17 @@ extern "C" int cdr3_plane_relax(cdr3_operator *op, const char *config_json, cons
 		std::memcpy(x, gx.cdata(), gx.size() * sizeof(double));
 	});
 }
+
+extern "C" int cdr3_solver_resident_ptrs(cdr3_solver *s, double **b_dev, double **x_dev)
+{
+	return guard([&] { *b_dev = s->b.dev(); *x_dev = s->x.dev(); });
+}
+
+extern "C" int cdr3_solver_vcycle_resident(cdr3_solver *s, void *stream)
+{
+	return guard([&] {
+		gpu::stream_guard on_callers_stream(stream);
+		s->b.dev(); s->x.dev();
+		s->each([&](auto &slv) { slv.vcycle(s->x, s->b); });
+	});
+}

@@ -351,6 +351,16 @@ int bmgx3_interp_add(bmgx_real *q, const bmgx_real *qc, const bmgx_real *so, bmg
                      const bmgx_real *ci, bmgx_len iic, bmgx_len jjc, bmgx_len kkc, bmgx_len iif,
                      bmgx_len jjf, bmgx_len kkf, int nstncl, int jpn, bmgx_stream_t s);
 
+/* bmgx3_restrict / bmgx3_interp_add (non-periodic) with the coarse arrays given as a window of PLANES of a thicker array
+ * (the slab-decomposed multi-GPU path, whose coarse arrays carry more halo planes than the fine array's coarsening
+ * reaches): qc and ci point at the window's first plane, kkc is the window's thickness, cstride the stride in doubles
+ * between the 26 weight arrays of ci (iic*jjc*KKC of the thick array). */
+int bmgx3_restrict_v(const bmgx_real *q, bmgx_real *qc, const bmgx_real *ci, bmgx_len nx, bmgx_len ny, bmgx_len nz,
+                     bmgx_len nxc, bmgx_len nyc, bmgx_len nzc, size_t cstride, bmgx_stream_t s);
+int bmgx3_interp_add_v(bmgx_real *q, const bmgx_real *qc, const bmgx_real *so, bmgx_real *res, const bmgx_real *ci,
+                       bmgx_len iic, bmgx_len jjc, bmgx_len kkc, bmgx_len iif, bmgx_len jjf, bmgx_len kkf, size_t cstride,
+                       bmgx_stream_t s);
+
 /* BMG3_SymStd_SETUP_interp_OI(so, soc, ci, iif, jjf, kkf, iic, jjc, kkc, ifd, nstncl, irelax,
  *                             jpn, yo), include/cedar/3d/interp.h:11-15; the `yo` scratch of
  * the reference is not needed (may be NULL) */

@@ -207,13 +207,19 @@ class planner
 public:
 	// split_levels: on levels 0 .. split_levels-1 a sweep that directly follows the exchange of its operands is split:
 	// the exchange starts, the interior is relaxed meanwhile, the frames after the halos have arrived
-	planner(int ndist, int W, int ncol0, int npre, int npost, int split_levels = 0)
-	    : ndist(ndist), W(W), ncol0(ncol0), npre(npre), npost(npost), split_levels(split_levels)
+	// ncol_coarse: lines of validity a sweep of a coarse level consumes (2D nine-point: its 4 colours; the slab-
+	// decomposed 3D path: 2, the depth of the colour ordering across planes).  inplace0 / inplace_coarse: the sweep
+	// kernel of that level works in place (3D 27-point) instead of from one array into the other.
+	planner(int ndist, int W, int ncol0, int npre, int npost, int split_levels = 0, int ncol_coarse = 4, bool inplace0 = false,
+	        bool inplace_coarse = false)
+	    : ndist(ndist), W(W), ncol0(ncol0), npre(npre), npost(npost), split_levels(split_levels), ncol_coarse(ncol_coarse),
+	      inplace0(inplace0), inplace_coarse(inplace_coarse)
 	{
 		if (npre + npost < 1) throw std::invalid_argument("a cycle needs at least one sweep");
 		// a whole 4-colour sweep over the extended array must leave the own points exact: colour c is exact out to line
 		// W - 1 - (c - 1), so W - 4 >= 0 and W odd
-		if (W < 5 || W % 2 == 0) throw std::invalid_argument("halo width must be odd and at least 5");
+		if (W < std::max(ncol0, ncol_coarse) + 1 || W % 2 == 0)
+			throw std::invalid_argument("halo width must be odd and at least the number of colours + 1 (2D: 5)");
 	}
 
 	// interpolation + Galerkin operators of the distributed levels, agglomerated operator
@@ -285,7 +291,8 @@ public:
 
 private:
 	static constexpr int INF = 1 << 20;
-	int ndist, W, ncol0, npre, npost, split_levels;
+	int ndist, W, ncol0, npre, npost, split_levels, ncol_coarse;
+	bool inplace0, inplace_coarse;
 	std::vector<plan_op> ops;
 	std::vector<std::array<int, 4>> val;   // X0, X1, B, RES: halo lines that hold the neighbours' exact values
 	std::vector<int> cur;                  // slot that holds the iterate of each level
@@ -356,11 +363,12 @@ private:
 		ops.push_back(o);
 		step++; last_all = step;
 	}
-	int ncol(int lvl) const { return lvl == 0 ? ncol0 : 4; }
+	int ncol(int lvl) const { return lvl == 0 ? ncol0 : ncol_coarse; }
+	bool inplace(int lvl) const { return lvl == 0 ? inplace0 : inplace_coarse; }
 
 	void sweep(int l, int dir)
 	{
-		const int nc = ncol(l), src = cur[l], dst = src == X0 ? X1 : X0;
+		const int nc = ncol(l), src = cur[l], dst = inplace(l) ? src : (src == X0 ? X1 : X0);
 		std::vector<int> need;
 		if (std::min(val[l][src] - 1, W - 1) - (nc - 1) < 0) need.push_back(src);
 		if (val[l][B] - (nc - 1) < 0) need.push_back(B);

@@ -178,6 +178,39 @@ int cdr3_solver_time_solves(cdr3_solver *solver, const double *b, int warmup, in
  * config_json carries "plane-config" as in test/3d/test-planes-ser.json.  Host arrays; x is updated in place. */
 int cdr3_plane_relax(cdr3_operator *op, const char *config_json, const char *dir, int updown, const double *b, double *x);
 
+/* the solver's own device-resident b and x and one V-cycle on them (see cdr2_solver_resident_ptrs) */
+int cdr3_solver_resident_ptrs(cdr3_solver *solver, double **b_dev, double **x_dev);
+int cdr3_solver_vcycle_resident(cdr3_solver *solver, void *stream);
+
+/* ---- slab-decomposed 3D solver across GPUs (cdr3::mpi::solver of the reference, include/cedar/3d/mpi/solver.h) ----
+ * The nx x ny x nz grid is cut into `nslabs` slabs of xy planes, one per GPU (include/cedar/3d/mpi/plan.h); protocol
+ * and semantics as cdr2_dist_*: create with the owned slab ids, set the own planes of the operator, move the IPC
+ * handles, connect, setup; ghost planes are pulled out of the two neighbours' device memory over NVLink; levels with
+ * at most `agglomerate` planes are solved replicated.  Point relaxation (7-point red-black fused, 27-point 8 colours).
+ * Host arrays of a slab: (entries,) nzl+2, ny+2, nx+2 with the own planes in 1..nzl. */
+typedef struct cdr3_dist cdr3_dist;
+int cdr3_dist_create(unsigned nx, unsigned ny, unsigned nz, int nslabs, int nstencil, int nowned, const int *owned_slabs,
+                     int nrelax_pre, int nrelax_post, int agglomerate, int halo_width, int cuda_graph, cdr3_dist **out);
+void cdr3_dist_destroy(cdr3_dist *d);
+int cdr3_dist_info(cdr3_dist *d, int *ndist, int *nlevels, int *halo_width, int *exchanges_per_cycle, int *ops_per_cycle);
+int cdr3_dist_slab_extent(cdr3_dist *d, int lvl, int slab, int *nx, int *ny, int *z0, int *nz);
+int cdr3_dist_export_handles(cdr3_dist *d, void *handles);
+int cdr3_dist_connect(cdr3_dist *d, const void *handles);
+int cdr3_dist_set_operator(cdr3_dist *d, int slab, const double *so);
+int cdr3_dist_setup(cdr3_dist *d);
+int cdr3_dist_upload(cdr3_dist *d, int slab, const char *which, const double *host);
+int cdr3_dist_download(cdr3_dist *d, int slab, const char *which, double *host);
+/* own planes of a level array -> host (entries, nzl, ny+2, nx+2); which = "A" | "P" */
+int cdr3_dist_level_array(cdr3_dist *d, int slab, int lvl, const char *which, double *out);
+int cdr3_dist_vcycle(cdr3_dist *d);
+int cdr3_dist_sync(cdr3_dist *d);
+int cdr3_dist_solve(cdr3_dist *d, int maxiter, double tol, double *hist, int hist_cap, int *niter, double *res0);
+int cdr3_dist_time_vcycles(cdr3_dist *d, int warmup, int n, float *ms_per_cycle);
+int cdr3_dist_plan_json(unsigned nx, unsigned ny, unsigned nz, int nslabs, int nstencil, int nrelax_pre, int nrelax_post,
+                        int agglomerate, int halo_width, const char *what, char *out, size_t cap, int *ndist);
+/* nx, ny, z0, nz, wb, wt, coarse window first plane and thickness */
+int cdr3_dist_geometry(unsigned nx, unsigned ny, unsigned nz, int nslabs, int ndist, int halo_width, int lvl, int slab, int *out8);
+
 #ifdef __cplusplus
 }
 #endif
