@@ -27,12 +27,21 @@ def rhs_slab(n, z0, nzl):
 def op_slab(name, n, z0, nzl):
     """own planes of gallery::poisson (7-point, src/3d/gallery.cc:7-56) / gallery::fe (27-point, :111-190)"""
     import cedar_b200.solver as cs
-    op = cs.Operator3(gallery=name, nx=n, ny=n, nz=3)     # interior planes of these operators are identical ...
+    if name == "poisson":
+        # the same expressions as gallery::poisson (cedar_b200/host/grid3.cc:92-109) with hx = hy = hz = 1/(n+1)
+        h = 1.0 / (n + 1)
+        xh = yh = zh = h * h / h
+        so = np.zeros((4, nzl + 2, n + 2, n + 2))
+        so[0, 1:-1, 1:-1, 1:-1] = 2.0 * xh + 2.0 * yh + 2.0 * zh
+        so[1, 1:-1, 1:-1, 2:-1] = 1.0 * xh
+        so[2, 1:-1, 2:-1, 1:-1] = 1.0 * yh
+        so[3, (2 if z0 == 0 else 1):-1, 1:-1, 1:-1] = 1.0 * zh
+        return so
+    op = cs.Operator3(gallery=name, nx=n, ny=n, nz=3)     # fe: constant entries; interior planes are identical ...
     a = np.array(op.array())
-    nst = a.shape[0]
-    so = np.zeros((nst, nzl + 2, n + 2, n + 2))
+    so = np.zeros((a.shape[0], nzl + 2, n + 2, n + 2))
     so[:, 1:-1] = a[:, 2][:, None]
-    if z0 == 0:                                           # ... except that plane 0 has no couplings downwards
+    if z0 == 0:                                           # ... except that the first plane has no couplings downwards
         so[:, 1] = a[:, 1]
     return so
 
