@@ -6,8 +6,10 @@
 // factor; y-lines stored transposed SOR(j,i,.) so every line is contiguous.
 //
 // Setup: the LDL' recurrence d(i+1) = d(i+1) - e(i)^2/d(i) is sequential per
-// line; one lane per line, 32x32 tiles staged through shared memory so global
-// traffic is coalesced.  Bitwise DPTTRF.
+// line; one lane per line, operands fetched 16 positions ahead of the chain.  For y-lines the lanes of a warp read
+// neighbouring columns (coalesced) and store with stride ny; for x-lines it is the other way round (the tiled
+// transpose through shared memory that would make both sides coalesced is not implemented: 10 % of the copy
+// roofline, setup only).  Bitwise DPTTRF.
 //
 // Solve: with the factor known, DPTTS2 is two first-order linear recurrences,
 //     y(i) = b(i) - e(i-1) y(i-1),      x(i) = y(i)/d(i) - e(i) x(i+1),

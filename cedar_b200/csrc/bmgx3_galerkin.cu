@@ -210,16 +210,8 @@ int launch(const Op3 &A, const Ci3 &W, double *soc, cudaStream_t st)
     const int nkmax = min(SLAB + 2, W.KKC);
     Slab S;
     S.plane = plane;
-    static bool pool_set = false;
-    if (!pool_set) {
-        // keep the scratch in the stream-ordered pool between calls (one setup runs this once per level)
-        int dev = 0;
-        cudaMemPool_t pool;
-        unsigned long long keep = ~0ull;
-        if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess)
-            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
-        pool_set = true;
-    }
+    // stream-ordered scratch from the device's default pool, as it is configured by the embedding application (the
+    // library does not touch the pool's release threshold)
     cudaError_t e = cudaMallocAsync((void **)&S.t, (size_t)NT * plane * nkmax * sizeof(double), st);
     if (e != cudaSuccess) return bmgx_set_cuda_error(e, "SETUP_ITLI3/scratch");
     dim3 b(32, 4);

@@ -9,8 +9,10 @@
 
 namespace cedar { namespace gpu {
 
-static bmgx_stream_t g_stream = nullptr;
-static bool g_stream_own = false;
+// the current stream is per host thread (like the batch context, the last-error text and the swap recorder): two
+// solvers driven from two threads never enqueue on each other's stream or into each other's graph capture
+static thread_local bmgx_stream_t g_stream = nullptr;
+static thread_local bool g_stream_own = false;
 static int g_avail = -1;
 static std::atomic<unsigned long long> g_extra{0};
 
@@ -32,7 +34,7 @@ bmgx_stream_t stream()
 
 void set_stream(bmgx_stream_t s)
 {
-	if (g_stream && g_stream_own) bmgx_stream_destroy(g_stream);
+	if (g_stream && g_stream_own) { bmgx_stream_sync(g_stream); bmgx_stream_destroy(g_stream); }
 	g_stream = s;
 	g_stream_own = false;
 }

@@ -632,14 +632,16 @@ class DistSolver2:
             l0, e0 = self.K.launches, self.exchanges
             with torch.cuda.graph(g, stream=self.stream):
                 self._ncycle(0, x, b) if self.ndist > 0 else self.vcycle(x, b)
-            self._graph_cost = (self.K.launches - l0, self.exchanges - e0)
+            if not hasattr(self, "_graph_costs"):
+                self._graph_costs = {}
+            self._graph_costs[key] = (self.K.launches - l0, self.exchanges - e0)
             self._graphs[key] = g
             for k in self.owned:
                 x[k].copy_(saved[k])
         with self._on_stream():
             g.replay()
-        self.K.launches += self._graph_cost[0]
-        self.exchanges += self._graph_cost[1]
+        self.K.launches += self._graph_costs[key][0]
+        self.exchanges += self._graph_costs[key][1]
 
     def vcycle_stream(self, x, b, bhs, xhs, graphed=True):
         """A stream of right-hand sides from and to pinned host memory (this rank's block of each): for every

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 #ifndef CEDAR_2D_CORE_BASE_TYPES_H
 #define CEDAR_2D_CORE_BASE_TYPES_H
 /* slot numbers of the 2D symmetric stencil storage (reference 2d/base_types.h:4-14;

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/2d/coarsen.h -- CUDA-backed Galerkin coarse-operator construction
 // (reference class galerkin, include/cedar/2d/coarsen.h:18-61).
 #ifndef CEDAR_2D_COARSEN_H

@@ -1,3 +1,4 @@
+/* API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root. */
 /* cedar/2d/interface/c/operator.h -- bmg2_operator_* of the reference's C interface
  * (include/cedar/2d/interface/c/operator.h:12-29, src/2d/interface/c/operator.cc).  Same names, argument order and
  * meaning: vertex-based, signed stencil entries in (bmg2_operator_set converts them to BoxMG's symmetric storage with

@@ -1,3 +1,4 @@
+/* API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root. */
 /* cedar/2d/interface/c/solver.h -- bmg2_solver_* of the reference's C interface
  * (include/cedar/2d/interface/c/solver.h:13-15, src/2d/interface/c/solver.cc): create = setup phase from the operator
  * (settings from ./config.json when it exists, defaults otherwise), run = solve from x = 0 on packed interior

@@ -1,3 +1,4 @@
+/* API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root. */
 /* cedar/2d/interface/c/topo.h -- bmg2_topo_create of the reference's C interface
  * (include/cedar/2d/interface/c/topo.h:14-20, src/2d/interface/c/topo.cc:10-69).
  *

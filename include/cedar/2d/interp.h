@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/2d/interp.h -- CUDA-backed interpolate-and-add and operator-induced
 // interpolation setup (reference interp_f90 / setup_interp_f90, src/2d/interp.cc:19-106).
 #ifndef CEDAR_2D_INTERP_H

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/2d/kernel_manager.h -- builds the serial 2D registry with the CUDA
 // kernels registered (and selected) under the name "system", the name the
 // reference uses for its Fortran-backed defaults (src/2d/kernel_manager.cc:16-42).

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/2d/matvec.h -- CUDA-backed operator application y = A x (reference matvec_f90 over
 // BMG2_SymStd_UTILS_matvec, include/cedar/2d/mpi/matvec.h / include/cedar/2d/matvec.h:20-50: k = kf, ifd from
 // the stencil type; the reference offers it on its MPI kernel list, here the serial registry carries it too).

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 #ifndef CEDAR_2D_INTER_PROLONG_OP_H
 #define CEDAR_2D_INTER_PROLONG_OP_H
 #include <iostream>

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/2d/relax.h -- CUDA-backed point and line relaxation kernels, registered
 // under the same interfaces as the reference's rbgs / lines<rdir>
 // (include/cedar/2d/relax.h:28-190): k = kf = 1, ifd from the stencil type,

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/2d/residual.h -- CUDA-backed residual kernel (reference residual_f90,
 // include/cedar/2d/residual.h:14-62: k = kf = 0, ifd from the stencil type).
 #ifndef CEDAR_2D_RESIDUAL_H

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/2d/restrict.h -- CUDA-backed restriction R = P^T (reference restrict_f90, src/2d/restrict.cc:16-32)
 #ifndef CEDAR_2D_INTER_RESTRICT_H
 #define CEDAR_2D_INTER_RESTRICT_H
@@ -13,7 +14,11 @@ public:
 		const prolong_op &P = R.getP();
 		int ibc;
 		bmgx_get_bc(params->per_mask(), &ibc);
-		gpu::check(bmgx2_restrict(fine.cdev(), coarse.dev(), P.cdev(), fine.len(0), fine.len(1), coarse.len(0),
+		// with periodic boundaries the kernel refreshes the ghost layer of the FINE vector first, as the reference does
+		// (BMG2_SymStd_restrict.f90:96-111): take the mutable pointer then, so that a host mirror is marked stale
+		const bool periodic = params->periodic[0] || params->periodic[1];
+		const real_t *fdev = periodic ? const_cast<grid_func &>(fine).dev() : fine.cdev();
+		gpu::check(bmgx2_restrict(fdev, coarse.dev(), P.cdev(), fine.len(0), fine.len(1), coarse.len(0),
 		                          coarse.len(1), ibc, gpu::stream()), "restrict");
 	}
 };

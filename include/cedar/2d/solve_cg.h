@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/2d/solve_cg.h -- CUDA-backed coarsest-grid direct solve (reference
 // solve_cg_f90, include/cedar/2d/solve_cg.h:17-65, src/2d/solve_cg.cc:14-30).
 #ifndef CEDAR_2D_SOLVE_CG_H

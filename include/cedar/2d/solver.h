@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/2d/solver.h -- cdr2::solver<fsten>: level-count rule, coarse sizes and
 // coarse-solve workspace of the reference (include/cedar/2d/solver.h:17-126),
 // over device-resident levels.

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 #ifndef CEDAR_2D_TYPES_H
 #define CEDAR_2D_TYPES_H
 #include <cedar/solver_types.h>

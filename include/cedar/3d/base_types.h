@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 #ifndef CEDAR_3D_BASE_TYPES_H
 #define CEDAR_3D_BASE_TYPES_H
 /* slot numbers of the 3D symmetric stencil storage (reference 3d/base_types.h;

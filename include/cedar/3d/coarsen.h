@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/3d/coarsen.h -- CUDA-backed 3D Galerkin coarse-operator construction
 // (reference class galerkin, include/cedar/3d/coarsen.h:23-62).
 #ifndef CEDAR_3D_COARSEN_H

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/3d/grid_func.h -- 3D grid function with one ghost layer (reference:
 // include/cedar/3d/grid_func.h, src/3d/grid_func.cc).  Norms of device-resident
 // data are reduced on the GPU (deterministic tree).

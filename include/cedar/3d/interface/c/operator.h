@@ -1,3 +1,4 @@
+/* API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root. */
 /* cedar/3d/interface/c/operator.h -- bmg3_operator_* (reference include/cedar/3d/interface/c/operator.h:12-31,
  * src/3d/interface/c/operator.cc): entries are given directly in BoxMG's 14 storage slots (cdr3_dir), off-diagonals
  * signed (stored negated); apply works on packed interior vectors (k outer, then j, i inner). */

@@ -1,3 +1,4 @@
+/* API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root. */
 /* cedar/3d/interface/c/solver.h -- bmg3_solver_* (reference include/cedar/3d/interface/c/solver.h) */
 #ifndef CEDAR_3D_INTERFACE_SOLVER_H
 #define CEDAR_3D_INTERFACE_SOLVER_H

@@ -1,3 +1,4 @@
+/* API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root. */
 /* cedar/3d/interface/c/topo.h -- bmg3_topo_create (reference include/cedar/3d/interface/c/topo.h); see the 2D twin:
  * communicator accepted and ignored, process grid 1 x 1 x 1. */
 #ifndef CEDAR_3D_INTERFACE_TOPO_H

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/3d/interp.h -- CUDA-backed 3D interpolate-and-add and operator-induced
 // interpolation setup (reference interp_f90 / setup_interp_f90: src/3d/interp.cc:17-45,
 // include/cedar/3d/interp.h:20-80).

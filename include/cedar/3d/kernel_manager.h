@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/3d/kernel_manager.h -- builds the serial 3D registry with the CUDA kernels
 // registered (and selected) under "system" (reference src/3d/kernel_manager.cc).
 #ifndef CEDAR_3D_KERNEL_MANAGER_H

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/3d/level_container.h -- level 0 is typed on the fine stencil, every
 // coarser level is 27-point (reference 3d/level_container.h).
 #ifndef CEDAR_3D_LEVEL_CONTAINER_H

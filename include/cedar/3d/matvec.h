@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/3d/matvec.h -- CUDA-backed 3D operator application y = A x (reference matvec_f90 over
 // BMG3_SymStd_UTILS_matvec, include/cedar/3d/mpi/matvec.h: kg = nog, ifd from the stencil type).
 #ifndef CEDAR_3D_MATVEC_H

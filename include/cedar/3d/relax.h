@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/3d/relax.h -- CUDA-backed 3D point relaxation, registered under the same
 // interface as the reference's rbgs (include/cedar/3d/relax.h:22-100): ifd from the
 // stencil type, BMG_RELAX_SYM always, boundary code from kernel_params::per_mask().

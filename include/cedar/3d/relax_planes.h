@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/3d/relax_planes.h -- plane relaxation: zebra over the planes of one direction,
 // each plane "solved" by a 2D BoxMG cycle (reference include/cedar/3d/relax_planes.h:35-261,
 // src/3d/relax_planes.cc).

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/3d/residual.h -- CUDA-backed 3D residual (reference residual_f90,
 // include/cedar/3d/residual.h:16-62: kg = nog = 1, ifd from the stencil type).
 #ifndef CEDAR_3D_RESIDUAL_H

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/3d/restrict.h -- CUDA-backed 3D restriction R = P^T (reference restrict_f90, src/3d/restrict.cc:14-32)
 #ifndef CEDAR_3D_INTER_RESTRICT_H
 #define CEDAR_3D_INTER_RESTRICT_H

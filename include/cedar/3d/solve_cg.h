@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/3d/solve_cg.h -- CUDA-backed coarsest-grid direct solve in 3D (reference
 // solve_cg_f90, include/cedar/3d/solve_cg.h, src/3d/solve_cg.cc).
 #ifndef CEDAR_3D_SOLVE_CG_H

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/3d/solver.h -- cdr3::solver<fsten>: level-count rule, coarse sizes and
 // coarse-solve workspace of the reference (include/cedar/3d/solver.h:18-130),
 // over device-resident levels.

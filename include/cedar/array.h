@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/array.h -- Fortran-ordered ND array with a host mirror and a
 // device-resident buffer.
 //

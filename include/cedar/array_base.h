@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 #ifndef CEDAR_ARRAY_BASE_H
 #define CEDAR_ARRAY_BASE_H
 namespace cedar {

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/config.h -- JSON configuration with dotted-path access, the interface
 // of the reference include/cedar/config.h (get / get-with-default / getvec /
 // set / getconf) over a small built-in JSON reader (no third-party parser).

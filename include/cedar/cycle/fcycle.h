@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/cycle/fcycle.h -- full-multigrid (F) cycle: restrict the right-hand side
 // to the coarsest level, solve, then interpolate up one level at a time running
 // a V-cycle on each (reference: include/cedar/cycle/fcycle.h:35-83).

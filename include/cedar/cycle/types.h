@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/cycle/types.h -- base class of the cycling strategies (reference: cycle/types.h:9-41)
 #ifndef CEDAR_CYCLE_TYPES_H
 #define CEDAR_CYCLE_TYPES_H

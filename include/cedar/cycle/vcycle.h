@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/cycle/vcycle.h -- the V-cycle (reference: include/cedar/cycle/vcycle.h:35-115):
 //   presmooth, residual, restrict, zero coarse x, (coarse solve | recurse),
 //   interpolate-and-add, postsmooth.

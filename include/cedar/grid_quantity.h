@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/grid_quantity.h -- ghost-aware index ranges (reference: grid_quantity.h:15-71)
 #ifndef CEDAR_GRID_QUANTITY_H
 #define CEDAR_GRID_QUANTITY_H

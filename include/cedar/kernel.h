@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/kernel.h -- base of every kernel implementation (reference: kernel.h:11-38)
 #ifndef CEDAR_KERNEL_H
 #define CEDAR_KERNEL_H

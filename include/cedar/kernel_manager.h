@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/kernel_manager.h -- the registry: add<K,Impl>(name), set<K>(name),
 // setup<K>(args...), run<K>(args...), add_halo(ptr).  Reference:
 // include/cedar/kernel_manager.h:11-94.  A missing kernel is logged, not thrown.

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/kernel_params.h -- parameters shared by every registered kernel
 // (reference: include/cedar/kernel_params.h:9-46, src/kernel_params.cc:61-97).
 #ifndef CEDAR_KERNEL_PARAMS_H

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/kernel_registry.h -- the kernel type lists (reference: kernel_registry.h:24-48).
 #ifndef CEDAR_KERNEL_REGISTRY_H
 #define CEDAR_KERNEL_REGISTRY_H

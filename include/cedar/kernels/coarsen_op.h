@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/kernels/coarsen_op.h -- abstract kernel interface `kernels::coarsen_op`.
 // Signatures follow the reference include/cedar/kernels/coarsen_op.h (l.23-40); an
 // implementation overrides the overloads it supports, anything left out logs

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/kernels/interp_add.h -- abstract kernel interface `kernels::interp_add`.
 // Signatures follow the reference include/cedar/kernels/interp_add.h (l.17-20); an
 // implementation overrides the overloads it supports, anything left out logs

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/kernels/line_relax.h -- abstract kernel interface `kernels::line_relax`.
 // Signatures follow the reference include/cedar/kernels/line_relax.h (l.22-39); an
 // implementation overrides the overloads it supports, anything left out logs

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/kernels/matvec.h -- abstract kernel interface `kernels::matvec`.
 // Signatures follow the reference include/cedar/kernels/matvec.h (l.17-24); an
 // implementation overrides the overloads it supports, anything left out logs

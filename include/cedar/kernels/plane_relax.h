@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/kernels/plane_relax.h -- abstract kernel interface `kernels::plane_relax`.
 // Signatures follow the reference include/cedar/kernels/plane_relax.h (l.21-31); an
 // implementation overrides the overloads it supports, anything left out logs

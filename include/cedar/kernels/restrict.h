@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/kernels/restrict.h -- abstract kernel interface `kernels::restriction`.
 // Signatures follow the reference include/cedar/kernels/restrict.h (l.17-19); an
 // implementation overrides the overloads it supports, anything left out logs

@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/kernels/setup_interp.h -- abstract kernel interface `kernels::setup_interp`.
 // Signatures follow the reference include/cedar/kernels/setup_interp.h (l.30-47); an
 // implementation overrides the overloads it supports, anything left out logs

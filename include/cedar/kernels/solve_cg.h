@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/kernels/solve_cg.h -- abstract kernel interface `kernels::solve_cg`.
 // Signatures follow the reference include/cedar/kernels/solve_cg.h (l.20-28); an
 // implementation overrides the overloads it supports, anything left out logs

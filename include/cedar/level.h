@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/level.h -- what a multilevel solve stores per level (reference: level.h:15-41)
 #ifndef CEDAR_LEVEL_H
 #define CEDAR_LEVEL_H

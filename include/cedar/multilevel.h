@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/multilevel.h -- generic multilevel driver (reference:
 // include/cedar/multilevel.h:26-322).  It only names kernel *types* and talks to
 // the registry (kman->setup<K> / kman->run<K>), so the CUDA-backed kernels plug

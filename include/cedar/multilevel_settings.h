@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/multilevel_settings.h -- solver settings read from the JSON config
 // (reference: include/cedar/multilevel_settings.h, src/multilevel_settings.cc:15-61).
 #ifndef CEDAR_MULTILEVEL_SETTINGS_H

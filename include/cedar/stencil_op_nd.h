@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/stencil_op_nd.h -- structured-grid stencil operator: array of shape
 // (n0+2, ..., n_{nd-1}+2, ndirs), i.e. structure-of-arrays by stencil direction
 // (reference: stencil_op_nd.h:41-78).  Symmetric storage: a point stores its

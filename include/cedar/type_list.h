@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/type_list.h -- type_list / type_cat / type_map: one name->implementation
 // map per kernel interface plus the name of the current default.  Same public
 // members as the reference (type_list.h:36-124: kerns, defaults, get_ptr, get,

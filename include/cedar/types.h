@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/types.h -- basic types of the B200-native Cedar host layer.
 // Mirrors the public names of the reference include/cedar/types.h:23-95
 // (len_t, real_t, exec_mode, relax_dir, cycle::Dir, range()) without Boost.

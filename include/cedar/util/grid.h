@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/util/grid.h -- evenly spaced sample points (reference: include/cedar/util/grid.h,
 // src/util/grid.cc).  Only the examples include this header.
 #ifndef CEDAR_UTIL_GRID_H

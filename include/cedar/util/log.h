@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/util/log.h -- levelled logging (status, info, error, debug, memory,
 // timer) selected by the "log" key of the JSON config, like the reference's
 // include/cedar/util/log.h; errors are reported, never thrown.

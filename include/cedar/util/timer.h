@@ -1,3 +1,4 @@
+// API surface after Cedar (c) 2016-2017 Cedar Developers, BSD-3-Clause -- see NOTICE at the repository root.
 // cedar/util/timer.h -- named timing regions.  The reference keeps hierarchical
 // MPI wall-clock timers (include/cedar/util/time_log.h); here a region is a pair
 // of host time stamps around enqueued GPU work, recorded only when the "timer"
