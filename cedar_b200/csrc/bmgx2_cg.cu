@@ -82,6 +82,13 @@ __global__ void __launch_bounds__(256) k_dpbtf2_upper(int n, int kd, double *abd
     if (threadIdx.x == 0) { g_cg_info = s_bad; if (info) *info = s_bad; }
 }
 
+int *bmgx_cg_info_ptr()
+{
+    int *p = nullptr;
+    cudaGetSymbolAddress((void **)&p, g_cg_info);
+    return p;
+}
+
 extern "C" int bmgx_cg_LU_info(int *info, bmgx_stream_t s)
 {
     cudaError_t e = cudaStreamSynchronize((cudaStream_t)s);
@@ -98,7 +105,7 @@ extern "C" int bmgx_cg_LU_info(int *info, bmgx_stream_t s)
 extern "C" int bmgx2_SETUP_cg_LU(const double *so, bmgx_len ii, bmgx_len jj, int nstncl, double *abd,
                                  bmgx_len nabd1, bmgx_len nabd2, int ibc, bmgx_stream_t s)
 {
-    if (!bmgx_nonperiodic(ibc)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SETUP_cg_LU: periodic BCs not supported");
+    if (!bmgx_nonperiodic(ibc)) return bmgx2_periodic_cg_lu(so, ii, jj, nstncl, abd, nabd1, nabd2, ibc, s);
     if (ii < 3 || jj < 3) return bmgx_set_error(BMGX_ERR_ARG, "SETUP_cg_LU: empty grid");
     unsigned n = (ii - 2) * (jj - 2);
     if (nabd1 < ii || nabd2 < n) return bmgx_set_error(BMGX_ERR_ARG, "SETUP_cg_LU: ABD too small");
@@ -153,7 +160,11 @@ extern "C" int bmgx2_SOLVE_cg(double *q, const double *qf, bmgx_len ii, bmgx_len
                               bmgx_len nabd1, bmgx_len nabd2, int jpn, bmgx_stream_t s)
 {
     (void)nabd2;
-    if (jpn != BMGX_BCs_definite) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SOLVE_cg: only definite, non-periodic");
+    {
+        const int ipn = jpn < 0 ? -jpn : jpn;
+        if (ipn >= 1 && ipn <= 3) return bmgx2_periodic_solve_cg(q, qf, ii, jj, abd, bbd, nabd1, jpn, s);
+    }
+    if (jpn != BMGX_BCs_definite) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SOLVE_cg: indefinite non-periodic not supported");
     launch_pdl(k_solve_cg, dim3(bmgx_batch()), dim3(32), 0, (cudaStream_t)s, q, qf, ii, jj, abd, bbd, nabd1);
     BMGX_LAUNCH_CHECK("SOLVE_cg");
     return BMGX_OK;

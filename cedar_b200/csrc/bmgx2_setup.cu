@@ -110,7 +110,10 @@ k_interp_centres(const double *__restrict__ so, double *ci, unsigned IIF, unsign
 static int interp_oi_stages(const double *so, double *ci, bmgx_len IIF, bmgx_len JJF, bmgx_len IIC, bmgx_len JJC, int ifd,
                             int jpn, unsigned stages, bmgx_stream_t s)
 {
-    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SETUP_interp_OI: periodic BCs not supported");
+    if (!bmgx_nonperiodic(jpn)) {
+        if (stages != 3u) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SETUP_interp_OI_stage: periodic BCs not supported on the decomposed path");
+        return bmgx2_periodic_interp_oi(so, ci, IIF, JJF, IIC, JJC, ifd, jpn, s);
+    }
     if (IIC < 3 || JJC < 3) return BMGX_OK;
     unsigned IICF1 = (IIF - 2) / 2 + 2, JJCF1 = (JJF - 2) / 2 + 2;
     cudaStream_t st = (cudaStream_t)s;

@@ -58,6 +58,14 @@ __device__ __forceinline__ void pdl_wait()
 int bmgx_wrap_x(double *q, unsigned ii, unsigned jbeg, unsigned jstep, unsigned nrow, cudaStream_t st);
 int bmgx_wrap_y(double *q, unsigned ii, unsigned jj, cudaStream_t st);
 
+// periodic branches of the interpolation setup and the coarsest-grid solve (bmgx2_periodic.cu)
+int bmgx2_periodic_interp_oi(const double *so, double *ci, bmgx_len IIF, bmgx_len JJF, bmgx_len IIC, bmgx_len JJC, int ifd,
+                             int jpn, bmgx_stream_t s);
+int bmgx2_periodic_cg_lu(const double *so, bmgx_len ii, bmgx_len jj, int nstncl, double *abd, bmgx_len nabd1, bmgx_len nabd2,
+                         int ibc, bmgx_stream_t s);
+int bmgx2_periodic_solve_cg(double *q, const double *qf, bmgx_len ii, bmgx_len jj, const double *abd, double *bbd, bmgx_len nabd1,
+                            int jpn, bmgx_stream_t s);
+
 static inline bool bmgx_nonperiodic(int jpn) { return jpn == BMGX_BCs_definite || jpn == BMGX_BCs_indef_nonper; }
 static inline unsigned cdiv(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
 

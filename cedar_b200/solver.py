@@ -99,7 +99,7 @@ def gpu_launches():
 
 
 def make_config(relaxation="point", nrelax_pre=2, nrelax_post=1, maxiter=10, tol=1e-8, num_levels=None,
-                cycle="v", cuda_graph=True, log=("error",), coarse_tail=None):
+                cycle="v", cuda_graph=True, log=("error",), coarse_tail=None, periodic=None):
     conf = {"log": list(log),
             "solver": {"relaxation": relaxation, "cycle": {"type": cycle, "nrelax-pre": nrelax_pre, "nrelax-post": nrelax_post},
                        "max-iter": maxiter, "tol": tol, "cuda-graph": bool(cuda_graph)}}
@@ -107,6 +107,8 @@ def make_config(relaxation="point", nrelax_pre=2, nrelax_post=1, maxiter=10, tol
         conf["solver"]["num-levels"] = int(num_levels)
     if coarse_tail is not None:
         conf["solver"]["coarse-tail"] = int(coarse_tail)
+    if periodic is not None:
+        conf["grid"] = {"periodic": [bool(p) for p in periodic]}
     return json.dumps(conf)
 
 

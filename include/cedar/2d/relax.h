@@ -39,6 +39,14 @@ public:
 		int updown = cdir == cycle::Dir::UP ? BMGX_UP : BMGX_DOWN;
 		int ibc;
 		bmgx_get_bc(params->per_mask(), &ibc);
+		if (ibc != BMGX_BCs_definite && ibc != BMGX_BCs_indef_nonper) {
+			// periodic boundaries: the in-place reference form, which refreshes the ghost columns after every colour
+			// and the ghost rows after the sweep (BMG2_SymStd_relax_GS.f90:139-224); the fused single-pass sweep has
+			// no periodic form
+			gpu::check(bmgx2_relax_GS(1, so.cdev(), b.cdev(), x.dev(), sor.cdev(), so.len(0), so.len(1), 1, ifd,
+			                          stencil_ndirs<sten>::value, 2, BMGX_RELAX_SYM, updown, ibc, gpu::stream()), "relax_GS");
+			return;
+		}
 		// one pass over memory for all colours: relax out of place into a scratch
 		// array of the same shape, then exchange the two device buffers (x keeps
 		// its identity on the host side; its device pointer alternates)

@@ -93,12 +93,16 @@ class Solver2:
     """Mirror of cdr2::solver<fsten> on the CPU oracle."""
 
     def __init__(self, so, relaxation="point", nrelax_pre=2, nrelax_post=1,
-                 num_levels=-1, min_coarse=3, cycle="v"):
+                 num_levels=-1, min_coarse=3, cycle="v", periodic=(False, False)):
         self.so = np.ascontiguousarray(so)
         nst, jj, ii = self.so.shape
         self.nx, self.ny = ii - 2, jj - 2
-        self.h = lib().orc2_solver_create(P(self.so), self.nx, self.ny, nst, RELAX[relaxation],
-                                          nrelax_pre, nrelax_post, num_levels, min_coarse)
+        lib().orc2_solver_create_per.restype = C.c_void_p
+        self.h = lib().orc2_solver_create_per(P(self.so), self.nx, self.ny, nst, RELAX[relaxation],
+                                              nrelax_pre, nrelax_post, num_levels, min_coarse,
+                                              int(bool(periodic[0])) + 2 * int(bool(periodic[1])))
+        if not self.h:
+            raise ValueError("periodic boundary conditions: point relaxation only")
         self.h = C.c_void_p(self.h)
         self.nlevels = lib().orc2_solver_nlevels(self.h)
         if cycle == "f":       # include/cedar/cycle/fcycle.h

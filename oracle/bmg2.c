@@ -428,13 +428,176 @@ int orc2_interp_add(double *q, const double *qc, double *res, const double *so, 
 static inline double oi_min2(double a, double b) { return a < b ? a : b; }
 static inline double oi_max2(double a, double b) { return a > b ? a : b; }
 
+/* ------------------------------------------------------------------------
+ * BMG2_SymStd_SETUP_interp_OI.f90:258-618, periodic boundary conditions (|jpn| = 1: y, 2: x, 3: both).
+ * Same weights as the non-periodic loops; what changes is which fine lines feed which coarse lines: the fine index
+ * of coarse index IC is produced by the reference's running update I = MAX(MOD(I+2,IIFC), MIN(I+2,3)) starting from
+ * IBEG (l.296-317: periodic directions start one coarse line earlier and may run one further), and the edge weights
+ * of the first and last coarse lines (CI(.,1,.), CI(.,JJC,.), CI(1,.,.), CI(IIC,.,.)) are computed from the wrapped
+ * fine lines (l.343-373, 394-425).  Loop structure and statement order are the reference's.
+ * ---------------------------------------------------------------------- */
+#define OI_SO(i, j, kk) A3(so, IIF, JJF, i, j, kk)
+static inline void oi_edge_x(const double *so, int IIF, int JJF, int i, int j, int nine, double *lr, double *ll)
+{
+    const double ZEPS = DBL_EPSILON;
+    double a, b;
+    if (nine) {
+        a = OI_SO(i, j, KW) + OI_SO(i, j, KNW) + OI_SO(i, j + 1, KSW);
+        b = OI_SO(i - 1, j, KW) + OI_SO(i - 1, j, KSW) + OI_SO(i - 1, j + 1, KNW);
+    } else {
+        a = OI_SO(i, j, KW);
+        b = OI_SO(i - 1, j, KW);
+    }
+    double ep = oi_min2(fabs(a / OI_SO(i - 1, j, KO)), fabs(b / OI_SO(i - 1, j, KO)));
+    double sum = a + b + OI_SO(i - 1, j, KS) + OI_SO(i - 1, j + 1, KS);
+    sum = a + b + (OI_SO(i - 1, j, KO) - sum) * oi_max2(OI_SO(i - 1, j, KO) - (1.0 + ep) * sum, 0.0)
+                      / (fabs(OI_SO(i - 1, j, KO) - (1.0 + ep) * sum) + ZEPS);
+    sum = 1.0 / sum;
+    *lr = a * sum;
+    *ll = b * sum;
+}
+static inline void oi_edge_y(const double *so, int IIF, int JJF, int i, int j, int nine, double *la, double *lb)
+{
+    const double ZEPS = DBL_EPSILON;
+    double a, b;
+    if (nine) {
+        a = OI_SO(i, j, KS) + OI_SO(i, j, KNW) + OI_SO(i + 1, j, KSW);
+        b = OI_SO(i, j - 1, KS) + OI_SO(i, j - 1, KSW) + OI_SO(i + 1, j - 1, KNW);
+    } else {
+        a = OI_SO(i, j, KS);
+        b = OI_SO(i, j - 1, KS);
+    }
+    /* the nine-point branch forms SUM before EP, the five-point branch EP before SUM (l.383-384 / 533-534): no
+     * dependence between the two statements */
+    double sum = a + b + OI_SO(i, j - 1, KW) + OI_SO(i + 1, j - 1, KW);
+    double ep = oi_min2(fabs(a / OI_SO(i, j - 1, KO)), fabs(b / OI_SO(i, j - 1, KO)));
+    sum = a + b + (OI_SO(i, j - 1, KO) - sum) * oi_max2(OI_SO(i, j - 1, KO) - (1.0 + ep) * sum, 0.0)
+                      / (fabs(OI_SO(i, j - 1, KO) - (1.0 + ep) * sum) + ZEPS);
+    sum = 1.0 / sum;
+    *la = a * sum;
+    *lb = b * sum;
+}
+static inline int oi_next(int i, int nfc) { int t = (i + 2) % nfc, m = i + 2 < 3 ? i + 2 : 3; return t > m ? t : m; }
+
+static int oi_periodic(const double *so, double *ci, int IIF, int JJF, int IIC, int JJC, int ifd, int ipn)
+{
+    const double ZEPS = DBL_EPSILON;
+    const int nine = ifd != 1;
+    const int IIC1 = IIC - 1, JJC1 = JJC - 1, IIF1 = IIF - 1, IIF2 = IIF - 2, JJF1 = JJF - 1, JJF2 = JJF - 2;
+    const int IICF = (IIF - 2) / 2 + 3, JJCF = (JJF - 2) / 2 + 3, IICF1 = IICF - 1, JJCF1 = JJCF - 1;
+    const int IIFC = 2 * (IICF - 2) + 2, JJFC = 2 * (JJCF - 2) + 2;
+    const int perx = (ipn == 2 || ipn == 3), pery = (ipn == 1 || ipn == 3);
+    int IBEG = 2, IBEGC = 3, IBEG_x = 2, IEND_x = IIF2, IENDC = IICF1, JENDC = JJCF1;
+    if (perx) {
+        IBEG = 0; IBEGC = 2;
+        if (IIC == IICF) { IENDC = IICF; IBEG_x = 3; IEND_x = IIF1; }
+    }
+    int JBEG = 2, JBEGC = 3, JBEG_y = 2, JEND_y = JJF2;
+    if (pery) {
+        JBEG = 0; JBEGC = 2;
+        if (JJC == JJCF) { JENDC = JJCF; JBEG_y = 3; JEND_y = JJF1; }
+    }
+#define CI(i, j, kk) A3(ci, IIC, JJC, i, j, kk)
+    int i, j;
+    /* x-edge weights LR, LL (l.322-340 / 475-492) */
+    j = 0;
+    for (int jc = 2; jc <= JJC1; jc++) {
+        j += 2;
+        i = IBEG;
+        for (int ic = IBEGC; ic <= IENDC; ic++) {
+            i = oi_next(i, IIFC);
+            oi_edge_x(so, IIF, JJF, i, j, nine, &CI(ic, jc, LR), &CI(ic, jc, LL));
+        }
+    }
+    if (pery) {   /* l.343-373 / 495-524: the last and first coarse lines from the wrapped fine lines */
+        i = IBEG; j = JBEG_y;
+        for (int ic = IBEGC; ic <= IENDC; ic++) {
+            i = oi_next(i, IIFC);
+            oi_edge_x(so, IIF, JJF, i, j, nine, &CI(ic, JJC, LR), &CI(ic, JJC, LL));
+        }
+        i = IBEG; j = JEND_y;
+        for (int ic = IBEGC; ic <= IENDC; ic++) {
+            i = oi_next(i, IIFC);
+            oi_edge_x(so, IIF, JJF, i, j, nine, &CI(ic, 1, LR), &CI(ic, 1, LL));
+        }
+    }
+    /* y-edge weights LA, LB (l.375-392 / 527-544) */
+    j = JBEG;
+    for (int jc = JBEGC; jc <= JENDC; jc++) {
+        j = oi_next(j, JJFC);
+        i = 0;
+        for (int ic = 2; ic <= IIC1; ic++) {
+            i += 2;
+            oi_edge_y(so, IIF, JJF, i, j, nine, &CI(ic, jc, LA), &CI(ic, jc, LB));
+        }
+    }
+    if (perx) {   /* l.394-425 / 546-577 */
+        i = IBEG_x; j = JBEG;
+        for (int jc = JBEGC; jc <= JENDC; jc++) {
+            j = oi_next(j, JJFC);
+            oi_edge_y(so, IIF, JJF, i, j, nine, &CI(IIC, jc, LA), &CI(IIC, jc, LB));
+        }
+        i = IEND_x; j = JBEG;
+        for (int jc = JBEGC; jc <= JENDC; jc++) {
+            j = oi_next(j, JJFC);
+            oi_edge_y(so, IIF, JJF, i, j, nine, &CI(1, jc, LA), &CI(1, jc, LB));
+        }
+    }
+    /* cell-centre weights (l.428-464 / 579-606) */
+    j = JBEG;
+    for (int jc = JBEGC; jc <= JENDC; jc++) {
+        j = oi_next(j, JJFC);
+        i = IBEG;
+        for (int ic = IBEGC; ic <= IENDC; ic++) {
+            i = oi_next(i, IIFC);
+            double sum, ep, o = OI_SO(i - 1, j - 1, KO);
+            if (nine) {
+                sum = OI_SO(i - 1, j - 1, KW) + OI_SO(i - 1, j, KNW) + OI_SO(i - 1, j, KS) + OI_SO(i, j, KSW)
+                      + OI_SO(i, j - 1, KW) + OI_SO(i, j - 1, KNW) + OI_SO(i - 1, j - 1, KS) + OI_SO(i - 1, j - 1, KSW);
+                ep = oi_min2(oi_min2(fabs((OI_SO(i - 1, j - 1, KSW) + OI_SO(i - 1, j - 1, KW) + OI_SO(i - 1, j, KNW)) / o),
+                                     fabs((OI_SO(i - 1, j, KNW) + OI_SO(i - 1, j, KS) + OI_SO(i, j, KSW)) / o)),
+                             oi_min2(fabs((OI_SO(i, j, KSW) + OI_SO(i, j - 1, KW) + OI_SO(i, j - 1, KNW)) / o),
+                                     fabs((OI_SO(i, j - 1, KNW) + OI_SO(i - 1, j - 1, KS) + OI_SO(i - 1, j - 1, KSW)) / o)));
+            } else {
+                sum = OI_SO(i - 1, j - 1, KW) + OI_SO(i - 1, j, KS) + OI_SO(i, j - 1, KW) + OI_SO(i - 1, j - 1, KS);
+                ep = oi_min2(oi_min2(fabs(OI_SO(i - 1, j - 1, KW) / o), fabs(OI_SO(i - 1, j, KS) / o)),
+                             oi_min2(fabs(OI_SO(i, j - 1, KW) / o), fabs(OI_SO(i - 1, j - 1, KS) / o)));
+            }
+            sum = sum + (o - sum) * oi_max2(o - (1.0 + ep) * sum, 0.0) / (fabs(o - (1.0 + ep) * sum) + ZEPS);
+            double s = 1.0 / sum;
+            if (nine) {
+                CI(ic, jc, LSW) = (OI_SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LL) + OI_SO(i - 1, j - 1, KW) * CI(ic - 1, jc, LB)
+                                   + OI_SO(i - 1, j - 1, KSW)) * s;
+                CI(ic, jc, LSE) = (OI_SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LR) + OI_SO(i, j - 1, KW) * CI(ic, jc, LB)
+                                   + OI_SO(i, j - 1, KNW)) * s;
+                CI(ic, jc, LNW) = (OI_SO(i - 1, j - 1, KW) * CI(ic - 1, jc, LA) + OI_SO(i - 1, j, KS) * CI(ic, jc, LL)
+                                   + OI_SO(i - 1, j, KNW)) * s;
+                CI(ic, jc, LNE) = (OI_SO(i - 1, j, KS) * CI(ic, jc, LR) + OI_SO(i, j - 1, KW) * CI(ic, jc, LA)
+                                   + OI_SO(i, j, KSW)) * s;
+            } else {
+                CI(ic, jc, LSW) = (OI_SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LL) + OI_SO(i - 1, j - 1, KW) * CI(ic - 1, jc, LB)) * s;
+                CI(ic, jc, LSE) = (OI_SO(i - 1, j - 1, KS) * CI(ic, jc - 1, LR) + OI_SO(i, j - 1, KW) * CI(ic, jc, LB)) * s;
+                CI(ic, jc, LNW) = (OI_SO(i - 1, j - 1, KW) * CI(ic - 1, jc, LA) + OI_SO(i - 1, j, KS) * CI(ic, jc, LL)) * s;
+                CI(ic, jc, LNE) = (OI_SO(i - 1, j, KS) * CI(ic, jc, LR) + OI_SO(i, j - 1, KW) * CI(ic, jc, LA)) * s;
+            }
+        }
+    }
+    return 0;
+#undef CI
+}
+#undef OI_SO
+
 static int oi_stage_mask = 3;   /* bit 0: edge weights, bit 1: cell-centre weights */
 int orc2_setup_interp_oi(const double *so, const double *soc, double *ci,
                          int IIF, int JJF, int IIC, int JJC, int ifd, int nstncl,
                          int jpn, int irelax)
 {
     (void)soc; (void)nstncl; (void)irelax;
-    if (jpn != 0 && jpn != -4) return -1;
+    if (jpn != 0 && jpn != -4) {
+        const int ipn = jpn < 0 ? -jpn : jpn;
+        if (ipn < 1 || ipn > 3) return -1;
+        return oi_periodic(so, ci, IIF, JJF, IIC, JJC, ifd, ipn);
+    }
     const double ZEPS = DBL_EPSILON; /* EPSILON(1.D0), l.78 */
     int IIC1 = IIC - 1, JJC1 = JJC - 1;
     int IICF = (IIF - 2) / 2 + 3, JJCF = (JJF - 2) / 2 + 3;
@@ -923,6 +1086,130 @@ int orc2_relax_lines_y(int k, const double *so, const double *qf, double *q, con
 #undef SOR
 }
 
+/* LAPACK DPOTRF('U') as its unblocked kernel DPOTF2: for every column j the diagonal minus DDOT of the column above
+ * it, square root, then row j of U right of the diagonal by DGEMV('Transpose') and DSCAL.  (LAPACK's blocked path
+ * sums in another order for n > NB; the reference pins no LAPACK, see DESIGN.md "Oracle".)  Returns INFO. */
+int orc_dpotf2_upper(int n, double *a, int lda)
+{
+#define AA(i, j) a[(size_t)((j)-1) * lda + ((i)-1)]
+    for (int j = 1; j <= n; j++) {
+        double dot = 0.0;
+        for (int k = 1; k <= j - 1; k++) dot = dot + AA(k, j) * AA(k, j);
+        double ajj = AA(j, j) - dot;
+        if (ajj <= 0.0 || ajj != ajj) { AA(j, j) = ajj; return j; }
+        ajj = sqrt(ajj);
+        AA(j, j) = ajj;
+        if (j < n) {
+            /* DGEMV('T', j-1, n-j, -1, A(1,j+1), lda, A(1,j), 1, 1, A(j,j+1), lda): y(c) = y(c) + (-1) * (column . x) */
+            for (int c = j + 1; c <= n; c++) {
+                double temp = 0.0;
+                for (int k = 1; k <= j - 1; k++) temp = temp + AA(k, c) * AA(k, j);
+                AA(j, c) = AA(j, c) + (-1.0) * temp;
+            }
+            double r = 1.0 / ajj;
+            for (int c = j + 1; c <= n; c++) AA(j, c) = r * AA(j, c);
+        }
+    }
+    return 0;
+#undef AA
+}
+
+/* LAPACK DPOTRS('U', n, 1): DTRSM('L','U','T','N') then DTRSM('L','U','N','N') in the reference BLAS loop order */
+void orc_dpotrs_upper(int n, const double *a, int lda, double *b)
+{
+#define AA(i, j) a[(size_t)((j)-1) * lda + ((i)-1)]
+    for (int i = 1; i <= n; i++) {
+        double temp = b[i - 1];
+        for (int k = 1; k <= i - 1; k++) temp = temp - AA(k, i) * b[k - 1];
+        temp = temp / AA(i, i);
+        b[i - 1] = temp;
+    }
+    for (int k = n; k >= 1; k--) {
+        if (b[k - 1] != 0.0) {
+            b[k - 1] = b[k - 1] / AA(k, k);
+            for (int i = 1; i <= k - 1; i++) b[i - 1] = b[i - 1] - b[k - 1] * AA(i, k);
+        }
+    }
+#undef AA
+}
+
+/* BMG2_SymStd_SETUP_cg_LU.f90:144-217 (9-pt) / 258-331 (5-pt): periodic in x, y or both -- the operator of the
+ * coarsest grid as a DENSE upper triangle ABD(N,N) (the wrap-around couplings leave the band), DPOTRF('U') */
+static int cg_lu_periodic(const double *so, int II, int JJ, int nstncl, double *abd, int nabd1, int nabd2, int ibc)
+{
+    const int ipn = ibc < 0 ? -ibc : ibc;
+    const int perx = (ipn == 2 || ipn == 3), pery = (ipn == 1 || ipn == 3), perxy = ipn == 3;
+    const int nine = nstncl == 5;
+    int I1 = II - 1, J1 = JJ - 1, I2 = I1 - 1, N = I2 * (J1 - 1);
+    if (nabd1 < N || nabd2 < N) return -2;
+#define SO(i, j, kq) A3(so, II, JJ, i, j, kq)
+#define ABD(i, j) abd[(size_t)((j)-1) * nabd1 + ((i)-1)]
+#define NSO(i, j, kq) (nine ? -SO(i, j, kq) : 0.0)   /* the five-point branch stores rZERO where the nine-point one has a corner coupling */
+    if (ibc == -3 && II == 4 && JJ == 4 && nine) {
+        /* l.121-143: periodic in both directions, four computational nodes */
+        ABD(1, 1) = SO(2, 2, KO);
+        ABD(2, 2) = SO(3, 2, KO);
+        ABD(1, 2) = -SO(2, 2, KW) - SO(3, 2, KW);
+        ABD(3, 3) = SO(2, 3, KO);
+        ABD(1, 3) = -SO(2, 2, KS) - SO(2, 3, KS);
+        ABD(2, 3) = -SO(3, 3, KNW) - SO(4, 2, KNW) - SO(4, 3, KSW) - SO(3, 2, KSW);
+        ABD(4, 4) = SO(3, 3, KO);
+        ABD(1, 4) = -SO(3, 3, KSW) - SO(2, 2, KSW) - SO(2, 3, KNW) - SO(3, 2, KNW);
+        ABD(2, 4) = -SO(3, 2, KS) - SO(3, 3, KS);
+        ABD(3, 4) = -SO(2, 3, KW) - SO(3, 3, KW);
+        ABD(4, 4) = ABD(4, 4) + SO(4, 4, KO);
+        return orc_dpotf2_upper(N, abd, nabd1);
+    }
+    int kk = 1, j;
+    ABD(1, 1) = SO(2, 2, KO);
+    for (int i = 3; i <= I1; i++) {
+        kk++;
+        ABD(kk, kk) = SO(i, 2, KO);
+        ABD(kk - 1, kk) = -SO(i, 2, KW);
+    }
+    if (perx) ABD(kk - I2 + 1, kk) = -SO(II, 2, KW);
+    for (j = 3; j <= J1; j++) {
+        if (perx) ABD(kk, kk + 1) = NSO(2, j, KSW);
+        for (int i = 2; i <= I1; i++) {
+            kk++;
+            ABD(kk, kk) = SO(i, j, KO);
+            if (i != 2) {
+                ABD(kk - 1, kk) = -SO(i, j, KW);
+                ABD(kk - I2 - 1, kk) = NSO(i, j, KSW);
+            }
+            ABD(kk - I2 + 1, kk) = NSO(i + 1, j, KNW);
+            ABD(kk - I2, kk) = -SO(i, j, KS);
+        }
+        if (perx) {
+            ABD(kk - I2 + 1, kk) = -SO(II, j, KW);
+            ABD(kk - 2 * I2 + 1, kk) = NSO(II, j, KNW);
+        }
+    }
+    /* the Fortran DO leaves J = J1 + 1 behind; SO(II,J1,KNW) below is written with J1 explicitly (l.209) */
+    if (pery) {
+        kk = kk - I2;
+        int J2 = (J1 - 2) * I2;
+        kk++;
+        ABD(kk - J2, kk) = -SO(2, JJ, KS);
+        ABD(kk - J2 + 1, kk) = NSO(3, JJ, KSW);
+        if (perxy) ABD(I2, kk) = NSO(2, JJ, KNW);
+        for (int i = 3; i <= I1; i++) {
+            kk++;
+            ABD(kk - J2, kk) = -SO(i, JJ, KS);
+            ABD(kk - J2 - 1, kk) = NSO(i, JJ, KNW);
+            ABD(kk - J2 + 1, kk) = NSO(i + 1, JJ, KSW);
+        }
+        ABD(kk - J2 + 1, kk) = 0.0;
+        if (perxy) ABD(1, kk) = NSO(II, JJ, KSW);
+        if (perx) ABD(kk - 2 * I2 + 1, kk) = NSO(II, J1, KNW);
+    }
+    if (ibc < 0) ABD(kk, kk) = ABD(kk, kk) + SO(I1, J1, KO);
+    return orc_dpotf2_upper(N, abd, nabd1);
+#undef SO
+#undef ABD
+#undef NSO
+}
+
 /* ------------------------------------------------------------------------
  * BMG2_SymStd_SETUP_cg_LU.f90:92-118 (9-pt) / 236-256 (5-pt), definite,
  * non-periodic.  ABD(NABD1,NABD2), NABD1 = II.
@@ -930,7 +1217,7 @@ int orc2_relax_lines_y(int k, const double *so, const double *qf, double *q, con
 int orc2_setup_cg_lu(const double *so, int II, int JJ, int nstncl,
                      double *abd, int nabd1, int nabd2, int ibc)
 {
-    if (ibc != 0 && ibc != -4) return -1;
+    if (ibc != 0 && ibc != -4) return cg_lu_periodic(so, II, JJ, nstncl, abd, nabd1, nabd2, ibc);
     int I1 = II - 1, J1 = JJ - 1, I2 = I1 - 1;
     int N = I2 * (J1 - 1);
     int kk = 0;
@@ -957,15 +1244,38 @@ int orc2_solve_cg(double *q, const double *qf, int II, int JJ,
                   const double *abd, double *bbd, int nabd1, int nabd2, int jpn)
 {
     (void)nabd2;
-    if (jpn != 0) return -1;
+    const int ipn = jpn < 0 ? -jpn : jpn;
+    if (ipn > 4) return -1;
+    const int periodic = ipn >= 1 && ipn <= 3;
     int I1 = II - 1, J1 = JJ - 1;
     int kk = 0;
     for (int j = 2; j <= J1; j++)
         for (int i = 2; i <= I1; i++) bbd[kk++] = A2(qf, II, i, j);
-    orc_dpbtrs_upper(kk, I1, abd, nabd1, bbd);
+    if (!periodic) orc_dpbtrs_upper(kk, I1, abd, nabd1, bbd);
+    else orc_dpotrs_upper(kk, abd, nabd1, bbd);          /* SOLVE_cg.f90:104-110 */
     kk = 0;
     for (int j = 2; j <= J1; j++)
         for (int i = 2; i <= I1; i++) A2(q, II, i, j) = bbd[kk++];
+    if (jpn != 0) {
+        /* SOLVE_cg.f90:125-143: subtract the mean (every boundary code but "definite, non-periodic") */
+        double cint = 0.0, qint = 0.0;
+        for (int j = 2; j <= J1; j++)
+            for (int i = 2; i <= I1; i++) { qint = qint + A2(q, II, i, j); cint = cint + 1; }
+        double c = -qint / cint;
+        for (int j = 2; j <= J1; j++)
+            for (int i = 2; i <= I1; i++) A2(q, II, i, j) = A2(q, II, i, j) + c;
+    }
+    /* SOLVE_cg.f90:145-166: ghost layer of the solution */
+    if (ipn == 1 || ipn == 3)
+        for (int i = 2; i <= I1; i++) { A2(q, II, i, JJ) = A2(q, II, i, 2); A2(q, II, i, 1) = A2(q, II, i, J1); }
+    if (ipn == 2 || ipn == 3)
+        for (int j = 2; j <= J1; j++) { A2(q, II, II, j) = A2(q, II, 2, j); A2(q, II, 1, j) = A2(q, II, I1, j); }
+    if (ipn == 3) {
+        A2(q, II, 1, 1) = A2(q, II, I1, J1);
+        A2(q, II, II, 1) = A2(q, II, 2, J1);
+        A2(q, II, 1, JJ) = A2(q, II, I1, 2);
+        A2(q, II, II, JJ) = A2(q, II, 2, 2);
+    }
     return 0;
 }
 

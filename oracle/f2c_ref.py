@@ -58,8 +58,9 @@ void dpbtrf_(char *uplo, int *n, int *kd, double *ab, int *ldab, int *info)
 { (void)uplo; *info = orc_dpbtf2_upper(*n, *kd, ab, *ldab); }
 void dpbtrs_(char *uplo, int *n, int *kd, int *nrhs, double *ab, int *ldab, double *b, int *ldb, int *info)
 { (void)uplo; for (int r = 0; r < *nrhs; r++) orc_dpbtrs_upper(*n, *kd, ab, *ldab, b + (size_t)r * *ldb); *info = 0; }
-void dpotrf_() { fprintf(stderr, "bmgref: DPOTRF (periodic coarse solve) not bound\n"); abort(); }
-void dpotrs_() { fprintf(stderr, "bmgref: DPOTRS (periodic coarse solve) not bound\n"); abort(); }
+void dpotrf_(char *uplo, int *n, double *a, int *lda, int *info) { (void)uplo; *info = orc_dpotf2_upper(*n, a, *lda); }
+void dpotrs_(char *uplo, int *n, int *nrhs, double *a, int *lda, double *b, int *ldb, int *info)
+{ (void)uplo; for (int r = 0; r < *nrhs; r++) orc_dpotrs_upper(*n, a, *lda, b + (size_t)r * *ldb); *info = 0; }
 void print_error(const char *s) { fprintf(stderr, "bmgref: %s\n", s); }
 """
 

@@ -32,6 +32,8 @@ struct orc2_solver {
     int nabd1, nabd2;
     double *linebuf;
     int fcycle;   /* 0: V-cycle (default), 1: F-cycle (cycle/fcycle.h) */
+    int ibc;      /* BMG_get_bc(per_mask): 0, 2 (periodic x), 1 (periodic y), 3 (both); every kernel wrapper of the
+                   * reference passes it on (include/cedar/2d/relax.h:84-86, src/2d/restrict.cc:27, interp.cc:28,46, ...) */
 };
 
 static double *zalloc(size_t n) { return (double *)calloc(n ? n : 1, sizeof(double)); }
@@ -58,7 +60,7 @@ static void relax_level(orc2_solver *s, int l, double *x, const double *b, int u
      * k = kf = 1, BMG_RELAX_SYM always. */
     switch (s->relaxation) {
     case ORC_RELAX_POINT:
-        orc2_relax_gs(1, L->A, b, x, L->SOR[0], II, JJ, 1, ifd, L->nstncl, 2, 1, updown, 0);
+        orc2_relax_gs(1, L->A, b, x, L->SOR[0], II, JJ, 1, ifd, L->nstncl, 2, 1, updown, s->ibc);
         break;
     case ORC_RELAX_LINE_X:
         orc2_relax_lines_x(1, L->A, b, x, L->SOR[0], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, 0);
@@ -83,7 +85,19 @@ orc2_solver *orc2_solver_create(const double *so, int nx, int ny, int nstncl,
                                 int relaxation, int nrelax_pre, int nrelax_post,
                                 int num_levels, int min_coarse)
 {
+    return orc2_solver_create_per(so, nx, ny, nstncl, relaxation, nrelax_pre, nrelax_post, num_levels, min_coarse, 0);
+}
+
+/* per_mask: bit 0 = periodic in x, bit 1 = periodic in y (kernel_params::per_mask, include/cedar/kernel_params.h:33-41);
+ * point relaxation only (the periodic line solves are not restated) */
+orc2_solver *orc2_solver_create_per(const double *so, int nx, int ny, int nstncl,
+                                    int relaxation, int nrelax_pre, int nrelax_post,
+                                    int num_levels, int min_coarse, int per_mask)
+{
+    static const int bcmap[4] = {0, 2, 1, 3};   /* BMG_get_bc.f90:13-22 */
+    if (per_mask && relaxation != ORC_RELAX_POINT) return NULL;
     orc2_solver *s = (orc2_solver *)calloc(1, sizeof(*s));
+    s->ibc = bcmap[per_mask & 3];
     s->relaxation = relaxation;
     s->npre = nrelax_pre;
     s->npost = nrelax_post;
@@ -112,7 +126,7 @@ orc2_solver *orc2_solver_create(const double *so, int nx, int ny, int nstncl,
     }
     s->linebuf = zalloc((size_t)maxlen + 2);
     olevel *C = &s->lv[nl - 1];
-    s->nabd1 = C->nx + 2;
+    s->nabd1 = s->ibc ? C->nx * C->ny : C->nx + 2;   /* 2d/solver.h:111-114: dense for periodic */
     s->nabd2 = C->nx * C->ny;
     s->ABD = zalloc((size_t)s->nabd1 * s->nabd2);
     s->bbd = zalloc((size_t)s->nabd2);
@@ -122,9 +136,9 @@ orc2_solver *orc2_solver_create(const double *so, int nx, int ny, int nstncl,
         olevel *F = &s->lv[l], *Cc = &s->lv[l + 1];
         int ifd = F->nstncl == 3 ? 1 : 0;
         orc2_setup_interp_oi(F->A, Cc->A, Cc->P, F->nx + 2, F->ny + 2, Cc->nx + 2, Cc->ny + 2,
-                             ifd, F->nstncl, 0, 0);
+                             ifd, F->nstncl, s->ibc, 0);
         orc2_setup_itli_ex(F->A, Cc->A, Cc->P, F->nx + 2, F->ny + 2, Cc->nx + 2, Cc->ny + 2,
-                           ifd, F->nstncl, 0);
+                           ifd, F->nstncl, s->ibc);
         switch (relaxation) {
         case ORC_RELAX_POINT:
             orc2_setup_recip(F->A, F->SOR[0], F->nx + 2, F->ny + 2, F->nstncl, 2);
@@ -141,7 +155,7 @@ orc2_solver *orc2_solver_create(const double *so, int nx, int ny, int nstncl,
             break;
         }
     }
-    orc2_setup_cg_lu(C->A, C->nx + 2, C->ny + 2, C->nstncl, s->ABD, s->nabd1, s->nabd2, 0);
+    orc2_setup_cg_lu(C->A, C->nx + 2, C->ny + 2, C->nstncl, s->ABD, s->nabd1, s->nabd2, s->ibc);
     return s;
 }
 
@@ -189,13 +203,13 @@ static void ncycle(orc2_solver *s, int l, double *x, const double *b)
     int ifd = L->nstncl == 3 ? 1 : 0;
     for (int i = 0; i < s->npre; i++) relax_level(s, l, x, b, 0);
     orc2_residual(0, L->A, b, x, L->res, II, JJ, 0, ifd, L->nstncl);
-    orc2_restrict(L->res, C->b, C->P, II, JJ, IIC, JJC, 0);
+    orc2_restrict(L->res, C->b, C->P, II, JJ, IIC, JJC, s->ibc);
     memset(C->x, 0, sizeof(double) * (size_t)IIC * JJC);
     if (l + 1 == s->nlevels - 1)
-        orc2_solve_cg(C->x, C->b, IIC, JJC, s->ABD, s->bbd, s->nabd1, s->nabd2, 0);
+        orc2_solve_cg(C->x, C->b, IIC, JJC, s->ABD, s->bbd, s->nabd1, s->nabd2, s->ibc);
     else
         ncycle(s, l + 1, C->x, C->b);
-    orc2_interp_add(x, C->x, L->res, L->A, C->P, IIC, JJC, II, JJ, L->nstncl, 0);
+    orc2_interp_add(x, C->x, L->res, L->A, C->P, IIC, JJC, II, JJ, L->nstncl, s->ibc);
     for (int i = 0; i < s->npost; i++) relax_level(s, l, x, b, 1);
 }
 
@@ -227,7 +241,7 @@ void orc2_solver_vcycle(orc2_solver *s, double *x, const double *b)
     if (s->fcycle && s->nlevels > 1) { fmg_cycle(s, 0, x, b); return; }
     if (s->nlevels == 1) {
         olevel *C = &s->lv[0];
-        orc2_solve_cg(x, b, C->nx + 2, C->ny + 2, s->ABD, s->bbd, s->nabd1, s->nabd2, 0);
+        orc2_solve_cg(x, b, C->nx + 2, C->ny + 2, s->ABD, s->bbd, s->nabd1, s->nabd2, s->ibc);
     } else {
         ncycle(s, 0, x, b);
     }

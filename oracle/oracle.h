@@ -13,6 +13,10 @@ int orc_get_max_threads(void);
 
 int orc_dpttrf(int n, double *d, double *e);
 void orc_dptts2(int n, const double *d, const double *e, double *b);
+/* LAPACK DPOTRF('U') as unblocked DPOTF2 and DPOTRS('U', nrhs = 1) in reference-BLAS loop order (dense Cholesky of the
+ * periodic coarse-grid operator) */
+int orc_dpotf2_upper(int n, double *a, int lda);
+void orc_dpotrs_upper(int n, const double *a, int lda, double *b);
 int orc_dpbtf2_upper(int n, int kd, double *ab, int ldab);
 void orc_dpbtrs_upper(int n, int kd, const double *ab, int ldab, double *x);
 
@@ -66,6 +70,9 @@ typedef struct orc2_solver orc2_solver;
 orc2_solver *orc2_solver_create(const double *so, int nx, int ny, int nstncl,
                                 int relaxation, int nrelax_pre, int nrelax_post,
                                 int num_levels, int min_coarse);
+/* per_mask: bit 0 periodic in x, bit 1 periodic in y; point relaxation only (NULL otherwise) */
+orc2_solver *orc2_solver_create_per(const double *so, int nx, int ny, int nstncl, int relaxation, int nrelax_pre,
+                                    int nrelax_post, int num_levels, int min_coarse, int per_mask);
 void orc2_solver_destroy(orc2_solver *s);
 int orc2_solver_nlevels(const orc2_solver *s);
 void orc2_solver_level_shape(const orc2_solver *s, int lvl, int *nx, int *ny);

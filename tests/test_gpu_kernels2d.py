@@ -353,3 +353,57 @@ def test_galerkin_periodic(cuda, abi, nx, ny, nine, jpn):
     assert oracle.lib().orc2_setup_itli_ex(P(so), P(soc), P(ci), II, JJ, iic, jjc, ifd_of(nine), nst, jpn) == 0
     abi.check(abi.lib.bmgx2_SETUP_ITLI_ex(ptr(d_so), ptr(d_soc), ptr(d_ci), II, JJ, iic, jjc, ifd_of(nine), nst, jpn, None))
     assert_bitwise(host(d_soc), soc, "periodic SETUP_ITLI_ex")
+
+
+# ---- periodic interpolation setup and coarsest-grid solve ---------------------------------------------------------
+@pytest.mark.parametrize("jpn", [1, 2, 3, -1, -2, -3])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(4, 4), (8, 6), (7, 5), (16, 17), (37, 64), (300, 301), (129, 256)])
+def test_periodic_interp_setup_bitwise(cuda, abi, nx, ny, nine, jpn):
+    """bmgx2_SETUP_interp_OI, periodic codes (BMG2_SymStd_SETUP_interp_OI.f90:258-618), against the oracle restatement
+    (pinned bitwise to the reference's kernel, tests/test_ref_parity_cpu.py)"""
+    L = oracle.lib()
+    rng = np.random.default_rng(nx * 29 + ny + nine + 100 * abs(jpn))
+    II, JJ = nx + 2, ny + 2
+    iic, jjc = II // 2 + 1 + II % 2, JJ // 2 + 1 + JJ % 2
+    nst, ifd = (5, 0) if nine else (3, 1)
+    so = 10.0 ** rng.uniform(-1, 1, size=(nst, JJ, II))
+    so[0] = so[1:].sum(axis=0) * 2.5 + 1.0
+    c0 = rng.standard_normal((8, jjc, iic))
+    want = c0.copy()
+    assert L.orc2_setup_interp_oi(P(so), None, P(want), II, JJ, iic, jjc, ifd, nst, jpn, 0) == 0
+    d_ci = dev(cuda, c0)
+    abi.check(abi.lib.bmgx2_SETUP_interp_OI(ptr(dev(cuda, so)), None, ptr(d_ci), II, JJ, iic, jjc, ifd, nst, jpn, 0, None))
+    assert_bitwise(host(d_ci), want, "periodic SETUP_interp_OI")
+
+
+@pytest.mark.parametrize("ibc", [1, 2, 3, -1, -2, -3])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(2, 2), (3, 3), (4, 5), (7, 4), (5, 6)])
+def test_periodic_coarse_solve_bitwise(cuda, abi, nx, ny, nine, ibc):
+    """bmgx2_SETUP_cg_LU / bmgx2_SOLVE_cg with periodic codes: dense upper triangle + DPOTF2 order, DPOTRS, mean
+    subtraction, ghost layer of the solution (SETUP_cg_LU.f90:121-217, 258-331; SOLVE_cg.f90:104-166)"""
+    import ctypes as C
+    L = oracle.lib()
+    rng = np.random.default_rng(nx * 7 + ny + nine + 50 * abs(ibc) + (ibc < 0))
+    nst = 5 if nine else 3
+    II, JJ = nx + 2, ny + 2
+    so = 10.0 ** rng.uniform(-1, 0, size=(nst, JJ, II))
+    so[0] = 12.0 + rng.uniform(0, 1, size=(JJ, II))
+    n = nx * ny
+    a = np.zeros((n, n))
+    assert L.orc2_setup_cg_lu(P(so), II, JJ, nst, P(a), n, n, ibc) == 0
+    d_abd = dev(cuda, rng.standard_normal((n, n)))                    # the entry point clears it
+    abi.check(abi.lib.bmgx2_SETUP_cg_LU(ptr(dev(cuda, so)), II, JJ, nst, ptr(d_abd), n, n, ibc, None))
+    info = C.c_int(-1)
+    abi.check(abi.lib.bmgx_cg_LU_info(C.byref(info), None))
+    assert info.value == 0
+    assert_bitwise(host(d_abd), a, "periodic ABD")
+    b = rng.standard_normal((JJ, II))
+    x0 = rng.standard_normal((JJ, II))
+    want = x0.copy()
+    w = np.zeros(n)
+    assert L.orc2_solve_cg(P(want), P(b), II, JJ, P(a), P(w), n, n, ibc) == 0
+    d_x, d_w = dev(cuda, x0), dev(cuda, np.zeros(n))
+    abi.check(abi.lib.bmgx2_SOLVE_cg(ptr(d_x), ptr(dev(cuda, b)), II, JJ, ptr(d_abd), ptr(d_w), n, n, ibc, None))
+    assert_bitwise(host(d_x), want, "periodic SOLVE_cg")

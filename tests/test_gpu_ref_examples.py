@@ -67,3 +67,30 @@ def test_c_application_against_the_reference_c_interface(cuda, tmp_path, n):
     m = re.search(r"apply_err (\S+) solve_err (\S+)", p.stdout)
     assert m and float(m.group(1)) < 1e-12 and float(m.group(2)) < 1e-9, p.stdout
     assert (tmp_path / "timer.json").exists()
+
+
+EXEP = os.path.join(ROOT, "examples", "_ref", "ser-periodic-2d")
+
+
+@pytest.mark.skipif(not os.path.isfile(EXEP), reason="examples/_ref not built (reference tree absent at build time)")
+def test_ser_periodic_2d_history_equals_oracle(cuda, tmp_path):
+    """the reference's examples/basic-2d-ser/periodic.cc, built unchanged, with its periodic-config.json (periodic in x,
+    300 x 300, point relaxation V(1,1)): the printed residual history equals the CPU oracle's periodic solve of the
+    same problem to the six printed digits, and the error norm agrees"""
+    import numpy as np
+    import oracle
+    from tests.util import periodic_problem2
+    cfg = open(os.path.join(ROOT, "examples", "basic-2d-ser", "periodic-config.json")).read()
+    (tmp_path / "config.json").write_text(cfg)
+    p = subprocess.run([EXEP], cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout + p.stderr
+    hist = [float(m) for m in re.findall(r"Iteration \d+ relative l2 norm: (\S+)", p.stdout)]
+    norm = float(re.search(r"Solution norm: (\S+)", p.stdout).group(1))
+    so, b, exact = periodic_problem2(300, 300, (True, False))
+    xr, hr, _ = oracle.Solver2(so, "point", 1, 1, periodic=(True, False)).solve(b, maxiter=10, tol=1e-10)
+    assert len(hist) == len(hr) == 10
+    for got, want in zip(hist, hr):
+        assert abs(got - want) <= 2e-6 * want, (got, want)
+    err = np.abs((exact - xr)[1:-1, 1:-1]).max()
+    assert abs(abs(norm) - err) <= 2e-6 * err, (norm, err)
+    assert "Finished Test" in p.stdout

@@ -240,3 +240,38 @@ def test_coarse_tail_kernel_is_bitwise_and_saves_launches(cs, case):
         assert_bitwise(x, xr, f"coarse-tail {tail} vs oracle")
         assert np.allclose(h, hr, rtol=1e-10, atol=0)
     assert out[33][2] < out[0][2] and out[129][2] <= out[33][2], {k: v[2] for k, v in out.items()}
+
+
+@pytest.mark.parametrize("case", [((True, False), 300, 300, 1, 1), ((False, True), 300, 300, 1, 1), ((True, False), 129, 200, 2, 1),
+                                  ((True, True), 64, 96, 1, 1), ((False, True), 37, 50, 1, 2)])
+def test_periodic_solver_matches_oracle(cs, case):
+    """grid.periodic (reference examples/basic-2d-ser/periodic.cc, periodic-config.json): every kernel of the cycle takes
+    its periodic branch -- interpolation setup, Galerkin operator, in-place point relaxation, restriction,
+    interpolate-and-add, dense coarse solve with mean subtraction.  Hierarchy and iterate bitwise the oracle's (itself
+    pinned kernel by kernel to the reference's Fortran), history to 1e-10."""
+    from tests.util import periodic_problem2
+    per, nx, ny, pre, post = case
+    so, b, exact = periodic_problem2(nx, ny, per)
+    if all(per):
+        so[0] += 0.05 * so[0, 1, 1]          # the doubly periodic Laplacian is singular: make it definite
+        so[0, 0, :] = so[0, ny, :]; so[0, ny + 1, :] = so[0, 1, :]; so[0, :, 0] = so[0, :, nx]; so[0, :, nx + 1] = so[0, :, 1]
+    ref = oracle.Solver2(so, "point", pre, post, periodic=per)
+    xr, hr, r0r = ref.solve(b, maxiter=8, tol=1e-30)
+    assert hr[-1] < hr[0]
+    sol = cs.Solver2(cs.Operator2(so), relaxation="point", nrelax_pre=pre, nrelax_post=post, maxiter=8, tol=1e-30, periodic=per)
+    assert sol.nlevels == ref.nlevels
+    for lvl in range(1, sol.nlevels):
+        assert_bitwise(sol.level_array(lvl, "P"), ref.level_array(lvl, "P"), f"P level {lvl}")
+        assert_bitwise(sol.level_array(lvl, "A"), ref.level_array(lvl, "A"), f"A level {lvl}")
+    x, h, r0 = sol.solve(b)
+    assert_bitwise(x, xr, "periodic solve")
+    assert len(h) == len(hr) and np.allclose(h, hr, rtol=1e-10, atol=0) and abs(r0 - r0r) <= 1e-12 * r0r
+
+
+def test_periodic_with_line_relaxation_is_refused_cleanly(cs):
+    """the Sherman-Morrison line solves of the periodic branch (relax_lines_x.f90:209-261) are not implemented: a clean
+    error, no wrong answer"""
+    from tests.util import periodic_problem2
+    so, b, _ = periodic_problem2(65, 65, (True, False))
+    with pytest.raises(cs.CedarError, match="periodic"):
+        cs.Solver2(cs.Operator2(so), relaxation="line-x", nrelax_pre=1, nrelax_post=1, periodic=(True, False))

@@ -13,7 +13,7 @@ REF = "/root/reference/examples"
 @pytest.mark.skipif(not os.path.isdir(REF), reason="reference tree not present")
 def test_reference_examples_build_unchanged():
     subprocess.check_call(["make", "-C", os.path.join(ROOT, "examples"), "-s"])
-    for name in ("ser-poisson-2d", "ser-poisson-3d"):
+    for name in ("ser-poisson-2d", "ser-poisson-3d", "ser-periodic-2d"):
         exe = os.path.join(ROOT, "examples", "_ref", name)
         assert os.path.isfile(exe) and os.access(exe, os.X_OK)
         # linked against the host layer and, through it, the CUDA C-ABI library

@@ -203,3 +203,69 @@ def test_residual_has_no_periodic_branch(nine, ibc):
     R.BMG2_SymStd_residual(ref.ip(0), P(so), P(b), P(q), P(r2), ref.ip(II), ref.ip(JJ), ref.ip(0), ref.ip(ifd),
                            ref.ip(nst), ref.ip(ibc), ref.ip(0), ref.ip(1), ref.ip(0))
     assert np.array_equal(r1, r2)
+
+
+@pytest.mark.parametrize("jpn", [1, 2, 3, -1, -2, -3])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(4, 4), (8, 6), (7, 5), (6, 9), (16, 17), (37, 64), (40, 31)])
+def test_periodic_interp_setup_bitwise_vs_reference(nx, ny, nine, jpn):
+    """Periodic branch of BMG2_SymStd_SETUP_interp_OI (f90:258-618): wrapped fine index sequences, the first and last
+    coarse lines from the wrapped fine lines; even and odd extents (the IIC == IICF cases of l.296-317)."""
+    R, L = ref.lib(), oracle.lib()
+    rng = np.random.default_rng(nx * 29 + ny + nine + 100 * abs(jpn))
+    II, JJ = nx + 2, ny + 2
+    iic, jjc = II // 2 + 1 + II % 2, JJ // 2 + 1 + JJ % 2
+    nst, ifd = (5, 0) if nine else (3, 1)
+    so = 10.0 ** rng.uniform(-1, 1, size=(nst, JJ, II))       # periodic operators carry couplings in the ghost layer too
+    so[0] = so[1:].sum(axis=0) * 2.5 + 1.0
+    soc = np.zeros((5, jjc, iic))
+    c1 = rng.standard_normal((8, jjc, iic))
+    c2 = c1.copy()
+    assert L.orc2_setup_interp_oi(P(so), P(soc), P(c1), II, JJ, iic, jjc, ifd, nst, jpn, 0) == 0
+    R.BMG2_SymStd_SETUP_interp_OI(P(so), P(soc), P(c2), II, JJ, iic, jjc, ifd, nst, jpn, 0)
+    assert np.array_equal(c1, c2)
+
+
+@pytest.mark.parametrize("ibc", [1, 2, 3, -1, -2, -3])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(2, 2), (3, 3), (4, 5), (7, 4), (5, 6)])
+def test_periodic_coarse_solve_bitwise_vs_reference(nx, ny, nine, ibc):
+    """Periodic branches of BMG2_SymStd_SETUP_cg_LU (f90:121-217, 258-331: dense upper triangle with the wrap-around
+    couplings, DPOTRF) and BMG2_SymStd_SOLVE_cg (f90:104-166: DPOTRS, mean subtraction for every code but 0, ghost
+    layer of the solution); DPOTRF / DPOTRS bound to the restatements in both libraries."""
+    R, L = ref.lib(), oracle.lib()
+    rng = np.random.default_rng(nx * 7 + ny + nine + 50 * abs(ibc) + (ibc < 0))
+    nst = 5 if nine else 3
+    II, JJ = nx + 2, ny + 2
+    so = 10.0 ** rng.uniform(-1, 0, size=(nst, JJ, II))
+    so[0] = 12.0 + rng.uniform(0, 1, size=(JJ, II))             # diagonally dominant whatever wraps around
+    n = nx * ny
+    a1, a2 = np.zeros((n, n)), np.zeros((n, n))
+    rc = L.orc2_setup_cg_lu(P(so), II, JJ, nst, P(a1), n, n, ibc)
+    R.BMG2_SymStd_SETUP_cg_LU(P(so), ref.ip(II), ref.ip(JJ), ref.ip(nst), P(a2), ref.ip(n), ref.ip(n), ref.ip(ibc))
+    assert rc == 0 and np.array_equal(a1, a2)
+    b = rng.standard_normal((JJ, II))
+    x1 = rng.standard_normal((JJ, II))
+    x2 = x1.copy()
+    w1, w2 = np.zeros(n), np.zeros(n)
+    assert L.orc2_solve_cg(P(x1), P(b), II, JJ, P(a1), P(w1), n, n, ibc) == 0
+    R.BMG2_SymStd_SOLVE_cg(P(x2), P(b), II, JJ, P(a2), P(w2), n, n, ibc)
+    assert np.array_equal(x1, x2)
+
+
+def test_dense_cholesky_restatement_against_scipy():
+    """orc_dpotf2_upper / orc_dpotrs_upper (what DPOTRF / DPOTRS are bound to) against scipy's LAPACK"""
+    import scipy.linalg as sl
+    L = oracle.lib()
+    rng = np.random.default_rng(3)
+    for n in (1, 2, 5, 12, 40):
+        M = rng.standard_normal((n, n))
+        A = M @ M.T + n * np.eye(n)
+        a = np.array(A.T, order="C")           # column-major upper triangle == row-major of the transpose
+        assert L.orc_dpotf2_upper(n, P(a), n) == 0
+        U = np.triu(a.T)
+        assert np.allclose(U, sl.cholesky(A, lower=False), rtol=1e-12, atol=1e-12)
+        b = rng.standard_normal(n)
+        x = b.copy()
+        L.orc_dpotrs_upper(n, P(a), n, P(x))
+        assert np.allclose(x, np.linalg.solve(A, b), rtol=1e-10, atol=1e-12)

@@ -110,3 +110,34 @@ def random_gf3(nx, ny, nz, rng):
     q = np.zeros((nz + 2, ny + 2, nx + 2))
     q[1:-1, 1:-1, 1:-1] = rng.standard_normal((nz, ny, nx))
     return q
+
+
+def periodic_problem2(nx, ny, periodic):
+    """operator, right-hand side and exact solution of the reference's examples/basic-2d-ser/periodic.cc:16-170
+    (5-point Laplacian with periodic wrap in the chosen directions), in Cedar storage with the periodic ghost copies"""
+    px, py = periodic
+    so = np.zeros((3, ny + 2, nx + 2))
+    n1, n2 = nx - (1 if px else 0), ny - (1 if py else 0)
+    hx, hy = 1.0 / (n1 + 1), 1.0 / (n2 + 1)
+    xh, yh = hy / hx, hx / hy
+    ibeg, jbeg = (1 if px else 2), (1 if py else 2)          # C++ 0-based indices with ghost: interior 1..n
+    so[2, jbeg:ny + 1, 1:nx + 1] = 1.0 * yh
+    so[1, 1:ny + 1, ibeg:nx + 1] = 1.0 * xh
+    so[0, 1:ny + 1, 1:nx + 1] = 2 * xh + 2 * yh
+    if px:
+        so[:, 1:ny + 1, ibeg - 1] = so[:, 1:ny + 1, nx]
+        so[:, 1:ny + 1, nx + 1] = so[:, 1:ny + 1, ibeg]
+    if py:
+        so[:, jbeg - 1, 1:nx + 1] = so[:, ny, 1:nx + 1]
+        so[:, ny + 1, 1:nx + 1] = so[:, jbeg, 1:nx + 1]
+    jj, ii = np.meshgrid(np.arange(ny + 2), np.arange(nx + 2), indexing="ij")
+    b = np.zeros((ny + 2, nx + 2))
+    rhs = 8 * (np.pi * np.pi) * np.sin(2 * np.pi * (ii * hx)) * np.sin(2 * np.pi * (jj * hy)) * (hx * hy)
+    b[1:-1, 1:-1] = rhs[1:-1, 1:-1]
+    if px:
+        b[:, 0] = b[:, nx]; b[:, nx + 1] = b[:, 1]
+    if py:
+        b[0, :] = b[ny, :]; b[ny + 1, :] = b[1, :]
+    exact = np.zeros((ny + 2, nx + 2))
+    exact[1:-1, 1:-1] = (np.sin(2 * np.pi * (ii * hx)) * np.sin(2 * np.pi * (jj * hy)))[1:-1, 1:-1]
+    return so, b, exact
