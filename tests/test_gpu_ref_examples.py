@@ -90,7 +90,7 @@ def test_ser_periodic_2d_history_equals_oracle(cuda, tmp_path):
     xr, hr, _ = oracle.Solver2(so, "point", 1, 1, periodic=(True, False)).solve(b, maxiter=10, tol=1e-10)
     assert len(hist) == len(hr) == 10
     for got, want in zip(hist, hr):
-        assert abs(got - want) <= 2e-6 * want, (got, want)
+        assert abs(got - want) <= 6e-6 * want, (got, want)          # six printed digits
     err = np.abs((exact - xr)[1:-1, 1:-1]).max()
-    assert abs(abs(norm) - err) <= 2e-6 * err, (norm, err)
+    assert abs(abs(norm) - err) <= 6e-6 * err, (norm, err)
     assert "Finished Test" in p.stdout
