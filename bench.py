@@ -45,10 +45,20 @@ import numpy as np  # noqa: E402
 
 METRIC = "MDOF/s per V-cycle (fine-grid unknowns / V-cycle time)"
 BYTES_PER_PT = {"relax9": 64, "relax5": 48}  # algorithmic bytes per fine point per sweep
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel at 4097^2, from the
-# `ncu --set full` capture summarised in profiles/r01_fine2d_ncu_full_summary.csv (k_relax9_fused<0>: 968.93 MB
-# read + 125.03 MB written; k_relax5_fused<0>: 696.12 + 121.11).  Only quoted for the size it was captured at.
-NCU_TRAFFIC_4097 = {"relax9": 1093.96e6, "relax5": 817.23e6}
+NCU_SUMMARY = "profiles/r02_fine2d_ncu_full_summary.csv"
+
+
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of `kernel` at 4097^2, read from the committed summary
+    of this round's `ncu --set full` capture (tools/ncu_summary.py of gpurun_out/r02_fine2d_full.ncu-rep); None if absent"""
+    import csv
+    try:
+        for row in csv.DictReader(open(os.path.join(ROOT, NCU_SUMMARY))):
+            if row["kernel"].startswith(kernel):
+                return float(row["dram__bytes_read.sum"]) + float(row["dram__bytes_write.sum"])
+    except (OSError, KeyError, ValueError):
+        pass
+    return None
 
 
 def parse():
@@ -743,8 +753,9 @@ def main():
                          "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
                          "peak_source": peak_src, "ms_per_launch": per_sweep_ms, "launches_per_sweep": sweep_launches,
                          "algorithmic_bytes": alg_bytes,
-                         "traffic": (NCU_TRAFFIC_4097["relax9" if a.gallery == "fe" else "relax5"] if n == 4097 else None),
-                         "traffic_source": "ncu --set full, profiles/r01_fine2d_ncu_full_summary.csv (bytes per launch)"},
+                         "traffic": (ncu_traffic("k_relax9_fused<0>" if a.gallery in ("fe", "hetero") else "k_relax5_fused<0>")
+                                     if n == 4097 else None),
+                         "traffic_source": f"ncu --set full of this round's build, {NCU_SUMMARY} (bytes per launch, 4097^2)"},
         }
         # whole-cycle roofline: SURVEY 8(d) 360 B/pt (9-pt V(1,1)) / 312 (5-pt fine)
         cyc_bytes = (360 if a.gallery == "fe" else 312) * dofs if (a.pre, a.post) == (1, 1) and a.relaxation == "point" else None
