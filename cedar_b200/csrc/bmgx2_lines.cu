@@ -6,8 +6,12 @@
 // factor; y-lines stored transposed SOR(j,i,.) so every line is contiguous.
 //
 // Setup: the LDL' recurrence d(i+1) = d(i+1) - e(i)^2/d(i) is sequential per
-// line; one lane per line, 32x32 tiles turned in shared memory so that every global access is coalesced
-// (k_setup_lines).  Bitwise DPTTRF.
+// line; one lane per line, operands fetched 16 positions ahead of the chain.  The kernel is bound by that chain, not
+// by memory: n dependent fp64 divisions per line (~200 cycles each: 4097 x 200 cycles = 0.4 ms at 1.9 GHz) however
+// the operands arrive; 0.80 ms at 4097^2 = 10 % of the copy roofline.  A variant that turned 32 x 32 tiles in shared
+// memory so that loads AND stores were coalesced (round 2) kept DPTTRF's bits but ran in 1.26 ms -- the transposes sit
+// on the chain's critical path -- and was dropped.  Going faster means evaluating the continued fraction as a scan of
+// 2 x 2 matrices, which gives up bitwise DPTTRF.  Setup only.
 //
 // Solve: with the factor known, DPTTS2 is two first-order linear recurrences,
 //     y(i) = b(i) - e(i-1) y(i-1),      x(i) = y(i)/d(i) - e(i) x(i+1),
@@ -30,70 +34,44 @@
 
 // ---------------------------------------------------------------- setup ----
 // line-major view: element (p, l) of line l at position p lives at
-//   src: so_d[p*sp + l*sl] (diag), so_o[...] (off-diag, negated on load); exactly one of sp, sl is 1
+//   src: so_d[p*sp + l*sl] (diag), so_o[...] (off-diag, negated on load)
 //   dst: sor[(size_t)l*dl + p] for D and sor[plane + l*dl + p] for L
-// DPTTRF per line: d = diag(1); for q = 2..n-2: e = -off(q)/d; L(q) = e; D(q-1) = d; d = diag(q) - e*(-off(q)).
-// One warp owns 32 lines and walks the positions in tiles of 32: the tile is loaded with the lanes along whichever
-// index is contiguous in the source (positions for x-lines, lines for y-lines), turned in shared memory (row pitch 33:
-// conflict free), the recurrence runs with one lane per line, and the factors leave with the lanes along the
-// positions -- every global access is a full 256-byte row.  The next tile's loads are in flight (registers) while the
-// chain of the current one runs.  Bitwise DPTTRF.
-#define SL_T 32
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(128)
 k_setup_lines(const double *__restrict__ so_d, const double *__restrict__ so_o, size_t sp, size_t sl,
               double *__restrict__ sor, size_t plane, size_t dl, unsigned n, unsigned nlines)
 {
-    __shared__ double td[SL_T][SL_T + 1], to[SL_T][SL_T + 1], tD[SL_T][SL_T + 1], tL[SL_T][SL_T + 1];
-    const unsigned lane = threadIdx.x;
-    const unsigned l0 = 1 + blockIdx.x * SL_T;            // first line of this warp (lines 1 .. nlines-2)
-    const unsigned lmax = nlines - 2, pmax = n - 2;       // positions 1 .. n-2
-    const bool xlines = sp == 1;
-    double rd[SL_T], ro[SL_T];
-    // loads of the tile starting at position p0: lane runs along the contiguous index
-    auto fetch = [&](unsigned p0) {
+    // lines are 1..nlines-2 (0-based interior 1..), positions 1..n-2 interior
+    unsigned l = blockIdx.x * blockDim.x + threadIdx.x + 1;
+    if (l > nlines - 2) return;
+    const double *pd = so_d + l * sl, *po = so_o + l * sl;
+    double *D = sor + (size_t)l * dl, *L = sor + plane + (size_t)l * dl;
+    // DPTTRF(n-2, D(1..), L(2..)) on d(p)=diag(p), e(p)=-off(p+1).  The recurrence is sequential, its operands
+    // are not: they are fetched 16 positions ahead so that the chain never waits for memory
+    double d = pd[(size_t)1 * sp];
+    constexpr unsigned U = 16;
+    for (unsigned p0 = 1; p0 + 1 <= n - 2; p0 += U) {
+        double eo[U], dn[U];
 #pragma unroll
-        for (unsigned r = 0; r < SL_T; r++) {
-            // x-lines: row r = line l0+r, lane = position p0+lane;  y-lines: row r = position p0+r, lane = line l0+lane
-            const unsigned l = xlines ? l0 + r : l0 + lane, p = xlines ? p0 + lane : p0 + r;
-            const bool ok = l <= lmax && p <= pmax;
-            const size_t a = (size_t)p * sp + (size_t)l * sl;
-            rd[r] = ok ? __ldg(so_d + a) : 1.0;
-            ro[r] = ok ? __ldg(so_o + a) : 0.0;
+        for (unsigned u = 0; u < U; u++) {
+            const unsigned p = p0 + u;
+            const bool ok = p + 1 <= n - 2;
+            eo[u] = ok ? __ldg(po + (size_t)(p + 1) * sp) : 0.0;
+            dn[u] = ok ? __ldg(pd + (size_t)(p + 1) * sp) : 0.0;
         }
-    };
-    fetch(1);
-    double d = 1.0;
-    const unsigned myline = l0 + lane;
-    for (unsigned p0 = 1; p0 <= pmax; p0 += SL_T) {
 #pragma unroll
-        for (unsigned r = 0; r < SL_T; r++) {
-            if (xlines) { td[r][lane] = rd[r]; to[r][lane] = ro[r]; }     // [line][position]
-            else { td[lane][r] = rd[r]; to[lane][r] = ro[r]; }
-        }
-        __syncwarp();
-        if (p0 + SL_T <= pmax) fetch(p0 + SL_T);
-#pragma unroll 4
-        for (unsigned q = 0; q < SL_T; q++) {
-            const unsigned p = p0 + q;
-            const double dg = td[lane][q], ei = -to[lane][q];
-            double e = ei;
-            if (p == 1) d = dg;
-            else { e = ei / d; d = dg - e * ei; }
-            tL[lane][q] = e;       // L(1) = -off(1): stored, never used by the solve
-            tD[lane][q] = d;
-        }
-        __syncwarp();
-#pragma unroll 4
-        for (unsigned r = 0; r < SL_T; r++) {
-            const unsigned l = l0 + r, p = p0 + lane;
-            if (l <= lmax && p <= pmax) {
-                sor[(size_t)l * dl + p] = tD[r][lane];
-                sor[plane + (size_t)l * dl + p] = tL[r][lane];
+        for (unsigned u = 0; u < U; u++) {
+            const unsigned p = p0 + u;
+            if (p + 1 <= n - 2) {
+                const double ei = -eo[u];
+                D[p] = d;
+                const double e = ei / d;
+                L[p + 1] = e;
+                d = dn[u] - e * ei;
             }
         }
-        __syncwarp();
     }
-    (void)myline;
+    D[n - 2] = d;
+    L[1] = -po[(size_t)1 * sp];  // SOR(2,j,2) = -SO(2,j,KW): stored, never used by the solve
 }
 
 extern "C" int bmgx2_SETUP_lines_x(const double *so, double *sor, bmgx_len nx, bmgx_len ny, int nstncl, int jpn,
@@ -104,7 +82,7 @@ extern "C" int bmgx2_SETUP_lines_x(const double *so, double *sor, bmgx_len nx, b
     if (nx < 3 || ny < 3) return BMGX_OK;
     size_t pl = (size_t)nx * ny;
     // line l = j (0-based), position p = i (0-based): src stride sp=1, sl=nx; dst line stride nx
-    k_setup_lines<<<cdiv(ny - 2, SL_T), 32, 0, (cudaStream_t)s>>>(so + (KO - 1) * pl, so + (KW - 1) * pl, 1, nx, sor,
+    k_setup_lines<<<cdiv(ny - 2, 128), 128, 0, (cudaStream_t)s>>>(so + (KO - 1) * pl, so + (KW - 1) * pl, 1, nx, sor,
                                                                   pl, nx, nx, ny);
     BMGX_LAUNCH_CHECK("SETUP_lines_x");
     return BMGX_OK;
@@ -118,7 +96,7 @@ extern "C" int bmgx2_SETUP_lines_y(const double *so, double *sor, bmgx_len nx, b
     if (nx < 3 || ny < 3) return BMGX_OK;
     size_t pl = (size_t)nx * ny;
     // line l = i, position p = j: src stride sp=nx, sl=1; dst SOR(j,i,.) line stride ny
-    k_setup_lines<<<cdiv(nx - 2, SL_T), 32, 0, (cudaStream_t)s>>>(so + (KO - 1) * pl, so + (KS - 1) * pl, nx, 1, sor,
+    k_setup_lines<<<cdiv(nx - 2, 128), 128, 0, (cudaStream_t)s>>>(so + (KO - 1) * pl, so + (KS - 1) * pl, nx, 1, sor,
                                                                   pl, ny, ny, nx);
     BMGX_LAUNCH_CHECK("SETUP_lines_y");
     return BMGX_OK;
