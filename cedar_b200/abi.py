@@ -24,6 +24,7 @@ SIGNATURES = {
     "bmgx_version": (C.c_char_p, []),
     "bmgx_last_error": (C.c_char_p, []),
     "bmgx_launch_count": (C.c_ulonglong, []),
+    "bmgx_scratch_trim": (C.c_int, [C.c_size_t]),
     "bmgx_stream_is_capturing": (_i, [_p, C.POINTER(_i)]),
     "bmgx_get_bc": (None, [_i, C.POINTER(_i)]),
     "bmgx_set_batch": (_i, [_u]),

@@ -558,3 +558,173 @@ extern "C" int bmgx2_relax_lines_y(int k, const double *so, const double *qf, do
     }
     return BMGX_OK;
 }
+
+// ---- lines across block cuts (the decomposed solver, cedar_b200/host/dist2.cc) ------------------------------
+// The blocks of a process row (x-lines) or column (y-lines) transpose their lines: every block computes the
+// right-hand side of its OWN points -- the serial kernels' expression, term for term -- and stores it straight into
+// the line buffer of the block that solves the line (peer memory over NVLink); the solver runs the serial solve
+// (k_liney_block / k_lines_y_solve on the line-major buffer, the very kernels of relax_lines_y's second step) on
+// whole lines and stores the solution into the owners' iterate.  Line buffer of a solver: rows 1 .. its lines,
+// row pitch len + 2, position p of a line (global F-index p + 1) at column p -- the layout of the serial y-lines'
+// transposed scratch, so the factor (SETUP_lines on a strip of gathered diagonals) and the solve are the serial ones.
+namespace {
+
+// destination of line t (0-based within the group) at line-buffer column c
+__device__ __forceinline__ double *line_slot(const bmgx_line_group &g, unsigned t, unsigned c)
+{
+    int m = 0;
+#pragma unroll 1
+    while (m + 1 < g.nmembers && t >= (unsigned)g.first[m + 1]) m++;
+    return g.lb[m] + (size_t)(1 + t - g.first[m]) * g.pitch + c;
+}
+
+// x-lines: thread per own point of a line of the colour (own lines t = t0, t0 + 2, ...)
+template <bool NINE>
+__global__ void __launch_bounds__(256)
+k_lines_rhs_push_x(const double *__restrict__ so, const double *__restrict__ qf, const double *__restrict__ q, unsigned II,
+                   unsigned JJ, unsigned wl, unsigned wb, unsigned nx, unsigned t0, unsigned col0, bmgx_line_group g)
+{
+    const unsigned il = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned t = t0 + 2 * blockIdx.y;
+    if (il >= nx) return;
+    const size_t pl = (size_t)II * JJ;
+    const double *ks = so + (KS - 1) * pl, *ksw = so + (KSW - 1) * pl, *knw = so + (KNW - 1) * pl;
+    const size_t c = (size_t)(wb + t) * II + wl + il;
+    double r = qf[c] + ks[c] * q[c - II] + ks[c + II] * q[c + II];
+    if (NINE)
+        r = r + ksw[c] * q[c - II - 1] + knw[c + 1] * q[c - II + 1] + knw[c + II] * q[c + II - 1]
+            + ksw[c + II + 1] * q[c + II + 1];
+    *line_slot(g, t, col0 + il) = r;
+}
+
+// y-lines: 32 lines (own columns of the colour) x 32 positions (own rows) per CTA, turned in shared memory so that
+// the stores into the line buffers run along the lines
+template <bool NINE>
+__global__ void __launch_bounds__(256)
+k_lines_rhs_push_y(const double *__restrict__ so, const double *__restrict__ qf, const double *__restrict__ q, unsigned II,
+                   unsigned JJ, unsigned wl, unsigned wb, unsigned nx, unsigned ny, unsigned t0, unsigned col0,
+                   bmgx_line_group g)
+{
+    __shared__ double tile[32][33];
+    const unsigned tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const size_t pl = (size_t)II * JJ;
+    const double *kw = so + (KW - 1) * pl, *ksw = so + (KSW - 1) * pl, *knw = so + (KNW - 1) * pl;
+    const unsigned t = t0 + 2 * (blockIdx.x * 32 + tx);   // own column
+    for (unsigned r = ty; r < 32; r += 8) {
+        const unsigned jl = blockIdx.y * 32 + r;          // own row
+        double v = 0.0;
+        if (t < nx && jl < ny) {
+            const size_t c = (size_t)(wb + jl) * II + wl + t;
+            v = qf[c] + kw[c] * q[c - 1] + kw[c + 1] * q[c + 1];
+            if (NINE)
+                v = v + ksw[c] * q[c - II - 1] + knw[c + 1] * q[c - II + 1] + knw[c + II] * q[c + II - 1]
+                    + ksw[c + II + 1] * q[c + II + 1];
+        }
+        tile[r][tx] = v;
+    }
+    __syncthreads();
+    for (unsigned r = ty; r < 32; r += 8) {
+        const unsigned tl = t0 + 2 * (blockIdx.x * 32 + r);
+        const unsigned jl = blockIdx.y * 32 + tx;
+        if (tl < nx && jl < ny) *line_slot(g, tl, col0 + jl) = tile[tx][r];
+    }
+}
+
+// solved lines -> the owners' iterate.  x-lines: CTA row = one of this solver's lines of the colour
+__global__ void __launch_bounds__(256)
+k_lines_scatter_push_x(const double *__restrict__ lb, size_t pitch, unsigned r0, unsigned tfirst, unsigned len,
+                       bmgx_line_owners o)
+{
+    const unsigned p = blockIdx.x * blockDim.x + threadIdx.x;   // 0-based global position along the line
+    const unsigned r = r0 + 2 * blockIdx.y;                     // line-buffer row
+    if (p >= len) return;
+    int m = 0;
+#pragma unroll 1
+    while (m + 1 < o.nmembers && p >= (unsigned)o.start[m + 1]) m++;
+    const unsigned t = tfirst + r - 1;                          // line within the group
+    o.q[m][(size_t)(o.w_across + t) * o.pitch[m] + o.w_along[m] + (p - o.start[m])] = __ldcg(lb + (size_t)r * pitch + 1 + p);
+}
+
+// y-lines: 32 of this solver's lines x 32 positions per CTA, turned so that the stores run along the owners' rows
+__global__ void __launch_bounds__(256)
+k_lines_scatter_push_y(const double *__restrict__ lb, size_t pitch, unsigned r0, unsigned nrows, unsigned tfirst, unsigned len,
+                       bmgx_line_owners o)
+{
+    __shared__ double tile[32][33];
+    const unsigned tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (unsigned k = ty; k < 32; k += 8) {
+        const unsigned r = r0 + 2 * (blockIdx.x * 32 + k), p = blockIdx.y * 32 + tx;
+        tile[k][tx] = (r <= nrows && p < len) ? __ldcg(lb + (size_t)r * pitch + 1 + p) : 0.0;
+    }
+    __syncthreads();
+    const unsigned r = r0 + 2 * (blockIdx.x * 32 + tx);
+    for (unsigned k = ty; k < 32; k += 8) {
+        const unsigned p = blockIdx.y * 32 + k;
+        if (r > nrows || p >= len) continue;
+        int m = 0;
+#pragma unroll 1
+        while (m + 1 < o.nmembers && p >= (unsigned)o.start[m + 1]) m++;
+        const unsigned t = tfirst + r - 1;
+        o.q[m][(size_t)(o.w_along[m] + (p - o.start[m])) * o.pitch[m] + o.w_across + t] = tile[tx][k];
+    }
+}
+
+}  // namespace
+
+extern "C" int bmgx2_lines_rhs_push(int dirn, int nine, const double *so, const double *qf, const double *q, bmgx_len ii,
+                                    bmgx_len jj, bmgx_len wl, bmgx_len wb, bmgx_len nx, bmgx_len ny, int first_findex,
+                                    bmgx_len col0, const bmgx_line_group *g, bmgx_stream_t s)
+{
+    if (!g || g->nmembers < 1 || g->nmembers > BMGX_LINE_GROUP_MAX)
+        return bmgx_set_error(BMGX_ERR_ARG, "lines_rhs_push: 1 .. BMGX_LINE_GROUP_MAX blocks share a line");
+    cudaStream_t st = (cudaStream_t)s;
+    // own lines of the colour: the group's first line has an even global index (F-index even), so line t has the
+    // parity of t
+    const unsigned t0 = (unsigned)(first_findex & 1);
+    const unsigned nl_all = dirn == 0 ? ny : nx;
+    if (t0 >= nl_all) return BMGX_OK;
+    const unsigned nl = (nl_all - t0 + 1) / 2;
+    if (dirn == 0) {
+        dim3 grid(cdiv(nx, 256), nl);
+        if (nine) k_lines_rhs_push_x<true><<<grid, 256, 0, st>>>(so, qf, q, ii, jj, wl, wb, nx, t0, col0, *g);
+        else k_lines_rhs_push_x<false><<<grid, 256, 0, st>>>(so, qf, q, ii, jj, wl, wb, nx, t0, col0, *g);
+    } else {
+        dim3 grid(cdiv(nl, 32), cdiv(ny, 32));
+        if (nine) k_lines_rhs_push_y<true><<<grid, 256, 0, st>>>(so, qf, q, ii, jj, wl, wb, nx, ny, t0, col0, *g);
+        else k_lines_rhs_push_y<false><<<grid, 256, 0, st>>>(so, qf, q, ii, jj, wl, wb, nx, ny, t0, col0, *g);
+    }
+    BMGX_LAUNCH_CHECK("lines_rhs_push");
+    return BMGX_OK;
+}
+
+extern "C" int bmgx2_lines_solve_T(double *lb, const double *sor, bmgx_len nrows2, bmgx_len len2, int ibeg, bmgx_stream_t s)
+{
+    // second step of relax_lines_y on a line-major buffer: "ii" = rows of the buffer, "jj" = its pitch
+    if (nrows2 < 3 || len2 < 3 || (unsigned)ibeg > nrows2 - 1) return BMGX_OK;
+    cudaStream_t st = (cudaStream_t)s;
+    const unsigned nl = (nrows2 - 1 - ibeg) / 2 + 1;
+    unsigned lg, threads; size_t smem;
+    if (line_plan(len2 - 2, &lg, &threads, &smem)) {
+        const unsigned nb = bmgx_batch();
+        if (nb != 1) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "lines_solve_T: not batched");
+        cudaError_t e = launch_liney(lg, nl, threads, smem, st, lb, sor, nrows2, len2, ibeg);
+        if (e != cudaSuccess) return bmgx_set_cuda_error(e, "lines_solve_T/attr");
+    } else
+        k_lines_y_solve<<<cdiv((size_t)nl * 32, 128), 128, 0, st>>>(lb, sor, nrows2, len2, ibeg);
+    BMGX_LAUNCH_CHECK("lines_solve_T");
+    return BMGX_OK;
+}
+
+extern "C" int bmgx2_lines_scatter_push(int dirn, const double *lb, bmgx_len nrows2, bmgx_len len2, int ibeg, bmgx_len tfirst,
+                                        const bmgx_line_owners *o, bmgx_stream_t s)
+{
+    if (!o || o->nmembers < 1 || o->nmembers > BMGX_LINE_GROUP_MAX)
+        return bmgx_set_error(BMGX_ERR_ARG, "lines_scatter_push: 1 .. BMGX_LINE_GROUP_MAX blocks share a line");
+    if (nrows2 < 3 || len2 < 3 || (unsigned)ibeg > nrows2 - 1) return BMGX_OK;
+    cudaStream_t st = (cudaStream_t)s;
+    const unsigned r0 = ibeg - 1, nrows = nrows2 - 2, nl = (nrows - r0) / 2 + 1, len = len2 - 2;
+    if (dirn == 0) k_lines_scatter_push_x<<<dim3(cdiv(len, 256), nl), 256, 0, st>>>(lb, len2, r0, tfirst, len, *o);
+    else k_lines_scatter_push_y<<<dim3(cdiv(nl, 32), cdiv(len, 32)), 256, 0, st>>>(lb, len2, r0, nrows, tfirst, len, *o);
+    BMGX_LAUNCH_CHECK("lines_scatter_push");
+    return BMGX_OK;
+}

@@ -210,9 +210,9 @@ int launch(const Op3 &A, const Ci3 &W, double *soc, cudaStream_t st)
     const int nkmax = min(SLAB + 2, W.KKC);
     Slab S;
     S.plane = plane;
-    // stream-ordered scratch from the device's default pool, as it is configured by the embedding application (the
-    // library does not touch the pool's release threshold)
-    cudaError_t e = cudaMallocAsync((void **)&S.t, (size_t)NT * plane * nkmax * sizeof(double), st);
+    // stream-ordered scratch from the library's own pool (bmgx_util.cu): cached across setups, the application's
+    // default pool is left alone
+    cudaError_t e = bmgx_scratch_alloc((void **)&S.t, (size_t)NT * plane * nkmax * sizeof(double), st);
     if (e != cudaSuccess) return bmgx_set_cuda_error(e, "SETUP_ITLI3/scratch");
     dim3 b(32, 4);
     for (int ka = 2; ka <= W.KKC - 1; ka += SLAB) {
@@ -227,10 +227,10 @@ int launch(const Op3 &A, const Ci3 &W, double *soc, cudaStream_t st)
         dim3 g2(cdiv(W.IIC - 2, 32), cdiv(W.JJC - 2, 4), kb - ka + 1);
         k3_ptap<<<g2, b, 0, st>>>(W, S, soc, ka);
         cudaError_t le = cudaGetLastError();
-        if (le != cudaSuccess) { cudaFreeAsync(S.t, st); return bmgx_set_cuda_error(le, "SETUP_ITLI3"); }
+        if (le != cudaSuccess) { bmgx_scratch_free(S.t, st); return bmgx_set_cuda_error(le, "SETUP_ITLI3"); }
         bmgx_count_launch(5);
     }
-    e = cudaFreeAsync(S.t, st);
+    e = bmgx_scratch_free(S.t, st);
     if (e != cudaSuccess) return bmgx_set_cuda_error(e, "SETUP_ITLI3/free");
     return BMGX_OK;
 }

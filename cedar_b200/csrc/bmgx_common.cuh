@@ -19,6 +19,9 @@ enum { MSOR = 2 };
 int bmgx_set_cuda_error(cudaError_t e, const char *where);
 int bmgx_set_error(int code, const char *msg);
 void bmgx_count_launch(unsigned n = 1);
+// stream-ordered workspace from the library's own memory pool (bmgx_util.cu)
+cudaError_t bmgx_scratch_alloc(void **p, size_t bytes, cudaStream_t st);
+cudaError_t bmgx_scratch_free(void *p, cudaStream_t st);
 // batch context (bmgx_set_batch): number of grid functions the batch-aware entry points process per call
 unsigned bmgx_batch();
 

@@ -24,6 +24,58 @@ extern "C" const char *bmgx_version(void) { return "bmgx 0.1 (sm_100a)"; }
 extern "C" const char *bmgx_last_error(void) { return g_err; }
 extern "C" unsigned long long bmgx_launch_count(void) { return g_launches.load(); }
 
+// ---- library-private scratch pool -------------------------------------------------
+// Setup kernels that need large transient workspace (3D Galerkin) take it stream-ordered
+// from a memory pool owned by this library, one per device, created on first use with
+// an unlimited release threshold so that repeated setups reuse the same pages instead
+// of paying cudaMalloc/cudaFree of >1 GB per call.  The application's default pool is
+// never touched; bmgx_scratch_trim() hands the cached pages back to the driver.
+#include <mutex>
+static std::mutex g_pool_mu;
+static cudaMemPool_t g_pool[64] = {};
+static cudaError_t scratch_pool(cudaMemPool_t *out)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    if (!g_pool[dev]) {
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        e = cudaMemPoolCreate(&g_pool[dev], &props);
+        if (e != cudaSuccess) { g_pool[dev] = nullptr; return e; }
+        unsigned long long keep = ~0ull;
+        e = cudaMemPoolSetAttribute(g_pool[dev], cudaMemPoolAttrReleaseThreshold, &keep);
+        if (e != cudaSuccess) return e;
+    }
+    *out = g_pool[dev];
+    return cudaSuccess;
+}
+cudaError_t bmgx_scratch_alloc(void **p, size_t bytes, cudaStream_t st)
+{
+    cudaMemPool_t pool;
+    cudaError_t e = scratch_pool(&pool);
+    if (e != cudaSuccess) return e;
+    return cudaMallocFromPoolAsync(p, bytes, pool, st);
+}
+cudaError_t bmgx_scratch_free(void *p, cudaStream_t st) { return cudaFreeAsync(p, st); }
+extern "C" int bmgx_scratch_trim(size_t keep_bytes)
+{
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return bmgx_set_cuda_error(e, "scratch_trim");
+    std::lock_guard<std::mutex> lk(g_pool_mu);
+    if (dev >= 0 && dev < 64 && g_pool[dev]) {
+        e = cudaMemPoolTrimTo(g_pool[dev], keep_bytes);
+        if (e != cudaSuccess) return bmgx_set_cuda_error(e, "scratch_trim");
+    }
+    return BMGX_OK;
+}
+
 // batch context, per host thread (the host layer is single threaded per solver)
 static thread_local unsigned g_batch = 1;
 unsigned bmgx_batch() { return g_batch; }

@@ -18,8 +18,8 @@ _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int)
 HANDLE_BYTES = 64
 
-lib.cdr2_dist_create.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, _ip, C.c_int, C.c_int, C.c_int,
-                                 C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+lib.cdr2_dist_create.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, _ip, C.c_int, C.c_int, C.c_char_p,
+                                 C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
 lib.cdr2_dist_sweep_rects.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                       _ip, C.c_int, _ip]
 lib.cdr2_dist_destroy.argtypes = [C.c_void_p]
@@ -39,8 +39,8 @@ lib.cdr2_dist_solve.argtypes = [C.c_void_p, C.c_int, C.c_double, _dp, C.c_int, _
 lib.cdr2_dist_time_vcycles.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float)]
 lib.cdr2_dist_vcycle_stream.argtypes = [C.c_void_p, C.c_int, C.POINTER(_dp), C.POINTER(_dp)]
 lib.cdr2_dist_profile_ops.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float), C.c_int, _ip]
-lib.cdr2_dist_plan_json.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
-                                    C.c_char_p, C.c_char_p, C.c_size_t, _ip]
+lib.cdr2_dist_plan_json.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int, C.c_int,
+                                    C.c_int, C.c_char_p, C.c_char_p, C.c_size_t, _ip]
 lib.cdr2_dist_geometry.argtypes = [C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _ip]
 
 _check = _cs._check
@@ -59,12 +59,12 @@ def _P(a):
 SPLIT_MIN = 0
 
 
-def plan(nx, ny, px, py, nst=5, pre=1, post=1, agglomerate=513, halo=15, what="cycle", split_min=SPLIT_MIN):
+def plan(nx, ny, px, py, nst=5, pre=1, post=1, agglomerate=513, halo=15, what="cycle", split_min=SPLIT_MIN, relaxation="point"):
     """(operation list, number of distributed levels): include/cedar/2d/mpi/plan.h; needs no device"""
     buf = C.create_string_buffer(1 << 20)
     nd = C.c_int()
-    _check(lib.cdr2_dist_plan_json(nx, ny, px, py, nst, pre, post, agglomerate, halo, split_min, what.encode(), buf, len(buf),
-                                   C.byref(nd)))
+    _check(lib.cdr2_dist_plan_json(nx, ny, px, py, nst, pre, post, relaxation.encode(), agglomerate, halo, split_min, what.encode(),
+                                   buf, len(buf), C.byref(nd)))
     return json.loads(buf.value.decode()), nd.value
 
 
@@ -121,11 +121,12 @@ class TorchComm:
 
 
 class DistSolver2:
-    """Block-decomposed BoxMG solver, point relaxation.  `blocks`: ids owned by this process (all of them when
-    comm is None: every block on this process's GPU)."""
+    """Block-decomposed BoxMG solver.  `blocks`: ids owned by this process (all of them when comm is None: every block
+    on this process's GPU).  relaxation: "point", "line-x", "line-y" or "line-xy" (lines that cross block cuts are
+    transposed over peer memory and solved whole, include/cedar/2d/mpi/plan.h)."""
 
     def __init__(self, nx, ny, decomp_shape, nst=5, blocks=None, nrelax_pre=1, nrelax_post=1, agglomerate=513, halo=15,
-                 cuda_graph=True, comm=None, split_min=SPLIT_MIN):
+                 cuda_graph=True, comm=None, split_min=SPLIT_MIN, relaxation="point"):
         px, py = decomp_shape
         self.nx, self.ny, self.px, self.py, self.nst, self.comm = nx, ny, px, py, nst, comm
         self.pre, self.post, self.agglomerate = nrelax_pre, nrelax_post, agglomerate
@@ -136,8 +137,9 @@ class DistSolver2:
         ids = (C.c_int * len(self.owned))(*self.owned)
         self.h = C.c_void_p()
         self.split_min = split_min
-        _check(lib.cdr2_dist_create(nx, ny, px, py, nst, len(self.owned), ids, nrelax_pre, nrelax_post, agglomerate, halo,
-                                    split_min, int(cuda_graph), C.byref(self.h)))
+        self.relaxation = relaxation
+        _check(lib.cdr2_dist_create(nx, ny, px, py, nst, len(self.owned), ids, nrelax_pre, nrelax_post, relaxation.encode(),
+                                    agglomerate, halo, split_min, int(cuda_graph), C.byref(self.h)))
         v = [C.c_int() for _ in range(5)]
         _check(lib.cdr2_dist_info(self.h, *[C.byref(t) for t in v]))
         self.ndist, self.nlevels, self.halo, self.exchanges_per_cycle, self.ops_per_cycle = [t.value for t in v]

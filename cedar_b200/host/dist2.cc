@@ -36,6 +36,16 @@ inline size_t up(size_t n) { return (n + ALIGN_D - 1) / ALIGN_D * ALIGN_D; }
 
 struct seg_table { bmgx_seg *dev = nullptr; int n = 0; int chunks = 1; };
 
+// lines of one direction through a block on one level (line relaxation across block cuts, plan.h line_group)
+struct line_store
+{
+	line_group grp;
+	double *sor = nullptr;                    // factor of the lines this block solves: 2 planes (mine + 2) x (len + 2)
+	double *strip = nullptr;                  // setup only: gathered diagonals, laid out like a serial operator
+	bmgx_line_group dst{};                    // where the right-hand sides go
+	std::map<int, bmgx_line_owners> own;      // where the solutions go, per iterate slot
+};
+
 struct dist_block
 {
 	int id = -1;
@@ -48,6 +58,7 @@ struct dist_block
 	double *tmpP = nullptr, *tmpA = nullptr;              // setup: contiguous coarse windows
 	double *work = nullptr, *red_all = nullptr, *norm_out = nullptr;
 	std::map<std::string, seg_table> segs;
+	std::map<std::pair<int, int>, line_store> lines;   // (level, direction)
 };
 
 }  // namespace
@@ -57,6 +68,7 @@ struct cdr2_dist
 	std::unique_ptr<decomp> dec;
 	std::unique_ptr<planner> plan;
 	int nst = 5, npre = 1, npost = 1, W = 15;
+	relax_kind relax = relax_kind::point;
 	bool use_graph = true;
 	double timeout_s = 10.0;
 	std::vector<dist_block> blk;                 // owned blocks
@@ -98,7 +110,22 @@ struct cdr2_dist
 		}
 		return o;
 	}
-	size_t arena_doubles(int b) const { return off_arr(b, dec->ndist + 1, 0); }
+	// line buffers (line relaxation) follow the arrays: one per relaxed level and line direction
+	bool relaxes(int dirn) const { return ((int)relax >> dirn) & 1; }
+	size_t off_lb(int b, int lvl, int dirn) const
+	{
+		size_t o = off_arr(b, dec->ndist + 1, 0);
+		for (int l = 0; l < dec->ndist; l++)
+			for (int dd = 0; dd < 2; dd++) {
+				if (!relaxes(dd)) continue;
+				if (l == lvl && dd == dirn) return o;
+				const line_group g = dec->lines(l, b, dd);
+				o += up((size_t)(g.mine() + 2) * (g.len + 2));
+			}
+		return o;
+	}
+	double *lb(int b, int lvl, int dirn) const { return reinterpret_cast<double *>(base[b]) + off_lb(b, lvl, dirn); }
+	size_t arena_doubles(int b) const { return off_lb(b, dec->ndist, 0); }
 	size_t plane_stride(int b, int lvl) const { const block_geom g = dec->geom(lvl, b); return (size_t)g.ii * g.jj; }
 	double *ptr(int b, int lvl, int a, int plane = 0) const
 	{
@@ -117,7 +144,7 @@ template <class F> int guard(F &&f)
 
 std::string key_of(const plan_op &o)
 {
-	std::string k = std::string(op_name(o.kind)) + ":" + std::to_string(o.lvl) + ":" + std::to_string(o.a);
+	std::string k = std::string(op_name(o.kind)) + ":" + std::to_string(o.lvl) + ":" + std::to_string(o.a) + ":" + std::to_string(o.dir);
 	for (int a : o.arrays) k += "," + std::to_string(a);
 	return k;
 }
@@ -188,6 +215,71 @@ std::vector<bmgx_seg> gather_segs(const cdr2_dist &d, int lvl, int a, double *gl
 	return v;
 }
 
+line_store &lines_of(cdr2_dist &d, dist_block &K, int lvl, int dirn)
+{
+	auto it = K.lines.find({lvl, dirn});
+	if (it != K.lines.end()) return it->second;
+	line_store ls;
+	ls.grp = d.dec->lines(lvl, K.id, dirn);
+	const line_group &g = ls.grp;
+	if (g.G > BMGX_LINE_GROUP_MAX) throw std::runtime_error("line relaxation: more than BMGX_LINE_GROUP_MAX blocks along a line");
+	ls.dst.nmembers = g.G;
+	ls.dst.pitch = (size_t)g.len + 2;
+	for (int m = 0; m <= g.G; m++) ls.dst.first[m] = g.first[m];
+	for (int m = 0; m < g.G; m++) ls.dst.lb[m] = d.lb(g.members[m], lvl, dirn);
+	return K.lines.emplace(std::make_pair(lvl, dirn), ls).first->second;
+}
+
+const bmgx_line_owners &owners_of(cdr2_dist &d, line_store &ls, int lvl, int dirn, int slot)
+{
+	auto it = ls.own.find(slot);
+	if (it != ls.own.end()) return it->second;
+	bmgx_line_owners o{};
+	const line_group &g = ls.grp;
+	o.nmembers = g.G;
+	for (int m = 0; m < g.G; m++) {
+		const block_geom h = d.dec->geom(lvl, g.members[m]);
+		o.start[m] = dirn == 0 ? h.x0 : h.y0;
+		o.w_along[m] = dirn == 0 ? h.wl : h.wb;
+		o.w_across = dirn == 0 ? h.wb : h.wl;
+		o.pitch[m] = h.ii;
+		o.q[m] = d.ptr(g.members[m], lvl, slot);
+	}
+	o.start[g.G] = g.len;
+	return ls.own.emplace(slot, o).first->second;
+}
+
+// diagonals (KO and the coupling along the line) of the lines this block solves, out of their owners' operators into
+// a strip laid out like a serial operator: x-lines (mine + 2) rows of len + 2, y-lines len + 2 rows of (mine + 2)
+std::vector<bmgx_seg> line_setup_segs(const cdr2_dist &d, int lvl, int dirn, const line_store &ls)
+{
+	std::vector<bmgx_seg> v;
+	const line_group &g = ls.grp;
+	const int mine = g.mine(), t0 = g.first[g.me];
+	if (mine == 0) return v;
+	const size_t sii = dirn == 0 ? g.len + 2 : mine + 2, sjj = dirn == 0 ? mine + 2 : g.len + 2;
+	const int planes[2] = {0, dirn == 0 ? 1 : 2};   // KO, KW | KS
+	for (int m = 0; m < g.G; m++) {
+		const int q = g.members[m];
+		const block_geom h = d.dec->geom(lvl, q);
+		for (int p : planes) {
+			bmgx_seg s{};
+			if (dirn == 0) {
+				s.src = d.ptr(q, lvl, A, p) + (size_t)(h.wb + t0) * h.ii + h.wl;
+				s.dst = ls.strip + (size_t)p * sii * sjj + sii + 1 + h.x0;
+				s.rows = mine; s.cols = h.nx;
+			} else {
+				s.src = d.ptr(q, lvl, A, p) + (size_t)h.wb * h.ii + h.wl + t0;
+				s.dst = ls.strip + (size_t)p * sii * sjj + (size_t)(1 + h.y0) * sii + 1;
+				s.rows = h.ny; s.cols = mine;
+			}
+			s.src_pitch = h.ii; s.dst_pitch = sii; s.src_rank = q;
+			v.push_back(s);
+		}
+	}
+	return v;
+}
+
 seg_table &table(cdr2_dist &d, dist_block &K, const plan_op &o)
 {
 	const std::string k = key_of(o);
@@ -199,6 +291,7 @@ seg_table &table(cdr2_dist &d, dist_block &K, const plan_op &o)
 	case op_kind::exchange: v = exchange_segs(d, o.lvl, K.id, o.arrays); break;
 	case op_kind::gather: v = gather_segs(d, nd, o.a, K.GB); break;   // GB = the replicated solver's own right-hand side
 	case op_kind::gather_op: v = gather_segs(d, nd, A, K.GA); break;
+	case op_kind::setup_lines: v = line_setup_segs(d, o.lvl, o.dir, lines_of(d, K, o.lvl, o.dir)); break;
 	case op_kind::norm:
 		for (int q = 0; q < d.nblocks(); q++) {
 			bmgx_seg s{};
@@ -239,6 +332,27 @@ void run_op(cdr2_dist &d, const plan_op &o)
 	case op_kind::join:
 		// the exchange started by the matching asynchronous operation has delivered the halos
 		if (d.overlap) check(bmgx_stream_wait_event(s, d.join_ev[o.id]), "join");
+		return;
+	case op_kind::setup_lines:
+		// gather the diagonals of my lines (every rank waits for every rank: the operators are complete), factor them
+		for (auto &K : d.blk) {
+			line_store &ls = lines_of(d, K, l, o.dir);
+			const int mine = ls.grp.mine();
+			if (mine == 0) continue;
+			const size_t n = (size_t)(mine + 2) * (ls.grp.len + 2);
+			check(bmgx_malloc((void **)&ls.strip, 3 * n * 8), "line strip");
+			check(bmgx_malloc((void **)&ls.sor, 2 * n * 8), "line factor");
+			check(bmgx_memset0(ls.strip, 3 * n * 8, s), "line strip");
+			check(bmgx_memset0(ls.sor, 2 * n * 8, s), "line factor");
+		}
+		step(d, o, s);
+		for (auto &K : d.blk) {
+			line_store &ls = lines_of(d, K, l, o.dir);
+			const int mine = ls.grp.mine();
+			if (mine == 0) continue;
+			if (o.dir == 0) check(bmgx2_SETUP_lines_x(ls.strip, ls.sor, ls.grp.len + 2, mine + 2, 3, 0, s), "SETUP_lines_x");
+			else check(bmgx2_SETUP_lines_y(ls.strip, ls.sor, mine + 2, ls.grp.len + 2, 3, 0, s), "SETUP_lines_y");
+		}
 		return;
 	case op_kind::exchange: case op_kind::sync: case op_kind::gather: case op_kind::gather_op: case op_kind::norm:
 		if (o.async && d.overlap) {
@@ -285,6 +399,22 @@ void run_op(cdr2_dist &d, const plan_op &o)
 					                               o.dir ? BMGX_UP : BMGX_DOWN, 0, br, (int)rs.size(), s), "relax_GS_oop_rects");
 			}
 			break;
+		case op_kind::lines_rhs: {
+			line_store &ls = lines_of(d, K, l, o.dir);
+			check(bmgx2_lines_rhs_push(o.dir, ifd ? 0 : 1, d.ptr(b, l, A), d.ptr(b, l, B), d.ptr(b, l, o.a), g.ii, g.jj, g.wl, g.wb,
+			                           g.nx, g.ny, o.part, 1 + (o.dir == 0 ? g.x0 : g.y0), &ls.dst, s), "lines_rhs_push");
+			break;
+		}
+		case op_kind::lines_solve: {
+			line_store &ls = lines_of(d, K, l, o.dir);
+			const int mine = ls.grp.mine();
+			if (mine == 0) break;
+			double *buf = d.lb(b, l, o.dir);
+			check(bmgx2_lines_solve_T(buf, ls.sor, mine + 2, ls.grp.len + 2, o.part, s), "lines_solve_T");
+			check(bmgx2_lines_scatter_push(o.dir, buf, mine + 2, ls.grp.len + 2, o.part, ls.grp.first[ls.grp.me],
+			                               &owners_of(d, ls, l, o.dir, o.a), s), "lines_scatter_push");
+			break;
+		}
 		case op_kind::residual:
 			check(bmgx2_residual(0, d.ptr(b, l, A), d.ptr(b, l, B), d.ptr(b, l, o.a), d.ptr(b, l, RES), g.ii, g.jj, 0, ifd, nst,
 			                     0, 0, 0, 0, s), "residual");
@@ -356,7 +486,7 @@ void run_op(cdr2_dist &d, const plan_op &o)
 			check(bmgx_memcpy_d2h(h, K.GA, n * 8, s), "agglomerated operator download");
 			check(bmgx_stream_sync(s), "sync");
 			const int nl = dec.nlevels - nd;
-			const std::string cfg = "{\"log\": [\"error\"], \"solver\": {\"relaxation\": \"point\", \"cycle\": {\"type\": \"v\", "
+			const std::string cfg = "{\"log\": [\"error\"], \"solver\": {\"relaxation\": \"" + std::string(relax_name(d.relax)) + "\", \"cycle\": {\"type\": \"v\", "
 			                        "\"nrelax-pre\": " + std::to_string(d.npre) + ", \"nrelax-post\": " + std::to_string(d.npost) +
 			                        "}, \"max-iter\": 1, \"tol\": 0, \"cuda-graph\": false, \"num-levels\": " + std::to_string(nl) + "}}";
 			if (cdr2_solver_create(K.cop, cfg.c_str(), &K.csol)) throw std::runtime_error(cdr_last_error());
@@ -413,12 +543,14 @@ dist_block &find(cdr2_dist &d, int b)
 extern "C" {
 
 int cdr2_dist_create(unsigned gnx, unsigned gny, int px, int py, int nstencil, int nowned, const int *owned, int nrelax_pre,
-                     int nrelax_post, int agglomerate, int halo_width, int split_min, int use_graph, cdr2_dist **out)
+                     int nrelax_post, const char *relaxation, int agglomerate, int halo_width, int split_min, int use_graph,
+                     cdr2_dist **out)
 {
 	return guard([&] {
 		if (nstencil != 3 && nstencil != 5) throw std::runtime_error("nstencil must be 3 or 5");
 		if (!cedar::gpu::available()) throw std::runtime_error("no CUDA device: the BoxMG kernels have no CPU fallback");
 		auto d = std::make_unique<cdr2_dist>();
+		d->relax = relax_from_name(relaxation ? relaxation : "point");
 		d->nst = nstencil; d->npre = nrelax_pre; d->npost = nrelax_post; d->W = halo_width; d->use_graph = use_graph != 0;
 		if (const char *t = getenv("CDR_HALO_TIMEOUT_S")) d->timeout_s = atof(t);
 		const int nl = compute_num_levels(gnx, gny);
@@ -430,7 +562,8 @@ int cdr2_dist_create(unsigned gnx, unsigned gny, int px, int py, int nstencil, i
 			catch (std::invalid_argument &) { if (ndist <= 1) throw; }
 		}
 		d->plan = std::make_unique<planner>(d->dec->ndist, halo_width, nstencil == 3 ? 2 : 4, nrelax_pre, nrelax_post,
-		                                    d->dec->split_levels(split_min));
+		                                    d->relax == relax_kind::point ? d->dec->split_levels(split_min) : 0, 4, false, false,
+		                                    d->relax);
 		d->p_setup = d->plan->setup(); d->p_cycle = d->plan->cycle(); d->p_norm = d->plan->norm();
 		if (const char *e = getenv("CDR_DIST_OVERLAP")) d->overlap = atoi(e) != 0;
 		for (auto &o : d->p_cycle)
@@ -483,6 +616,7 @@ void cdr2_dist_destroy(cdr2_dist *d)
 		for (auto &kv : K.segs) if (kv.second.dev) bmgx_free(kv.second.dev);
 		if (K.csol) cdr2_solver_destroy(K.csol);
 		if (K.cop) cdr2_operator_destroy(K.cop);
+		for (auto &kv : K.lines) { if (kv.second.sor) bmgx_free(kv.second.sor); if (kv.second.strip) bmgx_free(kv.second.strip); }
 		bmgx_free(K.GA); bmgx_free(K.tmpP); bmgx_free(K.tmpA); bmgx_free(K.work);
 		bmgx_free(K.arena);
 	}
@@ -566,7 +700,10 @@ int cdr2_dist_setup(cdr2_dist *d)
 		run(*d, d->p_setup);
 		check(bmgx_stream_sync(d->stream), "sync");
 		check_device_error(*d);
-		for (auto &K : d->blk) { bmgx_free(K.tmpP); bmgx_free(K.tmpA); bmgx_free(K.GA); K.tmpP = K.tmpA = K.GA = nullptr; }
+		for (auto &K : d->blk) {
+			bmgx_free(K.tmpP); bmgx_free(K.tmpA); bmgx_free(K.GA); K.tmpP = K.tmpA = K.GA = nullptr;
+			for (auto &kv : K.lines) if (kv.second.strip) { bmgx_free(kv.second.strip); kv.second.strip = nullptr; }
+		}
 		d->is_setup = true;
 	});
 }
@@ -748,7 +885,8 @@ int cdr2_dist_profile_ops(cdr2_dist *d, int n, float *out, int cap, int *nops)
 
 /* the operation lists as JSON (host only, no device needed): what = "setup", "cycle" or "norm" */
 int cdr2_dist_plan_json(unsigned gnx, unsigned gny, int px, int py, int nstencil, int nrelax_pre, int nrelax_post,
-                        int agglomerate, int halo_width, int split_min, const char *what, char *out, size_t cap, int *ndist_out)
+                        const char *relaxation, int agglomerate, int halo_width, int split_min, const char *what, char *out,
+                        size_t cap, int *ndist_out)
 {
 	return guard([&] {
 		const int nl = compute_num_levels(gnx, gny);
@@ -760,7 +898,9 @@ int cdr2_dist_plan_json(unsigned gnx, unsigned gny, int px, int py, int nstencil
 			try { dec = std::make_unique<decomp>(gnx, gny, px, py, ndist, halo_width); break; }
 			catch (std::invalid_argument &) { if (ndist <= 1) throw; }
 		}
-		planner pl(dec->ndist, halo_width, nstencil == 3 ? 2 : 4, nrelax_pre, nrelax_post, dec->split_levels(split_min));
+		const relax_kind rk = relax_from_name(relaxation ? relaxation : "point");
+		planner pl(dec->ndist, halo_width, nstencil == 3 ? 2 : 4, nrelax_pre, nrelax_post,
+		           rk == relax_kind::point ? dec->split_levels(split_min) : 0, 4, false, false, rk);
 		const std::string w(what);
 		const std::string js = planner::to_json(w == "setup" ? pl.setup() : w == "norm" ? pl.norm() : pl.cycle());
 		if (js.size() + 1 > cap) throw std::runtime_error("plan buffer too small");

@@ -47,6 +47,10 @@ const char *bmgx_version(void);
 const char *bmgx_last_error(void);
 /* number of kernels this library has launched so far (process wide) */
 unsigned long long bmgx_launch_count(void);
+/* Transient setup workspace (3D Galerkin) comes stream-ordered from a memory pool this library owns (one per
+ * device, cached between calls; the application's default pool is never reconfigured).  Return what is cached beyond
+ * keep_bytes to the driver. */
+int bmgx_scratch_trim(size_t keep_bytes);
 
 /* BMG_get_bc, src/2d/ftn/BMG_get_bc.f90:1-24 */
 void bmgx_get_bc(int per_mask, int *ibc);
@@ -165,6 +169,41 @@ int bmgx2_relax_lines_y(int k, const bmgx_real *so, const bmgx_real *qf, bmgx_re
                         const bmgx_real *sor, bmgx_real *b, bmgx_len ii, bmgx_len jj,
                         int kf, int ifd, int nstncl, int irelax_sym, int updown, int jpn,
                         bmgx_stream_t s);
+
+/* Lines that cross block cuts (the decomposed solver).  Counterpart of the reference's interface-system line solve
+ * BMG2_SymStd_relax_lines_x/_y of src/2d/ftn/mpi/ (LineSolve_A/B/C, :156-215) -- here the blocks that share lines
+ * transpose them over peer memory and the serial solve runs on whole lines (cedar_b200/csrc/bmgx2_lines.cu).
+ * A line buffer has rows 1 .. (lines its block solves), row pitch = global line length + 2, the unknown with global
+ * F-index p + 1 in column p; the factor `sor` (2 planes of the same shape) comes from bmgx2_SETUP_lines_x/_y on a
+ * strip of gathered diagonals. */
+#define BMGX_LINE_GROUP_MAX 16
+typedef struct {
+    int nmembers;                         /* blocks that share the lines */
+    int first[BMGX_LINE_GROUP_MAX + 1];   /* member m solves the group's lines first[m] .. first[m+1]-1 (even bounds) */
+    size_t pitch;                         /* global line length + 2 */
+    bmgx_real *lb[BMGX_LINE_GROUP_MAX];   /* line buffers of the members as mapped in this process */
+} bmgx_line_group;
+typedef struct {
+    int nmembers;
+    int start[BMGX_LINE_GROUP_MAX + 1];   /* member m owns the positions start[m] .. start[m+1]-1 (0-based) of a line */
+    int w_along[BMGX_LINE_GROUP_MAX];     /* array index of member m's first own point along the line */
+    int w_across;                         /* array index of the group's first line (the same for every member) */
+    size_t pitch[BMGX_LINE_GROUP_MAX];    /* row pitch of member m's array */
+    bmgx_real *q[BMGX_LINE_GROUP_MAX];    /* the members' iterates as mapped in this process */
+} bmgx_line_owners;
+/* right-hand sides of the own points (nx x ny, first at array entry [wb][wl]) of the lines of one colour -- dirn 0:
+ * x-lines, own rows t with t = first_findex (mod 2); dirn 1: y-lines, own columns likewise -- stored at column
+ * col0 + (own index along the line) of the line's row in its solver's buffer.  The expression is the serial
+ * kernels' (BMG2_SymStd_relax_lines_x.f90:100-128, _y.f90:99-127). */
+int bmgx2_lines_rhs_push(int dirn, int nine, const bmgx_real *so, const bmgx_real *qf, const bmgx_real *q, bmgx_len ii,
+                         bmgx_len jj, bmgx_len wl, bmgx_len wb, bmgx_len nx, bmgx_len ny, int first_findex,
+                         bmgx_len col0, const bmgx_line_group *g, bmgx_stream_t s);
+/* DPTTRS on the rows ibeg-1, ibeg+1, ... of a line buffer of nrows2 = lines + 2 rows and pitch len2 = length + 2, in
+ * place: the second step of bmgx2_relax_lines_y */
+int bmgx2_lines_solve_T(bmgx_real *lb, const bmgx_real *sor, bmgx_len nrows2, bmgx_len len2, int ibeg, bmgx_stream_t s);
+/* the solved rows of that colour -> the owners' iterates; tfirst = the group line held by row 1 */
+int bmgx2_lines_scatter_push(int dirn, const bmgx_real *lb, bmgx_len nrows2, bmgx_len len2, int ibeg, bmgx_len tfirst,
+                             const bmgx_line_owners *o, bmgx_stream_t s);
 
 /* BMG2_SymStd_residual(k, so, qf, q, res, ii, jj, kf, ifd, nstncl, ibc,
  *                      irelax, irelax_sym, updown)   [by reference there]

@@ -59,6 +59,24 @@ inline int compute_num_levels(int nx, int ny, int min_coarse = 3)   // include/c
 // array slots of a level
 enum arr { X0 = 0, X1 = 1, B = 2, RES = 3, A = 4, SOR = 5, P = 6, NARR = 7 };
 
+// Lines that cross block cuts.  The reference reduces every cut line to an interface system (LineSolve_A ->
+// gather -> LineSolve_B -> scatter -> LineSolve_C, src/2d/ftn/mpi/BMG2_SymStd_relax_lines_x.f90:156-215), three
+// latency-bound stages per colour whose arithmetic differs from the serial solve.  With every GPU one NVSwitch hop
+// from every other the lines are TRANSPOSED instead: the blocks of one process row (x-lines; column for y-lines)
+// share their lines out evenly; each block builds the right-hand side of its own points and stores it straight into
+// the line buffer of the line's solver (peer memory), the solver runs the serial factor/solve on whole lines and
+// stores the solution back into the owners' iterate.  Same operands, same order as the serial kernels: the
+// decomposed line relaxation equals the serial GPU solver bit for bit.
+struct line_group
+{
+	int G = 1, me = 0;               // blocks in the group and this block's place in it
+	std::vector<int> members;        // block ids, in line direction order
+	int nlines = 0, len = 0;         // lines the group owns (own extent across the lines), global line length
+	std::vector<int> first;          // first[m] .. first[m+1]: lines (0-based within the group) member m solves; even
+	int off0 = 0;                    // global interior index (0-based) of the group's first line
+	int mine() const { return first[me + 1] - first[me]; }
+};
+
 // geometry of one block on one level: own points and the halo-extended array that holds them
 struct block_geom
 {
@@ -109,6 +127,23 @@ struct decomp
 		g.wl = cx > 0 ? W : 1; g.wr = cx + 1 < px ? W : 1;
 		g.wb = cy > 0 ? W : 1; g.wt = cy + 1 < py ? W : 1;
 		g.ii = g.nx + g.wl + g.wr; g.jj = g.ny + g.wb + g.wt;
+		return g;
+	}
+	// the group of blocks that shares the lines of direction dirn (0 = x-lines: the process row, 1 = y-lines: the
+	// process column) through block b on level lvl, and how the group's lines are shared out
+	line_group lines(int lvl, int b, int dirn) const
+	{
+		const int cx = b % px, cy = b / px;
+		line_group g;
+		g.G = dirn == 0 ? px : py;
+		g.me = dirn == 0 ? cx : cy;
+		for (int m = 0; m < g.G; m++) g.members.push_back(dirn == 0 ? cy * px + m : m * px + cx);
+		const block_geom k = geom(lvl, b);
+		g.nlines = dirn == 0 ? k.ny : k.nx;
+		g.off0 = dirn == 0 ? k.y0 : k.x0;
+		g.len = gn[lvl][dirn];
+		if (g.off0 % 2) throw std::logic_error("block boundaries of a relaxed level must be even");
+		for (int m = 0; m <= g.G; m++) g.first.push_back(m == g.G ? g.nlines : (int)((long)m * g.nlines / g.G) / 2 * 2);
 		return g;
 	}
 	// leading levels on which every block has at least `split_min` own points per dimension (sweeps are split there)
@@ -177,7 +212,24 @@ inline std::vector<sweep_rect> sweep_rects(const block_geom &g, int nc, int part
 }
 
 enum class op_kind { exchange, sync, sweep, residual, restrict_, zero, gather, coarse, scatter, interp, copy, sumsq, norm,
-                     recip, setup_interp, galerkin, gather_op, setup_coarse, join };
+                     recip, setup_interp, galerkin, gather_op, setup_coarse, join, lines_rhs, lines_solve, setup_lines };
+
+// relaxation of the distributed levels (config "solver.relaxation": point, line-x, line-y, line-xy)
+enum class relax_kind { point = 0, line_x = 1, line_y = 2, line_xy = 3 };
+inline relax_kind relax_from_name(const std::string &n)
+{
+	if (n == "point") return relax_kind::point;
+	if (n == "line-x") return relax_kind::line_x;
+	if (n == "line-y") return relax_kind::line_y;
+	if (n == "line-xy") return relax_kind::line_xy;
+	throw std::invalid_argument("relaxation of the decomposed 2D solver: point, line-x, line-y or line-xy");
+}
+inline const char *relax_name(relax_kind k)
+{
+	static const char *n[] = {"point", "line-x", "line-y", "line-xy"};
+	return n[(int)k];
+}
+
 
 struct plan_op
 {
@@ -190,13 +242,15 @@ struct plan_op
 	bool async = false;         // exchange: runs beside the following operations until the matching `join`
 	int part = 0;               // sweep: 0 = whole array, 1 = interior, 2 = frames (sweep_rects)
 	int id = 0;                 // async exchange / join: running number of the pair within the list
+	// lines_rhs / lines_solve / setup_lines: dir = 0 x-lines, 1 y-lines; part = F-index parity class of the colour:
+	// the global F-index (2 = first interior line) of the colour's lines is part, part + 2, ...
 };
 
 inline const char *op_name(op_kind k)
 {
 	static const char *n[] = {"exchange", "sync", "sweep", "residual", "restrict", "zero", "gather", "coarse", "scatter",
 	                          "interp", "copy", "sumsq", "norm", "recip", "setup_interp", "galerkin", "gather_op",
-	                          "setup_coarse", "join"};
+	                          "setup_coarse", "join", "lines_rhs", "lines_solve", "setup_lines"};
 	return n[(int)k];
 }
 
@@ -211,9 +265,9 @@ public:
 	// decomposed 3D path: 2, the depth of the colour ordering across planes).  inplace0 / inplace_coarse: the sweep
 	// kernel of that level works in place (3D 27-point) instead of from one array into the other.
 	planner(int ndist, int W, int ncol0, int npre, int npost, int split_levels = 0, int ncol_coarse = 4, bool inplace0 = false,
-	        bool inplace_coarse = false)
+	        bool inplace_coarse = false, relax_kind relax = relax_kind::point)
 	    : ndist(ndist), W(W), ncol0(ncol0), npre(npre), npost(npost), split_levels(split_levels), ncol_coarse(ncol_coarse),
-	      inplace0(inplace0), inplace_coarse(inplace_coarse)
+	      inplace0(inplace0), inplace_coarse(inplace_coarse), relax(relax)
 	{
 		if (npre + npost < 1) throw std::invalid_argument("a cycle needs at least one sweep");
 		// a whole 4-colour sweep over the extended array must leave the own points exact: colour c is exact out to line
@@ -234,6 +288,15 @@ public:
 			push(op_kind::galerkin, l);              // writes A of level l+1
 			exchange(l + 1, {A}, false);
 		}
+		// line relaxation: every block pulls the diagonals of the lines it solves out of their owners' operators and
+		// factors them (a gather: every rank waits for every rank)
+		for (int l = 0; l < ndist && relax != relax_kind::point; l++)
+			for (int dirn = 0; dirn < 2; dirn++)
+				if ((int)relax & (1 << dirn)) {
+					plan_op o; o.kind = op_kind::setup_lines; o.lvl = l; o.dir = dirn; o.a = A; o.wait_all = true;
+					ops.push_back(o);
+					step++; last_all = step;
+				}
 		gather(op_kind::gather_op, ndist, A);
 		push(op_kind::setup_coarse, ndist);
 		return take();
@@ -293,6 +356,7 @@ private:
 	static constexpr int INF = 1 << 20;
 	int ndist, W, ncol0, npre, npost, split_levels, ncol_coarse;
 	bool inplace0, inplace_coarse;
+	relax_kind relax;
 	std::vector<plan_op> ops;
 	std::vector<std::array<int, 4>> val;   // X0, X1, B, RES: halo lines that hold the neighbours' exact values
 	std::vector<int> cur;                  // slot that holds the iterate of each level
@@ -366,8 +430,36 @@ private:
 	int ncol(int lvl) const { return lvl == 0 ? ncol0 : ncol_coarse; }
 	bool inplace(int lvl) const { return lvl == 0 ? inplace0 : inplace_coarse; }
 
+	// zebra line relaxation of the iterate, in place (src/2d/ftn/BMG2_SymStd_relax_lines_x.f90:83-99: on the way down
+	// the odd lines first; include/cedar/multilevel.h:165-180: x then y on the way down, y then x on the way up).  Per
+	// colour: right-hand sides of the own points into the solvers' line buffers; every rank waits for every rank; whole
+	// lines are solved and stored into their owners' iterate; the ghost exchange that follows waits for every rank too,
+	// because a block's own lines were written by the other blocks of its group.
+	void line_sweep(int l, int dir)
+	{
+		const int x = cur[l];
+		for (int k = 0; k < 2; k++) {
+			const int dirn = dir == 0 ? k : 1 - k;
+			if (!((int)relax & (1 << dirn))) continue;
+			for (int a = 0; a < 2; a++) {
+				const int first = dir == 0 ? 3 - a : 2 + a;
+				if (val[l][x] < 1) exchange(l, {x}, false);
+				plan_op r; r.kind = op_kind::lines_rhs; r.lvl = l; r.a = x; r.dir = dirn; r.part = first;
+				ops.push_back(r);
+				plan_op sy; sy.kind = op_kind::sync; sy.wait_all = true;
+				ops.push_back(sy);
+				step++; last_all = step;
+				before_write(l, x);
+				plan_op sv = r; sv.kind = op_kind::lines_solve;
+				ops.push_back(sv);
+				exchange(l, {x}, true);
+			}
+		}
+	}
+
 	void sweep(int l, int dir)
 	{
+		if (relax != relax_kind::point) { line_sweep(l, dir); return; }
 		const int nc = ncol(l), src = cur[l], dst = inplace(l) ? src : (src == X0 ? X1 : X0);
 		std::vector<int> need;
 		if (std::min(val[l][src] - 1, W - 1) - (nc - 1) < 0) need.push_back(src);

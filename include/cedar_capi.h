@@ -114,8 +114,8 @@ typedef struct cdr2_dist cdr2_dist;
  * the frames follow when the halos have arrived (0 = never; CDR_DIST_OVERLAP=0 in the environment runs the same
  * operation list without the second stream). */
 int cdr2_dist_create(unsigned nx, unsigned ny, int px, int py, int nstencil, int nowned, const int *owned_blocks,
-                     int nrelax_pre, int nrelax_post, int agglomerate, int halo_width, int split_min, int cuda_graph,
-                     cdr2_dist **out);
+                     int nrelax_pre, int nrelax_post, const char *relaxation, int agglomerate, int halo_width, int split_min,
+                     int cuda_graph, cdr2_dist **out);
 void cdr2_dist_destroy(cdr2_dist *d);
 int cdr2_dist_info(cdr2_dist *d, int *ndist, int *nlevels, int *halo_width, int *exchanges_per_cycle, int *ops_per_cycle);
 /* first own point (0-based global interior index) and own counts of a block on a distributed level */
@@ -142,7 +142,8 @@ int cdr2_dist_profile_ops(cdr2_dist *d, int n, float *ms_per_op, int cap, int *n
 /* host-only views of the schedule (no device needed): operation list as JSON, block geometry
  * (x0,y0,nx,ny, wl,wr,wb,wt, coarse window ox,oy,iic,jjc) */
 int cdr2_dist_plan_json(unsigned nx, unsigned ny, int px, int py, int nstencil, int nrelax_pre, int nrelax_post,
-                        int agglomerate, int halo_width, int split_min, const char *what, char *out, size_t cap, int *ndist);
+                        const char *relaxation, int agglomerate, int halo_width, int split_min, const char *what, char *out,
+                        size_t cap, int *ndist);
 /* rectangles of a split sweep (part 1 = interior, 2 = frames) of a block: 8 ints each (i0, j0, ni, nj, wi0, wi1, wj0, wj1),
  * the bmgx_rect of include/bmgx.h */
 int cdr2_dist_sweep_rects(unsigned nx, unsigned ny, int px, int py, int ndist, int halo_width, int lvl, int block,

@@ -16,14 +16,17 @@ NPL = {X0: 1, X1: 1, B: 1, RES: 1, SOR: 2, PI: 8}
 
 
 class PlanSim:
-    def __init__(self, nx, ny, px, py, so_blocks, pre=1, post=1, agglomerate=33, halo=15, dist=None, poison=True, split_min=0):
+    def __init__(self, nx, ny, px, py, so_blocks, pre=1, post=1, agglomerate=33, halo=15, dist=None, poison=True, split_min=0,
+                 relaxation="point"):
         """so_blocks: {block: (nst, nyl+2, nxl+2)} own entries of the blocks this process owns"""
         self.L = oracle.lib()
         self.nx, self.ny, self.px, self.py, self.W = nx, ny, px, py, halo
         self.pre, self.post, self.dist = pre, post, dist
         self.owned = sorted(so_blocks)
         self.nst = next(iter(so_blocks.values())).shape[0]
-        kw = dict(nst=self.nst, pre=pre, post=post, agglomerate=agglomerate, halo=halo, split_min=split_min)
+        self.relaxation = relaxation
+        self.lfac, self.lrhs = {}, {}
+        kw = dict(nst=self.nst, pre=pre, post=post, agglomerate=agglomerate, halo=halo, split_min=split_min, relaxation=relaxation)
         self.pending = {}
         self.p_setup, self.nd = d2.plan(nx, ny, px, py, what="setup", **kw)
         self.p_cycle, _ = d2.plan(nx, ny, px, py, what="cycle", **kw)
@@ -273,8 +276,92 @@ class PlanSim:
         self.GA = self._gather(self.nd, A)
 
     def op_setup_coarse(self, o):
-        self.csol = oracle.Solver2(self.GA, "point", self.pre, self.post, num_levels=self.nlevels - self.nd)
+        self.csol = oracle.Solver2(self.GA, self.relaxation, self.pre, self.post, num_levels=self.nlevels - self.nd)
         assert self.csol.nlevels == self.nlevels - self.nd
+
+    # -- line relaxation across block cuts: the blocks transpose their lines (plan.h line_group).  Here: the serial
+    # factor of the gathered operator, right-hand sides of the own points in the serial kernels' term order, DPTTS2 on
+    # whole lines, own segments back
+    def _allgather(self, parts):
+        if self.dist is None:
+            return parts
+        allp = [None] * self.dist.get_world_size()
+        self.dist.all_gather_object(allp, parts)
+        return {k: v for p in allp for k, v in p.items()}
+
+    def op_setup_lines(self, o):
+        self.exchanges += 1
+        l, dirn = o["lvl"], o["dir"]
+        GA = self._gather(l, A)
+        gx, gy = self.gn[l]
+        if dirn == 0:
+            sor = np.zeros((2, gy + 2, gx + 2))
+            assert self.L.orc2_setup_lines_x(P(GA), P(sor), gx + 2, gy + 2, self._nstl(l), 0) == 0
+        else:
+            sor = np.zeros((2, gx + 2, gy + 2))
+            assert self.L.orc2_setup_lines_y(P(GA), P(sor), gx + 2, gy + 2, self._nstl(l), 0) == 0
+        self.lfac[l, dirn] = sor
+
+    def op_lines_rhs(self, o):
+        l, dirn, t0 = o["lvl"], o["dir"], o["part"] & 1
+        for b, g in self._each(o):
+            so, qf, q = self.a[l, b, A], self.a[l, b, B][0], self.a[l, b, o["a"]][0]
+            assert g["y0"] % 2 == 0 and g["x0"] % 2 == 0
+            if dirn == 0:
+                rs, cs = slice(g["wb"] + t0, g["wb"] + g["ny"], 2), slice(g["wl"], g["wl"] + g["nx"])
+            else:
+                rs, cs = slice(g["wb"], g["wb"] + g["ny"]), slice(g["wl"] + t0, g["wl"] + g["nx"], 2)
+            sh = lambda a, dj, di: a[slice(rs.start + dj, rs.stop + dj, rs.step), slice(cs.start + di, cs.stop + di, cs.step)]
+            if dirn == 0:
+                r = sh(qf, 0, 0) + sh(so[2], 0, 0) * sh(q, -1, 0) + sh(so[2], 1, 0) * sh(q, 1, 0)
+            else:
+                r = sh(qf, 0, 0) + sh(so[1], 0, 0) * sh(q, 0, -1) + sh(so[1], 0, 1) * sh(q, 0, 1)
+            if not self._ifd(l):
+                r = r + sh(so[3], 0, 0) * sh(q, -1, -1) + sh(so[4], 0, 1) * sh(q, -1, 1) + sh(so[4], 1, 0) * sh(q, 1, -1) \
+                    + sh(so[3], 1, 1) * sh(q, 1, 1)
+            self.lrhs[b] = (rs, cs, r)
+
+    def op_lines_solve(self, o):
+        l, dirn, t0 = o["lvl"], o["dir"], o["part"] & 1
+        gx, gy = self.gn[l]
+        parts = {}
+        for b, g in self._each(o):
+            rs, cs, r = self.lrhs[b]
+            parts[b] = r
+        parts = self._allgather(parts)
+        R = np.zeros((gy, gx))      # global interior; only the lines of the colour are filled
+        for b, r in parts.items():
+            g = self.g[l, b]
+            if dirn == 0:
+                R[g["y0"] + t0:g["y0"] + g["ny"]:2, g["x0"]:g["x0"] + g["nx"]] = r
+            else:
+                R[g["y0"]:g["y0"] + g["ny"], g["x0"] + t0:g["x0"] + g["nx"]:2] = r
+        sor = self.lfac[l, dirn]
+        if dirn == 0:
+            lines = np.arange(t0, gy, 2)
+            bb, d, e = R[lines, :].copy(), sor[0, 1 + lines, 1:-1], sor[1, 1 + lines, 2:-1]
+        else:
+            lines = np.arange(t0, gx, 2)
+            bb, d, e = R[:, lines].T.copy(), sor[0, 1 + lines, 1:-1], sor[1, 1 + lines, 2:-1]
+        n = bb.shape[1]
+        if n == 1:
+            bb[:, 0] = bb[:, 0] * (1.0 / d[:, 0])
+        else:
+            for i in range(1, n):
+                bb[:, i] = bb[:, i] - bb[:, i - 1] * e[:, i - 1]
+            bb[:, n - 1] = bb[:, n - 1] / d[:, n - 1]
+            for i in range(n - 2, -1, -1):
+                bb[:, i] = bb[:, i] / d[:, i] - bb[:, i + 1] * e[:, i]
+        if dirn == 0:
+            R[lines, :] = bb
+        else:
+            R[:, lines] = bb.T
+        for b, g in self._each(o):
+            x = self.a[l, b, o["a"]][0]
+            if dirn == 0:
+                x[g["wb"] + t0:g["wb"] + g["ny"]:2, g["wl"]:g["wl"] + g["nx"]] = R[g["y0"] + t0:g["y0"] + g["ny"]:2, g["x0"]:g["x0"] + g["nx"]]
+            else:
+                x[g["wb"]:g["wb"] + g["ny"], g["wl"] + t0:g["wl"] + g["nx"]:2] = R[g["y0"]:g["y0"] + g["ny"], g["x0"] + t0:g["x0"] + g["nx"]:2]
 
     def op_sumsq(self, o):
         for b, _ in self._each(o):

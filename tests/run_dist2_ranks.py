@@ -20,14 +20,18 @@ def main():
     import cedar_b200.solver as cs
     from tests.util import random_gf, random_op2
     ok = True
-    for (nx, ny, nine, agg, halo, pre, post, split) in [(1025, 769, True, 65, 15, 1, 1, 0), (700, 900, False, 65, 7, 2, 1, 0),
-                                                        (2049, 1537, True, 129, 15, 1, 1, 128), (1400, 1800, True, 65, 9, 2, 2, 100)]:
+    for (nx, ny, nine, agg, halo, pre, post, split, relaxation) in [
+            (1025, 769, True, 65, 15, 1, 1, 0, "point"), (700, 900, False, 65, 7, 2, 1, 0, "point"),
+            (2049, 1537, True, 129, 15, 1, 1, 128, "point"), (1400, 1800, True, 65, 9, 2, 2, 100, "point"),
+            # lines across the block cuts: transposed over peer memory, solved whole (plan.h line_group)
+            (1025, 769, True, 65, 5, 1, 1, 0, "line-xy"), (1100, 900, False, 65, 5, 2, 1, 0, "line-x"),
+            (2049, 1537, True, 129, 7, 1, 1, 0, "line-y")]:
         px, py = d2.grid_decomp((nx, ny), world)
         rng = np.random.default_rng(nx + ny)
         so = random_op2(nx, ny, nine, rng)
         b = random_gf(nx, ny, rng)
         sol = d2.DistSolver2(nx, ny, (px, py), nst=so.shape[0], nrelax_pre=pre, nrelax_post=post, agglomerate=agg, halo=halo,
-                             comm=d2.TorchComm(), split_min=split)
+                             comm=d2.TorchComm(), split_min=split, relaxation=relaxation)
         ext = {rank: sol.extent(0, rank)}
         sol.set_operator(rank, d2.split_blocks(so, ext)[rank])
         sol.setup()
@@ -36,12 +40,12 @@ def main():
         sol.upload(rank, "x", np.zeros_like(bl))
         h, r0 = sol.solve(maxiter=8, tol=1e-30)       # 2 eager cycles, capture, replays
         x = sol.download(rank)
-        ser = cs.Solver2(cs.Operator2(so), relaxation="point", nrelax_pre=pre, nrelax_post=post, maxiter=8, tol=1e-30)
+        ser = cs.Solver2(cs.Operator2(so), relaxation=relaxation, nrelax_pre=pre, nrelax_post=post, maxiter=8, tol=1e-30)
         xs, hs, r0s = ser.solve(b)
         x0, y0, nxl, nyl = ext[rank]
         same = np.array_equal(x[1:-1, 1:-1], xs[1 + y0:1 + y0 + nyl, 1 + x0:1 + x0 + nxl])
         hist = len(h) == len(hs) and np.allclose(h, hs, rtol=1e-10, atol=0)
-        print(f"rank {rank}: {nx}x{ny} {px}x{py} halo {halo} V({pre},{post}) split {split}: bitwise {same}, history {hist}, "
+        print(f"rank {rank}: {nx}x{ny} {px}x{py} halo {halo} V({pre},{post}) {relaxation} split {split}: bitwise {same}, history {hist}, "
               f"{sol.exchanges_per_cycle} exchanges/cycle", flush=True)
         ok = ok and same and hist
         dist.barrier()

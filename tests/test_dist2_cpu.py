@@ -223,3 +223,88 @@ def test_plan_gloo_ranks_equal_serial(tmp_path, nx, ny, px, py, nine, agg, halo)
     for h in hs[1:]:
         assert np.array_equal(h, hs[0])          # every rank sees the same bits
     assert abs(hs[0][0] - r0r) <= 1e-12 * r0r and np.allclose(hs[0][1:] / hs[0][0], hr, rtol=1e-10, atol=0)
+
+
+# ---- line relaxation across block cuts (plan.h line_group: lines transposed between the blocks that share them) ----
+LINE_CASES = [
+    # nx, ny, px, py, nine, agglomerate, halo, pre, post, relaxation
+    (129, 129, 2, 2, True, 17, 5, 1, 1, "line-x"),
+    (129, 129, 2, 2, True, 17, 5, 1, 1, "line-y"),
+    (129, 129, 2, 2, True, 17, 5, 1, 1, "line-xy"),
+    (129, 97, 2, 1, False, 17, 7, 2, 1, "line-xy"),
+    (200, 131, 3, 2, True, 20, 9, 1, 2, "line-x"),
+    (161, 129, 1, 3, False, 17, 5, 1, 1, "line-y"),
+    (257, 129, 4, 2, True, 33, 15, 0, 2, "line-xy"),
+]
+
+
+@pytest.mark.parametrize("nx,ny,px,py,nine,agg,halo,pre,post,relaxation", LINE_CASES)
+def test_plan_line_relaxation_equals_serial(nx, ny, px, py, nine, agg, halo, pre, post, relaxation):
+    rng = np.random.default_rng(nx + 5 * ny + nine + halo)
+    so = random_op2(nx, ny, nine, rng)
+    b = random_gf(nx, ny, rng)
+    x0 = random_gf(nx, ny, rng)
+    ref = oracle.Solver2(so, relaxation, pre, post)
+    cyc, nd = d2.plan(nx, ny, px, py, nst=so.shape[0], pre=pre, post=post, agglomerate=agg, halo=halo, relaxation=relaxation)
+    ext = blocks_of(nx, ny, px, py, nd, halo)
+    sim = PlanSim(nx, ny, px, py, d2.split_blocks(so, ext), pre, post, agg, halo, relaxation=relaxation)
+    assert sim.nlevels == ref.nlevels and sim.nd == nd and nd >= 1
+    # per colour: right-hand sides, a synchronisation of all ranks, the solve, an exchange that waits for all ranks
+    kinds = [o["op"] for o in cyc]
+    ndir = 2 if relaxation == "line-xy" else 1
+    assert kinds.count("lines_rhs") == kinds.count("lines_solve") == nd * (pre + post) * 2 * ndir
+    for k, o in enumerate(cyc):
+        if o["op"] == "lines_solve":
+            assert cyc[k - 1]["op"] == "sync" and cyc[k - 2]["op"] == "lines_rhs"
+            assert cyc[k + 1]["op"] == "exchange" and cyc[k + 1]["wait_all"] and cyc[k + 1]["arrays"] == [o["a"]]
+    assert "sweep" not in kinds
+    xr = x0.copy()
+    for bb, v in d2.split_blocks(b, ext).items():
+        sim.set(bb, B, v)
+    for bb, v in d2.split_blocks(x0, ext).items():
+        sim.set(bb, X0, v)
+    for it in range(3):
+        ref.vcycle(xr, b)
+        sim.vcycle()
+        x = join({bb: sim.get(bb) for bb in range(px * py)}, ext, nx, ny)
+        assert np.array_equal(x, xr), f"cycle {it}"
+
+
+def _line_worker(rank, world, port, nx, ny, px, py, nine, agg, halo, relaxation, out):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        oracle.lib().orc_set_threads(1)
+        rng = np.random.default_rng(nx + ny + nine)
+        so = random_op2(nx, ny, nine, rng)
+        b = random_gf(nx, ny, rng)
+        _, nd = d2.plan(nx, ny, px, py, nst=so.shape[0], agglomerate=agg, halo=halo, relaxation=relaxation)
+        ext = blocks_of(nx, ny, px, py, nd, halo)
+        mine = {rank: ext[rank]}
+        sim = PlanSim(nx, ny, px, py, d2.split_blocks(so, mine), 1, 1, agg, halo, dist=dist, relaxation=relaxation)
+        sim.set(rank, B, d2.split_blocks(b, mine)[rank])
+        for _ in range(2):
+            sim.vcycle()
+        np.save(os.path.join(out, f"x{rank}.npy"), sim.get(rank))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_plan_line_relaxation_gloo_ranks(tmp_path):
+    nx, ny, px, py, nine, agg, halo, relaxation = 129, 97, 2, 1, True, 17, 5, "line-xy"
+    world = px * py
+    mp.spawn(_line_worker, args=(world, _free_port(), nx, ny, px, py, nine, agg, halo, relaxation, str(tmp_path)), nprocs=world,
+             join=True)
+    rng = np.random.default_rng(nx + ny + nine)
+    so = random_op2(nx, ny, nine, rng)
+    b = random_gf(nx, ny, rng)
+    ref = oracle.Solver2(so, relaxation, 1, 1)
+    xr = np.zeros_like(b)
+    for _ in range(2):
+        ref.vcycle(xr, b)
+    _, nd = d2.plan(nx, ny, px, py, nst=so.shape[0], agglomerate=agg, halo=halo, relaxation=relaxation)
+    ext = blocks_of(nx, ny, px, py, nd, halo)
+    x = join({r: np.load(tmp_path / f"x{r}.npy") for r in range(world)}, ext, nx, ny)
+    assert np.array_equal(x, xr)

@@ -209,6 +209,48 @@ def test_blocks_on_one_gpu_equal_serial(cuda, nx, ny, px, py, nine, agg, halo, p
     sol.close()
 
 
+LINE_CASES = [(257, 257, 2, 2, True, 33, 5, 1, 1, "line-x"), (257, 257, 2, 2, True, 33, 5, 1, 1, "line-y"),
+              (513, 257, 4, 2, True, 65, 5, 1, 1, "line-xy"), (300, 210, 2, 2, False, 33, 7, 2, 1, "line-xy"),
+              (385, 641, 1, 3, True, 65, 9, 1, 2, "line-y"), (641, 385, 3, 1, False, 65, 5, 1, 1, "line-x"),
+              (1025, 1025, 2, 2, True, 129, 15, 0, 2, "line-xy"),
+              # lines too long for shared memory: the warp-per-line solve, as in the serial kernels
+              (13001, 65, 2, 1, True, 17, 5, 1, 1, "line-x"), (65, 13001, 1, 2, False, 17, 5, 1, 1, "line-y")]
+
+
+@pytest.mark.parametrize("nx,ny,px,py,nine,agg,halo,pre,post,relaxation", LINE_CASES)
+def test_line_relaxation_across_cuts_equals_serial(cuda, nx, ny, px, py, nine, agg, halo, pre, post, relaxation):
+    """Zebra line relaxation with lines that cross the block cuts (reference: the interface-system solve of
+    src/2d/ftn/mpi/BMG2_SymStd_relax_lines_x.f90:156-215; here the lines are transposed between the blocks that share
+    them and solved whole): BITWISE the serial GPU solver, and the CPU oracle's history to the serial line kernels'
+    tolerance (their block-scan solve agrees with DPTTS2 to rounding, tests/test_gpu_kernels2d.py)."""
+    import cedar_b200.dist2 as d2
+    import cedar_b200.solver as cs
+    rng = np.random.default_rng(nx + ny + nine + halo)
+    so = random_op2(nx, ny, nine, rng)
+    b = random_gf(nx, ny, rng)
+    ser = cs.Solver2(cs.Operator2(so), relaxation=relaxation, nrelax_pre=pre, nrelax_post=post, maxiter=6, tol=1e-30)
+    sol = d2.DistSolver2(nx, ny, (px, py), nst=so.shape[0], nrelax_pre=pre, nrelax_post=post, agglomerate=agg, halo=halo,
+                         relaxation=relaxation)
+    nb = px * py
+    ext = {k: sol.extent(0, k) for k in range(nb)}
+    for k, v in d2.split_blocks(so, ext).items():
+        sol.set_operator(k, v)
+    sol.setup()
+    assert sol.ndist >= 1
+    for k, v in d2.split_blocks(b, ext).items():
+        sol.upload(k, "b", v)
+        sol.upload(k, "x", np.zeros_like(v))
+    h, r0 = sol.solve(maxiter=6, tol=1e-30)          # 2 eager cycles, capture, replays
+    xs, hs, r0s = ser.solve(b)
+    x = _join({k: sol.download(k)[1:-1, 1:-1] for k in range(nb)}, ext, nx, ny)
+    assert_bitwise(x, xs, f"{relaxation} vs serial GPU solver")
+    assert len(h) == len(hs) and np.allclose(h, hs, rtol=1e-10, atol=0) and abs(r0 - r0s) <= 1e-12 * r0s
+    if nx * ny < 400000:
+        ho = oracle.Solver2(so, relaxation, pre, post).solve(b, maxiter=6, tol=1e-30)[1]
+        assert np.allclose(h, ho, rtol=1e-8, atol=0)
+    sol.close()
+
+
 def test_stream_of_right_hand_sides_single_block_process(cuda):
     """vcycle_stream needs one block per process: refused with several"""
     import cedar_b200.dist2 as d2
