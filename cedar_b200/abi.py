@@ -41,6 +41,11 @@ SIGNATURES = {
     "bmgx2_SETUP_lines_y": (_i, [_p, _p, _u, _u, _i, _i, _p]),
     "bmgx2_relax_lines_x": (_i, [_i, _p, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx2_relax_lines_y": (_i, [_i, _p, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
+    "bmgx2_relax_lines_x_colour": (_i, [_p, _p, _p, _p, _u, _u, _i, _i, _p]),
+    "bmgx2_relax_lines_y_colour": (_i, [_p, _p, _p, _p, _p, _u, _u, _i, _i, _p]),
+    "bmgx2_lines_rhs_push": (_i, [_i, _i, _p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _u, _p, _p]),
+    "bmgx2_lines_solve_T": (_i, [_p, _p, _u, _u, _i, _p]),
+    "bmgx2_lines_scatter_push": (_i, [_i, _p, _u, _u, _i, _u, _p, _p]),
     "bmgx2_residual": (_i, [_i, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx2_matvec": (_i, [_i, _p, _p, _p, _u, _u, _i, _i, _i, _p]),
     "bmgx2_restrict": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _p]),
@@ -96,6 +101,21 @@ class Seg(C.Structure):
     """bmgx_seg of include/bmgx.h"""
     _fields_ = [("src", _p), ("dst", _p), ("rows", C.c_uint32), ("cols", C.c_uint32), ("src_pitch", C.c_uint64),
                 ("dst_pitch", C.c_uint64), ("src_rank", C.c_int32), ("reserved", C.c_int32)]
+
+
+LINE_GROUP_MAX = 16
+
+
+class LineGroup(C.Structure):
+    """bmgx_line_group of include/bmgx.h"""
+    _fields_ = [("nmembers", C.c_int), ("first", C.c_int * (LINE_GROUP_MAX + 1)), ("pitch", C.c_size_t),
+                ("lb", _p * LINE_GROUP_MAX)]
+
+
+class LineOwners(C.Structure):
+    """bmgx_line_owners of include/bmgx.h"""
+    _fields_ = [("nmembers", C.c_int), ("start", C.c_int * (LINE_GROUP_MAX + 1)), ("w_along", C.c_int * LINE_GROUP_MAX),
+                ("w_across", C.c_int), ("pitch", C.c_size_t * LINE_GROUP_MAX), ("q", _p * LINE_GROUP_MAX)]
 
 
 class Rect(C.Structure):

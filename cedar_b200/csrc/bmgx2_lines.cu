@@ -497,19 +497,16 @@ k_lines_y_scatter(const double *__restrict__ B, double *__restrict__ q, unsigned
     }
 }
 
-extern "C" int bmgx2_relax_lines_x(int k, const double *so, const double *qf, double *q, const double *sor,
-                                   double *b, bmgx_len ii, bmgx_len jj, int kf, int ifd, int nstncl,
-                                   int irelax_sym, int updown, int jpn, bmgx_stream_t s)
+// the lines jbeg, jbeg + 2, ... (one colour) of an x-line sweep
+extern "C" int bmgx2_relax_lines_x_colour(const double *so, const double *qf, double *q, const double *sor, bmgx_len ii,
+                                          bmgx_len jj, int nine_pt, int jbeg_, bmgx_stream_t s)
 {
-    (void)nstncl; (void)b;
-    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_x: periodic BCs not supported");
     if (ii < 3 || jj < 3) return BMGX_OK;
-    bool fwd = (irelax_sym == BMGX_RELAX_NONSYM) || (updown == BMGX_DOWN && irelax_sym == BMGX_RELAX_SYM);
-    for (int a = 0; a < 2; a++) {
-        unsigned jbeg = fwd ? 3 - a : 2 + a;  // DOWN: odd lines (3,5,..) first (relax_lines_x.f90:83-99)
-        if (jbeg > jj - 1) continue;
+    {
+        const unsigned jbeg = (unsigned)jbeg_;
+        const bool nine = nine_pt != 0;
+        if (jbeg < 2 || jbeg > jj - 1) return BMGX_OK;
         unsigned nl = (jj - 1 - jbeg) / 2 + 1;
-        const bool nine = (k < kf || ifd != 1);
         unsigned lg, threads; size_t smem;
         if (line_plan(ii - 2, &lg, &threads, &smem)) {
             cudaError_t e = nine ? launch_linex<true>(lg, nl, threads, smem, (cudaStream_t)s, so, qf, q, sor, ii, jj, jbeg)
@@ -526,22 +523,35 @@ extern "C" int bmgx2_relax_lines_x(int k, const double *so, const double *qf, do
     return BMGX_OK;
 }
 
-extern "C" int bmgx2_relax_lines_y(int k, const double *so, const double *qf, double *q, const double *sor,
+extern "C" int bmgx2_relax_lines_x(int k, const double *so, const double *qf, double *q, const double *sor,
                                    double *b, bmgx_len ii, bmgx_len jj, int kf, int ifd, int nstncl,
                                    int irelax_sym, int updown, int jpn, bmgx_stream_t s)
 {
-    (void)nstncl;
-    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_y: periodic BCs not supported");
+    (void)nstncl; (void)b;
+    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_x: periodic BCs not supported");
+    if (ii < 3 || jj < 3) return BMGX_OK;
+    bool fwd = (irelax_sym == BMGX_RELAX_NONSYM) || (updown == BMGX_DOWN && irelax_sym == BMGX_RELAX_SYM);
+    for (int a = 0; a < 2; a++) {
+        // DOWN: odd lines (3,5,..) first (relax_lines_x.f90:83-99)
+        int st = bmgx2_relax_lines_x_colour(so, qf, q, sor, ii, jj, (k < kf || ifd != 1) ? 1 : 0, fwd ? 3 - a : 2 + a, s);
+        if (st != BMGX_OK) return st;
+    }
+    return BMGX_OK;
+}
+
+// the lines ibeg, ibeg + 2, ... (one colour) of a y-line sweep
+extern "C" int bmgx2_relax_lines_y_colour(const double *so, const double *qf, double *q, const double *sor, double *b,
+                                          bmgx_len ii, bmgx_len jj, int nine_pt, int ibeg_, bmgx_stream_t s)
+{
     if (!b) return bmgx_set_error(BMGX_ERR_ARG, "relax_lines_y: scratch b (ii*jj doubles) required");
     if (ii < 3 || jj < 3) return BMGX_OK;
     cudaStream_t st = (cudaStream_t)s;
-    bool fwd = (irelax_sym == BMGX_RELAX_NONSYM) || (updown == BMGX_DOWN && irelax_sym == BMGX_RELAX_SYM);
-    for (int a = 0; a < 2; a++) {
-        unsigned ibeg = fwd ? 3 - a : 2 + a;
-        if (ibeg > ii - 1) continue;
+    {
+        const unsigned ibeg = (unsigned)ibeg_;
+        if (ibeg < 2 || ibeg > ii - 1) return BMGX_OK;
         unsigned nl = (ii - 1 - ibeg) / 2 + 1;
         dim3 g(cdiv(nl, 32), cdiv(jj - 2, 32), bmgx_batch());
-        if (k < kf || ifd != 1) k_lines_y_rhs<true><<<g, 256, 0, st>>>(so, qf, q, b, ii, jj, ibeg);
+        if (nine_pt) k_lines_y_rhs<true><<<g, 256, 0, st>>>(so, qf, q, b, ii, jj, ibeg);
         else k_lines_y_rhs<false><<<g, 256, 0, st>>>(so, qf, q, b, ii, jj, ibeg);
         BMGX_LAUNCH_CHECK("relax_lines_y/rhs");
         unsigned lg, threads; size_t smem;
@@ -555,6 +565,22 @@ extern "C" int bmgx2_relax_lines_y(int k, const double *so, const double *qf, do
         BMGX_LAUNCH_CHECK("relax_lines_y/solve");
         k_lines_y_scatter<<<g, 256, 0, st>>>(b, q, ii, jj, ibeg);
         BMGX_LAUNCH_CHECK("relax_lines_y/scatter");
+    }
+    return BMGX_OK;
+}
+
+extern "C" int bmgx2_relax_lines_y(int k, const double *so, const double *qf, double *q, const double *sor,
+                                   double *b, bmgx_len ii, bmgx_len jj, int kf, int ifd, int nstncl,
+                                   int irelax_sym, int updown, int jpn, bmgx_stream_t s)
+{
+    (void)nstncl;
+    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_y: periodic BCs not supported");
+    if (!b) return bmgx_set_error(BMGX_ERR_ARG, "relax_lines_y: scratch b (ii*jj doubles) required");
+    if (ii < 3 || jj < 3) return BMGX_OK;
+    bool fwd = (irelax_sym == BMGX_RELAX_NONSYM) || (updown == BMGX_DOWN && irelax_sym == BMGX_RELAX_SYM);
+    for (int a = 0; a < 2; a++) {
+        int st = bmgx2_relax_lines_y_colour(so, qf, q, sor, b, ii, jj, (k < kf || ifd != 1) ? 1 : 0, fwd ? 3 - a : 2 + a, s);
+        if (st != BMGX_OK) return st;
     }
     return BMGX_OK;
 }

@@ -215,7 +215,7 @@ class DistSolver2:
     def profile_ops(self, n=5):
         """[(operation dict, ms)] for one cycle: eager, host-synchronised per operation (diagnostic)"""
         ops, _ = plan(self.nx, self.ny, self.px, self.py, self.nst, self.pre, self.post, self.agglomerate, self.halo, "cycle",
-                      self.split_min)
+                      self.split_min, self.relaxation)
         out = (C.c_float * len(ops))()
         m = C.c_int()
         _check(lib.cdr2_dist_profile_ops(self.h, n, out, len(ops), C.byref(m)))

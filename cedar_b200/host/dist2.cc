@@ -120,7 +120,7 @@ struct cdr2_dist
 				if (!relaxes(dd)) continue;
 				if (l == lvl && dd == dirn) return o;
 				const line_group g = dec->lines(l, b, dd);
-				o += up((size_t)(g.mine() + 2) * (g.len + 2));
+				if (g.G > 1) o += up((size_t)(g.mine() + 2) * (g.len + 2));
 			}
 		return o;
 	}
@@ -256,7 +256,7 @@ std::vector<bmgx_seg> line_setup_segs(const cdr2_dist &d, int lvl, int dirn, con
 	std::vector<bmgx_seg> v;
 	const line_group &g = ls.grp;
 	const int mine = g.mine(), t0 = g.first[g.me];
-	if (mine == 0) return v;
+	if (mine == 0 || g.G == 1) return v;      // nothing to gather: no lines here, or whole lines in this block
 	const size_t sii = dirn == 0 ? g.len + 2 : mine + 2, sjj = dirn == 0 ? mine + 2 : g.len + 2;
 	const int planes[2] = {0, dirn == 0 ? 1 : 2};   // KO, KW | KS
 	for (int m = 0; m < g.G; m++) {
@@ -338,6 +338,12 @@ void run_op(cdr2_dist &d, const plan_op &o)
 		for (auto &K : d.blk) {
 			line_store &ls = lines_of(d, K, l, o.dir);
 			const int mine = ls.grp.mine();
+			if (ls.grp.G == 1) {
+				// no cut across these lines: the serial kernels on the block's own (halo-extended) arrays
+				check(bmgx_malloc((void **)&ls.sor, 2 * d.plane_stride(K.id, l) * 8), "line factor");
+				check(bmgx_memset0(ls.sor, 2 * d.plane_stride(K.id, l) * 8, s), "line factor");
+				continue;
+			}
 			if (mine == 0) continue;
 			const size_t n = (size_t)(mine + 2) * (ls.grp.len + 2);
 			check(bmgx_malloc((void **)&ls.strip, 3 * n * 8), "line strip");
@@ -349,6 +355,12 @@ void run_op(cdr2_dist &d, const plan_op &o)
 		for (auto &K : d.blk) {
 			line_store &ls = lines_of(d, K, l, o.dir);
 			const int mine = ls.grp.mine();
+			if (ls.grp.G == 1) {
+				const block_geom g = K.g[l];
+				if (o.dir == 0) check(bmgx2_SETUP_lines_x(d.ptr(K.id, l, A), ls.sor, g.ii, g.jj, d.nstl(l), 0, s), "SETUP_lines_x");
+				else check(bmgx2_SETUP_lines_y(d.ptr(K.id, l, A), ls.sor, g.ii, g.jj, d.nstl(l), 0, s), "SETUP_lines_y");
+				continue;
+			}
 			if (mine == 0) continue;
 			if (o.dir == 0) check(bmgx2_SETUP_lines_x(ls.strip, ls.sor, ls.grp.len + 2, mine + 2, 3, 0, s), "SETUP_lines_x");
 			else check(bmgx2_SETUP_lines_y(ls.strip, ls.sor, mine + 2, ls.grp.len + 2, 3, 0, s), "SETUP_lines_y");
@@ -401,6 +413,7 @@ void run_op(cdr2_dist &d, const plan_op &o)
 			break;
 		case op_kind::lines_rhs: {
 			line_store &ls = lines_of(d, K, l, o.dir);
+			if (ls.grp.G == 1) break;       // fused with the solve below
 			check(bmgx2_lines_rhs_push(o.dir, ifd ? 0 : 1, d.ptr(b, l, A), d.ptr(b, l, B), d.ptr(b, l, o.a), g.ii, g.jj, g.wl, g.wb,
 			                           g.nx, g.ny, o.part, 1 + (o.dir == 0 ? g.x0 : g.y0), &ls.dst, s), "lines_rhs_push");
 			break;
@@ -408,6 +421,17 @@ void run_op(cdr2_dist &d, const plan_op &o)
 		case op_kind::lines_solve: {
 			line_store &ls = lines_of(d, K, l, o.dir);
 			const int mine = ls.grp.mine();
+			if (ls.grp.G == 1) {
+				// whole lines live in this block: one colour of the serial sweep over the extended array (the halo lines are
+				// recomputed from stale neighbours and replaced by the exchange that follows)
+				if (o.dir == 0)
+					check(bmgx2_relax_lines_x_colour(d.ptr(b, l, A), d.ptr(b, l, B), d.ptr(b, l, o.a), ls.sor, g.ii, g.jj, ifd ? 0 : 1,
+					                                 o.part, s), "relax_lines_x");
+				else
+					check(bmgx2_relax_lines_y_colour(d.ptr(b, l, A), d.ptr(b, l, B), d.ptr(b, l, o.a), ls.sor, d.ptr(b, l, RES), g.ii,
+					                                 g.jj, ifd ? 0 : 1, o.part, s), "relax_lines_y");
+				break;
+			}
 			if (mine == 0) break;
 			double *buf = d.lb(b, l, o.dir);
 			check(bmgx2_lines_solve_T(buf, ls.sor, mine + 2, ls.grp.len + 2, o.part, s), "lines_solve_T");

@@ -112,6 +112,15 @@ def make_config(relaxation="point", nrelax_pre=2, nrelax_post=1, maxiter=10, tol
     return json.dumps(conf)
 
 
+def _host_view(owner, p, shape):
+    """numpy view of library-owned host memory that keeps `owner` (whose destructor frees it) alive as long as the
+    view or anything sliced from it is"""
+    n = int(np.prod(shape))
+    buf = (C.c_double * n).from_address(C.addressof(p.contents))
+    buf._owner = owner
+    return np.frombuffer(buf, dtype=np.float64).reshape(shape)
+
+
 class Operator2:
     """Host-side 2D stencil operator, shape (ndirs, ny+2, nx+2)."""
 
@@ -132,7 +141,7 @@ class Operator2:
         p = lib.cdr2_operator_data(self.h)
         if not p:
             raise CedarError(lib.cdr_last_error().decode())
-        return np.ctypeslib.as_array(p, shape=(self.nst, self.ny + 2, self.nx + 2))
+        return _host_view(self, p, (self.nst, self.ny + 2, self.nx + 2))
 
     def __del__(self):
         if getattr(self, "h", None):
@@ -305,7 +314,7 @@ class Operator3:
         p = lib.cdr3_operator_data(self.h)
         if not p:
             raise CedarError(lib.cdr_last_error().decode())
-        return np.ctypeslib.as_array(p, shape=(self.nst, self.nz + 2, self.ny + 2, self.nx + 2))
+        return _host_view(self, p, (self.nst, self.nz + 2, self.ny + 2, self.nx + 2))
 
     def __del__(self):
         if getattr(self, "h", None):

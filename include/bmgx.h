@@ -170,6 +170,12 @@ int bmgx2_relax_lines_y(int k, const bmgx_real *so, const bmgx_real *qf, bmgx_re
                         int kf, int ifd, int nstncl, int irelax_sym, int updown, int jpn,
                         bmgx_stream_t s);
 
+/* one colour of the sweeps above: the lines with F-index first, first + 2, ... (first = 2 or 3) */
+int bmgx2_relax_lines_x_colour(const bmgx_real *so, const bmgx_real *qf, bmgx_real *q, const bmgx_real *sor, bmgx_len ii,
+                               bmgx_len jj, int nine_pt, int first, bmgx_stream_t s);
+int bmgx2_relax_lines_y_colour(const bmgx_real *so, const bmgx_real *qf, bmgx_real *q, const bmgx_real *sor, bmgx_real *b,
+                               bmgx_len ii, bmgx_len jj, int nine_pt, int first, bmgx_stream_t s);
+
 /* Lines that cross block cuts (the decomposed solver).  Counterpart of the reference's interface-system line solve
  * BMG2_SymStd_relax_lines_x/_y of src/2d/ftn/mpi/ (LineSolve_A/B/C, :156-215) -- here the blocks that share lines
  * transpose them over peer memory and the serial solve runs on whole lines (cedar_b200/csrc/bmgx2_lines.cu).

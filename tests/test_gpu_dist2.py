@@ -213,6 +213,9 @@ LINE_CASES = [(257, 257, 2, 2, True, 33, 5, 1, 1, "line-x"), (257, 257, 2, 2, Tr
               (513, 257, 4, 2, True, 65, 5, 1, 1, "line-xy"), (300, 210, 2, 2, False, 33, 7, 2, 1, "line-xy"),
               (385, 641, 1, 3, True, 65, 9, 1, 2, "line-y"), (641, 385, 3, 1, False, 65, 5, 1, 1, "line-x"),
               (1025, 1025, 2, 2, True, 129, 15, 0, 2, "line-xy"),
+              # one direction without cuts: those lines are relaxed by the serial kernels on the block's extended arrays
+              (513, 385, 2, 1, True, 65, 5, 1, 1, "line-xy"), (385, 513, 1, 2, False, 65, 7, 1, 1, "line-xy"),
+              (513, 257, 1, 2, True, 33, 5, 2, 1, "line-x"),
               # lines too long for shared memory: the warp-per-line solve, as in the serial kernels
               (13001, 65, 2, 1, True, 17, 5, 1, 1, "line-x"), (65, 13001, 1, 2, False, 17, 5, 1, 1, "line-y")]
 

@@ -19,6 +19,9 @@ def main():
     ap.add_argument("--halo", type=int, default=15)
     ap.add_argument("--agglomerate", type=int, default=513)
     ap.add_argument("--reps", type=int, default=10)
+    ap.add_argument("--relaxation", default="point")
+    ap.add_argument("--global-n", type=int, default=0, help="global grid global-n^2 instead of n-1 own unknowns per block")
+    ap.add_argument("--decomp", default="", help="px,py under torchrun (default: the grid_decomp rule)")
     a = ap.parse_args()
     import torch
     import cedar_b200.dist2 as d2
@@ -31,12 +34,14 @@ def main():
         torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
         dist.init_process_group("gloo")
         comm = d2.TorchComm()
-        px, py = d2.grid_decomp((a.n - 1, a.n - 1), world)
+        px, py = [int(v) for v in a.decomp.split(",")] if a.decomp else d2.grid_decomp((a.n - 1, a.n - 1), world)
     else:
         px, py = [int(v) for v in a.blocks.split("x")]
     nb = a.n - 1
     gnx, gny = (px * nb + 1, py * nb + 1) if px * py > 1 else (a.n, a.n)
-    sol = d2.DistSolver2(gnx, gny, (px, py), agglomerate=a.agglomerate, halo=a.halo, comm=comm)
+    if a.global_n:
+        gnx = gny = a.global_n
+    sol = d2.DistSolver2(gnx, gny, (px, py), agglomerate=a.agglomerate, halo=a.halo, comm=comm, relaxation=a.relaxation)
     for k in sol.owned:
         ext = sol.extent(0, k)
         sol.set_operator(k, d2.gallery_fe_block((gnx, gny), ext))
@@ -47,9 +52,11 @@ def main():
     if rank == 0:
         agg = {}
         for o, t in prof:
-            agg.setdefault((o["op"], o["lvl"]), 0.0)
-            agg[o["op"], o["lvl"]] += t
-        print(json.dumps({"grid": f"{gnx}x{gny}", "blocks": f"{px}x{py}", "ranks": world, "halo": a.halo, "ms_per_cycle_graph": ms,
+            key = (o["op"] + (":xy"[1 + o["dir"]] if o["op"].startswith("lines") else ""), o["lvl"])
+            agg.setdefault(key, 0.0)
+            agg[key] += t
+        print(json.dumps({"grid": f"{gnx}x{gny}", "blocks": f"{px}x{py}", "ranks": world, "halo": a.halo, "relaxation": a.relaxation,
+                          "ms_per_cycle_graph": ms,
                           "sum_of_ops_ms": sum(t for _, t in prof), "exchanges": sol.exchanges_per_cycle,
                           "ops": [{"op": k[0], "lvl": k[1], "ms": round(v, 4)} for k, v in agg.items()]}))
     if world == 1 and px * py == 1:
