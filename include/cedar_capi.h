@@ -104,9 +104,10 @@ int cdr2_solve_host(int nstencil, unsigned nx, unsigned ny, const double *so, co
  * uploads the own entries of its blocks' operators, hands the others its IPC handles (the caller moves these bytes
  * between the processes: one all-gather), connects, and runs setup.  Ghost exchanges then go through peer memory
  * over NVLink (include/bmgx.h, bmgx_halo_step); collective calls (setup, vcycle, solve, time_vcycles,
- * vcycle_stream) must be made by all processes in the same order.  Point relaxation; results are bit for bit
- * those of the serial cdr2::solver on the global problem.  Levels of global size <= agglomerate are solved
- * replicated on every rank.  halo_width: odd, lines of the neighbours every array carries (15 = one exchange per
+ * vcycle_stream) must be made by all processes in the same order.  relaxation: "point", "line-x", "line-y" or
+ * "line-xy" (lines that cross block cuts are transposed between the blocks that share them and solved whole,
+ * include/cedar/2d/mpi/plan.h); results are bit for bit those of the serial cdr2::solver on the global problem.
+ * Levels of global size <= agglomerate are solved replicated on every rank.  halo_width: odd, lines of the neighbours every array carries (15 = one exchange per
  * level per V(1,1) cycle). */
 typedef struct cdr2_dist cdr2_dist;
 /* split_min: on the levels where every block has at least this many own points per dimension, a sweep that directly

@@ -141,3 +141,31 @@ def test_matvec3(cuda, abi, nx, ny, nz, full):
     d_y = cuda.zeros_like(d_q)
     abi.check(abi.lib.bmgx3_matvec(1, ptr(d_so), ptr(d_y), ptr(d_q), II, JJ, KK, 1, ifd, nst, None))
     assert_bitwise(host(d_y), ref, "matvec3")
+
+
+def test_relax27_residual_at_513_cubed(cuda, abi):
+    """BASELINE configs[3] at its full size: one DOWN and one UP 8-colour sweep and the residual of a 27-point operator
+    on 513^3 against the CPU oracle (all host cores), bitwise.  The operator is a random 2D field per stencil entry
+    times a random factor per plane (15 GB of independent random numbers would only slow the test down)."""
+    n = 513
+    II = JJ = KK = n + 2
+    rng = np.random.default_rng(513)
+    a2 = rng.uniform(0.5, 1.5, size=(14, 1, JJ, II))
+    ck = rng.uniform(0.5, 1.5, size=(14, KK, 1, 1))
+    so = np.empty((14, KK, JJ, II))
+    np.multiply(a2, ck, out=so)
+    so[0] *= 30.0                                            # a dominant diagonal keeps the sweep's values O(1)
+    q, b = random_gf3(n, n, n, rng), random_gf3(n, n, n, rng)
+    L = oracle.lib()
+    sor = np.zeros((2, KK, JJ, II))
+    L.orc3_setup_recip(P(so), P(sor), II, JJ, KK, 14, 2)
+    d_so, d_q, d_b, d_sor = dev(cuda, so), dev(cuda, q), dev(cuda, b), dev(cuda, sor)
+    for updown in (0, 1):
+        assert L.orc3_relax_gs(1, P(so), P(b), P(q), P(sor), II, JJ, KK, 0, 14, 2, 1, updown, 0) == 0
+        abi.check(abi.lib.bmgx3_relax_GS(1, ptr(d_so), ptr(d_b), ptr(d_q), ptr(d_sor), II, JJ, KK, 0, 14, 2, 1, updown, 0, None))
+        assert_bitwise(host(d_q), q, f"27-point sweep at 513^3, updown={updown}")
+    ref = np.zeros_like(q)
+    L.orc3_residual(1, 1, 0, P(q), P(b), P(so), P(ref), II, JJ, KK, 14)
+    d_r = cuda.zeros_like(d_q)
+    abi.check(abi.lib.bmgx3_residual(1, 1, 0, ptr(d_q), ptr(d_b), ptr(d_so), ptr(d_r), II, JJ, KK, 14, None))
+    assert_bitwise(host(d_r), ref, "27-point residual at 513^3")
