@@ -247,6 +247,9 @@ def time_fine_sweep(a, torch, reps=20):
     return per, alg, launches
 
 
+SETUP_PARTS = {}
+
+
 def _dist_problem(a, d2, cs, comm, rank, gnx, gny, px, py, gallery, pre, post, agglomerate, halo, graph=True):
     """block-decomposed solver for this rank's block + its pinned right-hand side; returns (solver, b block, setup s)"""
     import torch
@@ -256,14 +259,23 @@ def _dist_problem(a, d2, cs, comm, rank, gnx, gny, px, py, gallery, pre, post, a
     sol = d2.DistSolver2(gnx, gny, (px, py), nst=5, nrelax_pre=pre, nrelax_post=post, agglomerate=agglomerate, halo=halo,
                          cuda_graph=graph, comm=comm, split_min=a.split_min)
     ext = sol.extent(0, rank)
+    torch.cuda.synchronize()
     t1 = time.perf_counter()
     so = gen((gnx, gny), ext)
-    t_gen = time.perf_counter() - t1
+    t2 = time.perf_counter()
+    t_gen = t2 - t1
     sol.set_operator(rank, so)
+    torch.cuda.synchronize()
+    t3 = time.perf_counter()
     del so
     sol.setup()
     torch.cuda.synchronize()
-    setup_s = time.perf_counter() - t0 - t_gen
+    t4 = time.perf_counter()
+    setup_s = t4 - t0 - t_gen
+    # where the setup goes (this rank): arena + CUDA IPC + handle all-gather | H2D of the block's operator from pageable
+    # host memory | exchange + interpolation + Galerkin per level, replicated coarse solver
+    SETUP_PARTS.update({"create_connect_ms": (t1 - t0) * 1e3, "operator_upload_ms": (t3 - t2) * 1e3,
+                        "device_setup_ms": (t4 - t3) * 1e3})
     return sol, d2.rhs_sin_block((gnx, gny), ext), setup_s
 
 
@@ -327,6 +339,7 @@ def run_multi(a, torch, dist, world, rank, local):
         return run_multi_nccl(a, torch, dist, world, rank, local)
     sol, bl, setup_s = _dist_problem(a, d2, cs, comm, rank, gnx, gny, px, py, a.gallery, a.pre, a.post, a.agglomerate, a.halo,
                                      graph=not a.no_graph)
+    setup_parts = {k: round(v, 1) for k, v in SETUP_PARTS.items()}
     x0, y0, nxl, nyl = sol.extent(0, rank)
     sol.upload(rank, "b", bl)
     sampler = ClockSampler(local)
@@ -422,7 +435,8 @@ def run_multi(a, torch, dist, world, rank, local):
             "clocks": clocks,
             "setup": {"ms": setup_s * 1e3, "what": "arena allocation + IPC connect + block upload + distributed interpolation/"
                                                    "Galerkin setup + replicated serial setup of the agglomerated levels "
-                                                   "(host-side generation of the operator excluded)"},
+                                                   "(host-side generation of the operator excluded)",
+                      "parts_rank0": setup_parts},
             "solve": {"tol": a.tol, "iterations": len(hist), "ms": ms_solve, "final_rel_residual": float(hist[-1])},
             "parity_vs_serial": parity["result"], "parity_detail": parity,
             "roofline": {"bound": "hbm", "kernel": "whole V-cycle per GPU (k_relax9_fused dominates; single-GPU line has it alone)",

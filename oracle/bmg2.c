@@ -953,7 +953,8 @@ int orc2_setup_itli_ex(const double *so, double *soc, const double *ci,
 int orc2_setup_lines_x(const double *so, double *sor, int Nx, int Ny, int nstncl, int jpn)
 {
     (void)nstncl;
-    if (jpn != 0 && jpn != -4) return -1;
+    const int ipn = jpn < 0 ? -jpn : jpn;
+    const int per_x = ipn == 2 || ipn == 3;   /* SETUP_lines_x.f90:76-83: periodic in x */
 #define SO(i, j, kk) A3(so, Nx, Ny, i, j, kk)
 #define SOR(i, j, kk) A3(sor, Nx, Ny, i, j, kk)
 #pragma omp parallel for schedule(static)
@@ -961,6 +962,10 @@ int orc2_setup_lines_x(const double *so, double *sor, int Nx, int Ny, int nstncl
         for (int i = 2; i <= Nx - 1; i++) {
             SOR(i, j, 2) = -SO(i, j, KW);
             SOR(i, j, 1) = SO(i, j, KO);
+        }
+        if (per_x) {
+            SOR(2, j, 1) = SOR(2, j, 1) + SO(2, j, KW);
+            SOR(Nx - 1, j, 1) = SOR(Nx - 1, j, 1) + SO(Nx, j, KW);
         }
         orc_dpttrf(Nx - 2, &SOR(2, j, 1), &SOR(3, j, 2));
     }
@@ -972,7 +977,8 @@ int orc2_setup_lines_x(const double *so, double *sor, int Nx, int Ny, int nstncl
 int orc2_setup_lines_y(const double *so, double *sor, int Nx, int Ny, int nstncl, int jpn)
 {
     (void)nstncl;
-    if (jpn != 0 && jpn != -4) return -1;
+    const int ipn = jpn < 0 ? -jpn : jpn;
+    const int per_y = ipn == 1 || ipn == 3;   /* SETUP_lines_y.f90:77-84: periodic in y */
 #define SO(i, j, kk) A3(so, Nx, Ny, i, j, kk)
 #define SOR(j, i, kk) A3(sor, Ny, Nx, j, i, kk)
 #pragma omp parallel for schedule(static)
@@ -981,6 +987,10 @@ int orc2_setup_lines_y(const double *so, double *sor, int Nx, int Ny, int nstncl
             SOR(j, i, 2) = -SO(i, j, KS);
             SOR(j, i, 1) = SO(i, j, KO);
         }
+        if (per_y) {
+            SOR(2, i, 1) = SOR(2, i, 1) + SO(i, 2, KS);
+            SOR(Ny - 1, i, 1) = SOR(Ny - 1, i, 1) + SO(i, Ny, KS);
+        }
         orc_dpttrf(Ny - 2, &SOR(2, i, 1), &SOR(3, i, 2));
     }
     return 0;
@@ -988,15 +998,29 @@ int orc2_setup_lines_y(const double *so, double *sor, int Nx, int Ny, int nstncl
 #undef SOR
 }
 
+/* ghost refresh of a periodic direction (relax_lines_x.f90:279-290 and the like) */
+static void lines_wrap_y(double *q, int II, int JJ)
+{
+    for (int i = 1; i <= II; i++) { A2(q, II, i, 1) = A2(q, II, i, JJ - 1); A2(q, II, i, JJ) = A2(q, II, i, 2); }
+}
+static void lines_wrap_x(double *q, int II, int JJ)
+{
+    for (int j = 1; j <= JJ; j++) { A2(q, II, 1, j) = A2(q, II, II - 1, j); A2(q, II, II, j) = A2(q, II, 2, j); }
+}
+
 /* ------------------------------------------------------------------------
- * BMG2_SymStd_relax_lines_x.f90:76-170 (non-periodic)
+ * BMG2_SymStd_relax_lines_x.f90:68-310.  Lines not periodic in x (boundary codes definite and periodic in y only,
+ * l.73-168): right-hand side, DPTTRS; with y periodic the ghost rows are refreshed ONCE, after both colours
+ * (l.162-167).  Otherwise (l.170-306): the factor is that of the tridiagonal part with the two wrap couplings added
+ * to the end diagonals (SETUP_lines_x), and every line is corrected by Sherman-Morrison: a second solve with the wrap
+ * couplings as right-hand side (l.209-224), ghosts refreshed after every colour.
  * ---------------------------------------------------------------------- */
 int orc2_relax_lines_x(int k, const double *so, const double *qf, double *q, const double *sor,
                        double *b, int II, int JJ, int kf, int ifd, int nstncl,
                        int irelax_sym, int updown, int jpn)
 {
     (void)nstncl; (void)b;
-    if (jpn != 0 && jpn != -4) return -1;
+    const int ipn = jpn < 0 ? -jpn : jpn;
     int J1 = JJ - 1, I1 = II - 1;
     int jb0, jb1, jbs;
     if (irelax_sym == 0 || (updown == 0 && irelax_sym == 1)) {
@@ -1004,31 +1028,53 @@ int orc2_relax_lines_x(int k, const double *so, const double *qf, double *q, con
     } else {
         jb0 = 2; jb1 = 3; jbs = 1;
     }
+    const int nine = (k < kf || ifd != 1);
+    /* l.73-75: the first branch is taken for IPN = 0 and PER_y; IPN is compared with BMG_BCs_indef_nonper = -4, which an
+     * absolute value never equals, so the code -4 runs the second branch (whose correction vanishes when the ghost
+     * couplings are zero) without any ghost refresh */
+    const int per_line = !(ipn == 0 || ipn == 1);
+    const int wrap_x = ipn == 2 || ipn == 3, wrap_y = ipn == 1 || ipn == 3;
 #define SO(i, j, kk) A3(so, II, JJ, i, j, kk)
 #define Q(i, j) A2(q, II, i, j)
 #define QF(i, j) A2(qf, II, i, j)
 #define SOR(i, j, kk) A3(sor, II, JJ, i, j, kk)
     for (int jbeg = jb0; jbeg != jb1 + jbs; jbeg += jbs) {
         int jend = 2 * ((J1 - jbeg) / 2) + jbeg;
-        if (k < kf || ifd != 1) {
-#pragma omp parallel for schedule(static)
+#pragma omp parallel
+        {
+            double *B = per_line ? (double *)__builtin_malloc(sizeof(double) * (size_t)(II + 2)) : 0;
+#pragma omp for schedule(static)
             for (int j = jbeg; j <= jend; j += 2) {
-                for (int i = 2; i <= I1; i++)
-                    Q(i, j) = QF(i, j) + SO(i, j, KS) * Q(i, j - 1) + SO(i, j + 1, KS) * Q(i, j + 1)
-                              + SO(i, j, KSW) * Q(i - 1, j - 1) + SO(i + 1, j, KNW) * Q(i + 1, j - 1)
-                              + SO(i, j + 1, KNW) * Q(i - 1, j + 1)
-                              + SO(i + 1, j + 1, KSW) * Q(i + 1, j + 1);
+                if (nine) {
+                    for (int i = 2; i <= I1; i++)
+                        Q(i, j) = QF(i, j) + SO(i, j, KS) * Q(i, j - 1) + SO(i, j + 1, KS) * Q(i, j + 1)
+                                  + SO(i, j, KSW) * Q(i - 1, j - 1) + SO(i + 1, j, KNW) * Q(i + 1, j - 1)
+                                  + SO(i, j + 1, KNW) * Q(i - 1, j + 1)
+                                  + SO(i + 1, j + 1, KSW) * Q(i + 1, j + 1);
+                } else {
+                    for (int i = 2; i <= I1; i++)
+                        Q(i, j) = QF(i, j) + SO(i, j, KS) * Q(i, j - 1) + SO(i, j + 1, KS) * Q(i, j + 1);
+                }
                 orc_dptts2(I1 - 1, &SOR(2, j, 1), &SOR(3, j, 2), &Q(2, j));
+                if (per_line) {
+                    for (int i = 2; i <= I1; i++) B[i] = 0.0;
+                    B[2] = -SO(2, j, KW);
+                    B[I1] = -SO(II, j, KW);
+                    orc_dptts2(I1 - 1, &SOR(2, j, 1), &SOR(3, j, 2), &B[2]);
+                    double alpha = B[2] + B[I1];
+                    double beta = Q(2, j) + Q(I1, j);
+                    beta = beta / (1.0 + alpha);
+                    for (int i = 2; i <= I1; i++) Q(i, j) = Q(i, j) - beta * B[i];
+                }
             }
-        } else {
-#pragma omp parallel for schedule(static)
-            for (int j = jbeg; j <= jend; j += 2) {
-                for (int i = 2; i <= I1; i++)
-                    Q(i, j) = QF(i, j) + SO(i, j, KS) * Q(i, j - 1) + SO(i, j + 1, KS) * Q(i, j + 1);
-                orc_dptts2(I1 - 1, &SOR(2, j, 1), &SOR(3, j, 2), &Q(2, j));
-            }
+            if (B) __builtin_free(B);
+        }
+        if (per_line) {
+            if (wrap_y) lines_wrap_y(q, II, JJ);
+            if (wrap_x) lines_wrap_x(q, II, JJ);
         }
     }
+    if (!per_line && wrap_y) lines_wrap_y(q, II, JJ);
     return 0;
 #undef SO
 #undef Q
@@ -1037,14 +1083,16 @@ int orc2_relax_lines_x(int k, const double *so, const double *qf, double *q, con
 }
 
 /* ------------------------------------------------------------------------
- * BMG2_SymStd_relax_lines_y.f90:75-166 (non-periodic); SOR is (JJ,II,2).
+ * BMG2_SymStd_relax_lines_y.f90:68-300; SOR is (JJ,II,2).  Mirror image of the x version: lines not periodic in y
+ * (definite, periodic in x only: l.73-176, x ghosts refreshed once at the end), otherwise the Sherman-Morrison
+ * correction (l.178-296).
  * ---------------------------------------------------------------------- */
 int orc2_relax_lines_y(int k, const double *so, const double *qf, double *q, const double *sor,
                        double *bwork, int II, int JJ, int kf, int ifd, int nstncl,
                        int irelax_sym, int updown, int jpn)
 {
     (void)nstncl; (void)bwork;
-    if (jpn != 0 && jpn != -4) return -1;
+    const int ipn = jpn < 0 ? -jpn : jpn;
     int J1 = JJ - 1, I1 = II - 1;
     int ib0, ib1, ibs;
     if (irelax_sym == 0 || (updown == 0 && irelax_sym == 1)) {
@@ -1052,6 +1100,9 @@ int orc2_relax_lines_y(int k, const double *so, const double *qf, double *q, con
     } else {
         ib0 = 2; ib1 = 3; ibs = 1;
     }
+    const int nine = (k < kf || ifd != 1);
+    const int per_line = !(ipn == 0 || ipn == 2);     /* l.73-75, same quirk for the code -4 as in the x version */
+    const int wrap_x = ipn == 2 || ipn == 3, wrap_y = ipn == 1 || ipn == 3;
 #define SO(i, j, kk) A3(so, II, JJ, i, j, kk)
 #define Q(i, j) A2(q, II, i, j)
 #define QF(i, j) A2(qf, II, i, j)
@@ -1060,10 +1111,10 @@ int orc2_relax_lines_y(int k, const double *so, const double *qf, double *q, con
         int iend = 2 * ((I1 - ibeg) / 2) + ibeg;
 #pragma omp parallel
         {
-            double *B = (double *)__builtin_malloc(sizeof(double) * (size_t)(JJ + 1));
+            double *B = (double *)__builtin_malloc(sizeof(double) * (size_t)(2 * JJ + 2));
 #pragma omp for schedule(static)
             for (int i = ibeg; i <= iend; i += 2) {
-                if (k < kf || ifd != 1) {
+                if (nine) {
                     for (int j = 2; j <= J1; j++)
                         B[j] = QF(i, j) + SO(i, j, KW) * Q(i - 1, j) + SO(i + 1, j, KW) * Q(i + 1, j)
                                + SO(i, j, KSW) * Q(i - 1, j - 1) + SO(i + 1, j, KNW) * Q(i + 1, j - 1)
@@ -1074,11 +1125,27 @@ int orc2_relax_lines_y(int k, const double *so, const double *qf, double *q, con
                         B[j] = QF(i, j) + SO(i, j, KW) * Q(i - 1, j) + SO(i + 1, j, KW) * Q(i + 1, j);
                 }
                 orc_dptts2(J1 - 1, &SOR(2, i, 1), &SOR(3, i, 2), &B[2]);
-                for (int j = 2; j <= J1; j++) Q(i, j) = B[j];
+                if (per_line) {
+                    for (int j = 2; j <= J1; j++) B[JJ + j] = 0.0;
+                    B[JJ + 2] = -SO(i, 2, KS);
+                    B[JJ + J1] = -SO(i, JJ, KS);
+                    orc_dptts2(J1 - 1, &SOR(2, i, 1), &SOR(3, i, 2), &B[JJ + 2]);
+                    double alpha = B[JJ + 2] + B[JJ + J1];
+                    double beta = B[2] + B[J1];
+                    beta = beta / (1.0 + alpha);
+                    for (int j = 2; j <= J1; j++) Q(i, j) = B[j] - beta * B[JJ + j];
+                } else {
+                    for (int j = 2; j <= J1; j++) Q(i, j) = B[j];
+                }
             }
             __builtin_free(B);
         }
+        if (per_line) {
+            if (wrap_y) lines_wrap_y(q, II, JJ);
+            if (wrap_x) lines_wrap_x(q, II, JJ);
+        }
     }
+    if (!per_line && wrap_x) lines_wrap_x(q, II, JJ);
     return 0;
 #undef SO
 #undef Q

@@ -269,3 +269,38 @@ def test_dense_cholesky_restatement_against_scipy():
         x = b.copy()
         L.orc_dpotrs_upper(n, P(a), n, P(x))
         assert np.allclose(x, np.linalg.solve(A, b), rtol=1e-10, atol=1e-12)
+
+
+@pytest.mark.parametrize("jpn", [1, 2, 3, -1, -2, -3, -4])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(4, 4), (8, 6), (7, 5), (16, 17), (37, 64), (64, 38)])
+def test_periodic_line_relaxation_bitwise_vs_reference(nx, ny, nine, jpn):
+    """Periodic halves of SETUP_lines_x/_y (f90:76-83) and relax_lines_x/_y (x: f90:170-306, y: f90:178-296): wrap
+    couplings added to the end diagonals, Sherman-Morrison correction with a second solve per line, ghost refresh after
+    every colour -- and, for lines NOT periodic in their own direction, the other direction's ghosts refreshed only once
+    at the end (x: f90:162-167).  Ghosts start inconsistent with the interior, as the reference does not fix them."""
+    R, L = ref.lib(), oracle.lib()
+    rng = np.random.default_rng(nx * 17 + ny * 3 + nine + 10 * abs(jpn))
+    II, JJ = nx + 2, ny + 2
+    nst, ifd = (5, 0) if nine else (3, 1)
+    so = 10.0 ** rng.uniform(-1, 1, size=(nst, JJ, II))     # periodic operators carry couplings in the ghost layer too
+    so[0] = so[1:].sum(axis=0) * 2.5 + 1.0
+    b = rng.standard_normal((JJ, II))
+    q = rng.standard_normal((JJ, II))
+    x1, x2 = np.zeros((2, JJ, II)), np.zeros((2, JJ, II))
+    y1, y2 = np.zeros((2, II, JJ)), np.zeros((2, II, JJ))
+    assert L.orc2_setup_lines_x(P(so), P(x1), II, JJ, nst, jpn) == 0
+    R.BMG2_SymStd_SETUP_lines_x(P(so), P(x2), II, JJ, nst, jpn)
+    assert L.orc2_setup_lines_y(P(so), P(y1), II, JJ, nst, jpn) == 0
+    R.BMG2_SymStd_SETUP_lines_y(P(so), P(y2), II, JJ, nst, jpn)
+    assert np.array_equal(x1[:, 1:-1, 1:-1], x2[:, 1:-1, 1:-1]) and np.array_equal(y1[:, 1:-1, 1:-1], y2[:, 1:-1, 1:-1])
+    w1, w2 = np.zeros(4 * max(II, JJ)), np.zeros(4 * max(II, JJ))
+    q1, q2 = q.copy(), q.copy()
+    for ud in (0, 1, 1, 0):
+        assert L.orc2_relax_lines_x(1, P(so), P(b), P(q1), P(x1), P(w1), II, JJ, 1, ifd, nst, 1, ud, jpn) == 0
+        R.BMG2_SymStd_relax_lines_x(1, P(so), P(b), P(q2), P(x2), P(w2), II, JJ, 1, ifd, nst, 1, ud, jpn)
+        assert np.array_equal(q1, q2), f"x-lines updown={ud}"
+        assert L.orc2_relax_lines_y(1, P(so), P(b), P(q1), P(y1), P(w1), II, JJ, 1, ifd, nst, 1, ud, jpn) == 0
+        R.BMG2_SymStd_relax_lines_y(1, P(so), P(b), P(q2), P(y2), P(w2), II, JJ, 1, ifd, nst, 1, ud, jpn)
+        assert np.array_equal(q1, q2), f"y-lines updown={ud}"
+    assert not np.array_equal(q1, q)
