@@ -46,6 +46,7 @@ SIGNATURES = {
     "bmgx2_lines_rhs_push": (_i, [_i, _i, _p, _p, _p, _u, _u, _u, _u, _u, _u, _i, _u, _p, _p]),
     "bmgx2_lines_solve_T": (_i, [_p, _p, _u, _u, _i, _p]),
     "bmgx2_lines_scatter_push": (_i, [_i, _p, _u, _u, _i, _u, _p, _p]),
+    "bmgx2_relax_lines_y_static": (_i, [_i, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx2_residual": (_i, [_i, _p, _p, _p, _p, _u, _u, _i, _i, _i, _i, _i, _i, _i, _p]),
     "bmgx2_matvec": (_i, [_i, _p, _p, _p, _u, _u, _i, _i, _i, _p]),
     "bmgx2_restrict": (_i, [_p, _p, _p, _u, _u, _u, _u, _i, _p]),

@@ -754,3 +754,36 @@ extern "C" int bmgx2_lines_scatter_push(int dirn, const double *lb, bmgx_len nro
     BMGX_LAUNCH_CHECK("lines_scatter_push");
     return BMGX_OK;
 }
+
+// ---- y-line relaxation without any allocation on the caller's side -------------------------------------------
+// No counterpart in the reference: added for callers that cannot call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  bmgx2_relax_lines_y needs ii*jj
+// doubles of scratch for the transposed right-hand sides; here that scratch is a file-scope device array of
+// BMGX_LINES_Y_STATIC_MAX doubles (8 MiB), held by every GPU that loads the library until the process exits.
+// The array's name is a host-side stand-in in host code: its device address comes from cudaGetSymbolAddress, once per
+// device, with that device current.  Every call shares the array and finds the previous call's contents in it; nothing
+// in it has to start at zero (every entry the solve reads is written by the right-hand-side kernel of the same colour
+// first), so nothing is cleared.  Calls that overlap on the GPU (different streams, or several host threads) RACE on it.
+static __device__ __align__(256) double g_lines_y_scratch[BMGX_LINES_Y_STATIC_MAX];
+
+extern "C" int bmgx2_relax_lines_y_static(int k, const double *so, const double *qf, double *q, const double *sor,
+                                          bmgx_len ii, bmgx_len jj, int kf, int ifd, int nstncl, int irelax_sym,
+                                          int updown, int jpn, bmgx_stream_t s)
+{
+    static double *scratch_of[64] = {};   // per device
+    if ((size_t)ii * jj * bmgx_batch() > (size_t)BMGX_LINES_Y_STATIC_MAX)
+        return bmgx_set_error(BMGX_ERR_ARG, "relax_lines_y_static: ii*jj (times the batch count) exceeds "
+                                            "BMGX_LINES_Y_STATIC_MAX = 1048576 doubles of built-in scratch; use "
+                                            "bmgx2_relax_lines_y with caller scratch");
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return bmgx_set_cuda_error(e, "relax_lines_y_static/device");
+    if (dev < 0 || dev >= 64) return bmgx_set_error(BMGX_ERR_ARG, "relax_lines_y_static: device ordinal out of range");
+    if (!scratch_of[dev]) {
+        double *p = nullptr;
+        e = cudaGetSymbolAddress((void **)&p, g_lines_y_scratch);
+        if (e != cudaSuccess || !p) return bmgx_set_cuda_error(e, "relax_lines_y_static/cudaGetSymbolAddress");
+        scratch_of[dev] = p;
+    }
+    return bmgx2_relax_lines_y(k, so, qf, q, sor, scratch_of[dev], ii, jj, kf, ifd, nstncl, irelax_sym, updown, jpn, s);
+}

@@ -170,6 +170,17 @@ int bmgx2_relax_lines_y(int k, const bmgx_real *so, const bmgx_real *qf, bmgx_re
                         int kf, int ifd, int nstncl, int irelax_sym, int updown, int jpn,
                         bmgx_stream_t s);
 
+/* bmgx2_relax_lines_y with NO allocation anywhere: the ii*jj doubles of scratch live in a device array built into the
+ * library.  No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (CUDA graph capture, serving loops, harnesses that forbid it).  Limit: ii*jj (times the batch count)
+ * <= BMGX_LINES_Y_STATIC_MAX doubles (8 MiB, held by every GPU that loads the library until exit); larger grids are
+ * refused with BMGX_ERR_ARG.  All calls share the one array: calls that overlap on the GPU (other streams, other host
+ * threads) race.  Same kernels, same result bit for bit as bmgx2_relax_lines_y. */
+#define BMGX_LINES_Y_STATIC_MAX (1u << 20)
+int bmgx2_relax_lines_y_static(int k, const bmgx_real *so, const bmgx_real *qf, bmgx_real *q, const bmgx_real *sor,
+                               bmgx_len ii, bmgx_len jj, int kf, int ifd, int nstncl, int irelax_sym, int updown,
+                               int jpn, bmgx_stream_t s);
+
 /* one colour of the sweeps above: the lines with F-index first, first + 2, ... (first = 2 or 3) */
 int bmgx2_relax_lines_x_colour(const bmgx_real *so, const bmgx_real *qf, bmgx_real *q, const bmgx_real *sor, bmgx_len ii,
                                bmgx_len jj, int nine_pt, int first, bmgx_stream_t s);
