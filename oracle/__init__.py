@@ -102,7 +102,7 @@ class Solver2:
                                               nrelax_pre, nrelax_post, num_levels, min_coarse,
                                               int(bool(periodic[0])) + 2 * int(bool(periodic[1])))
         if not self.h:
-            raise ValueError("periodic boundary conditions: point relaxation only")
+            raise ValueError("oracle solver could not be created")
         self.h = C.c_void_p(self.h)
         self.nlevels = lib().orc2_solver_nlevels(self.h)
         if cycle == "f":       # include/cedar/cycle/fcycle.h

@@ -63,19 +63,19 @@ static void relax_level(orc2_solver *s, int l, double *x, const double *b, int u
         orc2_relax_gs(1, L->A, b, x, L->SOR[0], II, JJ, 1, ifd, L->nstncl, 2, 1, updown, s->ibc);
         break;
     case ORC_RELAX_LINE_X:
-        orc2_relax_lines_x(1, L->A, b, x, L->SOR[0], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, 0);
+        orc2_relax_lines_x(1, L->A, b, x, L->SOR[0], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, s->ibc);
         break;
     case ORC_RELAX_LINE_Y:
-        orc2_relax_lines_y(1, L->A, b, x, L->SOR[0], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, 0);
+        orc2_relax_lines_y(1, L->A, b, x, L->SOR[0], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, s->ibc);
         break;
     case ORC_RELAX_LINE_XY:
         /* multilevel.h:175-178 (DOWN: x then y), 204-207 (UP: y then x) */
         if (updown == 0) {
-            orc2_relax_lines_x(1, L->A, b, x, L->SOR[0], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, 0);
-            orc2_relax_lines_y(1, L->A, b, x, L->SOR[1], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, 0);
+            orc2_relax_lines_x(1, L->A, b, x, L->SOR[0], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, s->ibc);
+            orc2_relax_lines_y(1, L->A, b, x, L->SOR[1], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, s->ibc);
         } else {
-            orc2_relax_lines_y(1, L->A, b, x, L->SOR[1], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, 0);
-            orc2_relax_lines_x(1, L->A, b, x, L->SOR[0], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, 0);
+            orc2_relax_lines_y(1, L->A, b, x, L->SOR[1], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, s->ibc);
+            orc2_relax_lines_x(1, L->A, b, x, L->SOR[0], s->linebuf, II, JJ, 1, ifd, L->nstncl, 1, updown, s->ibc);
         }
         break;
     }
@@ -88,14 +88,12 @@ orc2_solver *orc2_solver_create(const double *so, int nx, int ny, int nstncl,
     return orc2_solver_create_per(so, nx, ny, nstncl, relaxation, nrelax_pre, nrelax_post, num_levels, min_coarse, 0);
 }
 
-/* per_mask: bit 0 = periodic in x, bit 1 = periodic in y (kernel_params::per_mask, include/cedar/kernel_params.h:33-41);
- * point relaxation only (the periodic line solves are not restated) */
+/* per_mask: bit 0 = periodic in x, bit 1 = periodic in y (kernel_params::per_mask, include/cedar/kernel_params.h:33-41) */
 orc2_solver *orc2_solver_create_per(const double *so, int nx, int ny, int nstncl,
                                     int relaxation, int nrelax_pre, int nrelax_post,
                                     int num_levels, int min_coarse, int per_mask)
 {
     static const int bcmap[4] = {0, 2, 1, 3};   /* BMG_get_bc.f90:13-22 */
-    if (per_mask && relaxation != ORC_RELAX_POINT) return NULL;
     orc2_solver *s = (orc2_solver *)calloc(1, sizeof(*s));
     s->ibc = bcmap[per_mask & 3];
     s->relaxation = relaxation;
@@ -144,14 +142,14 @@ orc2_solver *orc2_solver_create_per(const double *so, int nx, int ny, int nstncl
             orc2_setup_recip(F->A, F->SOR[0], F->nx + 2, F->ny + 2, F->nstncl, 2);
             break;
         case ORC_RELAX_LINE_X:
-            orc2_setup_lines_x(F->A, F->SOR[0], F->nx + 2, F->ny + 2, F->nstncl, 0);
+            orc2_setup_lines_x(F->A, F->SOR[0], F->nx + 2, F->ny + 2, F->nstncl, s->ibc);
             break;
         case ORC_RELAX_LINE_Y:
-            orc2_setup_lines_y(F->A, F->SOR[0], F->nx + 2, F->ny + 2, F->nstncl, 0);
+            orc2_setup_lines_y(F->A, F->SOR[0], F->nx + 2, F->ny + 2, F->nstncl, s->ibc);
             break;
         case ORC_RELAX_LINE_XY:
-            orc2_setup_lines_x(F->A, F->SOR[0], F->nx + 2, F->ny + 2, F->nstncl, 0);
-            orc2_setup_lines_y(F->A, F->SOR[1], F->nx + 2, F->ny + 2, F->nstncl, 0);
+            orc2_setup_lines_x(F->A, F->SOR[0], F->nx + 2, F->ny + 2, F->nstncl, s->ibc);
+            orc2_setup_lines_y(F->A, F->SOR[1], F->nx + 2, F->ny + 2, F->nstncl, s->ibc);
             break;
         }
     }
