@@ -38,7 +38,7 @@
 //   dst: sor[(size_t)l*dl + p] for D and sor[plane + l*dl + p] for L
 __global__ void __launch_bounds__(128)
 k_setup_lines(const double *__restrict__ so_d, const double *__restrict__ so_o, size_t sp, size_t sl,
-              double *__restrict__ sor, size_t plane, size_t dl, unsigned n, unsigned nlines)
+              double *__restrict__ sor, size_t plane, size_t dl, unsigned n, unsigned nlines, int per)
 {
     // lines are 1..nlines-2 (0-based interior 1..), positions 1..n-2 interior
     unsigned l = blockIdx.x * blockDim.x + threadIdx.x + 1;
@@ -47,7 +47,15 @@ k_setup_lines(const double *__restrict__ so_d, const double *__restrict__ so_o, 
     double *D = sor + (size_t)l * dl, *L = sor + plane + (size_t)l * dl;
     // DPTTRF(n-2, D(1..), L(2..)) on d(p)=diag(p), e(p)=-off(p+1).  The recurrence is sequential, its operands
     // are not: they are fetched 16 positions ahead so that the chain never waits for memory
+    // lines periodic in their own direction (SETUP_lines_x.f90:76-83): the wrap couplings SO(2,.,KW) and SO(Nx,.,KW) join
+    // the first and the last diagonal entry before the factorisation
+    const unsigned last = n - 2;
     double d = pd[(size_t)1 * sp];
+    if (per) {
+        d = d + po[(size_t)1 * sp];
+        if (last == 1) d = d + po[(size_t)(n - 1) * sp];
+    }
+    const double wrap_r = per ? po[(size_t)(n - 1) * sp] : 0.0;
     constexpr unsigned U = 16;
     for (unsigned p0 = 1; p0 + 1 <= n - 2; p0 += U) {
         double eo[U], dn[U];
@@ -66,7 +74,7 @@ k_setup_lines(const double *__restrict__ so_d, const double *__restrict__ so_o, 
                 D[p] = d;
                 const double e = ei / d;
                 L[p + 1] = e;
-                d = dn[u] - e * ei;
+                d = ((per && p + 1 == last) ? dn[u] + wrap_r : dn[u]) - e * ei;
             }
         }
     }
@@ -78,12 +86,12 @@ extern "C" int bmgx2_SETUP_lines_x(const double *so, double *sor, bmgx_len nx, b
                                    bmgx_stream_t s)
 {
     (void)nstncl;
-    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SETUP_lines_x: periodic BCs not supported");
     if (nx < 3 || ny < 3) return BMGX_OK;
+    const int ipn = jpn < 0 ? -jpn : jpn, per = (ipn == 2 || ipn == 3) ? 1 : 0;
     size_t pl = (size_t)nx * ny;
     // line l = j (0-based), position p = i (0-based): src stride sp=1, sl=nx; dst line stride nx
     k_setup_lines<<<cdiv(ny - 2, 128), 128, 0, (cudaStream_t)s>>>(so + (KO - 1) * pl, so + (KW - 1) * pl, 1, nx, sor,
-                                                                  pl, nx, nx, ny);
+                                                                  pl, nx, nx, ny, per);
     BMGX_LAUNCH_CHECK("SETUP_lines_x");
     return BMGX_OK;
 }
@@ -92,12 +100,12 @@ extern "C" int bmgx2_SETUP_lines_y(const double *so, double *sor, bmgx_len nx, b
                                    bmgx_stream_t s)
 {
     (void)nstncl;
-    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SETUP_lines_y: periodic BCs not supported");
     if (nx < 3 || ny < 3) return BMGX_OK;
+    const int ipn = jpn < 0 ? -jpn : jpn, per = (ipn == 1 || ipn == 3) ? 1 : 0;
     size_t pl = (size_t)nx * ny;
     // line l = i, position p = j: src stride sp=nx, sl=1; dst SOR(j,i,.) line stride ny
     k_setup_lines<<<cdiv(nx - 2, 128), 128, 0, (cudaStream_t)s>>>(so + (KO - 1) * pl, so + (KS - 1) * pl, nx, 1, sor,
-                                                                  pl, ny, ny, nx);
+                                                                  pl, ny, ny, nx, per);
     BMGX_LAUNCH_CHECK("SETUP_lines_y");
     return BMGX_OK;
 }
@@ -229,6 +237,24 @@ __device__ __forceinline__ void block_ldl_solve(double *sv, const double *se, co
     __syncthreads();
 }
 
+// Lines periodic in their own direction (relax_lines_x.f90:209-224): the factor is that of the tridiagonal part with the
+// wrap couplings added to its end diagonals; Sherman-Morrison puts the wrap back: a second solve with the couplings as
+// right-hand side (sz), then x = y - (y_first + y_last) / (1 + z_first + z_last) * z.  sv holds y on entry, x on exit.
+__device__ __forceinline__ void block_periodic_fix(double *sv, double *sz, const double *se, const double *__restrict__ D,
+                                                   unsigned m, unsigned C, double wl, double wr, Aff *wsum, Aff *wpre)
+{
+    for (unsigned p = 1 + threadIdx.x; p <= m; p += blockDim.x) sz[p - 1] = 0.0;
+    __syncthreads();
+    if (threadIdx.x == 0) { sz[0] = -wl; sz[m - 1] = -wr; }
+    block_ldl_solve(sz, se, D, m, C, wsum, wpre);
+    const double alpha = sz[0] + sz[m - 1];
+    double beta = sv[0] + sv[m - 1];
+    beta = beta / (1.0 + alpha);
+    __syncthreads();
+    for (unsigned p = 1 + threadIdx.x; p <= m; p += blockDim.x) sv[p - 1] = sv[p - 1] - beta * sz[p - 1];
+    __syncthreads();
+}
+
 // pull n doubles starting at base into L2 (one request per 32-byte sector, no destination
 // register, never waited on): the demand loads that follow are scheduled by ptxas in small
 // groups, each group paying one full memory latency -- after the prefetch that is an L2 hit
@@ -242,7 +268,7 @@ __device__ __forceinline__ void l2_prefetch_row(const double *base, unsigned n)
 template <bool NINE>
 __global__ void __launch_bounds__(1024)
 k_linex_block(const double *__restrict__ so, const double *__restrict__ qf, double *q,
-              const double *__restrict__ sor, unsigned II, unsigned JJ, unsigned jbeg, unsigned C)
+              const double *__restrict__ sor, unsigned II, unsigned JJ, unsigned jbeg, unsigned C, int per)
 {
     extern __shared__ double lsm[];
     __shared__ Aff wsum[32], wpre[32];
@@ -288,13 +314,17 @@ k_linex_block(const double *__restrict__ so, const double *__restrict__ qf, doub
         }
     }
     block_ldl_solve(sv, se, sor + row, m, C, wsum, wpre);
+    if (per) {
+        const double *kw = so + (KW - 1) * pl;
+        block_periodic_fix(sv, lsm + 2 * (m + 1), se, sor + row, m, C, kw[row + 1], kw[row + II - 1], wsum, wpre);
+    }
     for (unsigned i = 1 + threadIdx.x; i <= m; i += blockDim.x) q[row + i] = sv[i - 1];
 }
 
 // y-lines, step 2: one CTA per line i on the transposed right-hand side B(j,i), in place
 __global__ void __launch_bounds__(1024)
 k_liney_block(double *__restrict__ B, const double *__restrict__ sor, unsigned II, unsigned JJ, unsigned ibeg,
-              unsigned C)
+              unsigned C, const double *__restrict__ ks_per)
 {
     extern __shared__ double lsm[];
     __shared__ Aff wsum[32], wpre[32];
@@ -320,15 +350,18 @@ k_liney_block(double *__restrict__ B, const double *__restrict__ sor, unsigned I
         }
     }
     block_ldl_solve(sv, se, sor + row, m, C, wsum, wpre);
+    if (ks_per)   // the KS plane of the operator: SO(i,2,KS), SO(i,JJ,KS) are the wrap couplings of line i (relax_lines_y.f90:215-219)
+        block_periodic_fix(sv, lsm + 2 * (m + 1), se, sor + row, m, C, ks_per[(size_t)II + (i - 1)],
+                           ks_per[(size_t)(JJ - 1) * II + (i - 1)], wsum, wpre);
     for (unsigned p = 1 + threadIdx.x; p <= m; p += blockDim.x) B[row + p] = sv[p - 1];
 }
 
 // odd chunk length C and CTA width for a line of m unknowns; false if it does not fit.
 // Shared memory (16 B per unknown) bounds the lines resident per SM; the CTA width is
 // chosen so that those CTAs together keep ~1280 threads (<= 48 registers each) on the SM.
-static bool line_plan(unsigned m, unsigned *C, unsigned *threads, size_t *smem)
+static bool line_plan(unsigned m, unsigned *C, unsigned *threads, size_t *smem, unsigned nvec = 2)
 {
-    *smem = 2 * (size_t)(m + 1) * sizeof(double);
+    *smem = nvec * (size_t)(m + 1) * sizeof(double);
     if (*smem > 200 * 1024) return false;
     unsigned resident = (unsigned)((220 * 1024) / (*smem + 1024));
     if (resident < 1) resident = 1;
@@ -347,7 +380,8 @@ static bool line_plan(unsigned m, unsigned *C, unsigned *threads, size_t *smem)
 
 template <bool NINE>
 static cudaError_t launch_linex(unsigned C, unsigned nl, unsigned threads, size_t smem, cudaStream_t st, const double *so,
-                                const double *qf, double *q, const double *sor, unsigned II, unsigned JJ, unsigned jbeg)
+                                const double *qf, double *q, const double *sor, unsigned II, unsigned JJ, unsigned jbeg,
+                                int per = 0)
 {
     static bool attr_set = false;
     if (!attr_set) {
@@ -355,12 +389,12 @@ static cudaError_t launch_linex(unsigned C, unsigned nl, unsigned threads, size_
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    k_linex_block<NINE><<<dim3(nl, bmgx_batch()), threads, smem, st>>>(so, qf, q, sor, II, JJ, jbeg, C);
+    k_linex_block<NINE><<<dim3(nl, bmgx_batch()), threads, smem, st>>>(so, qf, q, sor, II, JJ, jbeg, C, per);
     return cudaSuccess;
 }
 
 static cudaError_t launch_liney(unsigned C, unsigned nl, unsigned threads, size_t smem, cudaStream_t st, double *B,
-                                const double *sor, unsigned II, unsigned JJ, unsigned ibeg)
+                                const double *sor, unsigned II, unsigned JJ, unsigned ibeg, const double *ks_per = nullptr)
 {
     static bool attr_set = false;
     if (!attr_set) {
@@ -368,7 +402,7 @@ static cudaError_t launch_liney(unsigned C, unsigned nl, unsigned threads, size_
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    k_liney_block<<<dim3(nl, bmgx_batch()), threads, smem, st>>>(B, sor, II, JJ, ibeg, C);
+    k_liney_block<<<dim3(nl, bmgx_batch()), threads, smem, st>>>(B, sor, II, JJ, ibeg, C, ks_per);
     return cudaSuccess;
 }
 
@@ -497,9 +531,9 @@ k_lines_y_scatter(const double *__restrict__ B, double *__restrict__ q, unsigned
     }
 }
 
-// the lines jbeg, jbeg + 2, ... (one colour) of an x-line sweep
-extern "C" int bmgx2_relax_lines_x_colour(const double *so, const double *qf, double *q, const double *sor, bmgx_len ii,
-                                          bmgx_len jj, int nine_pt, int jbeg_, bmgx_stream_t s)
+// the lines jbeg, jbeg + 2, ... (one colour) of an x-line sweep; per: the lines are periodic (Sherman-Morrison)
+static int linex_colour(const double *so, const double *qf, double *q, const double *sor, bmgx_len ii, bmgx_len jj,
+                        int nine_pt, int jbeg_, int per, bmgx_stream_t s)
 {
     if (ii < 3 || jj < 3) return BMGX_OK;
     {
@@ -508,11 +542,13 @@ extern "C" int bmgx2_relax_lines_x_colour(const double *so, const double *qf, do
         if (jbeg < 2 || jbeg > jj - 1) return BMGX_OK;
         unsigned nl = (jj - 1 - jbeg) / 2 + 1;
         unsigned lg, threads; size_t smem;
-        if (line_plan(ii - 2, &lg, &threads, &smem)) {
-            cudaError_t e = nine ? launch_linex<true>(lg, nl, threads, smem, (cudaStream_t)s, so, qf, q, sor, ii, jj, jbeg)
-                                 : launch_linex<false>(lg, nl, threads, smem, (cudaStream_t)s, so, qf, q, sor, ii, jj, jbeg);
+        if (line_plan(ii - 2, &lg, &threads, &smem, per ? 3 : 2)) {
+            cudaError_t e = nine ? launch_linex<true>(lg, nl, threads, smem, (cudaStream_t)s, so, qf, q, sor, ii, jj, jbeg, per)
+                                 : launch_linex<false>(lg, nl, threads, smem, (cudaStream_t)s, so, qf, q, sor, ii, jj, jbeg, per);
             if (e != cudaSuccess) return bmgx_set_cuda_error(e, "relax_lines_x/attr");
-        } else if (bmgx_batch() > 1)
+        } else if (per)
+            return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_x: periodic lines too long for shared memory (> 8500 unknowns)");
+        else if (bmgx_batch() > 1)
             return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_x: lines too long for the batched path");
         else if (nine)
             k_relax_lines_x<true><<<cdiv((size_t)nl * 32, 128), 128, 0, (cudaStream_t)s>>>(so, qf, q, sor, ii, jj, jbeg);
@@ -523,25 +559,45 @@ extern "C" int bmgx2_relax_lines_x_colour(const double *so, const double *qf, do
     return BMGX_OK;
 }
 
+extern "C" int bmgx2_relax_lines_x_colour(const double *so, const double *qf, double *q, const double *sor, bmgx_len ii,
+                                          bmgx_len jj, int nine_pt, int jbeg_, bmgx_stream_t s)
+{
+    return linex_colour(so, qf, q, sor, ii, jj, nine_pt, jbeg_, 0, s);
+}
+
 extern "C" int bmgx2_relax_lines_x(int k, const double *so, const double *qf, double *q, const double *sor,
                                    double *b, bmgx_len ii, bmgx_len jj, int kf, int ifd, int nstncl,
                                    int irelax_sym, int updown, int jpn, bmgx_stream_t s)
 {
     (void)nstncl; (void)b;
-    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_x: periodic BCs not supported");
     if (ii < 3 || jj < 3) return BMGX_OK;
+    // relax_lines_x.f90:73-75, 170: x periodic => Sherman-Morrison per line and a ghost refresh after every colour;
+    // y periodic only => the plain solve and ONE refresh of the ghost rows after both colours (l.162-167).  (The code
+    // -4 also enters the reference's second branch, with zero wrap couplings: a correction of exactly zero.)
+    const int ipn = jpn < 0 ? -jpn : jpn;
+    const bool wrap_x = ipn == 2 || ipn == 3, wrap_y = ipn == 1 || ipn == 3;
     bool fwd = (irelax_sym == BMGX_RELAX_NONSYM) || (updown == BMGX_DOWN && irelax_sym == BMGX_RELAX_SYM);
     for (int a = 0; a < 2; a++) {
         // DOWN: odd lines (3,5,..) first (relax_lines_x.f90:83-99)
-        int st = bmgx2_relax_lines_x_colour(so, qf, q, sor, ii, jj, (k < kf || ifd != 1) ? 1 : 0, fwd ? 3 - a : 2 + a, s);
+        int st = linex_colour(so, qf, q, sor, ii, jj, (k < kf || ifd != 1) ? 1 : 0, fwd ? 3 - a : 2 + a, wrap_x ? 1 : 0, s);
         if (st != BMGX_OK) return st;
+        if (wrap_x) {
+            for (unsigned nb = 0; nb < bmgx_batch(); nb++) {
+                double *qb = q + (size_t)nb * ii * jj;
+                if (wrap_y && bmgx_wrap_y(qb, ii, jj, (cudaStream_t)s)) return BMGX_ERR_CUDA;
+                if (bmgx_wrap_x(qb, ii, 1, 1, jj, (cudaStream_t)s)) return BMGX_ERR_CUDA;
+            }
+        }
     }
+    if (!wrap_x && wrap_y)
+        for (unsigned nb = 0; nb < bmgx_batch(); nb++)
+            if (bmgx_wrap_y(q + (size_t)nb * ii * jj, ii, jj, (cudaStream_t)s)) return BMGX_ERR_CUDA;
     return BMGX_OK;
 }
 
-// the lines ibeg, ibeg + 2, ... (one colour) of a y-line sweep
-extern "C" int bmgx2_relax_lines_y_colour(const double *so, const double *qf, double *q, const double *sor, double *b,
-                                          bmgx_len ii, bmgx_len jj, int nine_pt, int ibeg_, bmgx_stream_t s)
+// the lines ibeg, ibeg + 2, ... (one colour) of a y-line sweep; per: the lines are periodic (Sherman-Morrison)
+static int liney_colour(const double *so, const double *qf, double *q, const double *sor, double *b, bmgx_len ii, bmgx_len jj,
+                        int nine_pt, int ibeg_, int per, bmgx_stream_t s)
 {
     if (!b) return bmgx_set_error(BMGX_ERR_ARG, "relax_lines_y: scratch b (ii*jj doubles) required");
     if (ii < 3 || jj < 3) return BMGX_OK;
@@ -555,10 +611,13 @@ extern "C" int bmgx2_relax_lines_y_colour(const double *so, const double *qf, do
         else k_lines_y_rhs<false><<<g, 256, 0, st>>>(so, qf, q, b, ii, jj, ibeg);
         BMGX_LAUNCH_CHECK("relax_lines_y/rhs");
         unsigned lg, threads; size_t smem;
-        if (line_plan(jj - 2, &lg, &threads, &smem)) {
-            cudaError_t e = launch_liney(lg, nl, threads, smem, st, b, sor, ii, jj, ibeg);
+        if (line_plan(jj - 2, &lg, &threads, &smem, per ? 3 : 2)) {
+            cudaError_t e = launch_liney(lg, nl, threads, smem, st, b, sor, ii, jj, ibeg,
+                                         per ? so + (size_t)(KS - 1) * ii * jj : nullptr);
             if (e != cudaSuccess) return bmgx_set_cuda_error(e, "relax_lines_y/attr");
-        } else if (bmgx_batch() > 1)
+        } else if (per)
+            return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_y: periodic lines too long for shared memory (> 8500 unknowns)");
+        else if (bmgx_batch() > 1)
             return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_y: lines too long for the batched path");
         else
             k_lines_y_solve<<<cdiv((size_t)nl * 32, 128), 128, 0, st>>>(b, sor, ii, jj, ibeg);
@@ -569,19 +628,35 @@ extern "C" int bmgx2_relax_lines_y_colour(const double *so, const double *qf, do
     return BMGX_OK;
 }
 
+extern "C" int bmgx2_relax_lines_y_colour(const double *so, const double *qf, double *q, const double *sor, double *b,
+                                          bmgx_len ii, bmgx_len jj, int nine_pt, int ibeg_, bmgx_stream_t s)
+{
+    return liney_colour(so, qf, q, sor, b, ii, jj, nine_pt, ibeg_, 0, s);
+}
+
 extern "C" int bmgx2_relax_lines_y(int k, const double *so, const double *qf, double *q, const double *sor,
                                    double *b, bmgx_len ii, bmgx_len jj, int kf, int ifd, int nstncl,
                                    int irelax_sym, int updown, int jpn, bmgx_stream_t s)
 {
     (void)nstncl;
-    if (!bmgx_nonperiodic(jpn)) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_y: periodic BCs not supported");
     if (!b) return bmgx_set_error(BMGX_ERR_ARG, "relax_lines_y: scratch b (ii*jj doubles) required");
     if (ii < 3 || jj < 3) return BMGX_OK;
+    // relax_lines_y.f90:73-75, 178: the mirror image of the x version
+    const int ipn = jpn < 0 ? -jpn : jpn;
+    const bool wrap_x = ipn == 2 || ipn == 3, wrap_y = ipn == 1 || ipn == 3;
+    if (wrap_y && bmgx_batch() > 1) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_y: periodic lines are not batched");
     bool fwd = (irelax_sym == BMGX_RELAX_NONSYM) || (updown == BMGX_DOWN && irelax_sym == BMGX_RELAX_SYM);
     for (int a = 0; a < 2; a++) {
-        int st = bmgx2_relax_lines_y_colour(so, qf, q, sor, b, ii, jj, (k < kf || ifd != 1) ? 1 : 0, fwd ? 3 - a : 2 + a, s);
+        int st = liney_colour(so, qf, q, sor, b, ii, jj, (k < kf || ifd != 1) ? 1 : 0, fwd ? 3 - a : 2 + a, wrap_y ? 1 : 0, s);
         if (st != BMGX_OK) return st;
+        if (wrap_y) {
+            if (bmgx_wrap_y(q, ii, jj, (cudaStream_t)s)) return BMGX_ERR_CUDA;
+            if (wrap_x && bmgx_wrap_x(q, ii, 1, 1, jj, (cudaStream_t)s)) return BMGX_ERR_CUDA;
+        }
     }
+    if (!wrap_y && wrap_x)
+        for (unsigned nb = 0; nb < bmgx_batch(); nb++)
+            if (bmgx_wrap_x(q + (size_t)nb * ii * jj, ii, 1, 1, jj, (cudaStream_t)s)) return BMGX_ERR_CUDA;
     return BMGX_OK;
 }
 

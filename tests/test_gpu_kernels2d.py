@@ -200,8 +200,6 @@ def test_periodic_is_refused(cuda, abi):
     d = cuda.zeros((5, 6, 6), dtype=cuda.float64, device="cuda")
     st = abi.lib.bmgx2_relax_GS_oop(1, ptr(d), ptr(d[0]), ptr(d[1]), ptr(d[2]), ptr(d), 6, 6, 1, 0, 5, 2, 1, 0, 2, None)
     assert st == 2 and b"periodic" in abi.lib.bmgx_last_error()
-    st = abi.lib.bmgx2_SETUP_lines_x(ptr(d), ptr(d), 6, 6, 5, 2, None)
-    assert st == 2 and b"periodic" in abi.lib.bmgx_last_error()
 
 
 @pytest.mark.parametrize("nine", [False, True])
@@ -407,3 +405,45 @@ def test_periodic_coarse_solve_bitwise(cuda, abi, nx, ny, nine, ibc):
     d_x, d_w = dev(cuda, x0), dev(cuda, np.zeros(n))
     abi.check(abi.lib.bmgx2_SOLVE_cg(ptr(d_x), ptr(dev(cuda, b)), II, JJ, ptr(d_abd), ptr(d_w), n, n, ibc, None))
     assert_bitwise(host(d_x), want, "periodic SOLVE_cg")
+
+
+@pytest.mark.parametrize("jpn", [1, 2, 3, -3, -4])
+@pytest.mark.parametrize("nine", [False, True])
+@pytest.mark.parametrize("nx,ny", [(1, 1), (2, 3), (4, 4), (7, 5), (37, 64), (400, 257), (1030, 70)])
+def test_lines_periodic(cuda, abi, nx, ny, nine, jpn):
+    """Periodic halves of the line setup and the line sweeps (SETUP_lines_x.f90:76-83, relax_lines_x.f90:170-306,
+    relax_lines_y.f90:178-296; oracle pinned bitwise against the reference's own Fortran in
+    tests/test_ref_parity_cpu.py): the factor bitwise, the sweeps -- Sherman-Morrison second solve per line, ghost
+    refresh per colour -- to the tolerance of the non-periodic line sweeps (the block-scan solve rounds the chunk-entry
+    values differently from DPTTS2), ghost layer included."""
+    rng = np.random.default_rng(nx * 131 + ny * 7 + nine + 10 * abs(jpn))
+    II, JJ = nx + 2, ny + 2
+    nst = 5 if nine else 3
+    so = 10.0 ** rng.uniform(-1, 1, size=(nst, JJ, II))     # periodic operators carry couplings in the ghost layer
+    so[0] = so[1:].sum(axis=0) * 2.5 + 1.0
+    if jpn == -4:
+        so[:, 0, :] = 0; so[:, -1, :] = 0; so[:, :, 0] = 0; so[:, :, -1] = 0
+    b, q = rng.standard_normal((JJ, II)), rng.standard_normal((JJ, II))
+    L = oracle.lib()
+    sorx, sory = np.zeros((2, JJ, II)), np.zeros((2, II, JJ))
+    assert L.orc2_setup_lines_x(P(so), P(sorx), II, JJ, nst, jpn) == 0
+    assert L.orc2_setup_lines_y(P(so), P(sory), II, JJ, nst, jpn) == 0
+    d_so, d_q, d_b = dev(cuda, so), dev(cuda, q), dev(cuda, b)
+    d_sorx, d_sory = dev(cuda, np.zeros_like(sorx)), dev(cuda, np.zeros_like(sory))
+    abi.check(abi.lib.bmgx2_SETUP_lines_x(ptr(d_so), ptr(d_sorx), II, JJ, nst, jpn, None))
+    abi.check(abi.lib.bmgx2_SETUP_lines_y(ptr(d_so), ptr(d_sory), II, JJ, nst, jpn, None))
+    assert_bitwise(host(d_sorx)[:, 1:-1, 1:-1], sorx[:, 1:-1, 1:-1], "periodic SETUP_lines_x")
+    assert_bitwise(host(d_sory)[:, 1:-1, 1:-1], sory[:, 1:-1, 1:-1], "periodic SETUP_lines_y")
+    work = np.zeros(4 * max(II, JJ))
+    d_w = cuda.zeros((JJ, II), dtype=cuda.float64, device="cuda")
+    for sweep, updown in enumerate((0, 1, 1, 0)):
+        assert L.orc2_relax_lines_x(1, P(so), P(b), P(q), P(sorx), P(work), II, JJ, 1, ifd_of(nine), nst, 1, updown, jpn) == 0
+        abi.check(abi.lib.bmgx2_relax_lines_x(1, ptr(d_so), ptr(d_b), ptr(d_q), ptr(d_sorx), ptr(d_w), II, JJ, 1,
+                                              ifd_of(nine), nst, 1, updown, jpn, None))
+        scale = max(1.0, np.abs(q).max())
+        assert np.abs(host(d_q) - q).max() <= 1e-12 * scale, f"periodic relax_lines_x sweep {sweep}"
+        assert L.orc2_relax_lines_y(1, P(so), P(b), P(q), P(sory), P(work), II, JJ, 1, ifd_of(nine), nst, 1, updown, jpn) == 0
+        abi.check(abi.lib.bmgx2_relax_lines_y(1, ptr(d_so), ptr(d_b), ptr(d_q), ptr(d_sory), ptr(d_w), II, JJ, 1,
+                                              ifd_of(nine), nst, 1, updown, jpn, None))
+        scale = max(1.0, np.abs(q).max())
+        assert np.abs(host(d_q) - q).max() <= 1e-12 * scale, f"periodic relax_lines_y sweep {sweep}"

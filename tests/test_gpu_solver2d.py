@@ -268,10 +268,28 @@ def test_periodic_solver_matches_oracle(cs, case):
     assert len(h) == len(hr) and np.allclose(h, hr, rtol=1e-10, atol=0) and abs(r0 - r0r) <= 1e-12 * r0r
 
 
-def test_periodic_with_line_relaxation_is_refused_cleanly(cs):
-    """the Sherman-Morrison line solves of the periodic branch (relax_lines_x.f90:209-261) are not implemented: a clean
-    error, no wrong answer"""
+@pytest.mark.parametrize("relaxation", ["line-x", "line-y", "line-xy"])
+@pytest.mark.parametrize("case", [((True, False), 300, 300, 1, 1), ((False, True), 129, 200, 2, 1), ((True, True), 64, 96, 1, 1),
+                                  ((True, True), 257, 130, 1, 2)])
+def test_periodic_line_relaxation_solver_matches_oracle(cs, case, relaxation):
+    """grid.periodic with zebra line relaxation (relax_lines_x.f90:170-306, relax_lines_y.f90:178-296: Sherman-Morrison
+    second solve per periodic line, ghost refresh per colour).  Hierarchy bitwise the oracle's, the residual history to the
+    tolerance of the non-periodic line cycles (the GPU line solve agrees with DPTTS2 to rounding), down to a floor."""
     from tests.util import periodic_problem2
-    so, b, _ = periodic_problem2(65, 65, (True, False))
-    with pytest.raises(cs.CedarError, match="periodic"):
-        cs.Solver2(cs.Operator2(so), relaxation="line-x", nrelax_pre=1, nrelax_post=1, periodic=(True, False))
+    per, nx, ny, pre, post = case
+    so, b, exact = periodic_problem2(nx, ny, per)
+    if all(per):
+        so[0] += 0.05 * so[0, 1, 1]          # the doubly periodic Laplacian is singular: make it definite
+        so[0, 0, :] = so[0, ny, :]; so[0, ny + 1, :] = so[0, 1, :]; so[0, :, 0] = so[0, :, nx]; so[0, :, nx + 1] = so[0, :, 1]
+    ref = oracle.Solver2(so, relaxation, pre, post, periodic=per)
+    xr, hr, r0r = ref.solve(b, maxiter=8, tol=1e-30)
+    assert hr[-1] < hr[0]
+    sol = cs.Solver2(cs.Operator2(so), relaxation=relaxation, nrelax_pre=pre, nrelax_post=post, maxiter=8, tol=1e-30, periodic=per)
+    assert sol.nlevels == ref.nlevels
+    for lvl in range(1, sol.nlevels):
+        assert_bitwise(sol.level_array(lvl, "P"), ref.level_array(lvl, "P"), f"P level {lvl}")
+        assert_bitwise(sol.level_array(lvl, "A"), ref.level_array(lvl, "A"), f"A level {lvl}")
+    x, h, r0 = sol.solve(b)
+    assert len(h) == len(hr) and abs(r0 - r0r) <= 1e-12 * r0r
+    assert np.allclose(h, hr, rtol=1e-8, atol=1e-12), (h, hr)
+    assert np.abs(x - xr).max() <= 1e-9 * np.abs(xr).max()
