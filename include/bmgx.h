@@ -34,7 +34,7 @@ typedef void    *bmgx_stream_t;
 enum {
     BMGX_OK = 0,
     BMGX_ERR_CUDA = 1,        /* CUDA runtime error, see bmgx_last_error() */
-    BMGX_ERR_UNSUPPORTED = 2, /* e.g. periodic boundary conditions (not yet) */
+    BMGX_ERR_UNSUPPORTED = 2, /* e.g. periodic boundary conditions in 3D (not built) */
     BMGX_ERR_ARG = 3
 };
 
@@ -160,7 +160,10 @@ int bmgx2_SETUP_lines_y(const bmgx_real *so, bmgx_real *sor, bmgx_len nx, bmgx_l
 
 /* BMG2_SymStd_relax_lines_x / _y (k, so, qf, q, sor, b, ii, jj, kf, ifd,
  *                                 nstncl, irelax_sym, updown, jpn)
- * include/cedar/2d/relax.h:20-25; `b` is scratch of >= ii*jj doubles. */
+ * include/cedar/2d/relax.h:20-25; `b` is scratch of >= ii*jj doubles.  All boundary codes: lines periodic in their own
+ * direction get the Sherman-Morrison second solve (relax_lines_x.f90:209-224) inside the line solver, the ghost layer
+ * is refreshed as the reference does (per colour, or once after both colours for the other direction); periodic lines
+ * of more than ~8500 unknowns are refused (BMGX_ERR_UNSUPPORTED). */
 int bmgx2_relax_lines_x(int k, const bmgx_real *so, const bmgx_real *qf, bmgx_real *q,
                         const bmgx_real *sor, bmgx_real *b, bmgx_len ii, bmgx_len jj,
                         int kf, int ifd, int nstncl, int irelax_sym, int updown, int jpn,

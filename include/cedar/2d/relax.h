@@ -95,11 +95,25 @@ public:
 			gpu::check(bmgx2_relax_lines_x(1, so.cdev(), b.cdev(), x.dev(), sor.cdev(), res.dev(), so.len(0), so.len(1),
 			                               1, ifd, stencil_ndirs<sten>::value, BMGX_RELAX_SYM, updown, ibc,
 			                               gpu::stream()), "relax_lines_x");
-		else
-			gpu::check(bmgx2_relax_lines_y(1, so.cdev(), b.cdev(), x.dev(), sor.cdev(), res.dev(), so.len(0), so.len(1),
+		else {
+			// The y sweep needs ii*jj doubles for the transposed right-hand sides.  The reference uses `res` as its 2*jj
+			// work vector and clears it again (relax_lines_y.f90:229-231), so the ghost layer of res stays zero -- which
+			// the periodic restriction relies on where it does not refresh the fine vector's ghosts.  With periodic
+			// boundaries the scratch is therefore an array of the kernel's own; otherwise res serves (nothing reads its
+			// ghost layer).
+			real_t *work = res.dev();
+			if (ibc != BMGX_BCs_definite && ibc != BMGX_BCs_indef_nonper) {
+				auto &tmp = scratch[std::make_pair(x.len(0), x.len(1))];
+				if (tmp.size() != x.size()) tmp = grid_func(x.shape(0), x.shape(1));
+				work = tmp.dev();
+			}
+			gpu::check(bmgx2_relax_lines_y(1, so.cdev(), b.cdev(), x.dev(), sor.cdev(), work, so.len(0), so.len(1),
 			                               1, ifd, stencil_ndirs<sten>::value, BMGX_RELAX_SYM, updown, ibc,
 			                               gpu::stream()), "relax_lines_y");
+		}
 	}
+private:
+	std::map<std::pair<len_t, len_t>, grid_func> scratch;
 };
 
 }}

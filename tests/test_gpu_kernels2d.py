@@ -409,7 +409,7 @@ def test_periodic_coarse_solve_bitwise(cuda, abi, nx, ny, nine, ibc):
 
 @pytest.mark.parametrize("jpn", [1, 2, 3, -3, -4])
 @pytest.mark.parametrize("nine", [False, True])
-@pytest.mark.parametrize("nx,ny", [(1, 1), (2, 3), (4, 4), (7, 5), (37, 64), (400, 257), (1030, 70)])
+@pytest.mark.parametrize("nx,ny", [(2, 3), (4, 4), (7, 5), (9, 5), (17, 9), (37, 64), (257, 130), (400, 257), (1030, 70)])
 def test_lines_periodic(cuda, abi, nx, ny, nine, jpn):
     """Periodic halves of the line setup and the line sweeps (SETUP_lines_x.f90:76-83, relax_lines_x.f90:170-306,
     relax_lines_y.f90:178-296; oracle pinned bitwise against the reference's own Fortran in
@@ -420,9 +420,12 @@ def test_lines_periodic(cuda, abi, nx, ny, nine, jpn):
     II, JJ = nx + 2, ny + 2
     nst = 5 if nine else 3
     so = 10.0 ** rng.uniform(-1, 1, size=(nst, JJ, II))     # periodic operators carry couplings in the ghost layer
-    so[0] = so[1:].sum(axis=0) * 2.5 + 1.0
-    if jpn == -4:
+    so[0] = so[1:].sum(axis=0) * 2.5 + 25.0                 # every line's tridiagonal matrix positive definite
+    if jpn == -4:                                           # not periodic: no couplings to or inside the ghost layer
         so[:, 0, :] = 0; so[:, -1, :] = 0; so[:, :, 0] = 0; so[:, :, -1] = 0
+        so[1, :, 1] = 0; so[2, 1, :] = 0
+        if nine:
+            so[3, :, 1] = 0; so[3, 1, :] = 0; so[4, :, 1] = 0; so[4, -2, :] = 0
     b, q = rng.standard_normal((JJ, II)), rng.standard_normal((JJ, II))
     L = oracle.lib()
     sorx, sory = np.zeros((2, JJ, II)), np.zeros((2, II, JJ))
