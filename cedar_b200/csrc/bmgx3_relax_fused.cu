@@ -23,8 +23,18 @@
 #include "bmgx3_common.cuh"
 
 #define R7_SX 64
-#define R7_SY 16
-#define R7_NT 256
+// tile 64 x 32 with 512 threads, one CTA per SM (128 registers): 385^3 0.926 ms, 513^3 2.08 ms per sweep; 64 x 16 with 256
+// threads and two CTAs per SM: 0.935 / 2.2 ms (fewer recomputed halo rows win); 80 registers for three CTAs spill: 1.67 ms
+#ifndef R7_SY
+#define R7_SY 32
+#endif
+#ifndef R7_NT
+#define R7_NT 512      // R7_SX * R7_SY / 4: four iterate elements and two (column pair, row) items per thread
+#endif
+#ifndef R7_MINB
+#define R7_MINB 1
+#endif
+#define R7_WR (R7_NT / 32)   // rows between the two items of a thread
 #define R7_OX (R7_SX - 4)
 #define R7_OY (R7_SY - 4)
 #define R7_RING 5
@@ -41,11 +51,13 @@ struct G7 {
 struct Col7 { double pw, pwe, ps, psn, kbd, sor, qf; };
 
 // FIRST_ODD: the first colour is (i+j+k) odd (DOWN sweep); else even (UP)
-template <bool FIRST_ODD>
-__global__ void __launch_bounds__(R7_NT, 2)
-k3_relax7_fused(G7 g, const double *__restrict__ qin, double *__restrict__ qout, int band_h)
+// INNER: the whole tile, halo included, lies inside the array in x and y (and its update window inside the interior), so
+// every in-plane bounds test is true at compile time; two thirds of the CTAs of a 385^3 sweep
+template <bool FIRST_ODD, bool INNER>
+__device__ __forceinline__ void relax7_body(const G7 &g, const double *__restrict__ qin, double *__restrict__ qout, int band_h)
 {
-    __shared__ double ring[R7_RING][R7_SY][R7_SX];
+    extern __shared__ double ring_raw[];
+    double (*ring)[R7_SY][R7_SX] = reinterpret_cast<double (*)[R7_SY][R7_SX]>(ring_raw);
     const int t = threadIdx.x, lane = t & 31, w = t >> 5;
     const int II = g.II, JJ = g.JJ, KK = g.KK;
     const int gi0 = 1 + (int)blockIdx.x * R7_OX - 2, gj0 = 1 + (int)blockIdx.y * R7_OY - 2;
@@ -60,7 +72,7 @@ k3_relax7_fused(G7 g, const double *__restrict__ qin, double *__restrict__ qout,
 #pragma unroll
     for (int n = 0; n < 4; n++) {
         const int e = t + n * R7_NT, gi = gi0 + (e & 63), gj = gj0 + (e >> 6);
-        eok[n] = gi >= 1 && gi <= II && gj >= 1 && gj <= JJ;
+        eok[n] = INNER || (gi >= 1 && gi <= II && gj >= 1 && gj <= JJ);
         eoff[n] = eok[n] ? (long long)(gj - 1) * II + (gi - 1) : 0;
     }
     auto load_plane = [&](int p, double (&v)[4]) {
@@ -88,16 +100,17 @@ k3_relax7_fused(G7 g, const double *__restrict__ qin, double *__restrict__ qout,
     }
     // items: rows ly = w and w + 8, column pair (2 lane, 2 lane + 1)
     const int c0 = gi0 + 2 * lane;
-    const bool k0 = c0 >= 1 && c0 <= II, k1 = c0 + 1 >= 1 && c0 + 1 <= II, k2 = c0 + 2 >= 1 && c0 + 2 <= II;
+    const bool k0 = INNER || (c0 >= 1 && c0 <= II), k1 = INNER || (c0 + 1 >= 1 && c0 + 1 <= II),
+               k2 = INNER || (c0 + 2 >= 1 && c0 + 2 <= II);   // (the pair of the last lane reaches one column past the tile)
     long long ioff[2];
     bool rok[2], rnok[2];
     Col7 sv[2];          // second-colour column set of plane p-1
     double kbc[2][2];    // KB(c0,p), KB(c1,p)
 #pragma unroll
     for (int n = 0; n < 2; n++) {
-        const int gj = gj0 + w + 8 * n;
-        rok[n] = gj >= 1 && gj <= JJ;
-        rnok[n] = gj + 1 >= 1 && gj + 1 <= JJ;
+        const int gj = gj0 + w + R7_WR * n;
+        rok[n] = INNER || (gj >= 1 && gj <= JJ);
+        rnok[n] = INNER || (gj + 1 >= 1 && gj + 1 <= JJ);
         ioff[n] = (long long)(gj - 1) * II + (c0 - 1);
         sv[n] = Col7{0, 0, 0, 0, 0, 0, 0};
         const bool pok = kb - 1 >= 1 && kb - 1 <= KK;
@@ -153,10 +166,10 @@ k3_relax7_fused(G7 g, const double *__restrict__ qin, double *__restrict__ qout,
         // ---- first colour on plane p
 #pragma unroll
         for (int n = 0; n < 2; n++) {
-            const int ly = w + 8 * n, gj = gj0 + ly;
+            const int ly = w + R7_WR * n, gj = gj0 + ly;
             a0[n] = (((c0 + gj + p) & 1) == pF);
             const int lx = 2 * lane + (a0[n] ? 0 : 1), ca = c0 + (a0[n] ? 0 : 1);
-            if (pin && gj >= 2 && gj <= JJ - 1 && ca >= 2 && ca <= II - 1 && lx >= 1 && lx <= R7_SX - 2 && ly >= 1
+            if (pin && (INNER || (gj >= 2 && gj <= JJ - 1 && ca >= 2 && ca <= II - 1)) && lx >= 1 && lx <= R7_SX - 2 && ly >= 1
                 && ly <= R7_SY - 2) {
                 const double cw = a0[n] ? pw0[n] : pw1[n], ce = a0[n] ? pw1[n] : pw2[n];
                 const double cs = a0[n] ? ps0[n] : ps1[n], cn = a0[n] ? pn0[n] : pn1[n];
@@ -172,9 +185,9 @@ k3_relax7_fused(G7 g, const double *__restrict__ qin, double *__restrict__ qout,
         const bool bin = p - 1 >= max(2, kb) && p - 1 <= min(KK - 1, ke);
 #pragma unroll
         for (int n = 0; n < 2; n++) {
-            const int ly = w + 8 * n, gj = gj0 + ly;
+            const int ly = w + R7_WR * n, gj = gj0 + ly;
             const int lx = 2 * lane + (a0[n] ? 0 : 1), ca = c0 + (a0[n] ? 0 : 1);
-            if (bin && gj >= 2 && gj <= JJ - 1 && ca >= 2 && ca <= II - 1 && lx >= 2 && lx <= R7_SX - 3 && ly >= 2
+            if (bin && (INNER || (gj >= 2 && gj <= JJ - 1 && ca >= 2 && ca <= II - 1)) && lx >= 2 && lx <= R7_SX - 3 && ly >= 2
                 && ly <= R7_SY - 3) {
                 const double cu = a0[n] ? kbc[n][0] : kbc[n][1];
                 const double v = sv[n].qf + sv[n].pw * ring[s_m1][ly][lx - 1] + sv[n].psn * ring[s_m1][ly + 1][lx]
@@ -205,6 +218,17 @@ k3_relax7_fused(G7 g, const double *__restrict__ qin, double *__restrict__ qout,
     }
 }
 
+template <bool FIRST_ODD>
+__global__ void __launch_bounds__(R7_NT, R7_MINB)
+k3_relax7_fused(G7 g, const double *__restrict__ qin, double *__restrict__ qout, int band_h)
+{
+    const int gi0 = 1 + (int)blockIdx.x * R7_OX - 2, gj0 = 1 + (int)blockIdx.y * R7_OY - 2;
+    // halo inside the array (one column more for the last lane's pair) and the update window inside the interior
+    const bool inner = gi0 >= 1 && gi0 + R7_SX <= g.II && gj0 >= 1 && gj0 + R7_SY <= g.JJ;
+    if (inner) relax7_body<FIRST_ODD, true>(g, qin, qout, band_h);
+    else relax7_body<FIRST_ODD, false>(g, qin, qout, band_h);
+}
+
 }  // namespace
 
 // Out-of-place form of bmgx3_relax_GS for the 7-point operator (ifd == 1): reads q_in, writes
@@ -224,15 +248,23 @@ extern "C" int bmgx3_relax_GS_oop(int kg, const double *so, const double *qf, co
     g.pw = so + (KPW - 1) * pl; g.ps = so + (KPS - 1) * pl; g.kb = so + (KB - 1) * pl;
     g.sor = sor + (MSOR - 1) * pl; g.qf = qf; g.II = (int)ii; g.JJ = (int)jj; g.KK = (int)kk;
     const unsigned ntx = cdiv(ii, R7_OX), nty = cdiv(jj, R7_OY);
-    // about four resident waves (148 SMs x 2 CTAs) of equal bands
-    unsigned nb = (4 * 296 + ntx * nty - 1) / (ntx * nty);
+    // about four resident waves (148 SMs x R7_MINB CTAs) of equal bands
+    unsigned nb = (4 * 148 * R7_MINB + ntx * nty - 1) / (ntx * nty);
     if (nb < 1) nb = 1;
     unsigned band_h = (kk + nb - 1) / nb;
     if (band_h < 8) band_h = 8;
     dim3 grid(ntx, nty, cdiv(kk, band_h));
     // DOWN: pts = 1 first, i.e. (i+j+k) odd (relax_GS.f90:144-154); UP: even first
-    if (!up) k3_relax7_fused<true><<<grid, R7_NT, 0, (cudaStream_t)s>>>(g, q_in, q_out, (int)band_h);
-    else k3_relax7_fused<false><<<grid, R7_NT, 0, (cudaStream_t)s>>>(g, q_in, q_out, (int)band_h);
+    const size_t smem = sizeof(double) * R7_RING * R7_SY * R7_SX;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(k3_relax7_fused<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(k3_relax7_fused<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return bmgx_set_cuda_error(e, "relax_GS3_oop/attr");
+        attr_set = true;
+    }
+    if (!up) k3_relax7_fused<true><<<grid, R7_NT, smem, (cudaStream_t)s>>>(g, q_in, q_out, (int)band_h);
+    else k3_relax7_fused<false><<<grid, R7_NT, smem, (cudaStream_t)s>>>(g, q_in, q_out, (int)band_h);
     BMGX_LAUNCH_CHECK("relax_GS3_oop");
     return BMGX_OK;
 }
