@@ -23,6 +23,7 @@ extern "C" int bmgx2_SETUP_recip(const double *so, double *sor, bmgx_len nx, bmg
     (void)nstncl;
     if (nsor_v < 2) return bmgx_set_error(BMGX_ERR_ARG, "SETUP_recip: nsor_v < 2");
     if (nx < 3 || ny < 3) return BMGX_OK;
+    if (ny - 2 > 65535) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "SETUP_recip: more than 65535 interior rows (one row per CTA row of the launch grid)");
     dim3 g(cdiv(nx - 2, 256), ny - 2);
     k_setup_recip<<<g, 256, 0, (cudaStream_t)s>>>(so, sor, nx, ny);
     BMGX_LAUNCH_CHECK("SETUP_recip");
@@ -67,6 +68,8 @@ static int relax_gs_passes(int k, const double *so, const double *qf, double *q,
         return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_GS_pass: periodic BCs not supported on the decomposed path");
     const bool perx = periodic && (ipn == 2 || ipn == 3), pery = periodic && (ipn == 1 || ipn == 3);
     if (ii < 3 || jj < 3) return BMGX_OK;
+    if (jj - 2 > 65535)
+        return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_GS (in place): more than 65535 interior rows; use relax_GS_oop, which walks the rows in bands");
     cudaStream_t st = (cudaStream_t)s;
     bool fwd = (irelax_sym == BMGX_RELAX_NONSYM) || (updown == BMGX_DOWN && irelax_sym == BMGX_RELAX_SYM);
     unsigned I1 = ii - 1, J1 = jj - 1;
