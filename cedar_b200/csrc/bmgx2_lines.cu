@@ -531,6 +531,106 @@ k_lines_y_scatter(const double *__restrict__ B, double *__restrict__ q, unsigned
     }
 }
 
+// ---- y-lines, both colours without touching q in between ----------------------------------------------------
+// After the first colour's solve the scratch B holds the new values of those lines, line-contiguous; the second colour's
+// right-hand sides need exactly them (columns i-1, i+1).  Instead of scattering them into q (half-written sectors:
+// 303 MB moved for 134 MB of payload, ncu) and reading q back, the second colour takes them straight from B through a
+// shared-memory tile, and ONE transpose of the whole of B (every line is solved by then) writes q in full sectors.
+// Same operands, same expression: bit for bit the result of the three-kernel form.
+template <bool NINE>
+__global__ void __launch_bounds__(256)
+k_lines_y_rhs_fromB(const double *__restrict__ so, const double *__restrict__ qf, const double *__restrict__ q,
+                    double *B, unsigned II, unsigned JJ, unsigned ibeg)
+{
+    __shared__ double nb[33][35];   // neighbour lines ibeg-1+2k (k = 0..32) x positions j0-1 .. j0+32
+    __shared__ double tile[32][33];
+    const unsigned tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+    const size_t pl = (size_t)II * JJ;
+    const double *kw = so + (KW - 1) * pl, *ksw = so + (KSW - 1) * pl, *knw = so + (KNW - 1) * pl;
+    const unsigned i0 = ibeg + 2 * blockIdx.x * 32;   // first line of the tile (F-index)
+    const unsigned j0 = 2 + blockIdx.y * 32;          // first position of the tile (F-index)
+    // new values of the other colour's lines out of B; ghost columns / rows (never in B) out of q
+    for (unsigned e = threadIdx.x; e < 33 * 34; e += 256) {
+        const unsigned k = e / 34, c = e - k * 34;
+        const unsigned il = i0 - 1 + 2 * k, j = j0 - 1 + c;   // F-indices
+        double v = 0.0;
+        if (il >= 1 && il <= II && j >= 1 && j <= JJ) {
+            if (il >= 2 && il <= II - 1 && j >= 2 && j <= JJ - 1) v = __ldcg(B + (size_t)(il - 1) * JJ + (j - 1));
+            else v = q[(size_t)(j - 1) * II + (il - 1)];
+        }
+        nb[k][c] = v;
+    }
+    __syncthreads();
+    const unsigned i = i0 + 2 * tx;
+    for (unsigned r = ty; r < 32; r += 8) {
+        const unsigned j = j0 + r;
+        double v = 0.0;
+        if (i <= II - 1 && j <= JJ - 1) {
+            const size_t c = IX2(II, i, j);
+            // q(i-1, .) = nb[tx][.], q(i+1, .) = nb[tx + 1][.]; position j sits in column r + 1
+            v = qf[c] + kw[c] * nb[tx][r + 1] + kw[c + 1] * nb[tx + 1][r + 1];
+            if (NINE)
+                v = v + ksw[c] * nb[tx][r] + knw[c + 1] * nb[tx + 1][r] + knw[c + II] * nb[tx][r + 2]
+                    + ksw[c + II + 1] * nb[tx + 1][r + 2];
+        }
+        tile[r][tx] = v;
+    }
+    __syncthreads();
+    for (unsigned r = ty; r < 32; r += 8) {
+        const unsigned il = i0 + 2 * r;
+        const unsigned j = j0 + tx;
+        if (il <= II - 1 && j <= JJ - 1) B[(size_t)(il - 1) * JJ + (j - 1)] = tile[tx][r];
+    }
+}
+
+// q(i,j) = B(j,i) for all interior points
+__global__ void __launch_bounds__(256)
+k_lines_y_transpose_back(const double *__restrict__ B, double *__restrict__ q, unsigned II, unsigned JJ)
+{
+    __shared__ double tile[32][33];
+    const unsigned tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    for (unsigned r = ty; r < 32; r += 8) {
+        const unsigned il = 2 + blockIdx.x * 32 + r, j = 2 + blockIdx.y * 32 + tx;
+        tile[r][tx] = (il <= II - 1 && j <= JJ - 1) ? __ldcs(B + (size_t)(il - 1) * JJ + (j - 1)) : 0.0;
+    }
+    __syncthreads();
+    const unsigned i = 2 + blockIdx.x * 32 + tx;
+    for (unsigned r = ty; r < 32; r += 8) {
+        const unsigned j = 2 + blockIdx.y * 32 + r;
+        if (i <= II - 1 && j <= JJ - 1) q[IX2(II, i, j)] = tile[tx][r];
+    }
+}
+
+// one non-periodic y sweep, both colours, q written once at the end; false: not applicable (use the per-colour form)
+static int liney_sweep_merged(const double *so, const double *qf, double *q, const double *sor, double *b, bmgx_len ii,
+                              bmgx_len jj, int nine_pt, bool fwd, bmgx_stream_t s, bool *done)
+{
+    *done = false;
+    unsigned lg, threads; size_t smem;
+    if (bmgx_batch() != 1 || ii < 5 || !line_plan(jj - 2, &lg, &threads, &smem)) return BMGX_OK;
+    cudaStream_t st = (cudaStream_t)s;
+    for (int a = 0; a < 2; a++) {
+        const unsigned ibeg = fwd ? 3 - a : 2 + a;
+        const unsigned nl = (ii - 1 - ibeg) / 2 + 1;
+        dim3 g(cdiv(nl, 32), cdiv(jj - 2, 32));
+        if (a == 0) {
+            if (nine_pt) k_lines_y_rhs<true><<<g, 256, 0, st>>>(so, qf, q, b, ii, jj, ibeg);
+            else k_lines_y_rhs<false><<<g, 256, 0, st>>>(so, qf, q, b, ii, jj, ibeg);
+        } else {
+            if (nine_pt) k_lines_y_rhs_fromB<true><<<g, 256, 0, st>>>(so, qf, q, b, ii, jj, ibeg);
+            else k_lines_y_rhs_fromB<false><<<g, 256, 0, st>>>(so, qf, q, b, ii, jj, ibeg);
+        }
+        BMGX_LAUNCH_CHECK("relax_lines_y/rhs");
+        cudaError_t e = launch_liney(lg, nl, threads, smem, st, b, sor, ii, jj, ibeg);
+        if (e != cudaSuccess) return bmgx_set_cuda_error(e, "relax_lines_y/attr");
+        BMGX_LAUNCH_CHECK("relax_lines_y/solve");
+    }
+    k_lines_y_transpose_back<<<dim3(cdiv(ii - 2, 32), cdiv(jj - 2, 32)), 256, 0, st>>>(b, q, ii, jj);
+    BMGX_LAUNCH_CHECK("relax_lines_y/transpose");
+    *done = true;
+    return BMGX_OK;
+}
+
 // the lines jbeg, jbeg + 2, ... (one colour) of an x-line sweep; per: the lines are periodic (Sherman-Morrison)
 static int linex_colour(const double *so, const double *qf, double *q, const double *sor, bmgx_len ii, bmgx_len jj,
                         int nine_pt, int jbeg_, int per, bmgx_stream_t s)
@@ -646,6 +746,11 @@ extern "C" int bmgx2_relax_lines_y(int k, const double *so, const double *qf, do
     const bool wrap_x = ipn == 2 || ipn == 3, wrap_y = ipn == 1 || ipn == 3;
     if (wrap_y && bmgx_batch() > 1) return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_lines_y: periodic lines are not batched");
     bool fwd = (irelax_sym == BMGX_RELAX_NONSYM) || (updown == BMGX_DOWN && irelax_sym == BMGX_RELAX_SYM);
+    if (!wrap_x && !wrap_y) {
+        bool done = false;
+        int st = liney_sweep_merged(so, qf, q, sor, b, ii, jj, (k < kf || ifd != 1) ? 1 : 0, fwd, s, &done);
+        if (st != BMGX_OK || done) return st;
+    }
     for (int a = 0; a < 2; a++) {
         int st = liney_colour(so, qf, q, sor, b, ii, jj, (k < kf || ifd != 1) ? 1 : 0, fwd ? 3 - a : 2 + a, wrap_y ? 1 : 0, s);
         if (st != BMGX_OK) return st;
