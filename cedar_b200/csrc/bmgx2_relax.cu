@@ -53,6 +53,40 @@ k_relax_colour(const double *__restrict__ so, const double *__restrict__ qf, dou
     q[c] = acc * sor[(MSOR - 1) * pl + c];
 }
 
+// 9-point: the two colours of one row class (they differ in the parity of i and are consecutive in the sweep order) in
+// ONE launch.  A CTA owns a whole row: the second colour sees the first colour's new values of its own row after a
+// barrier, every other neighbour (rows j-1, j+1) belongs to the other row class, which this launch does not touch.
+// Both colours pull the same sectors of every array (the second pass from L1/L2), so a sweep moves half the DRAM bytes of
+// four single-colour launches.  PERX: the row's ghost columns are refreshed after each colour, as the reference does
+// (relax_GS.f90:163-166).  Rows are mapped to blockIdx.x (no 65535 limit).
+template <bool PERX>
+__global__ void __launch_bounds__(256)
+k_relax_rowpair9(const double *__restrict__ so, const double *__restrict__ qf, double *q, const double *__restrict__ sor,
+                 unsigned II, unsigned JJ, unsigned ifirst, unsigned jbeg)
+{
+    const unsigned j = jbeg + 2 * blockIdx.x;
+    if (j > JJ - 1) return;
+    const size_t pl = (size_t)II * JJ, row = (size_t)(j - 1) * II;
+    const double *kw = so + (KW - 1) * pl, *ks = so + (KS - 1) * pl, *ksw = so + (KSW - 1) * pl, *knw = so + (KNW - 1) * pl;
+    const double *rs = sor + (MSOR - 1) * pl;
+#pragma unroll 1
+    for (int pass = 0; pass < 2; pass++) {
+        const unsigned ibeg = pass == 0 ? ifirst : 5 - ifirst;   // 2 <-> 3
+        for (unsigned i = ibeg + 2 * threadIdx.x; i <= II - 1; i += 2 * blockDim.x) {
+            const size_t c = row + (i - 1);
+            double acc = qf[c] + kw[c] * q[c - 1] + kw[c + 1] * q[c + 1] + ks[c] * q[c - II] + ks[c + II] * q[c + II];
+            acc = acc + ksw[c] * q[c - II - 1] + knw[c + 1] * q[c - II + 1] + knw[c + II] * q[c + II - 1]
+                  + ksw[c + II + 1] * q[c + II + 1];
+            q[c] = acc * rs[c];
+        }
+        __syncthreads();
+        if (PERX) {
+            if (threadIdx.x == 0) { q[row] = q[row + II - 2]; q[row + II - 1] = q[row + 1]; }
+            __syncthreads();
+        }
+    }
+}
+
 // Periodic boundaries (BMG2_SymStd_relax_GS.f90:139-224): the reference refreshes the x ghosts of a row after each
 // colour of that row and the y ghost rows once, after the whole sweep.  One colour never reads its own rows' x
 // ghosts written in the same pass, so refreshing them for all rows of the pass right after the pass is the same.
@@ -68,12 +102,23 @@ static int relax_gs_passes(int k, const double *so, const double *qf, double *q,
         return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_GS_pass: periodic BCs not supported on the decomposed path");
     const bool perx = periodic && (ipn == 2 || ipn == 3), pery = periodic && (ipn == 1 || ipn == 3);
     if (ii < 3 || jj < 3) return BMGX_OK;
-    if (jj - 2 > 65535)
-        return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_GS (in place): more than 65535 interior rows; use relax_GS_oop, which walks the rows in bands");
+    const bool pair9 = (k < kf || ifd != 1) && passes == 0xfu && ii - 1 >= 3;
+    if (!pair9 && jj - 2 > 65535)
+        return bmgx_set_error(BMGX_ERR_UNSUPPORTED, "relax_GS (in place, 5-point or single passes): more than 65535 interior rows; use relax_GS_oop, which walks the rows in bands");
     cudaStream_t st = (cudaStream_t)s;
     bool fwd = (irelax_sym == BMGX_RELAX_NONSYM) || (updown == BMGX_DOWN && irelax_sym == BMGX_RELAX_SYM);
     unsigned I1 = ii - 1, J1 = jj - 1;
-    if (k < kf || ifd != 1) {
+    if (pair9) {
+        // whole sweep: one launch per row class, both x colours in it
+        for (int a = 0; a < 2; a++) {
+            unsigned jbeg = fwd ? 2 + a : 3 - a;
+            if (jbeg > J1) continue;
+            unsigned nrow = (J1 - jbeg) / 2 + 1;
+            if (perx) k_relax_rowpair9<true><<<nrow, 256, 0, st>>>(so, qf, q, sor, ii, jj, fwd ? 2 : 3, jbeg);
+            else k_relax_rowpair9<false><<<nrow, 256, 0, st>>>(so, qf, q, sor, ii, jj, fwd ? 2 : 3, jbeg);
+            BMGX_LAUNCH_CHECK("relax_GS/9 pair");
+        }
+    } else if (k < kf || ifd != 1) {
         for (int a = 0; a < 2; a++) {
             unsigned jbeg = fwd ? 2 + a : 3 - a;
             if (jbeg > J1) continue;
