@@ -94,3 +94,26 @@ def test_ser_periodic_2d_history_equals_oracle(cuda, tmp_path):
     err = np.abs((exact - xr)[1:-1, 1:-1]).max()
     assert abs(abs(norm) - err) <= 6e-6 * err, (norm, err)
     assert "Finished Test" in p.stdout
+
+
+@pytest.mark.skipif(not os.path.isfile(EXEP), reason="examples/_ref not built (reference tree absent at build time)")
+@pytest.mark.parametrize("relaxation", ["line-x", "line-y", "line-xy"])
+def test_ser_periodic_2d_with_line_relaxation(cuda, tmp_path, relaxation):
+    """the same unchanged example main with the config's relaxation switched to zebra lines: lines periodic in x take the
+    Sherman-Morrison branch (relax_lines_x.f90:170-306), y-lines the plain branch with one ghost refresh per sweep; the
+    printed history follows the CPU oracle (pinned to the reference's Fortran) to the printed digits"""
+    import numpy as np
+    import oracle
+    from tests.util import periodic_problem2
+    cfg = open(os.path.join(ROOT, "examples", "basic-2d-ser", "periodic-config.json")).read()
+    assert '"relaxation": "point"' in cfg
+    (tmp_path / "config.json").write_text(cfg.replace('"relaxation": "point"', f'"relaxation": "{relaxation}"'))
+    p = subprocess.run([EXEP], cwd=tmp_path, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout + p.stderr
+    hist = [float(m) for m in re.findall(r"Iteration \d+ relative l2 norm: (\S+)", p.stdout)]
+    so, b, exact = periodic_problem2(300, 300, (True, False))
+    xr, hr, _ = oracle.Solver2(so, relaxation, 1, 1, periodic=(True, False)).solve(b, maxiter=10, tol=1e-10)
+    assert len(hist) == len(hr) and len(hist) >= 3
+    for got, want in zip(hist, hr):
+        assert abs(got - want) <= 2e-5 * want + 1e-14, (got, want)
+    assert "Finished Test" in p.stdout
