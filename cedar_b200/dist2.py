@@ -7,6 +7,8 @@ all-gather of a few bytes) -- what an MPI application would do with MPI_Allgathe
 Also here: the block-wise problem generators of the bench and the tests (host side, numpy)."""
 import ctypes as C
 import json
+import os
+import time
 import math
 
 import numpy as np
@@ -138,8 +140,11 @@ class DistSolver2:
         self.h = C.c_void_p()
         self.split_min = split_min
         self.relaxation = relaxation
+        _t = [time.perf_counter()]
+        _timing = os.environ.get("CDR_DIST_TIMING") == "1"
         _check(lib.cdr2_dist_create(nx, ny, px, py, nst, len(self.owned), ids, nrelax_pre, nrelax_post, relaxation.encode(),
                                     agglomerate, halo, split_min, int(cuda_graph), C.byref(self.h)))
+        _t.append(time.perf_counter())
         v = [C.c_int() for _ in range(5)]
         _check(lib.cdr2_dist_info(self.h, *[C.byref(t) for t in v]))
         self.ndist, self.nlevels, self.halo, self.exchanges_per_cycle, self.ops_per_cycle = [t.value for t in v]
@@ -155,9 +160,15 @@ class DistSolver2:
                 for k, b in enumerate(np.frombuffer(ob, dtype=np.int32)):
                     merged[b * HANDLE_BYTES:(b + 1) * HANDLE_BYTES] = hb[k * HANDLE_BYTES:(k + 1) * HANDLE_BYTES]
             handles = C.create_string_buffer(bytes(merged), nb * HANDLE_BYTES)
+        _t.append(time.perf_counter())
         _check(lib.cdr2_dist_connect(self.h, handles))
+        _t.append(time.perf_counter())
         if comm is not None:
             comm.barrier()        # every arena is mapped (and cleared) before anyone signals into it
+        _t.append(time.perf_counter())
+        if _timing and (comm is None or comm.rank == 0):
+            print("cdr2 dist timing (ms): create %.1f  handles %.1f  connect %.1f  barrier %.1f" %
+                  tuple((b - a) * 1e3 for a, b in zip(_t[:-1], _t[1:])), flush=True)
 
     def extent(self, lvl, block):
         v = [C.c_int() for _ in range(4)]
