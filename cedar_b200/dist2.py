@@ -35,6 +35,13 @@ lib.cdr2_dist_setup.argtypes = [C.c_void_p]
 lib.cdr2_dist_upload.argtypes = [C.c_void_p, C.c_int, C.c_char_p, _dp]
 lib.cdr2_dist_download.argtypes = [C.c_void_p, C.c_int, C.c_char_p, _dp]
 lib.cdr2_dist_level_array.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p, _dp]
+lib.cdr2_dist_upload_level.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p, _dp]
+lib.cdr2_dist_extended_array.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p, _dp]
+lib.cdr2_dist_level_ptr.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p]
+lib.cdr2_dist_level_ptr.restype = C.c_void_p
+lib.cdr2_dist_halo_exchanger.argtypes = [C.c_void_p]
+lib.cdr2_dist_halo_exchanger.restype = C.c_void_p
+lib.cdr2_dist_exchange.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
 lib.cdr2_dist_vcycle.argtypes = [C.c_void_p]
 lib.cdr2_dist_sync.argtypes = [C.c_void_p]
 lib.cdr2_dist_solve.argtypes = [C.c_void_p, C.c_int, C.c_double, _dp, C.c_int, _ip, _dp]
@@ -202,6 +209,28 @@ class DistSolver2:
         out = np.zeros((npl, nyl, nxl))
         _check(lib.cdr2_dist_level_array(self.h, block, lvl, which.encode(), _P(out)))
         return out if npl > 1 else out[0]
+
+    def upload_level(self, block, lvl, which, a):
+        """own points of a level array: (nyl, nxl) for grid functions, (planes, nyl, nxl) for the operator (which = "A")"""
+        _check(lib.cdr2_dist_upload_level(self.h, block, lvl, which.encode(), _P(np.ascontiguousarray(a, dtype=np.float64))))
+
+    def extended_array(self, block, lvl, which):
+        """the whole halo-extended array of a level: (jj, ii) or (planes, jj, ii)"""
+        g = geometry(self.nx, self.ny, self.px, self.py, self.ndist, self.halo, lvl, block)
+        npl = (self.nst if lvl == 0 else 5) if which == "A" else 1
+        out = np.zeros((npl, g["jj"], g["ii"]))
+        _check(lib.cdr2_dist_extended_array(self.h, block, lvl, which.encode(), _P(out)))
+        return out if npl > 1 else out[0]
+
+    def exchange(self, lvl, which, block=None):
+        """one ghost exchange of an array through the reference's halo_exchanger_base interface (exchange_func /
+        exchange_sten with the reference's level number k = ndist + 1 - lvl); collective"""
+        block = self.owned[0] if block is None else block
+        ptr = lib.cdr2_dist_level_ptr(self.h, block, lvl, which.encode())
+        if not ptr:
+            raise _cs.CedarError(lib.cdr_last_error().decode())
+        _check(lib.cdr2_dist_exchange(self.h, self.ndist + 1 - lvl, 1 if which == "A" else 0, ptr))
+        _check(lib.cdr2_dist_sync(self.h))
 
     def vcycle(self, sync=True):
         _check(lib.cdr2_dist_vcycle(self.h))

@@ -22,6 +22,7 @@
 #include <bmgx.h>
 #include <cedar_capi.h>
 #include <cedar/gpu.h>
+#include <cedar/halo_exchanger_base.h>
 #include <cedar/2d/mpi/plan.h>
 
 using namespace cedar::cdr2::mpi;
@@ -84,6 +85,7 @@ struct cdr2_dist
 	int warm = 0;
 	bool connected = false, is_setup = false;
 	size_t sync_words = 0;
+	std::unique_ptr<cedar::halo_exchanger_base> exchanger;   // the reference's seam over the peer-memory exchange
 	// e2e staging
 	double *db[2] = {nullptr, nullptr}, *dx[2] = {nullptr, nullptr};
 	bmgx_stream_t s_up = nullptr, s_down = nullptr;
@@ -322,6 +324,33 @@ void step(cdr2_dist &d, const plan_op &o, bmgx_stream_t st)
 	}
 }
 
+// The reference's ghost-exchange seam (include/cedar/halo_exchanger_base.h; reference kernels/halo_exchange.h:22-31,
+// called from inside its MPI kernels as halof->exchange_func(k, q)) over the peer-memory exchange: one pull of the W
+// halo lines of the array `gf` / `so` on level k out of the neighbours' arrays.  k is the reference's level number
+// (k = number of distributed levels + 1 is the finest grid, k = 1 the agglomerated one).  The pointer names the array
+// (iterate, right-hand side, residual or operator of an owned block); the call is collective: every process makes it,
+// and it exchanges that array for all the blocks the process owns.
+struct peer_exchanger : cedar::halo_exchanger_base
+{
+	cdr2_dist *d;
+	explicit peer_exchanger(cdr2_dist *d) : d(d) {}
+	void exchange(int k, const double *p, bool sten)
+	{
+		const int lvl = d->dec->ndist + 1 - k;
+		if (lvl < 0 || lvl > d->dec->ndist) throw std::runtime_error("halo exchange: level out of range");
+		if (!d->connected) throw std::runtime_error("halo exchange: cdr2_dist_connect has not run");
+		for (auto &K : d->blk)
+			for (int a : {X0, X1, B, RES, A}) {
+				if ((a == A) != sten || d->ptr(K.id, lvl, a) != p) continue;
+				plan_op o; o.kind = op_kind::exchange; o.lvl = lvl; o.arrays = {a};
+				step(*d, o, d->stream);
+				return;
+			}
+		throw std::runtime_error("halo exchange: the pointer is not a level array of a block owned by this process");
+	}
+	void exchange_func(int k, cedar::real_t *gf) override { exchange(k, gf, false); }
+	void exchange_sten(int k, cedar::real_t *so) override { exchange(k, so, true); }
+};
 
 void run_op(cdr2_dist &d, const plan_op &o)
 {
@@ -767,6 +796,67 @@ int cdr2_dist_level_array(cdr2_dist *d, int block, int lvl, const char *which, d
 			check(bmgx_memcpy2d_d2h(out + (size_t)p * g.nx * g.ny, g.nx, d->ptr(block, lvl, a, p) + (size_t)g.wb * g.ii + g.wl, g.ii,
 			                        g.nx, g.ny, d->stream), "level array download");
 		check(bmgx_stream_sync(d->stream), "sync");
+	});
+}
+
+/* own points of a grid function of any distributed level <- host (nyl, nxl); which = "x" | "b" | "res"; planes of the
+ * operator: which = "A" with host (planes, nyl, nxl) */
+int cdr2_dist_upload_level(cdr2_dist *d, int block, int lvl, const char *which, const double *host)
+{
+	return guard([&] {
+		dist_block &K = find(*d, block);
+		if (lvl < 0 || lvl > d->dec->ndist) throw std::runtime_error("level out of range");
+		const std::string w(which);
+		const int a = w == "A" ? A : w == "b" ? B : w == "res" ? RES : X0;
+		const block_geom g = K.g[lvl];
+		for (int p = 0; p < d->planes(lvl, a); p++)
+			check(bmgx_memcpy2d_h2d(d->ptr(block, lvl, a, p) + (size_t)g.wb * g.ii + g.wl, g.ii, host + (size_t)p * g.nx * g.ny, g.nx,
+			                        g.nx, g.ny, d->stream), "level array upload");
+		check(bmgx_stream_sync(d->stream), "sync");
+	});
+}
+
+/* the whole halo-extended array of a level -> host (planes, jj, ii) with the extents of cdr2_dist_geometry */
+int cdr2_dist_extended_array(cdr2_dist *d, int block, int lvl, const char *which, double *out)
+{
+	return guard([&] {
+		dist_block &K = find(*d, block);
+		if (lvl < 0 || lvl > d->dec->ndist) throw std::runtime_error("level out of range");
+		const std::string w(which);
+		const int a = w == "A" ? A : w == "b" ? B : w == "res" ? RES : X0;
+		const block_geom g = K.g[lvl];
+		check(bmgx_memcpy_d2h(out, d->ptr(block, lvl, a), (size_t)d->planes(lvl, a) * g.ii * g.jj * 8, d->stream), "extended array");
+		check(bmgx_stream_sync(d->stream), "sync");
+	});
+}
+
+/* device pointer of a level array of an owned block (what the reference's kernels hand to halof->exchange_func) */
+double *cdr2_dist_level_ptr(cdr2_dist *d, int block, int lvl, const char *which)
+{
+	double *p = nullptr;
+	guard([&] {
+		find(*d, block);
+		if (lvl < 0 || lvl > d->dec->ndist) throw std::runtime_error("level out of range");
+		const std::string w(which);
+		p = d->ptr(block, lvl, w == "A" ? A : w == "b" ? B : w == "res" ? RES : X0);
+	});
+	return p;
+}
+
+/* the solver's ghost exchanger as the reference's halo_exchanger_base (C++ callers: static_cast to
+ * cedar::halo_exchanger_base * and hand it to kernel_manager::add_halo) */
+void *cdr2_dist_halo_exchanger(cdr2_dist *d)
+{
+	if (!d->exchanger) d->exchanger = std::make_unique<peer_exchanger>(d);
+	return d->exchanger.get();
+}
+
+/* one ghost exchange through that interface: exchange_func(k, ptr) (stencil == 0) or exchange_sten(k, ptr); collective */
+int cdr2_dist_exchange(cdr2_dist *d, int k, int stencil, double *ptr)
+{
+	return guard([&] {
+		auto *h = static_cast<cedar::halo_exchanger_base *>(cdr2_dist_halo_exchanger(d));
+		if (stencil) h->exchange_sten(k, ptr); else h->exchange_func(k, ptr);
 	});
 }
 

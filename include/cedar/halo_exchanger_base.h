@@ -4,9 +4,10 @@
 #include <cedar/types.h>
 namespace cedar {
 // seam the reference's MPI kernels use to refresh ghost layers from inside a kernel (reference:
-// halo_exchanger_base.h, kernels/halo_exchange.h:22-31).  Kept for source compatibility only: nothing installs an
-// exchanger here.  The multi-GPU solvers (cdr2_dist_* / cdr3_dist_*, cedar_b200/host/dist2.cc, dist3.cc) schedule
-// their ghost exchanges themselves (include/cedar/2d/mpi/plan.h) as peer-memory pulls between kernels.
+// halo_exchanger_base.h, kernels/halo_exchange.h:22-31; installed with kernel_manager::add_halo).  The multi-GPU solver
+// implements it over its peer-memory exchange (cedar_b200/host/dist2.cc peer_exchanger, handed out by
+// cdr2_dist_halo_exchanger; contract test tests/test_gpu_dist2.py::test_halo_exchange_contract); its own cycle does
+// not go through it but schedules the exchanges between kernels (include/cedar/2d/mpi/plan.h).
 class halo_exchanger_base
 {
 public:

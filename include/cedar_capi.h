@@ -132,6 +132,20 @@ int cdr2_dist_upload(cdr2_dist *d, int block, const char *which, const double *h
 int cdr2_dist_download(cdr2_dist *d, int block, const char *which, double *host);
 /* own points of a level array -> host (planes, nyl, nxl); which = "A" | "P" | "SOR" | "x" | "b" | "res" */
 int cdr2_dist_level_array(cdr2_dist *d, int block, int lvl, const char *which, double *out);
+/* own points of an array of any distributed level <- host: grid functions (nyl, nxl), which = "x" | "b" | "res";
+ * the operator (planes, nyl, nxl), which = "A" */
+int cdr2_dist_upload_level(cdr2_dist *d, int block, int lvl, const char *which, const double *host);
+/* the whole halo-extended array of a level -> host (planes, jj, ii), extents as cdr2_dist_geometry reports them */
+int cdr2_dist_extended_array(cdr2_dist *d, int block, int lvl, const char *which, double *out);
+/* The reference's ghost-exchange seam (include/cedar/halo_exchanger_base.h; reference
+ * include/cedar/kernels/halo_exchange.h:22-31: exchange_func(k, gf), exchange_sten(k, so), called from inside its MPI
+ * kernels) over the peer-memory exchange.  k: the reference's level number (distributed levels + 1 = finest, 1 = the
+ * agglomerated level); the pointer is the device array of an owned block (cdr2_dist_level_ptr); collective.
+ * cdr2_dist_halo_exchanger returns the object (a cedar::halo_exchanger_base *, for kernel_manager::add_halo),
+ * cdr2_dist_exchange makes one call through it. */
+double *cdr2_dist_level_ptr(cdr2_dist *d, int block, int lvl, const char *which);
+void *cdr2_dist_halo_exchanger(cdr2_dist *d);
+int cdr2_dist_exchange(cdr2_dist *d, int k, int stencil, double *ptr);
 /* one V-cycle on the resident x, b (enqueued; cdr2_dist_sync waits and reports exchange time-outs) */
 int cdr2_dist_vcycle(cdr2_dist *d);
 int cdr2_dist_sync(cdr2_dist *d);

@@ -303,3 +303,45 @@ def test_c5_operator_history_equals_oracle(cuda):
     x = _join({k: sol.download(k)[1:-1, 1:-1] for k in range(px * py)}, ext, n, n)
     assert_bitwise(x, xo, "C5 operator, 40 cycles")
     sol.close()
+
+
+@pytest.mark.parametrize("px,py", [(3, 3), (3, 2), (2, 3), (4, 1)])
+def test_halo_exchange_contract(cuda, px, py):
+    """The reference's contract for a ghost exchange (test/2d/mpi/test_halo.cc, MPIHalo2: fill the interior with the
+    global index cj * NGx + ci -- stencils: (...) * ndirs + k --, exchange on every level, every ghost must equal the
+    formula), through the reference's own seam: halo_exchanger_base::exchange_func / exchange_sten
+    (cdr2_dist_halo_exchanger; include/cedar/kernels/halo_exchange.h:22-31 of the reference).  Here the ghost region is W
+    lines deep; lines beyond the physical boundary stay as they were (zero)."""
+    import cedar_b200.dist2 as d2
+    nx, ny, W = 333, 270, 5
+    sol = d2.DistSolver2(nx, ny, (px, py), agglomerate=40, halo=W)
+    nb = px * py
+    assert sol.ndist >= 2
+    for lvl in range(sol.ndist + 1):
+        ext = {k: sol.extent(lvl, k) for k in range(nb)}
+        gnx = max(x0 + nxl for (x0, y0, nxl, nyl) in ext.values())
+        gny = max(y0 + nyl for (x0, y0, nxl, nyl) in ext.values())
+        nst = 5
+        for k, (x0, y0, nxl, nyl) in ext.items():
+            cj, ci = np.meshgrid(np.arange(y0, y0 + nyl), np.arange(x0, x0 + nxl), indexing="ij")
+            f = (cj * gnx + ci + 1).astype(np.float64)
+            sol.upload_level(k, lvl, "x", f)
+            sol.upload_level(k, lvl, "A", np.stack([f * nst + p for p in range(nst)]))
+        sol.exchange(lvl, "x")
+        sol.exchange(lvl, "A")
+        for k, (x0, y0, nxl, nyl) in ext.items():
+            g = d2.geometry(nx, ny, px, py, sol.ndist, W, lvl, k)
+            rows = np.arange(g["jj"]) - g["wb"] + y0          # global row / column of every entry of the extended array
+            cols = np.arange(g["ii"]) - g["wl"] + x0
+            cj, ci = np.meshgrid(rows, cols, indexing="ij")
+            inside = (cj >= 0) & (cj < gny) & (ci >= 0) & (ci < gnx)
+            want = np.where(inside, cj * gnx + ci + 1, 0).astype(np.float64)
+            assert_bitwise(sol.extended_array(k, lvl, "x"), want, f"grid function, level {lvl}, block {k}")
+            a = sol.extended_array(k, lvl, "A")
+            for p in range(nst):
+                assert_bitwise(a[p], np.where(inside, want * nst + p, 0.0), f"stencil plane {p}, level {lvl}, block {k}")
+    # a pointer that is no level array is refused
+    import cedar_b200.solver as cs
+    with pytest.raises(cs.CedarError):
+        d2._check(d2.lib.cdr2_dist_exchange(sol.h, 1, 0, 12345))
+    sol.close()
