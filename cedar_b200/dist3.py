@@ -27,6 +27,13 @@ lib.cdr3_dist_setup.argtypes = [C.c_void_p]
 lib.cdr3_dist_upload.argtypes = [C.c_void_p, C.c_int, C.c_char_p, _dp]
 lib.cdr3_dist_download.argtypes = [C.c_void_p, C.c_int, C.c_char_p, _dp]
 lib.cdr3_dist_level_array.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p, _dp]
+lib.cdr3_dist_upload_level.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p, _dp]
+lib.cdr3_dist_extended_array.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p, _dp]
+lib.cdr3_dist_level_ptr.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_char_p]
+lib.cdr3_dist_level_ptr.restype = C.c_void_p
+lib.cdr3_dist_halo_exchanger.argtypes = [C.c_void_p]
+lib.cdr3_dist_halo_exchanger.restype = C.c_void_p
+lib.cdr3_dist_exchange.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
 lib.cdr3_dist_vcycle.argtypes = [C.c_void_p]
 lib.cdr3_dist_sync.argtypes = [C.c_void_p]
 lib.cdr3_dist_solve.argtypes = [C.c_void_p, C.c_int, C.c_double, _dp, C.c_int, _ip, _dp]
@@ -121,6 +128,29 @@ class DistSolver3:
         out = np.zeros((ne, nz, ny + 2, nx + 2))
         _check(lib.cdr3_dist_level_array(self.h, slab, lvl, which.encode(), _P(out)))
         return out
+
+    def _entries(self, lvl, which):
+        return (self.nst if lvl == 0 else 14) if which == "A" else 1
+
+    def upload_level(self, slab, lvl, which, a):
+        """own planes of a level array: (entries, nzl, ny+2, nx+2)"""
+        _check(lib.cdr3_dist_upload_level(self.h, slab, lvl, which.encode(), _P(np.ascontiguousarray(a, dtype=np.float64))))
+
+    def extended_array(self, slab, lvl, which):
+        """the whole halo-extended array of a level: (entries, kk, ny+2, nx+2)"""
+        g = geometry(self.nx, self.ny, self.nz, self.np, self.ndist, self.halo, lvl, slab)
+        out = np.zeros((self._entries(lvl, which), g["kk"], g["jj"], g["ii"]))
+        _check(lib.cdr3_dist_extended_array(self.h, slab, lvl, which.encode(), _P(out)))
+        return out
+
+    def exchange(self, lvl, which, slab=None):
+        """one ghost exchange through the reference's halo_exchanger_base interface (k = ndist + 1 - lvl); collective"""
+        slab = self.owned[0] if slab is None else slab
+        ptr = lib.cdr3_dist_level_ptr(self.h, slab, lvl, which.encode())
+        if not ptr:
+            raise _cs.CedarError(lib.cdr_last_error().decode())
+        _check(lib.cdr3_dist_exchange(self.h, self.ndist + 1 - lvl, 1 if which == "A" else 0, ptr))
+        _check(lib.cdr3_dist_sync(self.h))
 
     def vcycle(self, sync=True):
         _check(lib.cdr3_dist_vcycle(self.h))

@@ -16,6 +16,7 @@
 #include <bmgx.h>
 #include <cedar_capi.h>
 #include <cedar/gpu.h>
+#include <cedar/halo_exchanger_base.h>
 #include <cedar/3d/mpi/plan.h>
 
 using namespace cedar::cdr3::mpi;
@@ -67,6 +68,7 @@ struct cdr3_dist
 	int warm = 0;
 	bool connected = false, is_setup = false;
 	size_t sync_words = 0;
+	std::unique_ptr<cedar::halo_exchanger_base> exchanger;   // the reference's seam over the peer-memory exchange
 
 	int nblocks() const { return dec->np; }
 	int nstl(int lvl) const { return lvl == 0 ? nst : 14; }
@@ -186,6 +188,29 @@ void step(cdr3_dist &d, const plan_op &o)
 		                     d.timeout_s, d.stream), "halo step");
 	}
 }
+
+// halo_exchanger_base over the slab exchange: see peer_exchanger in dist2.cc (k = distributed levels + 1 is the finest grid)
+struct slab_exchanger : cedar::halo_exchanger_base
+{
+	cdr3_dist *d;
+	explicit slab_exchanger(cdr3_dist *d) : d(d) {}
+	void exchange(int k, const double *p, bool sten)
+	{
+		const int lvl = d->dec->ndist + 1 - k;
+		if (lvl < 0 || lvl > d->dec->ndist) throw std::runtime_error("halo exchange: level out of range");
+		if (!d->connected) throw std::runtime_error("halo exchange: cdr3_dist_connect has not run");
+		for (auto &K : d->blk)
+			for (int a : {(int)a2::X0, (int)a2::X1, (int)a2::B, (int)a2::RES, (int)a2::A}) {
+				if ((a == a2::A) != sten || d->ptr(K.id, lvl, a) != p) continue;
+				plan_op o; o.kind = op_kind::exchange; o.lvl = lvl; o.arrays = {a};
+				step(*d, o);
+				return;
+			}
+		throw std::runtime_error("halo exchange: the pointer is not a level array of a slab owned by this process");
+	}
+	void exchange_func(int k, cedar::real_t *gf) override { exchange(k, gf, false); }
+	void exchange_sten(int k, cedar::real_t *so) override { exchange(k, so, true); }
+};
 
 void run_op(cdr3_dist &d, const plan_op &o)
 {
@@ -534,6 +559,60 @@ int cdr3_dist_level_array(cdr3_dist *d, int slab_id, int lvl, const char *which,
 			check(bmgx_memcpy_d2h(out + (size_t)e * pl * g.nz, d->ptr(slab_id, lvl, a, e) + (size_t)g.wb * pl, pl * g.nz * 8, d->stream),
 			      "level array download");
 		check(bmgx_stream_sync(d->stream), "sync");
+	});
+}
+
+static int slot3(const char *which)
+{
+	const std::string w(which);
+	return w == "A" ? a2::A : w == "b" ? a2::B : w == "res" ? a2::RES : a2::X0;
+}
+/* own planes of an array of any distributed level <- host (entries, nzl, ny+2, nx+2); which = "x" | "b" | "res" | "A" */
+int cdr3_dist_upload_level(cdr3_dist *d, int slab_id, int lvl, const char *which, const double *host)
+{
+	return guard([&] {
+		slab &K = find(*d, slab_id);
+		if (lvl < 0 || lvl > d->dec->ndist) throw std::runtime_error("level out of range");
+		const int a = slot3(which);
+		const slab_geom g = K.g[lvl];
+		const size_t pl = (size_t)g.ii * g.jj;
+		for (int e = 0; e < d->planes(lvl, a); e++)
+			check(bmgx_memcpy_h2d(d->ptr(slab_id, lvl, a, e) + (size_t)g.wb * pl, host + (size_t)e * pl * g.nz, pl * g.nz * 8, d->stream),
+			      "level array upload");
+		check(bmgx_stream_sync(d->stream), "sync");
+	});
+}
+/* the whole halo-extended array of a level -> host (entries, kk, ny+2, nx+2) */
+int cdr3_dist_extended_array(cdr3_dist *d, int slab_id, int lvl, const char *which, double *out)
+{
+	return guard([&] {
+		find(*d, slab_id);
+		if (lvl < 0 || lvl > d->dec->ndist) throw std::runtime_error("level out of range");
+		const int a = slot3(which);
+		check(bmgx_memcpy_d2h(out, d->ptr(slab_id, lvl, a), (size_t)d->planes(lvl, a) * d->vol(slab_id, lvl) * 8, d->stream), "extended array");
+		check(bmgx_stream_sync(d->stream), "sync");
+	});
+}
+double *cdr3_dist_level_ptr(cdr3_dist *d, int slab_id, int lvl, const char *which)
+{
+	double *p = nullptr;
+	guard([&] {
+		find(*d, slab_id);
+		if (lvl < 0 || lvl > d->dec->ndist) throw std::runtime_error("level out of range");
+		p = d->ptr(slab_id, lvl, slot3(which));
+	});
+	return p;
+}
+void *cdr3_dist_halo_exchanger(cdr3_dist *d)
+{
+	if (!d->exchanger) d->exchanger = std::make_unique<slab_exchanger>(d);
+	return d->exchanger.get();
+}
+int cdr3_dist_exchange(cdr3_dist *d, int k, int stencil, double *ptr)
+{
+	return guard([&] {
+		auto *h = static_cast<cedar::halo_exchanger_base *>(cdr3_dist_halo_exchanger(d));
+		if (stencil) h->exchange_sten(k, ptr); else h->exchange_func(k, ptr);
 	});
 }
 

@@ -218,6 +218,13 @@ int cdr3_dist_upload(cdr3_dist *d, int slab, const char *which, const double *ho
 int cdr3_dist_download(cdr3_dist *d, int slab, const char *which, double *host);
 /* own planes of a level array -> host (entries, nzl, ny+2, nx+2); which = "A" | "P" */
 int cdr3_dist_level_array(cdr3_dist *d, int slab, int lvl, const char *which, double *out);
+/* as in 2D: own planes of any level <- host (entries, nzl, ny+2, nx+2); the whole halo-extended array -> host (entries, kk,
+ * ny+2, nx+2); the reference's halo_exchanger_base seam over the slab exchange (k = distributed levels + 1 = finest) */
+int cdr3_dist_upload_level(cdr3_dist *d, int slab, int lvl, const char *which, const double *host);
+int cdr3_dist_extended_array(cdr3_dist *d, int slab, int lvl, const char *which, double *out);
+double *cdr3_dist_level_ptr(cdr3_dist *d, int slab, int lvl, const char *which);
+void *cdr3_dist_halo_exchanger(cdr3_dist *d);
+int cdr3_dist_exchange(cdr3_dist *d, int k, int stencil, double *ptr);
 int cdr3_dist_vcycle(cdr3_dist *d);
 int cdr3_dist_sync(cdr3_dist *d);
 int cdr3_dist_solve(cdr3_dist *d, int maxiter, double tol, double *hist, int hist_cap, int *niter, double *res0);

@@ -63,3 +63,35 @@ def test_ranks_equal_serial_3d(cuda, world):
     r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "DIST3 RANKS OK" in r.stdout
+
+
+@pytest.mark.parametrize("full", [False, True])
+def test_halo_exchange_contract_3d(cuda, full):
+    """the reference's ghost-exchange contract (test/3d/mpi/test_halo.cc: global-index pattern in, every ghost checked,
+    grid functions and stencils, every level) through halo_exchanger_base over the slab exchange"""
+    import cedar_b200.dist3 as d3
+    n, nzg, slabs, W = 33, 130, 4, 3
+    nst = 14 if full else 4
+    sol = d3.DistSolver3(n, n, nzg, slabs, nst=nst, agglomerate=17, halo=W)
+    assert sol.ndist >= 2
+    for lvl in range(sol.ndist + 1):
+        ext = {k: sol.extent(lvl, k) for k in range(slabs)}
+        gnz = max(z0 + nz for (_, _, z0, nz) in ext.values())
+        ne = nst if lvl == 0 else 14
+        for k, (nx, ny, z0, nz) in ext.items():
+            kk, jj, ii = np.meshgrid(np.arange(z0, z0 + nz), np.arange(ny + 2), np.arange(nx + 2), indexing="ij")
+            f = ((kk * (ny + 2) + jj) * (nx + 2) + ii + 1).astype(np.float64)
+            sol.upload_level(k, lvl, "x", f[None])
+            sol.upload_level(k, lvl, "A", np.stack([f * ne + p for p in range(ne)]))
+        sol.exchange(lvl, "x")
+        sol.exchange(lvl, "A")
+        for k, (nx, ny, z0, nz) in ext.items():
+            g = d3.geometry(n, n, nzg, slabs, sol.ndist, W, lvl, k)
+            kk, jj, ii = np.meshgrid(np.arange(g["kk"]) - g["wb"] + z0, np.arange(ny + 2), np.arange(nx + 2), indexing="ij")
+            inside = (kk >= 0) & (kk < gnz)
+            want = np.where(inside, (kk * (ny + 2) + jj) * (nx + 2) + ii + 1, 0).astype(np.float64)
+            assert_bitwise(sol.extended_array(k, lvl, "x")[0], want, f"grid function, level {lvl}, slab {k}")
+            a = sol.extended_array(k, lvl, "A")
+            for p in range(ne):
+                assert_bitwise(a[p], np.where(inside, want * ne + p, 0.0), f"stencil entry {p}, level {lvl}, slab {k}")
+    sol.close()
