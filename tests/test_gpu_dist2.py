@@ -216,6 +216,8 @@ LINE_CASES = [(257, 257, 2, 2, True, 33, 5, 1, 1, "line-x"), (257, 257, 2, 2, Tr
               # one direction without cuts: those lines are relaxed by the serial kernels on the block's extended arrays
               (513, 385, 2, 1, True, 65, 5, 1, 1, "line-xy"), (385, 513, 1, 2, False, 65, 7, 1, 1, "line-xy"),
               (513, 257, 1, 2, True, 33, 5, 2, 1, "line-x"),
+              # the shapes of the reference's MPILines.MLRelaxX / MLRelaxY (test/2d/mpi/test_lines.cc: 800 x 10 and 10 x 800, np 7)
+              (800, 10, 7, 1, False, 5, 5, 2, 1, "line-x"), (10, 800, 1, 7, False, 5, 5, 2, 1, "line-y"),
               # lines too long for shared memory: the warp-per-line solve, as in the serial kernels
               (13001, 65, 2, 1, True, 17, 5, 1, 1, "line-x"), (65, 13001, 1, 2, False, 17, 5, 1, 1, "line-y")]
 
@@ -345,3 +347,42 @@ def test_halo_exchange_contract(cuda, px, py):
     with pytest.raises(cs.CedarError):
         d2._check(d2.lib.cdr2_dist_exchange(sol.h, 1, 0, 12345))
     sol.close()
+
+
+@pytest.mark.parametrize("np_", [1, 3, 4, 8])
+@pytest.mark.parametrize("case", ["Isotropic", "StrongX", "StrongY"])
+def test_reference_mpi_poisson2_cases(cuda, case, np_):
+    """The reference's distributed acceptance tests MPIPoisson2.{Isotropic,StrongX,StrongY} (test/2d/mpi/test_poisson.cc,
+    run there with mpiexec -np 1, 3, 4, 8): 200 x 200, Poisson with point relaxation, diag_diffusion(1, 1e-4) with
+    line-x, diag_diffusion(1e-4, 1) with line-y; default solver settings (V(2,1), at most 10 cycles, tol 1e-8); asserts:
+    final residual norm < 1e-8 and |x - sin(2 pi x) sin(2 pi y)|_inf < 1e-4.  The process grid is the reference's
+    (grid_decomp); blocks live on one GPU here, the 8-GPU form of the same path is tests/run_dist2_ranks.py."""
+    import cedar_b200.dist2 as d2
+    import cedar_b200.solver as cs
+    n, eps = 200, 1e-4
+    dx, dy, relaxation = {"Isotropic": (1.0, 1.0, "point"), "StrongX": (1.0, eps, "line-x"), "StrongY": (eps, 1.0, "line-y")}[case]
+    op = cs.Operator2(gallery="diag_diffusion", nx=n, ny=n, dx=dx, dy=dy)
+    so = np.array(op.array())
+    h = 1.0 / (n + 1)
+    xs = np.arange(n + 2) * h
+    X, Y = np.meshgrid(xs, xs, indexing="xy")
+    exact = np.sin(2 * np.pi * X) * np.sin(2 * np.pi * Y)
+    b = np.zeros((n + 2, n + 2))
+    b[1:-1, 1:-1] = (4 * np.pi ** 2 * (dx + dy) * exact * h * h)[1:-1, 1:-1]
+    if np_ == 1:
+        x, hist, r0 = cs.Solver2(cs.Operator2(so), relaxation=relaxation, nrelax_pre=2, nrelax_post=1, maxiter=10, tol=1e-8).solve(b)
+    else:
+        px, py = d2.grid_decomp((n, n), np_)
+        sol = d2.DistSolver2(n, n, (px, py), nst=3, nrelax_pre=2, nrelax_post=1, agglomerate=25, halo=5, relaxation=relaxation)
+        ext = {k: sol.extent(0, k) for k in range(np_)}
+        for k, v in d2.split_blocks(so, ext).items():
+            sol.set_operator(k, v)
+        sol.setup()
+        for k, v in d2.split_blocks(b, ext).items():
+            sol.upload(k, "b", v)
+            sol.upload(k, "x", np.zeros_like(v))
+        hist, r0 = sol.solve(maxiter=10, tol=1e-8)
+        x = _join({k: sol.download(k)[1:-1, 1:-1] for k in range(np_)}, ext, n, n)
+        sol.close()
+    assert hist[-1] * r0 < 1e-8, (hist, r0)
+    assert np.abs(exact[1:-1, 1:-1] - x[1:-1, 1:-1]).max() < 1e-4
