@@ -95,3 +95,39 @@ def test_halo_exchange_contract_3d(cuda, full):
             for p in range(ne):
                 assert_bitwise(a[p], np.where(inside, want * ne + p, 0.0), f"stencil entry {p}, level {lvl}, slab {k}")
     sol.close()
+
+
+@pytest.mark.parametrize("np_", [1, 3, 8])
+def test_reference_mpi_poisson3_case(cuda, np_):
+    """The reference's distributed acceptance test MPIPoisson3.Isotropic (test/3d/mpi/test_poisson.cc:100-134): 200^3
+    7-point Poisson, point relaxation, default settings (V(2,1), at most 10 cycles, tol 1e-8): final residual norm < 1e-8
+    and |x - sin(2 pi x) sin(2 pi y) sin(2 pi z)|_inf < 1e-4 -- on 1 (serial solver), 3 and 8 slabs."""
+    import cedar_b200.dist3 as d3
+    import cedar_b200.solver as cs
+    n = 200
+    op = cs.Operator3(gallery="poisson", nx=n, ny=n, nz=n)
+    so = np.array(op.array())
+    h = 1.0 / (n + 1)
+    s1 = np.sin(2 * np.pi * h * np.arange(n + 2))
+    exact = s1[:, None, None] * s1[None, :, None] * s1[None, None, :]
+    b = np.zeros((n + 2,) * 3)
+    b[1:-1, 1:-1, 1:-1] = (12 * np.pi ** 2 * h ** 3 * exact)[1:-1, 1:-1, 1:-1]      # examples/basic-3d-ser/poisson.cc:16-38
+    if np_ == 1:
+        x, hist, r0 = cs.Solver3(cs.Operator3(so), relaxation="point", nrelax_pre=2, nrelax_post=1, maxiter=10, tol=1e-8).solve(b)
+    else:
+        sol = d3.DistSolver3(n, n, n, np_, nst=4, nrelax_pre=2, nrelax_post=1, agglomerate=25, halo=5)
+        ext = {k: sol.extent(0, k) for k in range(np_)}
+        for k, v in d3.split_slabs(so, ext).items():
+            sol.set_operator(k, v)
+        sol.setup()
+        for k, v in d3.split_slabs(b, ext).items():
+            sol.upload(k, "b", v)
+            sol.upload(k, "x", np.zeros_like(v))
+        hist, r0 = sol.solve(maxiter=10, tol=1e-8)
+        x = np.zeros_like(b)
+        for k in range(np_):
+            _, _, z0, nzl = ext[k]
+            x[1 + z0:1 + z0 + nzl] = sol.download(k)[1:-1]
+        sol.close()
+    assert hist[-1] * r0 < 1e-8, (hist, r0)
+    assert np.abs(exact[1:-1, 1:-1, 1:-1] - x[1:-1, 1:-1, 1:-1]).max() < 1e-4
